@@ -1,0 +1,104 @@
+"""ctypes binding of libb200ctc.so (the C ABI declared in include/b200ctc.h).
+
+The library is loaded lazily.  There is NO fallback: if the shared library is
+missing, or a compute call is made without a CUDA device, a ``RuntimeError`` is
+raised - the reference's torch path is never used silently instead.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import POINTER, c_char_p, c_float, c_int, c_int64, c_size_t, c_void_p
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200ctc.so")
+_lib = None
+
+DTYPE_CODE = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}
+
+_P = c_void_p
+# name -> (restype, argtypes); mirrors include/b200ctc.h one to one
+SIGNATURES = {
+    "b200ctc_abi_version": (c_int, []),
+    "b200ctc_last_error": (c_char_p, []),
+    "b200ctc_launch_count": (c_int64, []),
+    "b200ctc_reset_launch_count": (None, []),
+    "b200ctc_device_info": (c_int, [POINTER(c_int), POINTER(c_int), POINTER(c_int)]),
+    "b200ctc_softmax_fwd": (c_int, [_P, _P, c_int64, c_int, c_int, c_int, _P]),
+    "b200ctc_softmax_bwd": (c_int, [_P, _P, _P, c_int64, c_int, c_int, c_int, _P]),
+    "b200ctc_argmax": (c_int, [_P, _P, c_int64, c_int, c_int, _P]),
+    "b200ctc_greedy_decode": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_int, _P, _P, _P]),
+    "b200ctc_loss_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
+    "b200ctc_loss_fwd": (c_int, [_P, c_int, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int,
+                                 c_int, c_int, _P, _P, c_size_t, _P]),
+    "b200ctc_loss_bwd": (c_int, [_P, c_int, _P, c_int, c_int, c_int, c_int, c_int, c_int, _P,
+                                 c_int, c_float, _P, _P, c_size_t, _P]),
+    "b200ctc_align_workspace_bytes": (c_size_t, [c_int, c_int]),
+    "b200ctc_forced_align": (c_int, [_P, _P, c_int, c_int, c_int, c_int, _P, _P, c_size_t, _P]),
+    "b200ctc_prefix_pad": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_float, _P]),
+    "b200ctc_prefix_init_state": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, c_float, _P, _P]),
+    "b200ctc_prefix_window": (c_int, [_P, c_int, c_int, _P, _P]),
+    "b200ctc_prefix_step": (c_int, [_P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int,
+                                    c_int, c_int, c_int, c_int, c_int, c_float, _P, _P, _P, _P,
+                                    _P, _P]),
+    "b200ctc_prefix_select": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int,
+                                      _P, _P, _P]),
+    "b200ctc_loss_fwd_bwd_host": (c_int, [_P, c_int, _P, _P, _P, c_int, c_int, c_int, c_int,
+                                          c_int, c_float, _P, _P, POINTER(c_void_p), c_int]),
+    "b200ctc_host_pipeline_release": (None, []),
+}
+
+
+def lib():
+    """Load (once) and return the ctypes handle; raises if the .so is missing."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} not found: build it with `python -m espnet1_b200.build` "
+                "(there is no CPU / PyTorch fallback for the CTC hot path)")
+        h = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(h, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = h
+    return _lib
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc != 0:
+        msg = lib().b200ctc_last_error().decode(errors="replace")
+        raise RuntimeError(f"libb200ctc {what} failed (status {rc}): {msg}")
+
+
+def stream_ptr(device) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def require_cuda(t: torch.Tensor, name: str) -> None:
+    if not t.is_cuda:
+        raise RuntimeError(
+            f"{name} must be a CUDA tensor: the B200 CTC path has no CPU fallback "
+            f"(got device {t.device})")
+
+
+def dtype_code(t: torch.Tensor) -> int:
+    try:
+        return DTYPE_CODE[t.dtype]
+    except KeyError:
+        raise TypeError(f"unsupported dtype {t.dtype}; expected fp32/fp16/bf16") from None
+
+
+def ptr(t) -> int:
+    return 0 if t is None else t.data_ptr()
+
+
+def launch_count() -> int:
+    return int(lib().b200ctc_launch_count())
+
+
+def reset_launch_count() -> None:
+    lib().b200ctc_reset_launch_count()

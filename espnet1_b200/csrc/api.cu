@@ -1,0 +1,67 @@
+// Library-level entry points: error string, launch counter, device info.
+#include <stdarg.h>
+
+#include "common.cuh"
+
+namespace b200ctc {
+
+static thread_local char g_err[512] = "";
+static thread_local int64_t g_launches = 0;
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+void count_launch(int n) { g_launches += n; }
+
+int check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("%s: %s", what, cudaGetErrorString(e));
+    return B200CTC_ERR_DEVICE;
+  }
+  return B200CTC_OK;
+}
+
+int sm_count() {
+  static thread_local int cached_dev = -1, cached = 0;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  if (dev != cached_dev) {
+    cudaDeviceProp p;
+    if (cudaGetDeviceProperties(&p, dev) != cudaSuccess) return 148;
+    cached = p.multiProcessorCount;
+    cached_dev = dev;
+  }
+  return cached;
+}
+
+}  // namespace b200ctc
+
+extern "C" {
+
+int b200ctc_abi_version(void) { return B200CTC_ABI_VERSION; }
+const char* b200ctc_last_error(void) { return b200ctc::g_err; }
+int64_t b200ctc_launch_count(void) { return b200ctc::g_launches; }
+void b200ctc_reset_launch_count(void) { b200ctc::g_launches = 0; }
+
+int b200ctc_device_info(int* sms, int* major, int* minor) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  cudaDeviceProp p;
+  if (e == cudaSuccess) e = cudaGetDeviceProperties(&p, dev);
+  if (e != cudaSuccess) {
+    b200ctc::set_error("no CUDA device: %s (this library has no CPU fallback)",
+                       cudaGetErrorString(e));
+    return B200CTC_ERR_DEVICE;
+  }
+  if (sms) *sms = p.multiProcessorCount;
+  if (major) *major = p.major;
+  if (minor) *minor = p.minor;
+  return B200CTC_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,315 @@
+// CTC forward: (1) label prep, (2) fused row pass "A": log-sum-exp over the
+// vocabulary + gather of the lattice emissions, streamed through shared memory
+// by the TMA engine (1-D bulk copies, mbarrier ring), (3) alpha/beta lattice
+// recursion (ctc_lattice.cuh), one CTA per utterance and direction.
+#include "ctc_lattice.cuh"
+#include "ctc_ws.cuh"
+
+namespace b200ctc {
+
+// ------------------------------------------------------------------ prep
+// int64 labels -> per-utterance int32 rows (k = 0 is the blank), duplicate
+// chains (so that repeated labels are accumulated deterministically by one
+// owner thread in the backward), clamped lengths.
+__global__ void __launch_bounds__(128) prep_kernel(const int64_t* __restrict__ targets,
+                                                   const int64_t* __restrict__ offs,
+                                                   const int64_t* __restrict__ in_lens,
+                                                   const int64_t* __restrict__ tgt_lens, int T,
+                                                   int V, int Lmax, int Lp, int blank,
+                                                   UttInfo* __restrict__ utt,
+                                                   int* __restrict__ lab, int* __restrict__ dup) {
+  __shared__ int s_bad, s_head;
+  const int b = blockIdx.x;
+  long long L64 = tgt_lens[b], T64 = in_lens[b];
+  const int L = (int)(L64 < 0 ? 0 : (L64 > Lmax ? Lmax : L64));
+  const int Tb = (int)(T64 < 0 ? 0 : (T64 > T ? T : T64));
+  const int64_t base = offs[b];
+  int* lb = lab + (size_t)b * Lp;
+  int* db = dup + (size_t)b * Lp;
+  if (threadIdx.x == 0) { s_bad = 0; s_head = 0x7fffffff; }
+  __syncthreads();
+  for (int k = threadIdx.x; k < Lp; k += 128) {
+    int v = blank;
+    if (k >= 1 && k <= L) {
+      long long t = targets[base + k - 1];
+      if (t < 0 || t >= V) { s_bad = 1; t = t < 0 ? 0 : V - 1; }
+      v = (int)t;
+    }
+    lb[k] = v;
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < Lp; k += 128) {
+    int code = 0;
+    if (k >= 1 && k <= L) {
+      const int v = lb[k];
+      bool first = (v != blank);
+      for (int j = 1; j < k && first; ++j) first = lb[j] != v;
+      int next = 0;
+      for (int j = k + 1; j <= L; ++j)
+        if (lb[j] == v) { next = j; break; }
+      code = next | (first ? kDupFirst : 0);
+      if (v == blank) atomicMin(&s_head, k);
+    }
+    db[k] = code;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    UttInfo u;
+    u.lam = 0; u.aend = 0; u.msum = 0;
+    u.T = Tb; u.L = L; u.zeroed = 0; u.infinite = 0;
+    u.blank_head = s_head == 0x7fffffff ? 0 : s_head;
+    u.bad_label = s_bad; u.pad[0] = u.pad[1] = 0;
+    utt[b] = u;
+  }
+}
+
+// --------------------------------------------------------- pass A (rows)
+template <typename T>
+struct Elems { static constexpr int N = sizeof(T) == 4 ? 4 : 8; };
+
+template <typename T>
+__device__ __forceinline__ void unpack16(const uint4& raw, float* f) {
+  if (sizeof(T) == 4) {
+    f[0] = __uint_as_float(raw.x); f[1] = __uint_as_float(raw.y);
+    f[2] = __uint_as_float(raw.z); f[3] = __uint_as_float(raw.w);
+  } else {
+    const T* h = reinterpret_cast<const T*>(&raw);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) f[i] = to_f32<T>(h[i]);
+  }
+}
+
+constexpr int kMaxStages = 8;
+
+// Persistent CTAs; each loops over (b,t) rows.  TMA=true: rows arrive in an
+// NSTAGE-deep shared-memory ring via cp.async.bulk; TMA=false (row bytes or
+// base not 16-B aligned): the CTA copies the row itself.
+template <typename T, int NT, int PER, int GMAX, bool TMA>
+__global__ void __launch_bounds__(NT) lse_gather_kernel(
+    const T* __restrict__ logits, int B, int Tfr, int V, const UttInfo* __restrict__ utt,
+    const int* __restrict__ lab, int Lp, float* __restrict__ lse2, float* __restrict__ mt,
+    float* __restrict__ em, int nstage, int stage_stride) {
+  constexpr int N = Elems<T>::N;
+  extern __shared__ __align__(128) unsigned char stages[];
+  __shared__ __align__(8) uint64_t bars[kMaxStages];
+  __shared__ float red[2][32];
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int64_t nrows = (int64_t)B * Tfr;
+  const uint32_t row_bytes = (uint32_t)V * sizeof(T);
+  const int nchunk = V / N;
+  const int ntail = V - nchunk * N;
+
+  int64_t gp = blockIdx.x;  // producer cursor (thread 0)
+  uint32_t np = 0;
+  auto issue_next = [&]() {
+    while (gp < nrows) {
+      const int b = (int)(gp / Tfr);
+      const int t = (int)(gp - (int64_t)b * Tfr);
+      if (t < utt[b].T) break;
+      gp += gridDim.x;
+    }
+    if (gp < nrows) {
+      const int st = np % nstage;
+      mbar_expect_tx(&bars[st], row_bytes);
+      bulk_g2s(stages + (size_t)st * stage_stride, logits + gp * V, row_bytes, &bars[st]);
+      ++np;
+      gp += gridDim.x;
+    }
+  };
+  if (TMA) {
+    if (tid == 0) {
+      for (int i = 0; i < nstage; ++i) mbar_init(&bars[i], 1);
+      fence_mbar_init();
+    }
+    __syncthreads();
+    if (tid == 0)
+      for (int i = 0; i < nstage; ++i) issue_next();
+  }
+
+  uint32_t n = 0;
+  for (int64_t g = blockIdx.x; g < nrows; g += gridDim.x) {
+    const int b = (int)(g / Tfr);
+    const int t = (int)(g - (int64_t)b * Tfr);
+    const int Tb = utt[b].T;
+    if (t >= Tb) continue;
+    const int L = utt[b].L;
+    const unsigned char* stg;
+    if (TMA) {
+      const int st = n % nstage;
+      stg = stages + (size_t)st * stage_stride;
+      mbar_wait(&bars[st], (n / nstage) & 1);
+    } else {
+      stg = stages;
+      const T* src = logits + g * V;
+      T* dst = reinterpret_cast<T*>(stages);
+      for (int i = tid; i < V; i += NT) dst[i] = src[i];
+      __syncthreads();
+    }
+    // whole row -> registers
+    float x[PER][N];
+    float m = kNegInf;
+#pragma unroll
+    for (int j = 0; j < PER; ++j) {
+      const int i = tid + j * NT;
+      if (i < nchunk) {
+        unpack16<T>(reinterpret_cast<const uint4*>(stg)[i], x[j]);
+#pragma unroll
+        for (int e = 0; e < N; ++e) m = fmaxf(m, x[j][e]);
+      }
+    }
+    float xt = kNegInf;
+    if (tid < ntail) {
+      xt = to_f32<T>(reinterpret_cast<const T*>(stg)[nchunk * N + tid]);
+      m = fmaxf(m, xt);
+    }
+    // lattice emissions: raw logits of blank (k=0) and the L labels
+    float gv[GMAX];
+    const int* lb = lab + (size_t)b * Lp;
+#pragma unroll
+    for (int j = 0; j < GMAX; ++j) {
+      const int k = tid + j * NT;
+      gv[j] = kNegInf;
+      if (k <= L) {
+        gv[j] = to_f32<T>(reinterpret_cast<const T*>(stg)[lb[k]]);
+        m = fmaxf(m, gv[j]);  // no-op numerically; forces the read before the barrier
+      }
+    }
+    // block max
+    m = warp_max(m);
+    if (lane == 0) red[0][wid] = m;
+    __syncthreads();
+    m = warp_max(lane < NT / 32 ? red[0][lane] : kNegInf);
+    // every thread holds its part of the row in registers: the stage is free
+    if (TMA && tid == 0) issue_next();
+    const float mm = (m == kNegInf) ? 0.f : m;
+    const float m2 = mm * kLog2e;
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < PER; ++j) {
+      const int i = tid + j * NT;
+      if (i < nchunk) {
+#pragma unroll
+        for (int e = 0; e < N; ++e) s += ex2(fmaf(x[j][e], kLog2e, -m2));
+      }
+    }
+    if (tid < ntail) s += ex2(fmaf(xt, kLog2e, -m2));
+    s = warp_sum(s);
+    if (lane == 0) red[1][wid] = s;
+    __syncthreads();
+    s = warp_sum(lane < NT / 32 ? red[1][lane] : 0.f);
+    const float l2s = log2f(s);
+    if (tid == 0) {
+      lse2[g] = m2 + l2s;
+      mt[g] = -l2s;
+    }
+    float* er = em + (size_t)g * Lp;
+#pragma unroll
+    for (int j = 0; j < GMAX; ++j) {
+      const int k = tid + j * NT;
+      if (k <= L) er[k] = fmaf(gv[j], kLog2e, -m2);
+    }
+    ++n;
+  }
+}
+
+// launch helper -------------------------------------------------------------
+template <typename T, int NT>
+static int launch_pass_a(const void* logits, int B, int Tfr, int V, const LossLayout& w,
+                         unsigned char* ws, cudaStream_t st) {
+  constexpr int N = Elems<T>::N;
+  constexpr int PER = 32 / N, GMAX = 8;
+  const size_t row_bytes = (size_t)V * sizeof(T);
+  const bool tma = (row_bytes % 16 == 0) && ((reinterpret_cast<uintptr_t>(logits) & 15) == 0);
+  const int stride = (int)align_up(row_bytes, 128);
+  int nstage, ctas_per_sm;
+  if (stride * 2 <= 100 * 1024) { ctas_per_sm = 2; nstage = (100 * 1024) / stride; }
+  else { ctas_per_sm = 1; nstage = (200 * 1024) / stride; }
+  if (nstage > 4) nstage = 4;
+  if (!tma) nstage = 1;
+  B2_REQUIRE(nstage >= 1, "ctc_loss: V=%d too large for the shared-memory row path", V);
+  const size_t smem = (size_t)nstage * stride;
+  const int64_t rows = (int64_t)B * Tfr;
+  int grid = sm_count() * ctas_per_sm * (NT <= 256 ? 1 : 1);
+  if (grid > rows) grid = (int)rows;
+  auto* utt = reinterpret_cast<const UttInfo*>(ws + w.utt);
+  auto* lab = reinterpret_cast<const int*>(ws + w.lab);
+  auto* lse2 = reinterpret_cast<float*>(ws + w.lse2);
+  auto* mt = reinterpret_cast<float*>(ws + w.mt);
+  auto* em = reinterpret_cast<float*>(ws + w.em);
+  if (tma) {
+    auto k = lse_gather_kernel<T, NT, PER, GMAX, true>;
+    cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k<<<grid, NT, smem, st>>>(static_cast<const T*>(logits), B, Tfr, V, utt, lab, w.Lp, lse2, mt,
+                              em, nstage, stride);
+  } else {
+    auto k = lse_gather_kernel<T, NT, PER, GMAX, false>;
+    cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k<<<grid, NT, smem, st>>>(static_cast<const T*>(logits), B, Tfr, V, utt, lab, w.Lp, lse2, mt,
+                              em, nstage, stride);
+  }
+  count_launch();
+  return check_launch("ctc lse_gather");
+}
+
+template <typename T>
+static int dispatch_pass_a(const void* logits, int B, int Tfr, int V, const LossLayout& w,
+                           unsigned char* ws, cudaStream_t st) {
+  constexpr int N = Elems<T>::N;
+  const int need_v = (V + 31) / 32;                    // threads so that NT*PER*N >= V (PER*N = 32)
+  const int need_l = (w.Lmax + 1 + 7) / 8;            // threads so that NT*GMAX >= L+1
+  const int need = need_v > need_l ? need_v : need_l;
+  if (need <= 256) return launch_pass_a<T, 256>(logits, B, Tfr, V, w, ws, st);
+  if (need <= 512) return launch_pass_a<T, 512>(logits, B, Tfr, V, w, ws, st);
+  if (need <= 1024) return launch_pass_a<T, 1024>(logits, B, Tfr, V, w, ws, st);
+  set_error("ctc_loss: V=%d / max_tgt_len=%d exceed the supported row size", V, w.Lmax);
+  return B200CTC_ERR_ARG;
+}
+
+}  // namespace b200ctc
+
+using namespace b200ctc;
+
+extern "C" size_t b200ctc_loss_workspace_bytes(int B, int T, int V, int max_tgt_len) {
+  if (B < 0 || T < 0 || V <= 0 || max_tgt_len < 0) return 0;
+  return make_loss_layout(B, T, V, max_tgt_len).total;
+}
+
+extern "C" int b200ctc_loss_fwd(const void* logits, int dtype, const int64_t* targets,
+                                const int64_t* tgt_offsets, const int64_t* in_lens,
+                                const int64_t* tgt_lens, int B, int T, int V, int max_tgt_len,
+                                int blank, int zero_infinity, int need_grad, float* nll, void* ws_,
+                                size_t ws_bytes, b200ctc_stream_t stream) {
+  B2_REQUIRE(B >= 0 && T >= 0 && V > 0 && max_tgt_len >= 0, "loss_fwd: bad shape");
+  if (B == 0) return B200CTC_OK;
+  B2_REQUIRE(logits && tgt_offsets && in_lens && tgt_lens && nll && ws_, "loss_fwd: null pointer");
+  B2_REQUIRE(targets || max_tgt_len == 0, "loss_fwd: null targets");
+  B2_REQUIRE(blank >= 0 && blank < V, "loss_fwd: blank=%d outside [0,%d)", blank, V);
+  B2_REQUIRE(dtype >= 0 && dtype <= 2, "loss_fwd: unknown dtype %d", dtype);
+  B2_REQUIRE(2 * (int64_t)max_tgt_len + 1 <= kMaxLattice,
+             "loss_fwd: max_tgt_len=%d exceeds the supported lattice width %d", max_tgt_len,
+             kMaxLattice);
+  const LossLayout w = make_loss_layout(B, T, V, max_tgt_len);
+  if (ws_bytes < w.total) {
+    set_error("loss_fwd: workspace %zu < required %zu bytes", ws_bytes, w.total);
+    return B200CTC_ERR_WORKSPACE;
+  }
+  B2_REQUIRE((reinterpret_cast<uintptr_t>(ws_) & 255) == 0, "loss_fwd: workspace must be 256-B aligned");
+  unsigned char* ws = static_cast<unsigned char*>(ws_);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  auto* utt = reinterpret_cast<UttInfo*>(ws + w.utt);
+  prep_kernel<<<B, 128, 0, st>>>(targets, tgt_offsets, in_lens, tgt_lens, T, V, max_tgt_len, w.Lp,
+                                 blank, utt, reinterpret_cast<int*>(ws + w.lab),
+                                 reinterpret_cast<int*>(ws + w.dup));
+  count_launch();
+  int rc = check_launch("ctc prep");
+  if (rc) return rc;
+  if (T > 0) {
+    switch (dtype) {
+      case B200CTC_F32: rc = dispatch_pass_a<float>(logits, B, T, V, w, ws, st); break;
+      case B200CTC_F16: rc = dispatch_pass_a<__half>(logits, B, T, V, w, ws, st); break;
+      default: rc = dispatch_pass_a<__nv_bfloat16>(logits, B, T, V, w, ws, st); break;
+    }
+    if (rc) return rc;
+  }
+  return launch_lattice(w, ws, T, zero_infinity, need_grad, nll, st);
+}

@@ -1,0 +1,203 @@
+"""Drop-in for ``espnet.nets.ctc_prefix_score.CTCPrefixScoreTH`` (B200 CUDA).
+
+Mirrors /root/reference/espnet/nets/ctc_prefix_score.py:11-269: constructor
+``(x, xlens, blank, eos, margin=0)`` that pads the caller's ``x`` in place,
+``__call__(y, state, scoring_ids=None, att_w=None) -> (scores, state5)``,
+``index_select_state``, ``extend_prob``, ``extend_state`` and the public
+attributes callers read.  The per-frame Python loop of the reference
+(``:156-161``) is ONE kernel launch here; there is no CPU fallback.
+"""
+from __future__ import annotations
+
+import torch
+
+from ..._lib import check, lib, ptr, require_cuda, stream_ptr
+
+
+class CTCPrefixScoreTH(object):
+    """Batch processing of CTCPrefixScore (Watanabe et al. 2017, Algorithm 2;
+    Seki et al. 2019) on the GPU."""
+
+    def __init__(self, x, xlens, blank, eos, margin=0):
+        """Construct CTC prefix scorer
+
+        :param torch.Tensor x: input label posterior sequences (B, T, O)
+        :param torch.Tensor xlens: input lengths (B,)
+        :param int blank: blank label id
+        :param int eos: end-of-sequence id
+        :param int margin: margin parameter for windowing (0 means no windowing)
+        """
+        require_cuda(x, "CTCPrefixScoreTH x")
+        self.logzero = -10000000000.0
+        self.blank = blank
+        self.eos = eos
+        self.batch = x.size(0)
+        self.input_length = x.size(1)
+        self.odim = x.size(2)
+        self.dtype = x.dtype
+        self.device = x.device
+        xl = torch.as_tensor(xlens)
+        self._xlens_dev = xl.to(device=self.device, dtype=torch.int64).contiguous()
+        self.end_frames = xl - 1  # same object kind as the reference (:55)
+        self._end_frames_dev = self._xlens_dev - 1
+        self._set_lp(x, pad=True)
+        self.margin = margin
+        if margin > 0:
+            self.frame_ids = torch.arange(self.input_length, dtype=self.dtype, device=self.device)
+        self.idx_bh = None
+        self.idx_b = torch.arange(self.batch, device=self.device)
+        self.idx_bo = (self.idx_b * self.odim).unsqueeze(1)
+        self.scoring_num = 0
+
+    # -- log-prob storage -------------------------------------------------
+    def _set_lp(self, x, pad):
+        B, T, V = x.shape
+        inplace = x.dtype == torch.float32 and x.is_contiguous()
+        lp = x if inplace else x.to(torch.float32).contiguous()
+        if pad:
+            check(lib().b200ctc_prefix_pad(ptr(lp), ptr(self._xlens_dev), B, T, V, self.blank,
+                                           self.logzero, stream_ptr(self.device)), "prefix_pad")
+            if not inplace:  # keep the reference's side effect on the caller's tensor (:47-50)
+                x.copy_(lp.to(x.dtype))
+        self._lp = lp
+
+    @property
+    def x(self):
+        """(2, T, B, O) stack [labels, blank broadcast] as the reference exposes (:52-54);
+        materialised only when somebody asks for it."""
+        xn = self._lp.transpose(0, 1)
+        xb = xn[:, :, self.blank].unsqueeze(2).expand(-1, -1, self.odim)
+        return torch.stack([xn, xb]).to(self.dtype)
+
+    # -- scoring ----------------------------------------------------------
+    def __call__(self, y, state, scoring_ids=None, att_w=None):
+        """Compute CTC prefix scores for next labels
+
+        :param list y: prefix label sequences
+        :param tuple state: previous CTC state
+        :param torch.Tensor scoring_ids: candidate ids per hypothesis (BW, snum)
+        :param torch.Tensor att_w: attention weights to decide CTC window
+        :return new_state, ctc_local_scores (BW, O)
+        """
+        dev, T, V = self.device, self.input_length, self.odim
+        if isinstance(y, torch.Tensor):
+            output_length = y.size(1) - 1
+            last_ids = y[:, -1].to(device=dev, dtype=torch.int64).contiguous()
+        else:
+            output_length = len(y[0]) - 1
+            last_ids = torch.as_tensor([int(yi[-1]) for yi in y], dtype=torch.int64).to(dev)
+        n_bh = last_ids.numel()
+        n_hyps = n_bh // self.batch
+        self.scoring_num = scoring_ids.size(-1) if scoring_ids is not None else 0
+        st = stream_ptr(dev)
+        if state is None:
+            r_prev = torch.empty(T, 2, n_bh, dtype=torch.float32, device=dev)
+            check(lib().b200ctc_prefix_init_state(ptr(self._lp), self.batch, T, V, n_hyps,
+                                                  self.blank, self.logzero, ptr(r_prev), st),
+                  "prefix_init_state")
+            s_prev, f_min_prev, f_max_prev = None, 0, 1
+        else:
+            r_prev, s_prev, f_min_prev, f_max_prev = state
+            r_prev = r_prev.to(torch.float32).contiguous()
+            if isinstance(s_prev, torch.Tensor):
+                s_prev = s_prev.to(torch.float32).expand(n_bh, V).contiguous()
+            else:
+                s_prev = None if float(s_prev) == 0.0 else torch.full(
+                    (n_bh, V), float(s_prev), dtype=torch.float32, device=dev)
+
+        if self.scoring_num > 0:
+            snum = self.scoring_num
+            ids = scoring_ids.to(device=dev, dtype=torch.int64).contiguous()
+            idmap = torch.empty(n_bh, V, dtype=torch.int64, device=dev)
+        else:
+            snum, ids, idmap = V, None, None
+
+        # window (:144-153); one global window for the whole batch like the reference
+        if att_w is not None and self.margin > 0:
+            mm = torch.empty(2, dtype=torch.float32, device=dev)
+            aw = att_w.to(torch.float32).contiguous()
+            check(lib().b200ctc_prefix_window(ptr(aw), n_bh, T, ptr(mm), st), "prefix_window")
+            lo, hi = mm.cpu().tolist()  # the reference syncs here too (:146-147)
+            f_min = max(int(lo), f_min_prev)
+            f_max = max(int(hi), f_max_prev)
+            start = min(f_max_prev, max(f_min - self.margin, output_length, 1))
+            end = min(f_max + self.margin, T)
+        else:
+            f_min = f_max = 0
+            start = max(output_length, 1)
+            end = T
+
+        r = torch.empty(T, 2, n_bh, snum, dtype=torch.float32, device=dev)
+        log_psi = torch.empty(n_bh, V, dtype=torch.float32, device=dev)
+        scores = torch.empty(n_bh, V, dtype=torch.float32, device=dev)
+        rsum = torch.empty(T, n_bh, dtype=torch.float32, device=dev)
+        check(lib().b200ctc_prefix_step(ptr(self._lp), ptr(r_prev), ptr(s_prev), ptr(last_ids),
+                                        ptr(ids), ptr(self._end_frames_dev), self.batch, n_hyps,
+                                        T, V, snum, output_length, start, end, self.blank,
+                                        self.eos, self.logzero, ptr(r), ptr(log_psi), ptr(scores),
+                                        ptr(idmap), ptr(rsum), st), "prefix_step")
+        if self.dtype != torch.float32:
+            scores, r, log_psi = scores.to(self.dtype), r.to(self.dtype), log_psi.to(self.dtype)
+        return scores, (r, log_psi, f_min, f_max, idmap)
+
+    def index_select_state(self, state, best_ids):
+        """Select CTC states according to best ids
+
+        :param state    : CTC state
+        :param best_ids : index numbers selected by beam pruning (B, W)
+        :return selected_state
+        """
+        r, s, f_min, f_max, scoring_idmap = state
+        dev, V = self.device, self.odim
+        T, _, n_bh, snum = r.shape
+        n_hyps = n_bh // self.batch
+        best = best_ids.to(device=dev, dtype=torch.int64).contiguous()
+        W = best.size(1)
+        rc = r.to(torch.float32).contiguous()
+        sc = s.to(torch.float32).contiguous()
+        r_new = torch.empty(T, 2, self.batch * W, dtype=torch.float32, device=dev)
+        s_new = torch.empty(self.batch * W, V, dtype=torch.float32, device=dev)
+        check(lib().b200ctc_prefix_select(ptr(rc), ptr(sc), ptr(scoring_idmap), ptr(best),
+                                          self.batch, n_hyps, W, T, V, snum, ptr(r_new),
+                                          ptr(s_new), stream_ptr(dev)), "prefix_select")
+        if self.dtype != torch.float32:
+            r_new, s_new = r_new.to(self.dtype), s_new.to(self.dtype)
+        return r_new, s_new, f_min, f_max
+
+    # -- streaming (:222-269), batch == 1 ---------------------------------
+    def extend_prob(self, x):
+        """Extend CTC prob.
+
+        :param torch.Tensor x: input label posterior sequences (B, T, O)
+        """
+        if self.input_length < x.shape[1]:
+            old = self._lp
+            new = x.to(torch.float32).contiguous().clone()
+            new[:, : old.shape[1]] = old  # keep the already-scored prefix (:238)
+            self._lp = new
+            self.input_length = x.size(1)
+            self.end_frames = torch.as_tensor([x.size(1)]) - 1
+            self._xlens_dev = torch.full((self.batch,), x.size(1), dtype=torch.int64,
+                                         device=self.device)
+            self._end_frames_dev = self._xlens_dev - 1
+            if self.margin > 0:
+                self.frame_ids = torch.arange(self.input_length, dtype=self.dtype,
+                                              device=self.device)
+
+    def extend_state(self, state):
+        """Compute CTC prefix state for the extended input (blank running sum).
+
+        :param state    : CTC state
+        :return ctc_state
+        """
+        if state is None:
+            return state
+        r_prev, s_prev, f_min_prev, f_max_prev = state
+        T = self.input_length
+        r_new = torch.full((T, 2), self.logzero, dtype=r_prev.dtype, device=self.device)
+        start = max(r_prev.shape[0], 1)
+        r_new[0:start] = r_prev
+        if start < T:
+            tail = self._lp[0, start:, self.blank].to(r_prev.dtype)
+            r_new[start:, 1] = r_new[start - 1, 1] + torch.cumsum(tail, 0)
+        return (r_new, s_prev, f_min_prev, f_max_prev)

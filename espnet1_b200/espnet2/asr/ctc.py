@@ -1,0 +1,115 @@
+"""Drop-in for ``espnet2.asr.ctc.CTC`` on top of the B200 CUDA library.
+
+Mirrors /root/reference/espnet2/asr/ctc.py:6-127: same constructor signature
+(the ``--ctc_conf`` surface, ``:19-28``), same attributes (``ctc_lo`` keeps the
+checkpoint keys ``ctc.ctc_lo.{weight,bias}``, ``ctc_type``, ``reduce``,
+``dropout_rate``), same methods and result conventions.  ``ctc_lo`` stays a
+cuBLAS GEMM (dense contraction, out of the hot-path scope); everything after
+the logits runs in libb200ctc.so and there is no CPU fallback.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as F
+
+from ... import functional as B
+
+
+class CTC(torch.nn.Module):
+    """CTC module (B200-native).
+
+    Args:
+        odim: dimension of outputs
+        encoder_output_size: number of encoder projection units
+        dropout_rate: dropout rate (0.0 ~ 1.0)
+        ctc_type: builtin or gtnctc
+        reduce: reduce the CTC loss into a scalar
+        ignore_nan_grad: same as zero_infinity (kept for backward compatibility)
+        zero_infinity: zero infinite losses and the associated gradients
+    """
+
+    def __init__(
+        self,
+        odim: int,
+        encoder_output_size: int,
+        dropout_rate: float = 0.0,
+        ctc_type: str = "builtin",
+        reduce: bool = True,
+        ignore_nan_grad: bool = None,
+        zero_infinity: bool = True,
+    ):
+        super().__init__()
+        eprojs = encoder_output_size
+        self.dropout_rate = dropout_rate
+        self.ctc_lo = torch.nn.Linear(eprojs, odim)
+        self.ctc_type = ctc_type
+        if ignore_nan_grad is not None:  # reference :35-36
+            zero_infinity = ignore_nan_grad
+        self.zero_infinity = bool(zero_infinity)
+
+        if self.ctc_type == "builtin":
+            self.ctc_loss = self._builtin_ctc_loss
+        elif self.ctc_type == "gtnctc":
+            # reference :43-46 delegates to the optional third-party `gtn` WFST
+            # library on CPU threads; that backend is outside the CUDA hot path.
+            raise NotImplementedError(
+                'ctc_type="gtnctc" needs the third-party gtn library and is not part of the '
+                'B200 CTC path; use ctc_type="builtin"')
+        else:
+            raise ValueError(f'ctc_type must be "builtin" or "gtnctc": {self.ctc_type}')
+
+        self.reduce = reduce
+
+    # same call convention as torch.nn.CTCLoss(reduction="none") but fed with
+    # batch-major LOGITS: log-softmax is fused into the loss kernels.
+    def _builtin_ctc_loss(self, logits_btv, th_target, th_ilen, th_olen, max_tgt_len=None):
+        return B.ctc_loss(logits_btv, th_target, th_ilen, th_olen, blank=0,
+                          zero_infinity=self.zero_infinity, max_tgt_len=max_tgt_len)
+
+    def loss_fn(self, th_pred, th_target, th_ilen, th_olen, max_tgt_len=None) -> torch.Tensor:
+        """th_pred is (T, B, V) like the reference (:52); a transposed view of a
+        batch-major tensor (what ``forward`` passes) costs no copy."""
+        if self.ctc_type != "builtin":
+            raise NotImplementedError
+        logits = th_pred.transpose(0, 1)  # (B, T, V); contiguous when th_pred was a view
+        loss = self.ctc_loss(logits, th_target, th_ilen, th_olen, max_tgt_len)
+        size = th_pred.size(1)
+        if self.reduce:
+            loss = loss.sum() / size  # batch-size average (:58-60)
+        else:
+            loss = loss / size
+        return loss
+
+    def forward(self, hs_pad, hlens, ys_pad, ys_lens):
+        """Calculate CTC loss.
+
+        Args:
+            hs_pad: batch of padded hidden state sequences (B, Tmax, D)
+            hlens: batch of lengths of hidden state sequences (B)
+            ys_pad: batch of padded character id sequence tensor (B, Lmax)
+            ys_lens: batch of lengths of character sequence (B)
+        """
+        # NOTE: F.dropout defaults to training=True exactly like the reference (:82)
+        ys_hat = self.ctc_lo(F.dropout(hs_pad, p=self.dropout_rate))
+        ys_hat = ys_hat.transpose(0, 1)  # (B, T, V) -> (T, B, V) view
+        # (B, L) -> (sum L,) without the reference's per-utterance Python loop (:91)
+        Lmax = ys_pad.size(1)
+        lens_dev = torch.as_tensor(ys_lens).to(device=ys_pad.device)
+        keep = torch.arange(Lmax, device=ys_pad.device).unsqueeze(0) < lens_dev.unsqueeze(1)
+        ys_true = ys_pad[keep]
+        loss = self.loss_fn(ys_hat, ys_true, hlens, ys_lens, max_tgt_len=Lmax).to(
+            device=hs_pad.device, dtype=hs_pad.dtype
+        )
+        return loss
+
+    def softmax(self, hs_pad):
+        """softmax of frame activations: (B, Tmax, eprojs) -> (B, Tmax, odim)."""
+        return B.softmax(self.ctc_lo(hs_pad))
+
+    def log_softmax(self, hs_pad):
+        """log_softmax of frame activations: (B, Tmax, eprojs) -> (B, Tmax, odim)."""
+        return B.log_softmax(self.ctc_lo(hs_pad))
+
+    def argmax(self, hs_pad):
+        """argmax of frame activations: (B, Tmax, eprojs) -> (B, Tmax) int64."""
+        return B.argmax(self.ctc_lo(hs_pad))

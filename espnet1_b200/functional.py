@@ -1,0 +1,157 @@
+"""torch-facing wrappers over the C ABI (autograd Functions + plain ops).
+
+PyTorch is used for device memory, streams and autograd plumbing only; every
+arithmetic step of the hot path runs in libb200ctc.so.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+from ._lib import check, dtype_code, lib, ptr, require_cuda, stream_ptr
+
+
+def _rows(x: torch.Tensor):
+    V = x.shape[-1]
+    return x.numel() // max(V, 1), V
+
+
+class _SoftmaxFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, mode):
+        require_cuda(x, "softmax input")
+        xc = x.contiguous()
+        y = torch.empty_like(xc)
+        rows, V = _rows(xc)
+        check(lib().b200ctc_softmax_fwd(ptr(xc), ptr(y), rows, V, dtype_code(xc), mode,
+                                        stream_ptr(xc.device)), "softmax_fwd")
+        ctx.mode = mode
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        dyc = dy.contiguous()
+        dx = torch.empty_like(y)
+        rows, V = _rows(y)
+        check(lib().b200ctc_softmax_bwd(ptr(y), ptr(dyc), ptr(dx), rows, V, dtype_code(y),
+                                        ctx.mode, stream_ptr(y.device)), "softmax_bwd")
+        return dx, None
+
+
+def log_softmax(x: torch.Tensor) -> torch.Tensor:
+    """log-softmax over the last dim (espnet2/asr/ctc.py:117)."""
+    return _SoftmaxFn.apply(x, 0)
+
+
+def softmax(x: torch.Tensor) -> torch.Tensor:
+    """softmax over the last dim (espnet2/asr/ctc.py:107)."""
+    return _SoftmaxFn.apply(x, 1)
+
+
+def argmax(x: torch.Tensor) -> torch.Tensor:
+    """argmax over the last dim, int64, first-max tie rule (espnet2/asr/ctc.py:127)."""
+    require_cuda(x, "argmax input")
+    xc = x.detach().contiguous()
+    rows, V = _rows(xc)
+    out = torch.empty(xc.shape[:-1], dtype=torch.int64, device=xc.device)
+    check(lib().b200ctc_argmax(ptr(xc), ptr(out), rows, V, dtype_code(xc), stream_ptr(xc.device)),
+          "argmax")
+    return out
+
+
+def greedy_decode(logits: torch.Tensor, in_lens=None, blank: int = 0):
+    """Best-path decode: (ids (B,T) padded with -1, lens (B,))."""
+    require_cuda(logits, "greedy_decode input")
+    xc = logits.detach().contiguous()
+    B, T, V = xc.shape
+    ids = torch.empty(B, T, dtype=torch.int64, device=xc.device)
+    lens = torch.empty(B, dtype=torch.int64, device=xc.device)
+    il = None if in_lens is None else in_lens.to(device=xc.device, dtype=torch.int64).contiguous()
+    check(lib().b200ctc_greedy_decode(ptr(xc), ptr(il), B, T, V, dtype_code(xc), blank, ptr(ids),
+                                      ptr(lens), stream_ptr(xc.device)), "greedy_decode")
+    return ids, lens
+
+
+class _CTCLossFn(torch.autograd.Function):
+    """nll (B,) fp32 = CTCLoss(reduction='none')(log_softmax(logits)); the
+    backward writes d/dlogits in one pass (no (T,B,V) log-prob tensor exists)."""
+
+    @staticmethod
+    def forward(ctx, logits, targets, tgt_offsets, in_lens, tgt_lens, max_tgt_len, blank,
+                zero_infinity):
+        require_cuda(logits, "CTC logits")
+        x = logits.contiguous()
+        B, T, V = x.shape
+        dev = x.device
+        need_grad = bool(ctx.needs_input_grad[0])
+        nbytes = lib().b200ctc_loss_workspace_bytes(B, T, V, max_tgt_len)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        nll = torch.empty(B, dtype=torch.float32, device=dev)
+        check(lib().b200ctc_loss_fwd(ptr(x), dtype_code(x), ptr(targets), ptr(tgt_offsets),
+                                     ptr(in_lens), ptr(tgt_lens), B, T, V, max_tgt_len, blank,
+                                     int(zero_infinity), int(need_grad), ptr(nll), ptr(ws), nbytes,
+                                     stream_ptr(dev)), "loss_fwd")
+        ctx.save_for_backward(x, in_lens, ws)
+        ctx.cfg = (B, T, V, max_tgt_len, blank, int(zero_infinity), nbytes)
+        return nll
+
+    @staticmethod
+    def backward(ctx, g):
+        x, in_lens, ws = ctx.saved_tensors
+        B, T, V, lmax, blank, zinf, nbytes = ctx.cfg
+        grad = torch.empty_like(x)
+        if g.stride(0) == 0 or g.numel() == 1:  # expanded scalar (loss.sum()/B)
+            gs = g.reshape(-1)[:1].to(torch.float32).contiguous()
+            stride = 0
+        else:
+            gs = g.to(torch.float32).contiguous()
+            stride = 1
+        check(lib().b200ctc_loss_bwd(ptr(x), dtype_code(x), ptr(in_lens), B, T, V, lmax, blank,
+                                     zinf, ptr(gs), stride, 1.0, ptr(grad), ptr(ws), nbytes,
+                                     stream_ptr(x.device)), "loss_bwd")
+        return grad, None, None, None, None, None, None, None
+
+
+def ctc_loss(logits, targets, in_lens, tgt_lens, blank: int = 0, zero_infinity: bool = True,
+             max_tgt_len: int | None = None, tgt_offsets=None) -> torch.Tensor:
+    """Per-utterance CTC negative log-likelihood from LOGITS.
+
+    logits (B,T,V) batch-major activations (fp32/fp16/bf16, CUDA); targets 1-D
+    concatenated int64 labels; in_lens / tgt_lens (B,).  Equivalent to
+    ``F.ctc_loss(logits.transpose(0,1).log_softmax(2), ..., reduction="none")``.
+    ``max_tgt_len`` may be given to avoid a device->host sync.
+    """
+    require_cuda(logits, "CTC logits")
+    dev = logits.device
+    tl_dev = torch.as_tensor(tgt_lens).to(device=dev, dtype=torch.int64).contiguous()
+    il_dev = torch.as_tensor(in_lens).to(device=dev, dtype=torch.int64).contiguous()
+    tg_dev = torch.as_tensor(targets).to(device=dev, dtype=torch.int64).contiguous()
+    if max_tgt_len is None:
+        src = tgt_lens if not (isinstance(tgt_lens, torch.Tensor) and tgt_lens.is_cuda) else tl_dev
+        max_tgt_len = int(torch.as_tensor(src).max()) if tl_dev.numel() else 0
+    if tgt_offsets is None:
+        tgt_offsets = torch.zeros(tl_dev.numel() + 1, dtype=torch.int64, device=dev)
+        torch.cumsum(tl_dev, 0, out=tgt_offsets[1:])
+    return _CTCLossFn.apply(logits, tg_dev, tgt_offsets, il_dev, tl_dev, int(max_tgt_len),
+                            int(blank), bool(zero_infinity))
+
+
+def forced_align(lp: torch.Tensor, target: torch.Tensor, blank: int = 0) -> torch.Tensor:
+    """Viterbi alignment of one utterance; lp (T,V) fp32 log-probs, target (L,)."""
+    require_cuda(lp, "forced_align input")
+    lpc = lp.detach().to(torch.float32).contiguous()
+    tg = target.to(device=lpc.device, dtype=torch.int64).contiguous()
+    T, V = lpc.shape
+    L = tg.numel()
+    n = lib().b200ctc_align_workspace_bytes(T, L)
+    ws = torch.empty(n, dtype=torch.uint8, device=lpc.device)
+    out = torch.empty(T, dtype=torch.int64, device=lpc.device)
+    check(lib().b200ctc_forced_align(ptr(lpc), ptr(tg), T, V, L, blank, ptr(out), ptr(ws), n,
+                                     stream_ptr(lpc.device)), "forced_align")
+    return out
+
+
+launch_count = _lib.launch_count
+reset_launch_count = _lib.reset_launch_count

@@ -1,0 +1,157 @@
+/*
+ * b200ctc.h - C ABI of the B200-native ESPnet CTC hot path (libb200ctc.so).
+ *
+ * The reference (DavidLBick/espnet-1) is pure Python and has NO native FFI for
+ * this path: its boundary is the Python class API.  Each entry point below
+ * states which reference call it replaces (file:line relative to the reference
+ * tree); INTEGRATION.md shows the ctypes binding a maintainer would add.
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer owned by the caller unless the name ends
+ *    in `_host`; nothing is allocated or freed behind the caller's back except
+ *    inside the `*_host` pipeline helpers (which own a cached staging arena).
+ *  - every call is asynchronous on `stream` (a cudaStream_t passed as void*).
+ *  - return value: 0 = OK, negative = error; b200ctc_last_error() gives a
+ *    thread-local message.  There is NO CPU fallback: without a CUDA device
+ *    (or with a non-sm_100 device) compute calls fail with B200CTC_ERR_DEVICE.
+ *  - dtype codes: 0 = fp32, 1 = fp16, 2 = bf16 (arithmetic is always fp32).
+ *  - thread-safe as long as distinct streams use distinct workspaces.
+ */
+#ifndef B200CTC_H_
+#define B200CTC_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200CTC_ABI_VERSION 1
+
+#define B200CTC_OK 0
+#define B200CTC_ERR_ARG (-1)     /* bad argument (null pointer, size, dtype) */
+#define B200CTC_ERR_DEVICE (-2)  /* no usable CUDA device / launch failure   */
+#define B200CTC_ERR_WORKSPACE (-3) /* workspace too small                    */
+
+#define B200CTC_F32 0
+#define B200CTC_F16 1
+#define B200CTC_BF16 2
+
+typedef void* b200ctc_stream_t; /* cudaStream_t */
+
+/* ---- library -------------------------------------------------------------- */
+int b200ctc_abi_version(void);
+const char* b200ctc_last_error(void);
+/* number of kernels launched by this library on the calling thread since the
+ * last reset (bench.py's `gpu_launches`). */
+int64_t b200ctc_launch_count(void);
+void b200ctc_reset_launch_count(void);
+/* fills sm_count / compute capability of the current device */
+int b200ctc_device_info(int* sm_count, int* cc_major, int* cc_minor);
+
+/* ---- (a1) vocabulary soft-max family --------------------------------------
+ * replaces Tensor.log_softmax / F.softmax / torch.argmax over the last dim:
+ *   espnet2/asr/ctc.py:107,117,127 ; espnet/nets/pytorch_backend/ctc.py:142,152,161 ;
+ *   espnet/nets/scorers/ctc.py:35,96,138.
+ * `x` is (rows, V) row-major with row stride V, same dtype in and out.
+ * mode: 0 = log_softmax, 1 = softmax.                                         */
+int b200ctc_softmax_fwd(const void* x, void* y, int64_t rows, int V, int dtype,
+                        int mode, b200ctc_stream_t stream);
+/* autograd backward of the above: dx from y (the forward OUTPUT) and dy.      */
+int b200ctc_softmax_bwd(const void* y, const void* dy, void* dx, int64_t rows,
+                        int V, int dtype, int mode, b200ctc_stream_t stream);
+/* first index of the row maximum (NaN counts as the maximum), int64 out.      */
+int b200ctc_argmax(const void* x, int64_t* out, int64_t rows, int V, int dtype,
+                   b200ctc_stream_t stream);
+/* best-path decode (espnet/nets/e2e_asr_common.py:159-191): argmax per frame,
+ * collapse repeats, drop blanks.  x (B,T,V); out_ids (B,T) int64 padded with
+ * -1; out_lens (B,) int64.  in_lens may be NULL (all T).                      */
+int b200ctc_greedy_decode(const void* x, const int64_t* in_lens, int B, int T,
+                          int V, int dtype, int blank, int64_t* out_ids,
+                          int64_t* out_lens, b200ctc_stream_t stream);
+
+/* ---- (a2,a3) CTC loss and its gradient w.r.t. the logits ------------------
+ * replaces  th_pred.log_softmax(2) + torch.nn.CTCLoss(reduction="none",
+ * zero_infinity=..) and the autograd backward of both:
+ *   espnet2/asr/ctc.py:39-41,52-62 ; espnet/nets/pytorch_backend/ctc.py:38-40,56-65.
+ * logits: (B,T,V) batch-major pre-softmax activations (what ctc_lo emits,
+ *   espnet2/asr/ctc.py:82), row stride V.  targets: 1-D concatenated labels
+ *   (espnet2/asr/ctc.py:91) with tgt_offsets (B+1,) prefix sums.
+ * fwd writes nll (B,) fp32 (0 where infeasible and zero_infinity) and keeps
+ * the lattices in `ws`; bwd consumes `ws` and writes
+ *   grad[b,t,v] = gscale_mul * gscale[b*gscale_stride] * d nll[b] / d logits[b,t,v]
+ * (zeros for t >= in_lens[b]); gscale may be NULL (=1), gscale_stride is 0 for
+ * a scalar upstream gradient, 1 for a per-utterance one.                      */
+size_t b200ctc_loss_workspace_bytes(int B, int T, int V, int max_tgt_len);
+int b200ctc_loss_fwd(const void* logits, int dtype, const int64_t* targets,
+                     const int64_t* tgt_offsets, const int64_t* in_lens,
+                     const int64_t* tgt_lens, int B, int T, int V,
+                     int max_tgt_len, int blank, int zero_infinity, int need_grad,
+                     float* nll, void* ws, size_t ws_bytes, b200ctc_stream_t stream);
+int b200ctc_loss_bwd(const void* logits, int dtype, const int64_t* in_lens,
+                     int B, int T, int V, int max_tgt_len, int blank,
+                     int zero_infinity, const float* gscale, int gscale_stride,
+                     float gscale_mul, void* grad, const void* ws, size_t ws_bytes,
+                     b200ctc_stream_t stream);
+/* forced alignment (espnet/nets/pytorch_backend/ctc.py:163-226): max-semiring
+ * lattice with back-pointers for ONE utterance; lp (T,V) fp32 log-probs,
+ * out_ids (T,) int64 = label emitted at each frame (tgt_len >= 1).            */
+size_t b200ctc_align_workspace_bytes(int T, int tgt_len);
+int b200ctc_forced_align(const float* lp, const int64_t* target, int T, int V,
+                         int tgt_len, int blank, int64_t* out_ids, void* ws,
+                         size_t ws_bytes, b200ctc_stream_t stream);
+
+/* ---- (a4-a7) batched CTC prefix scoring -----------------------------------
+ * replaces CTCPrefixScoreTH (espnet/nets/ctc_prefix_score.py:11-269).        */
+/* constructor padding (:47-50): frames t >= xlens[b] become logzero with
+ * blank = 0, IN PLACE on the caller's (B,T,V) fp32 log-prob tensor.           */
+int b200ctc_prefix_pad(float* lp, const int64_t* xlens, int B, int T, int V,
+                       int blank, float logzero, b200ctc_stream_t stream);
+/* initial state (:83-91): r (T,2,B*n_hyps) with r[:,0]=logzero and
+ * r[:,1] = running sum over t of lp[b,t,blank].                               */
+int b200ctc_prefix_init_state(const float* lp, int B, int T, int V, int n_hyps,
+                              int blank, float logzero, float* r0,
+                              b200ctc_stream_t stream);
+/* attention window (:144-147): f_arg[h] = sum_t att_w[h,t]*t ; writes
+ * minmax[0]=min_h f_arg, minmax[1]=max_h f_arg (fp32).                        */
+int b200ctc_prefix_window(const float* att_w, int n_bh, int T, float* minmax,
+                          b200ctc_stream_t stream);
+/* one scoring step (__call__, :68-187) over frames [start,end).
+ *  r_prev (T,2,n_bh) ; s_prev (n_bh,V) or NULL (=0) ; last_ids (n_bh) ;
+ *  scoring_ids (n_bh,snum) or NULL (then snum must equal V) ;
+ *  outputs: r (T,2,n_bh,snum), log_psi (n_bh,V), scores (n_bh,V),
+ *  idmap (n_bh,V) int64 (-1 = not scored; NULL iff scoring_ids is NULL).      */
+int b200ctc_prefix_step(const float* lp, const float* r_prev, const float* s_prev,
+                        const int64_t* last_ids, const int64_t* scoring_ids,
+                        const int64_t* end_frames, int B, int n_hyps, int T, int V,
+                        int snum, int out_len, int start, int end, int blank,
+                        int eos, float logzero, float* r, float* log_psi,
+                        float* scores, int64_t* idmap, float* rsum_ws /*(T,n_bh) scratch*/,
+                        b200ctc_stream_t stream);
+/* index_select_state (:189-220): best_ids (B,W) flat (hyp*V + label) ids.     */
+int b200ctc_prefix_select(const float* r, const float* log_psi,
+                          const int64_t* idmap, const int64_t* best_ids, int B,
+                          int n_hyps, int W, int T, int V, int snum, float* r_new,
+                          float* s_new, b200ctc_stream_t stream);
+
+/* ---- host-buffer pipeline (bench.py `e2e`) --------------------------------
+ * Same arithmetic as loss_fwd + loss_bwd, but logits/targets/lengths are HOST
+ * buffers (pinned for full speed) and nll (and optionally grad) are returned
+ * to HOST buffers: utterance chunks are copied H2D on a copy stream while the
+ * previous chunk computes.  Blocks until the results are in host memory.
+ * grad_host may be NULL (loss only; the gradient stays in the device arena
+ * returned through *grad_dev_out when that pointer is non-NULL).              */
+int b200ctc_loss_fwd_bwd_host(const void* logits_host, int dtype,
+                              const int64_t* targets_host,
+                              const int64_t* in_lens_host,
+                              const int64_t* tgt_lens_host, int B, int T, int V,
+                              int blank, int zero_infinity, float gscale,
+                              float* nll_host, void* grad_host,
+                              void** grad_dev_out, int chunk_utts);
+void b200ctc_host_pipeline_release(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200CTC_H_ */
