@@ -1,0 +1,374 @@
+#!/usr/bin/env python3
+"""bench.py - CTC fwd+bwd utt-frames/s on synthetic logits (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+One "step" = one pass of the hot path over one batch: log-softmax + CTC loss
+(+ the batch-size-normalised scalar) forward and the gradient w.r.t. the
+logits backward, through the drop-in ``espnet2.asr.ctc.CTC.loss_fn`` path.
+N=1 workload: config C2 (B=64, T=500, V=5000, L in [75,150], fp32).  N>1: every
+rank owns its own C2-shaped shard (weak scaling, utterances shard with no
+data-path collective) and the ranks all-reduce two scalars per step.
+Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement".
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+C2 = dict(B=64, T=500, V=5000, lmin=75, lmax=150)
+METRIC = "ctc_fwd_bwd_utt_frames_per_s"
+UNIT = "utt-frames/s"
+
+
+def synth(cfg, seed, device="cpu", pin=False):
+    """SURVEY 8(d) synthetic inputs: logits ~ N(0,1)*2, labels uniform in [1,V)."""
+    g = torch.Generator().manual_seed(seed)
+    B, T, V = cfg["B"], cfg["T"], cfg["V"]
+    logits = torch.empty(B, T, V, pin_memory=pin)
+    logits.normal_(generator=g).mul_(2.0)
+    tl = torch.randint(cfg["lmin"], cfg["lmax"] + 1, (B,), generator=g)
+    il = torch.full((B,), T, dtype=torch.long)
+    tg = torch.randint(1, V, (int(tl.sum()),), generator=g)
+    return logits, tg, il, tl
+
+
+def algorithmic_bytes(cfg, esize=4):
+    """bytes = B*T*(2*V*esize + 2*S*4), S = 2*Lmax+1."""
+    S = 2 * cfg["lmax"] + 1
+    return cfg["B"] * cfg["T"] * (2 * cfg["V"] * esize + 2 * S * 4)
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([c.strip() for c in out.strip().split(",")])
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def summary(self):
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 6
+                          for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+def cpu_reference_step(case, threads):
+    from oracle import espnet_cpu
+
+    torch.set_num_threads(threads)
+    logits, tg, il, tl = case
+    t0 = time.perf_counter()
+    espnet_cpu.logits_loss_and_grad(logits, tg, il, tl)
+    return time.perf_counter() - t0
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU path (log_softmax + CTCLoss + backward
+    on torch CPU kernels, oracle/espnet_cpu.py) with all host threads, same config."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    case = synth(C2, 1234)
+    for _ in range(max(1, min(args.warmup, 2))):
+        cpu_reference_step(case, threads)
+    times = [cpu_reference_step(case, threads) for _ in range(args.steps)]
+    dt = sum(times) / len(times)
+    val = C2["B"] * C2["T"] / dt
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": "C2 LibriSpeech-100 BPE-5000 CTC: B=64,T=500,V=5000,L in [75,150], fp32 fwd+bwd"},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": "full C2 batch per step: torch-CPU log_softmax+ctc_loss(reduction=none,"
+                                   "zero_infinity)+backward via oracle/espnet_cpu.py"},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def time_region(fn, steps, dist_on, dev):
+    """barrier + synchronize, CUDA events on the launching stream, max over ranks."""
+    import torch.distributed as dist
+
+    if dist_on:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize(dev)
+    if dist_on:
+        dist.barrier()
+    ms = torch.tensor([e0.elapsed_time(e1) / steps], device=dev)
+    if dist_on:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms)
+
+
+def bench_prefix(dev, steps=20):
+    """Secondary metric: CTCPrefixScoreTH beam steps/s, config C3 (batch=32, beam=10,
+    V=5000, T=500), one step = __call__ + index_select_state with the state carried."""
+    from espnet1_b200.espnet.nets.ctc_prefix_score import CTCPrefixScoreTH
+    from oracle.prefix_torch import PrefixOracle
+
+    B, W, V, T = 32, 10, 5000, 500
+    g = torch.Generator().manual_seed(1234)
+    lpz = torch.log_softmax(torch.randn(B, T, V, generator=g) * 2, dim=2)
+    xl = torch.randint(250, T + 1, (B,), generator=g)
+    xl[0] = T
+    tt = torch.arange(T, dtype=torch.float32)
+
+    def inputs(i, snum, margin, device):
+        gi = torch.Generator().manual_seed(77 + i)
+        local = torch.randn(B * W, V, generator=gi)
+        part = torch.topk(local, snum, dim=-1)[1].to(device) if snum else None
+        att = None
+        if margin:
+            c = T * (i + 1) / 60.0 + (torch.rand(B * W, generator=gi) * 10 - 5)
+            att = torch.softmax(-((tt[None] - c[:, None]) ** 2) / 128.0, dim=1).to(device)
+        best = torch.topk(local.view(B, -1), W, 1)[1].to(device)
+        return part, att, best
+
+    out = {}
+    for name, snum, margin, n, n_cpu in (("snum15_margin0", 15, 0, steps, 3),
+                                         ("snum15_margin20", 15, 20, steps, 3),
+                                         ("fullvocab_margin20", None, 20, 3, 0)):
+        sc = CTCPrefixScoreTH(lpz.clone().to(dev), xl, 0, V - 1, margin=margin)
+        pre = [inputs(i, snum, margin, dev) for i in range(n + 1)]
+        y = [[V - 1] * 1 for _ in range(B * W)]
+        state, ms = None, []
+        for i in range(n + 1):
+            part, att, best = pre[i]
+            yy = [[V - 1] * (i + 1) for _ in range(B * W)]
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            _, st5 = sc(yy, state, part, att)
+            state = sc.index_select_state(st5, best)
+            e1.record()
+            torch.cuda.synchronize(dev)
+            if i > 0:
+                ms.append(e0.elapsed_time(e1))
+            del st5
+        entry = {"gpu_ms_per_step": sum(ms) / len(ms), "gpu_steps_per_s": 1e3 * len(ms) / sum(ms)}
+        if n_cpu:
+            ora = PrefixOracle(lpz.clone(), xl, 0, V - 1, margin)
+            state, ts = None, []
+            for i in range(n_cpu + 1):
+                part, att, best = inputs(i, snum, margin, "cpu")
+                yy = [[V - 1] * (i + 1) for _ in range(B * W)]
+                t0 = time.perf_counter()
+                _, st5 = ora.score(yy, state, part, att)
+                state = ora.select(st5, best)
+                if i > 0:
+                    ts.append(time.perf_counter() - t0)
+            entry["cpu_steps_per_s"] = len(ts) / sum(ts)
+            entry["gpu_over_cpu"] = entry["gpu_steps_per_s"] / entry["cpu_steps_per_s"]
+        else:
+            entry["cpu_steps_per_s"] = None
+        out[name] = entry
+        del sc, state
+        torch.cuda.empty_cache()
+    return out
+
+
+def run_gpu(args):
+    import ctypes
+
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the B200 CTC path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist_on = world > 1
+    if dist_on:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    from espnet1_b200 import _lib
+    from espnet1_b200.build import build_library
+    from espnet1_b200.espnet2.asr.ctc import CTC
+
+    build_library()
+    L = _lib.lib()
+    cfg = C2
+    B, T, V = cfg["B"], cfg["T"], cfg["V"]
+    host_logits, tg_h, il_h, tl_h = synth(cfg, 1234 + rank, pin=True)
+    x = host_logits.to(dev).requires_grad_(True)
+    tg, il, tl = tg_h.to(dev), il_h.to(dev), tl_h.to(dev)
+    module = CTC(V, 8).to(dev)
+    wbuf = torch.zeros(2, device=dev)
+
+    def step():
+        x.grad = None
+        loss = module.loss_fn(x.transpose(0, 1), tg, il, tl, max_tgt_len=cfg["lmax"])
+        if dist_on:  # [sum_b nll_b, B_local] -> global batch-weighted loss (2 floats over NCCL)
+            wbuf[0] = loss.detach() * B
+            wbuf[1] = B
+            dist.all_reduce(wbuf)
+        loss.backward()
+        return loss
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    sampler = ClockSampler(local)
+    sampler.start()
+    _lib.reset_launch_count()
+    L.b200ctc_profile_enable(1)
+    ms = time_region(step, args.steps, dist_on, dev)
+    L.b200ctc_profile_enable(0)
+    launches = _lib.launch_count() * world
+    pm = (ctypes.c_float * 8)()
+    pc = (ctypes.c_int * 8)()
+    L.b200ctc_profile_read(pm, pc, 8)
+    names = ["prep", "lse_gather", "lattice", "grad_rows"]
+    phases = {n: (pm[i] / pc[i] if pc[i] else None) for i, n in enumerate(names)}
+
+    # ---- e2e: host buffers through the C-ABI pipeline (H2D + compute + D2H of the loss)
+    nll_h = torch.empty(B, dtype=torch.float32).pin_memory()
+    grad_dev = ctypes.c_void_p()
+
+    def e2e_call():
+        rc = L.b200ctc_loss_fwd_bwd_host(host_logits.data_ptr(), 0, tg_h.data_ptr(), il_h.data_ptr(),
+                                         tl_h.data_ptr(), B, T, V, 0, 1, 1.0 / B, nll_h.data_ptr(),
+                                         None, ctypes.byref(grad_dev), 8)
+        _lib.check(rc, "loss_fwd_bwd_host")
+
+    for _ in range(3):
+        e2e_call()
+    if dist_on:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    n_e2e = max(3, min(args.steps, 10))
+    t0 = time.perf_counter()
+    for _ in range(n_e2e):
+        e2e_call()
+    torch.cuda.synchronize(dev)
+    e2e_s = torch.tensor([(time.perf_counter() - t0) / n_e2e], device=dev)
+    if dist_on:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+    L.b200ctc_host_pipeline_release()
+    e2e_ok = abs(float(nll_h.sum()) / B - float(step().detach())) <= 1e-4 * abs(float(nll_h.sum()) / B)
+
+    if rank != 0:
+        if dist_on:
+            dist.destroy_process_group()
+        return
+    peak, peak_src = peaks()
+    alg = algorithmic_bytes(cfg)
+    gr_ms = phases["grad_rows"]
+    line = {
+        "metric": METRIC, "value": world * B * T / (ms * 1e-3), "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": "C2 LibriSpeech-100 BPE-5000 CTC: B=64,T=500,V=5000,L in [75,150], fp32 fwd+bwd"
+                               + (" per rank (utterance-sharded, 2-scalar NCCL all-reduce)" if dist_on else ""),
+                   "l2": "inputs (640 MB logits) exceed the 126 MB L2; no flush needed",
+                   "api": "espnet1_b200.espnet2.asr.ctc.CTC.loss_fn + backward"},
+        "roofline": {"bound": "hbm", "kernel": "grad_rows_kernel (pass B: softmax - occupancy, written once)",
+                     "achieved": alg / (gr_ms * 1e-3) / 1e9 if gr_ms else None, "peak": peak,
+                     "unit": "GB/s", "frac": (alg / (gr_ms * 1e-3) / 1e9 / peak) if gr_ms else None,
+                     "traffic": None, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": alg,
+                     "note": "achieved = SURVEY 8(d) algorithmic bytes of the whole fwd+bwd step / "
+                             "duration of the dominant kernel; 'step' below divides by the whole step"},
+        "roofline_step": {"achieved": alg / (ms * 1e-3) / 1e9, "frac": alg / (ms * 1e-3) / 1e9 / peak,
+                          "frac_of_8TBps_nominal": alg / (ms * 1e-3) / 8e12},
+        "kernel_ms": phases,
+        "e2e": {"value": world * B * T / float(e2e_s), "unit": UNIT,
+                "h2d_bytes_per_step": host_logits.numel() * 4 + 8 * (tg_h.numel() + 3 * B + 1),
+                "d2h_bytes_per_step": 4 * B, "ms_per_step": float(e2e_s) * 1e3,
+                "api": "b200ctc_loss_fwd_bwd_host (pinned host logits in, loss out; grad stays on device)",
+                "matches_device_path": bool(e2e_ok)},
+        "gpu_launches": int(launches * 1),
+        "clocks": sampler.summary(),
+    }
+    if world == 1 and not args.quick:
+        case = (host_logits, tg_h, il_h, tl_h)
+        threads = os.cpu_count() or 1
+        t1 = cpu_reference_step(case, threads)
+        reps = max(2, min(20, int(12.0 / max(t1, 1e-3))))
+        best = min(cpu_reference_step(case, threads) for _ in range(reps))
+        line["cpu_baseline"] = {"value": B * T / best, "unit": UNIT, "cores": threads, "kind": "port",
+                                "sample": f"full C2 batch, best of {reps} (torch-CPU log_softmax+ctc_loss+backward, "
+                                          "oracle/espnet_cpu.py)"}
+        # same-GPU library comparison: PyTorch's own CUDA kernels for the same arithmetic
+        xr = x.detach().clone().requires_grad_(True)
+
+        def torch_step():
+            xr.grad = None
+            lp = xr.transpose(0, 1).log_softmax(2)
+            nll = torch.nn.functional.ctc_loss(lp, tg, il, tl, reduction="none", zero_infinity=True)
+            (nll.sum() / B).backward()
+
+        for _ in range(3):
+            torch_step()
+        line["torch_cuda_library_ms_per_step"] = time_region(torch_step, 10, False, dev)
+        del xr
+        line["prefix_score"] = bench_prefix(dev)
+    print(json.dumps(line), flush=True)
+    if dist_on:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--quick", action="store_true", help="skip CPU baseline / prefix / library extras")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

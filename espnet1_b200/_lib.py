@@ -25,6 +25,8 @@ SIGNATURES = {
     "b200ctc_last_error": (c_char_p, []),
     "b200ctc_launch_count": (c_int64, []),
     "b200ctc_reset_launch_count": (None, []),
+    "b200ctc_profile_enable": (None, [c_int]),
+    "b200ctc_profile_read": (c_int, [POINTER(c_float), POINTER(c_int), c_int]),
     "b200ctc_device_info": (c_int, [POINTER(c_int), POINTER(c_int), POINTER(c_int)]),
     "b200ctc_softmax_fwd": (c_int, [_P, _P, c_int64, c_int, c_int, c_int, _P]),
     "b200ctc_softmax_bwd": (c_int, [_P, _P, _P, c_int64, c_int, c_int, c_int, _P]),

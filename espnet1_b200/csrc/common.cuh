@@ -15,6 +15,10 @@ void set_error(const char* fmt, ...);
 void count_launch(int n = 1);
 int check_launch(const char* what);  // cudaGetLastError -> status
 int sm_count();
+// profiling phases: 0 prep, 1 lse_gather (pass A), 2 lattice, 3 grad_rows (pass B),
+// 4 prefix_step, 5 softmax family
+constexpr int kProfPhases = 8;
+void prof_mark(int phase, int end, cudaStream_t st);
 
 #define B2_REQUIRE(cond, ...)        \
   do {                               \

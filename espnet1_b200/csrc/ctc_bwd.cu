@@ -275,12 +275,19 @@ extern "C" int b200ctc_loss_bwd(const void* logits, int dtype, const int64_t* in
   }
   const unsigned char* ws = static_cast<const unsigned char*>(ws_);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int rc;
+  prof_mark(3, 0, st);
   switch (dtype) {
     case B200CTC_F32:
-      return dispatch_pass_b<float>(logits, grad, B, T, V, blank, w, ws, gscale, gscale_stride, gscale_mul, st);
+      rc = dispatch_pass_b<float>(logits, grad, B, T, V, blank, w, ws, gscale, gscale_stride, gscale_mul, st);
+      break;
     case B200CTC_F16:
-      return dispatch_pass_b<__half>(logits, grad, B, T, V, blank, w, ws, gscale, gscale_stride, gscale_mul, st);
+      rc = dispatch_pass_b<__half>(logits, grad, B, T, V, blank, w, ws, gscale, gscale_stride, gscale_mul, st);
+      break;
     default:
-      return dispatch_pass_b<__nv_bfloat16>(logits, grad, B, T, V, blank, w, ws, gscale, gscale_stride, gscale_mul, st);
+      rc = dispatch_pass_b<__nv_bfloat16>(logits, grad, B, T, V, blank, w, ws, gscale, gscale_stride, gscale_mul, st);
+      break;
   }
+  prof_mark(3, 1, st);
+  return rc;
 }

@@ -297,19 +297,26 @@ extern "C" int b200ctc_loss_fwd(const void* logits, int dtype, const int64_t* ta
   unsigned char* ws = static_cast<unsigned char*>(ws_);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   auto* utt = reinterpret_cast<UttInfo*>(ws + w.utt);
+  prof_mark(0, 0, st);
   prep_kernel<<<B, 128, 0, st>>>(targets, tgt_offsets, in_lens, tgt_lens, T, V, max_tgt_len, w.Lp,
                                  blank, utt, reinterpret_cast<int*>(ws + w.lab),
                                  reinterpret_cast<int*>(ws + w.dup));
   count_launch();
+  prof_mark(0, 1, st);
   int rc = check_launch("ctc prep");
   if (rc) return rc;
   if (T > 0) {
+    prof_mark(1, 0, st);
     switch (dtype) {
       case B200CTC_F32: rc = dispatch_pass_a<float>(logits, B, T, V, w, ws, st); break;
       case B200CTC_F16: rc = dispatch_pass_a<__half>(logits, B, T, V, w, ws, st); break;
       default: rc = dispatch_pass_a<__nv_bfloat16>(logits, B, T, V, w, ws, st); break;
     }
+    prof_mark(1, 1, st);
     if (rc) return rc;
   }
-  return launch_lattice(w, ws, T, zero_infinity, need_grad, nll, st);
+  prof_mark(2, 0, st);
+  rc = launch_lattice(w, ws, T, zero_infinity, need_grad, nll, st);
+  prof_mark(2, 1, st);
+  return rc;
 }

@@ -241,6 +241,7 @@ extern "C" int b200ctc_prefix_step(const float* lp, const float* r_prev, const f
              "prefix_step: bad window [%d,%d) or ids", start, end);
   const int n_bh = B * n_hyps;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  prof_mark(4, 0, st);
   prefix_rsum_kernel<<<blocks((size_t)T * n_bh, 256), 256, 0, st>>>(r_prev, T, n_bh, rsum_ws);
   count_launch();
   if (scoring_ids) {
@@ -252,6 +253,7 @@ extern "C" int b200ctc_prefix_step(const float* lp, const float* r_prev, const f
       lp, r_prev, rsum_ws, s_prev, last_ids, scoring_ids, end_frames, n_bh, n_hyps, T, V, snum,
       out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap);
   count_launch();
+  prof_mark(4, 1, st);
   return check_launch("prefix_step");
 }
 

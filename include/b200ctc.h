@@ -47,6 +47,12 @@ const char* b200ctc_last_error(void);
  * last reset (bench.py's `gpu_launches`). */
 int64_t b200ctc_launch_count(void);
 void b200ctc_reset_launch_count(void);
+/* optional per-phase timing with CUDA events recorded on the caller's stream
+ * around the library's own launches (phase ids: 0 prep, 1 lse_gather, 2 lattice,
+ * 3 grad_rows, 4 prefix_step, 5 softmax family).  profile_read synchronises,
+ * returns per-phase total milliseconds / launch counts and clears the log. */
+void b200ctc_profile_enable(int on);
+int b200ctc_profile_read(float* ms_total, int* counts, int n);
 /* fills sm_count / compute capability of the current device */
 int b200ctc_device_info(int* sm_count, int* cc_major, int* cc_minor);
 

@@ -1,0 +1,138 @@
+"""GPU parity: CUDA CTC path (through the C ABI) vs the oracle and the golden fixtures.
+
+Tolerances (BASELINE.json): loss 1e-5 relative, gradient 1e-4 absolute in fp32,
+integer outputs identical.
+"""
+import numpy as np
+import pytest
+import torch
+
+from _util import close, load_npz
+
+pytestmark = pytest.mark.gpu
+
+LOSS_RTOL = 1e-5
+GRAD_ATOL = 1e-4
+
+
+def _dev():
+    return torch.device("cuda:0")
+
+
+@pytest.fixture(scope="module")
+def gm():
+    return load_npz("ctc_module.npz")
+
+
+def _mk_espnet2(gm, **kw):
+    from espnet1_b200.espnet2.asr.ctc import CTC
+
+    V, D = gm["weight"].shape
+    m = CTC(V, D, **kw).to(_dev())
+    with torch.no_grad():
+        m.ctc_lo.weight.copy_(torch.tensor(gm["weight"]))
+        m.ctc_lo.bias.copy_(torch.tensor(gm["bias"]))
+    return m
+
+
+def test_espnet2_module_matches_reference_fixture(gm):
+    d = _dev()
+    m = _mk_espnet2(gm)
+    hs = torch.tensor(gm["hs"], device=d)
+    hl, yp, yl = (torch.tensor(gm[k], device=d) for k in ("hlens", "ys_pad", "ys_lens"))
+    B = hs.shape[0]
+    for reduce, tag in ((True, "reduce"), (False, "noreduce")):
+        m.reduce = reduce
+        m.zero_grad()
+        x = hs.clone().requires_grad_(True)
+        loss = m(x, hl, yp, yl)
+        close(loss, gm[f"loss_{tag}"], LOSS_RTOL, 1e-6)
+        (loss if reduce else (loss * torch.arange(1, B + 1, device=d)).sum()).backward()
+        close(x.grad, gm[f"ghs_{tag}"], 0, GRAD_ATOL)
+        close(m.ctc_lo.weight.grad, gm[f"gw_{tag}"], 1e-4, GRAD_ATOL)
+        close(m.ctc_lo.bias.grad, gm[f"gb_{tag}"], 1e-4, GRAD_ATOL)
+
+
+def test_espnet2_zero_infinity_false_keeps_inf(gm):
+    d = _dev()
+    m = _mk_espnet2(gm, zero_infinity=False, reduce=False)
+    loss = m(torch.tensor(gm["hs"], device=d), torch.tensor(gm["hlens"], device=d),
+             torch.tensor(gm["ys_pad"], device=d), torch.tensor(gm["ys_lens"], device=d))
+    ref = gm["loss_noreduce_keepinf"]
+    assert np.isinf(ref[3]) and torch.isinf(loss[3])
+    keep = np.isfinite(ref)
+    close(loss.detach().cpu().numpy()[keep], ref[keep], LOSS_RTOL, 1e-6)
+    m2 = _mk_espnet2(gm, ignore_nan_grad=True, zero_infinity=False)
+    assert m2.zero_infinity is True  # ignore_nan_grad overrides (ctc.py:35-36)
+
+
+def test_ctc_type_handling(gm):
+    from espnet1_b200.espnet2.asr.ctc import CTC
+
+    with pytest.raises(ValueError):
+        CTC(5, 4, ctc_type="nope")
+    with pytest.raises(NotImplementedError):
+        CTC(5, 4, ctc_type="gtnctc")
+    m = CTC(5, 4)
+    assert sorted(k for k, _ in m.named_parameters()) == ["ctc_lo.bias", "ctc_lo.weight"]
+
+
+def test_cpu_tensor_fails_loudly(gm):
+    m = _mk_espnet2(gm).cpu()
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        m(torch.tensor(gm["hs"]), torch.tensor(gm["hlens"]), torch.tensor(gm["ys_pad"]),
+          torch.tensor(gm["ys_lens"]))
+
+
+def test_legacy_module_matches_reference_fixture(gm):
+    from espnet1_b200.espnet.nets.pytorch_backend.ctc import CTC
+
+    d = _dev()
+    V, D = gm["weight"].shape
+    for reduce, tag in ((True, "reduce"), (False, "noreduce")):
+        m = CTC(V, D, 0.0, reduce=reduce).to(d)
+        with torch.no_grad():
+            m.ctc_lo.weight.copy_(torch.tensor(gm["weight"]))
+            m.ctc_lo.bias.copy_(torch.tensor(gm["bias"]))
+        x = torch.tensor(gm["hs"], device=d).requires_grad_(True)
+        loss = m(x, torch.tensor(gm["hlens"], device=d), torch.tensor(gm["ys_pad"], device=d))
+        close(loss, gm[f"legacy_loss_{tag}"], LOSS_RTOL, 1e-6)
+        loss.sum().backward()
+        close(x.grad, gm[f"legacy_ghs_{tag}"], 0, GRAD_ATOL)
+    ali = m.forced_align(torch.tensor(gm["hs"][0:1], device=d),
+                         gm["ys_pad"][0][: gm["ys_lens"][0]].tolist())
+    np.testing.assert_array_equal(np.asarray(ali), gm["forced_align_utt0"])
+
+
+def test_softmax_family_vs_fixture(gm):
+    d = _dev()
+    m = _mk_espnet2(gm)
+    hs = torch.tensor(gm["hs"], device=d)
+    with torch.no_grad():
+        close(m.log_softmax(hs), gm["log_softmax"], 1e-5, 1e-6)
+        close(m.softmax(hs), gm["softmax"], 1e-5, 1e-7)
+        np.testing.assert_array_equal(m.argmax(hs).cpu().numpy(), gm["argmax"])
+
+
+def test_c1_logits_boundary_vs_fixture_and_oracle():
+    from espnet1_b200 import functional as F
+    from oracle import ctc_numpy
+
+    g = load_npz("ctc_c1.npz")
+    d = _dev()
+    x = torch.tensor(g["logits"], device=d).requires_grad_(True)
+    nll = F.ctc_loss(x, torch.tensor(g["targets"]), torch.tensor(g["in_lens"]),
+                     torch.tensor(g["tgt_lens"]))
+    close(nll, g["nll"], LOSS_RTOL, 0)
+    (nll.sum() / x.shape[0]).backward()
+    close(x.grad, g["grad"], 0, GRAD_ATOL)
+    # attribution against the fp64 oracle: the CUDA lattice is MORE accurate
+    # than the reference's fp32 log-space one
+    off = np.concatenate(([0], np.cumsum(g["tgt_lens"])))
+    tg = [g["targets"][off[i]: off[i + 1]] for i in range(len(g["tgt_lens"]))]
+    n64, g64 = ctc_numpy.ctc_loss_and_grad(g["logits"], tg, g["in_lens"],
+                                           grad_out=1.0 / len(tg), dtype=np.float64)
+    err_ours = np.abs(x.grad.cpu().numpy() - g64).max()
+    err_ref = np.abs(g["grad"] - g64).max()
+    assert err_ours <= max(2 * err_ref, 2e-6), (err_ours, err_ref)
+    close(nll.detach().cpu().numpy().astype(np.float64), n64, 2e-6, 0)

@@ -1,0 +1,137 @@
+"""GPU parity on seeded random inputs: CUDA path vs the torch-CPU port of the
+reference path (oracle.espnet_cpu) - ragged, edge and full-size cases."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import espnet_cpu
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def make_case(B, T, V, lmin, lmax, seed, ragged=True, scale=2.0, repeat_p=0.0):
+    g = torch.Generator().manual_seed(seed)
+    logits = torch.randn(B, T, V, generator=g) * scale
+    tl = torch.randint(lmin, lmax + 1, (B,), generator=g)
+    il = torch.randint(max(1, T * 3 // 5), T + 1, (B,), generator=g) if ragged else torch.full((B,), T)
+    il[0] = T
+    tgts = []
+    for l in tl.tolist():
+        t = torch.randint(1, V, (l,), generator=g)
+        if repeat_p > 0 and l > 1:
+            rep = torch.rand(l, generator=g) < repeat_p
+            for i in range(1, l):
+                if rep[i]:
+                    t[i] = t[i - 1]
+        tgts.append(t)
+    return logits, torch.cat(tgts) if tgts else torch.zeros(0, dtype=torch.long), il, tl
+
+
+def run_cuda(logits, tg, il, tl, dtype=torch.float32, zero_infinity=True):
+    from espnet1_b200 import functional as F
+
+    x = logits.to(DEV, dtype).requires_grad_(True)
+    nll = F.ctc_loss(x, tg, il, tl, zero_infinity=zero_infinity)
+    (nll.sum() / x.shape[0]).backward()
+    return nll.detach().cpu(), x.grad.detach().float().cpu()
+
+
+def compare(logits, tg, il, tl, dtype=torch.float32, rtol=1e-5, atol=1e-4):
+    src = logits.to(dtype).float()  # the reference sees the same rounded inputs
+    ref_nll, ref_g = espnet_cpu.logits_loss_and_grad(src, tg, il, tl)
+    nll, g = run_cuda(logits, tg, il, tl, dtype)
+    np.testing.assert_allclose(nll.numpy(), ref_nll.numpy(), rtol=rtol, atol=1e-6)
+    np.testing.assert_allclose(g.numpy(), ref_g.numpy(), rtol=0, atol=atol)
+    return nll, g
+
+
+@pytest.mark.parametrize("B,T,V,lmin,lmax", [
+    (8, 200, 30, 25, 50),      # C1 (V*4 not a multiple of 16 -> non-TMA row path)
+    (3, 50, 5000, 5, 20),      # C2 vocabulary, TMA row path
+    (4, 64, 1000, 1, 30),
+    (2, 33, 7, 0, 3),          # tiny vocab, empty targets possible
+    (5, 40, 257, 3, 12),       # odd V (scalar tail)
+])
+def test_random_cases_fp32(B, T, V, lmin, lmax):
+    compare(*make_case(B, T, V, lmin, lmax, seed=100 + V))
+
+
+def test_repeated_labels_and_small_vocab():
+    compare(*make_case(6, 120, 6, 10, 40, seed=5, repeat_p=0.5))
+
+
+def test_edge_lengths():
+    logits, _, _, _ = make_case(4, 12, 16, 1, 1, seed=9)
+    tg = torch.tensor([3, 3, 3, 5, 1, 2, 3, 4, 5, 6, 7])
+    tl = torch.tensor([3, 1, 0, 7])   # utt0 "3 3 3" needs 5 frames; utt3 needs 7
+    il = torch.tensor([12, 1, 4, 6])  # utt3 infeasible (7 labels in 6 frames) -> zeroed
+    nll, g = compare(logits, tg, il, tl)
+    assert nll[3] == 0 and torch.all(g[3] == 0)
+    assert torch.all(g[1, 1:] == 0) and torch.all(g[2, 4:] == 0)
+
+
+def test_zero_infinity_false():
+    logits, _, _, _ = make_case(2, 6, 8, 1, 1, seed=3)
+    tg = torch.tensor([1, 1, 1, 1, 2])
+    tl, il = torch.tensor([4, 1]), torch.tensor([6, 6])
+    nll, g = run_cuda(logits, tg, il, tl, zero_infinity=False)
+    assert torch.isinf(nll[0]) and torch.isfinite(nll[1])
+    assert torch.isnan(g[0]).all() and torch.isfinite(g[1]).all()
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_half_precision_inputs(dtype):
+    # inputs rounded to 16 bit on both sides; arithmetic fp32; grad rounded to 16 bit
+    compare(*make_case(4, 80, 1000, 5, 25, seed=77), dtype=dtype, rtol=2e-5, atol=2e-3)
+
+
+def test_long_form_lattice():
+    """C4 shape per utterance: T=4000, L up to 1200 (lattice 2401 wide, 3 positions/thread)."""
+    compare(*make_case(2, 4000, 512, 600, 1200, seed=11, ragged=False), rtol=1e-5)
+
+
+def test_c2_full_size_vs_cpu_reference():
+    """C2: B=64,T=500,V=5000,L in [75,150], ragged + gradient invariants."""
+    case = make_case(64, 500, 5000, 75, 150, seed=1234)
+    nll, g = compare(*case)
+    il = case[2]
+    # d/dlogits of a function of softmax sums to ~0 over the vocabulary
+    assert g.sum(-1).abs().max() < 2e-5
+    for b in range(64):
+        assert torch.all(g[b, il[b]:] == 0)
+
+
+def test_grad_scale_vector_and_forward_only():
+    from espnet1_b200 import functional as F
+
+    logits, tg, il, tl = make_case(5, 60, 300, 4, 15, seed=21)
+    w = torch.arange(1, 6, dtype=torch.float32)
+    x = logits.to(DEV).requires_grad_(True)
+    nll = F.ctc_loss(x, tg, il, tl)
+    (nll * w.to(DEV)).sum().backward()
+    xr = logits.clone().requires_grad_(True)
+    lp = xr.transpose(0, 1).log_softmax(2)
+    ref = torch.nn.functional.ctc_loss(lp, tg, il, tl, reduction="none", zero_infinity=True)
+    (ref * w).sum().backward()
+    np.testing.assert_allclose(x.grad.cpu().numpy(), xr.grad.numpy(), rtol=0, atol=5e-4)
+    with torch.no_grad():
+        n2 = F.ctc_loss(logits.to(DEV), tg, il, tl)
+    np.testing.assert_allclose(n2.cpu().numpy(), ref.detach().numpy(), rtol=1e-5)
+
+
+def test_greedy_decode_matches_oracle():
+    from espnet1_b200 import functional as F
+    from oracle import ctc_numpy
+
+    g = torch.Generator().manual_seed(4)
+    x = torch.randn(5, 700, 40, generator=g)
+    x[:, :, 0] += 1.5  # plenty of blanks and repeats
+    il = torch.tensor([700, 512, 1, 300, 257])
+    ids, lens = F.greedy_decode(x.to(DEV), il.to(DEV))
+    am = ctc_numpy.argmax(x.numpy())
+    for b in range(5):
+        want = ctc_numpy.greedy_collapse(am[b, : il[b]])
+        assert lens[b].item() == len(want)
+        assert ids[b, : len(want)].tolist() == want
+        assert torch.all(ids[b, len(want):] == -1)
