@@ -1,6 +1,8 @@
 // Library-level entry points: error string, launch counter, device info.
 #include <stdarg.h>
 
+#include <atomic>
+#include <mutex>
 #include <vector>
 
 #include "common.cuh"
@@ -8,7 +10,8 @@
 namespace b200ctc {
 
 static thread_local char g_err[512] = "";
-static thread_local int64_t g_launches = 0;
+// process-wide: autograd runs backward launches on its own engine thread
+static std::atomic<int64_t> g_launches{0};
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -29,14 +32,16 @@ int check_launch(const char* what) {
 }
 
 // ---- optional per-phase CUDA-event profiling (bench.py roofline) -----------
-static thread_local bool g_prof = false;
-static thread_local std::vector<cudaEvent_t> g_ev[kProfPhases][2];
+static std::atomic<bool> g_prof{false};
+static std::mutex g_prof_mu;
+static std::vector<cudaEvent_t> g_ev[kProfPhases][2];
 
 void prof_mark(int phase, int end, cudaStream_t st) {
   if (!g_prof || phase < 0 || phase >= kProfPhases) return;
   cudaEvent_t e;
   if (cudaEventCreate(&e) != cudaSuccess) return;
   cudaEventRecord(e, st);
+  std::lock_guard<std::mutex> lk(g_prof_mu);
   g_ev[phase][end ? 1 : 0].push_back(e);
 }
 
@@ -59,13 +64,14 @@ extern "C" {
 
 int b200ctc_abi_version(void) { return B200CTC_ABI_VERSION; }
 const char* b200ctc_last_error(void) { return b200ctc::g_err; }
-int64_t b200ctc_launch_count(void) { return b200ctc::g_launches; }
+int64_t b200ctc_launch_count(void) { return b200ctc::g_launches.load(); }
 void b200ctc_reset_launch_count(void) { b200ctc::g_launches = 0; }
 
 void b200ctc_profile_enable(int on) { b200ctc::g_prof = on != 0; }
 
 int b200ctc_profile_read(float* ms_total, int* counts, int n) {
   using namespace b200ctc;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
   for (int p = 0; p < kProfPhases; ++p) {
     float tot = 0.f;
     int cnt = 0;

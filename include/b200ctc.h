@@ -43,7 +43,7 @@ typedef void* b200ctc_stream_t; /* cudaStream_t */
 /* ---- library -------------------------------------------------------------- */
 int b200ctc_abi_version(void);
 const char* b200ctc_last_error(void);
-/* number of kernels launched by this library on the calling thread since the
+/* number of kernels launched by this library (process-wide) since the
  * last reset (bench.py's `gpu_launches`). */
 int64_t b200ctc_launch_count(void);
 void b200ctc_reset_launch_count(void);

@@ -87,8 +87,21 @@ def test_half_precision_inputs(dtype):
 
 
 def test_long_form_lattice():
-    """C4 shape per utterance: T=4000, L up to 1200 (lattice 2401 wide, 3 positions/thread)."""
-    compare(*make_case(2, 4000, 512, 600, 1200, seed=11, ragged=False), rtol=1e-5)
+    """C4 shape per utterance: T=4000, L up to 1200 (lattice 2401 wide, 3 positions/thread).
+
+    At NLL ~ 2.5e4 the reference's fp32 log-space lattice is itself off by ~4e-2 per
+    gradient element (ulp(2.5e4) = 2e-3 in the exponent; measured vs torch fp64), so the
+    fp32 reference cannot be the yardstick here: the truth is the SAME torch-CPU path run
+    in fp64, and we must be at least 20x closer to it than the fp32 reference is."""
+    logits, tg, il, tl = make_case(2, 4000, 512, 600, 1200, seed=11, ragged=False)
+    n64, g64 = espnet_cpu.logits_loss_and_grad(logits.double(), tg, il, tl)
+    n32, g32 = espnet_cpu.logits_loss_and_grad(logits, tg, il, tl)
+    nll, g = run_cuda(logits, tg, il, tl)
+    np.testing.assert_allclose(nll.numpy(), n64.numpy(), rtol=1e-5)
+    np.testing.assert_allclose(nll.numpy(), n32.numpy(), rtol=1e-5)
+    err_ours = (g.double() - g64).abs().max().item()
+    err_ref = (g32.double() - g64).abs().max().item()
+    assert err_ours < 1e-3 and err_ours * 20 < err_ref, (err_ours, err_ref)
 
 
 def test_c2_full_size_vs_cpu_reference():
