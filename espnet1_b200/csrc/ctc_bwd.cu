@@ -5,51 +5,20 @@
 //     grad[b,t,v] = g_b * ( softmax(x)[v] - sum_{s: l_s = v} gamma_t(s) )
 // (= autograd of log_softmax + ctc_loss, espnet2/asr/ctc.py:54-55; the
 // analytically-zero term softmax * sum_v g_lp is dropped.)
-#include "ctc_ws.cuh"
+#include "rows_common.cuh"
 
 namespace b200ctc {
-
-template <typename T>
-struct ElemsB { static constexpr int N = sizeof(T) == 4 ? 4 : 8; };
-
-template <typename T>
-__device__ __forceinline__ void unpack16b(const uint4& raw, float* f) {
-  if (sizeof(T) == 4) {
-    f[0] = __uint_as_float(raw.x); f[1] = __uint_as_float(raw.y);
-    f[2] = __uint_as_float(raw.z); f[3] = __uint_as_float(raw.w);
-  } else {
-    const T* h = reinterpret_cast<const T*>(&raw);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) f[i] = to_f32<T>(h[i]);
-  }
-}
-template <typename T>
-__device__ __forceinline__ void store16(T* p, const float* f) {
-  if (sizeof(T) == 4) {
-    __stcs(reinterpret_cast<float4*>(p), make_float4(f[0], f[1], f[2], f[3]));
-  } else {
-    uint4 t;
-    T* h = reinterpret_cast<T*>(&t);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) h[i] = from_f32<T>(f[i]);
-    __stcs(reinterpret_cast<uint4*>(p), t);
-  }
-}
-
-constexpr int kMaxStagesB = 8;
 
 template <typename T, int NT, int PER, bool TMA>
 __global__ void __launch_bounds__(NT) grad_rows_kernel(
     const T* __restrict__ logits, T* __restrict__ grad, int B, int Tfr, int V, int blank,
     const UttInfo* __restrict__ utt, const int* __restrict__ lab, const int* __restrict__ dup,
-    int Lp, int Sp, const float* __restrict__ lse2, const float* __restrict__ mt,
+    int Lp, int Sp, const float* __restrict__ lse2, const float* __restrict__ qt,
     const float* __restrict__ alpha, const float* __restrict__ beta,
-    const double* __restrict__ offA, const double* __restrict__ offB,
-    const float* __restrict__ gscale, int gstride, float gmul, int nstage, int stage_stride,
-    int pbuf_len) {
-  constexpr int N = ElemsB<T>::N;
+    const float* __restrict__ gscale, int gstride, float gmul, int nstage, int stage_stride) {
+  constexpr int N = Elems<T>::N;
   extern __shared__ __align__(128) unsigned char dsm[];
-  __shared__ __align__(8) uint64_t bars[kMaxStagesB];
+  __shared__ __align__(8) uint64_t bars[kMaxRowStages];
   __shared__ float wp[32];
   unsigned char* stages = dsm;
   float* pbuf = reinterpret_cast<float*>(dsm + (size_t)nstage * stage_stride);  // [Lp]
@@ -58,23 +27,18 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
   const uint32_t row_bytes = (uint32_t)V * sizeof(T);
   const int nchunk = V / N;
   const int ntail = V - nchunk * N;
-  (void)pbuf_len;
 
-  int64_t gp = blockIdx.x;
+  RowCursor pc;
+  pc.init(blockIdx.x, gridDim.x, Tfr);
   uint32_t np = 0;
-  auto row_live = [&](int64_t g) {
-    const int b = (int)(g / Tfr);
-    const int t = (int)(g - (int64_t)b * Tfr);
-    return t < utt[b].T && !utt[b].zeroed;
-  };
   auto issue_next = [&]() {
-    while (gp < nrows && !row_live(gp)) gp += gridDim.x;
-    if (gp < nrows) {
+    while (pc.g < nrows && (pc.t >= utt[pc.b].T || utt[pc.b].zeroed)) pc.next();
+    if (pc.g < nrows) {
       const int st = np % nstage;
       mbar_expect_tx(&bars[st], row_bytes);
-      bulk_g2s(stages + (size_t)st * stage_stride, logits + gp * V, row_bytes, &bars[st]);
+      bulk_g2s(stages + (size_t)st * stage_stride, logits + pc.g * V, row_bytes, &bars[st]);
       ++np;
-      gp += gridDim.x;
+      pc.next();
     }
   };
   if (TMA) {
@@ -88,16 +52,27 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
   }
 
   uint32_t n = 0;
-  for (int64_t g = blockIdx.x; g < nrows; g += gridDim.x) {
-    const int b = (int)(g / Tfr);
-    const int t = (int)(g - (int64_t)b * Tfr);
+  RowCursor rc;
+  rc.init(blockIdx.x, gridDim.x, Tfr);
+  // per-row scalars are fetched one row ahead (their latency hides behind the current row)
+  float l2_nx = rc.g < nrows ? lse2[rc.g] : 0.f;
+  float q_nx = rc.g < nrows ? qt[rc.g] : 0.f;
+  for (; rc.g < nrows; rc.next()) {
+    const int b = rc.b, t = rc.t;
+    const int64_t g = rc.g;
+    const float l2 = l2_nx, q = q_nx;
+    if (g + rc.stride < nrows) {
+      l2_nx = lse2[g + rc.stride];
+      q_nx = qt[g + rc.stride];
+    }
     const UttInfo u = utt[b];
     T* gr = grad + g * V;
+    const bool al16 = (reinterpret_cast<uintptr_t>(gr) & 15) == 0;
     if (t >= u.T || u.zeroed) {  // padded frame or zeroed utterance: gradient is 0
       float z[N];
 #pragma unroll
       for (int e = 0; e < N; ++e) z[e] = 0.f;
-      if ((reinterpret_cast<uintptr_t>(gr) & 15) == 0) {
+      if (al16) {
         for (int i = tid; i < nchunk; i += NT) store16<T>(gr + i * N, z);
         if (tid < ntail) gr[nchunk * N + tid] = from_f32<T>(0.f);
       } else {
@@ -105,21 +80,17 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
       }
       continue;
     }
-    // ---- per-row scalars (independent of the row data: issued before the wait)
     const int L = u.L, S = 2 * L + 1;
-    const float l2 = lse2[g];
-    const float mrow = mt[g];
     float gb = gmul * (gscale ? gscale[(size_t)b * gstride] : 1.f);
-    if (u.infinite) gb = __int_as_float(0x7fc00000);  // inf loss kept (!zero_infinity): NaN row
-    float o_t;
-    {
-      const double o = (offA[g] + offB[g]) - u.aend - u.lam;
-      o_t = u.infinite ? __int_as_float(0x7fc00000) : (float)o;  // inf loss kept -> NaN grads
+    float o_t = q;  // = mt + offA + offB - aend - lam  (finalize_kernel)
+    if (u.infinite) {  // inf loss kept (!zero_infinity): the reference's gradient is NaN
+      gb = __int_as_float(0x7fc00000);
+      o_t = gb;
     }
     const float* al = alpha + (size_t)g * Sp;
     const float* be = beta + (size_t)g * Sp;
     const int* lb = lab + (size_t)b * Lp;
-    constexpr int SM = 4;  // lattice positions per thread kept in flight
+    constexpr int SM = 3;  // lattice positions per thread whose loads are issued before the wait
     float ab[SM];
 #pragma unroll
     for (int j = 0; j < SM; ++j) {
@@ -139,7 +110,7 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
       __syncthreads();
     }
     const T* xs = reinterpret_cast<const T*>(stg);
-    // ---- phase 1a: occupancies gamma_t(s) = 2^(alpha+beta-em+o_t)
+    // ---- phase 1a: occupancies gamma_t(s) = 2^(alpha + beta - lp2(l_s) + o_t)
     float blank_part = 0.f;
     for (int s0 = 0; s0 < S; s0 += NT * SM) {
 #pragma unroll
@@ -150,8 +121,8 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
           const bool odd = s & 1;
           const int k = odd ? (s + 1) >> 1 : 0;
           const int v = odd ? lb[k] : blank;
-          const float emv = fmaf(to_f32<T>(xs[v]), kLog2e, -l2) - mrow;
-          const float p = ex2(abv - emv + o_t);
+          const float lp2 = fmaf(to_f32<T>(xs[v]), kLog2e, -l2);
+          const float p = ex2(abv - lp2 + o_t);
           if (odd) pbuf[k] = p; else blank_part += p;
         }
       }
@@ -159,13 +130,12 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
     blank_part = warp_sum(blank_part);
     if (lane == 0) wp[wid] = blank_part;
     // ---- phase 1b: dense part, g_b * softmax(x), straight from registers
-    const bool al16 = (reinterpret_cast<uintptr_t>(gr) & 15) == 0;
 #pragma unroll
     for (int j = 0; j < PER; ++j) {
       const int i = tid + j * NT;
       if (i < nchunk) {
         float x[N];
-        unpack16b<T>(reinterpret_cast<const uint4*>(stg)[i], x);
+        unpack16<T>(reinterpret_cast<const uint4*>(stg)[i], x);
 #pragma unroll
         for (int e = 0; e < N; ++e) x[e] = gb * ex2(fmaf(x[e], kLog2e, -l2));
         if (al16) store16<T>(gr + i * N, x);
@@ -209,34 +179,27 @@ template <typename T, int NT>
 static int launch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, int blank,
                          const LossLayout& w, const unsigned char* ws, const float* gscale,
                          int gstride, float gmul, cudaStream_t st) {
-  constexpr int PER = 32 / ElemsB<T>::N;
-  const size_t row_bytes = (size_t)V * sizeof(T);
-  const bool tma = (row_bytes % 16 == 0) && ((reinterpret_cast<uintptr_t>(logits) & 15) == 0);
-  const int stride = (int)align_up(row_bytes, 128);
+  constexpr int PER = 40 / Elems<T>::N;
   const size_t extra = align_up(sizeof(float) * (size_t)w.Lp, 128);
-  int nstage, ctas_per_sm;
-  if ((size_t)stride * 2 + extra <= 100 * 1024) { ctas_per_sm = 2; nstage = (int)((100 * 1024 - extra) / stride); }
-  else { ctas_per_sm = 1; nstage = (int)((200 * 1024 - extra) / stride); }
-  if (nstage > 4) nstage = 4;
-  if (!tma && nstage > 1) nstage = 1;
-  B2_REQUIRE(nstage >= 1, "ctc_loss bwd: V=%d too large for the shared-memory row path", V);
-  const size_t smem = (size_t)nstage * stride + extra;
+  const RowLaunchCfg c = row_launch_cfg(logits, (size_t)V * sizeof(T), extra, NT, "B200CTC_B");
+  B2_REQUIRE((size_t)c.nstage * c.stride + extra <= 226 * 1024,
+             "ctc_loss bwd: V=%d too large for the shared-memory row path", V);
+  const size_t smem = (size_t)c.nstage * c.stride + extra;
   const int64_t rows = (int64_t)B * Tfr;
-  int grid = sm_count() * ctas_per_sm;
-  if (grid > rows) grid = (int)rows;
-  auto args = [&](auto k) {
+  int64_t grid = (int64_t)sm_count() * c.ctas_per_sm;
+  if (grid > rows) grid = rows;
+  auto go = [&](auto k) {
     cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k<<<grid, NT, smem, st>>>(
+    k<<<(unsigned)grid, NT, smem, st>>>(
         static_cast<const T*>(logits), static_cast<T*>(grad), B, Tfr, V, blank,
         reinterpret_cast<const UttInfo*>(ws + w.utt), reinterpret_cast<const int*>(ws + w.lab),
         reinterpret_cast<const int*>(ws + w.dup), w.Lp, w.Sp,
-        reinterpret_cast<const float*>(ws + w.lse2), reinterpret_cast<const float*>(ws + w.mt),
+        reinterpret_cast<const float*>(ws + w.lse2), reinterpret_cast<const float*>(ws + w.qt),
         reinterpret_cast<const float*>(ws + w.alpha), reinterpret_cast<const float*>(ws + w.beta),
-        reinterpret_cast<const double*>(ws + w.offA), reinterpret_cast<const double*>(ws + w.offB),
-        gscale, gstride, gmul, nstage, stride, w.Lp);
+        gscale, gstride, gmul, c.nstage, c.stride);
   };
-  if (tma) args(grad_rows_kernel<T, NT, PER, true>);
-  else args(grad_rows_kernel<T, NT, PER, false>);
+  if (c.tma) go(grad_rows_kernel<T, NT, PER, true>);
+  else go(grad_rows_kernel<T, NT, PER, false>);
   count_launch();
   return check_launch("ctc grad_rows");
 }
@@ -245,7 +208,8 @@ template <typename T>
 static int dispatch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, int blank,
                            const LossLayout& w, const unsigned char* ws, const float* gscale,
                            int gstride, float gmul, cudaStream_t st) {
-  const int need = (V + 31) / 32;
+  const int need = (V + 39) / 40;
+  if (need <= 128) return launch_pass_b<T, 128>(logits, grad, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, st);
   if (need <= 256) return launch_pass_b<T, 256>(logits, grad, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, st);
   if (need <= 512) return launch_pass_b<T, 512>(logits, grad, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, st);
   if (need <= 1024) return launch_pass_b<T, 1024>(logits, grad, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, st);

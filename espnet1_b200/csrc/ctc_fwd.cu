@@ -3,7 +3,7 @@
 // by the TMA engine (1-D bulk copies, mbarrier ring), (3) alpha/beta lattice
 // recursion (ctc_lattice.cuh), one CTA per utterance and direction.
 #include "ctc_lattice.cuh"
-#include "ctc_ws.cuh"
+#include "rows_common.cuh"
 
 namespace b200ctc {
 
@@ -64,56 +64,39 @@ __global__ void __launch_bounds__(128) prep_kernel(const int64_t* __restrict__ t
 }
 
 // --------------------------------------------------------- pass A (rows)
-template <typename T>
-struct Elems { static constexpr int N = sizeof(T) == 4 ? 4 : 8; };
-
-template <typename T>
-__device__ __forceinline__ void unpack16(const uint4& raw, float* f) {
-  if (sizeof(T) == 4) {
-    f[0] = __uint_as_float(raw.x); f[1] = __uint_as_float(raw.y);
-    f[2] = __uint_as_float(raw.z); f[3] = __uint_as_float(raw.w);
-  } else {
-    const T* h = reinterpret_cast<const T*>(&raw);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) f[i] = to_f32<T>(h[i]);
-  }
-}
-
-constexpr int kMaxStages = 8;
-
 // Persistent CTAs; each loops over (b,t) rows.  TMA=true: rows arrive in an
 // NSTAGE-deep shared-memory ring via cp.async.bulk; TMA=false (row bytes or
-// base not 16-B aligned): the CTA copies the row itself.
-template <typename T, int NT, int PER, int GMAX, bool TMA>
+// base not 16-B aligned): the CTA copies the row itself.  Few threads per row
+// (128 for V<=5120) keep the reduction overhead per element small; several
+// CTAs per SM overlap each other's barriers.
+template <typename T, int NT, int PER, bool TMA>
 __global__ void __launch_bounds__(NT) lse_gather_kernel(
     const T* __restrict__ logits, int B, int Tfr, int V, const UttInfo* __restrict__ utt,
     const int* __restrict__ lab, int Lp, float* __restrict__ lse2, float* __restrict__ mt,
     float* __restrict__ em, int nstage, int stage_stride) {
   constexpr int N = Elems<T>::N;
-  extern __shared__ __align__(128) unsigned char stages[];
-  __shared__ __align__(8) uint64_t bars[kMaxStages];
+  extern __shared__ __align__(128) unsigned char dsm[];
+  __shared__ __align__(8) uint64_t bars[kMaxRowStages];
   __shared__ float red[2][32];
+  unsigned char* stages = dsm;
+  float* gbuf = reinterpret_cast<float*>(dsm + (size_t)nstage * stage_stride);  // [2][Lp]
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int64_t nrows = (int64_t)B * Tfr;
   const uint32_t row_bytes = (uint32_t)V * sizeof(T);
   const int nchunk = V / N;
   const int ntail = V - nchunk * N;
 
-  int64_t gp = blockIdx.x;  // producer cursor (thread 0)
+  RowCursor pc;  // producer cursor (thread 0 only)
+  pc.init(blockIdx.x, gridDim.x, Tfr);
   uint32_t np = 0;
   auto issue_next = [&]() {
-    while (gp < nrows) {
-      const int b = (int)(gp / Tfr);
-      const int t = (int)(gp - (int64_t)b * Tfr);
-      if (t < utt[b].T) break;
-      gp += gridDim.x;
-    }
-    if (gp < nrows) {
+    while (pc.g < nrows && pc.t >= utt[pc.b].T) pc.next();
+    if (pc.g < nrows) {
       const int st = np % nstage;
       mbar_expect_tx(&bars[st], row_bytes);
-      bulk_g2s(stages + (size_t)st * stage_stride, logits + gp * V, row_bytes, &bars[st]);
+      bulk_g2s(stages + (size_t)st * stage_stride, logits + pc.g * V, row_bytes, &bars[st]);
       ++np;
-      gp += gridDim.x;
+      pc.next();
     }
   };
   if (TMA) {
@@ -127,12 +110,13 @@ __global__ void __launch_bounds__(NT) lse_gather_kernel(
   }
 
   uint32_t n = 0;
-  for (int64_t g = blockIdx.x; g < nrows; g += gridDim.x) {
-    const int b = (int)(g / Tfr);
-    const int t = (int)(g - (int64_t)b * Tfr);
-    const int Tb = utt[b].T;
-    if (t >= Tb) continue;
-    const int L = utt[b].L;
+  RowCursor rc;
+  for (rc.init(blockIdx.x, gridDim.x, Tfr); rc.g < nrows; rc.next()) {
+    const int b = rc.b;
+    const int2 TL = *reinterpret_cast<const int2*>(&utt[b].T);  // {T, L}
+    if (rc.t >= TL.x) continue;
+    const int L = TL.y;
+    const int64_t g = rc.g;
     const unsigned char* stg;
     if (TMA) {
       const int st = n % nstage;
@@ -162,24 +146,18 @@ __global__ void __launch_bounds__(NT) lse_gather_kernel(
       xt = to_f32<T>(reinterpret_cast<const T*>(stg)[nchunk * N + tid]);
       m = fmaxf(m, xt);
     }
-    // lattice emissions: raw logits of blank (k=0) and the L labels
-    float gv[GMAX];
+    // raw logits of the blank (k = 0) and the L labels -> scratch (double buffered per row)
+    float* gb = gbuf + (n & 1) * Lp;
     const int* lb = lab + (size_t)b * Lp;
-#pragma unroll
-    for (int j = 0; j < GMAX; ++j) {
-      const int k = tid + j * NT;
-      gv[j] = kNegInf;
-      if (k <= L) {
-        gv[j] = to_f32<T>(reinterpret_cast<const T*>(stg)[lb[k]]);
-        m = fmaxf(m, gv[j]);  // no-op numerically; forces the read before the barrier
-      }
-    }
+    for (int k = tid; k <= L; k += NT) gb[k] = to_f32<T>(reinterpret_cast<const T*>(stg)[lb[k]]);
     // block max
     m = warp_max(m);
-    if (lane == 0) red[0][wid] = m;
-    __syncthreads();
-    m = warp_max(lane < NT / 32 ? red[0][lane] : kNegInf);
-    // every thread holds its part of the row in registers: the stage is free
+    if (NT > 32) {
+      if (lane == 0) red[0][wid] = m;
+      __syncthreads();
+      m = warp_max(lane < NT / 32 ? red[0][lane] : kNegInf);
+    }
+    // every thread holds its part of the row in registers / scratch: the stage is free
     if (TMA && tid == 0) issue_next();
     const float mm = (m == kNegInf) ? 0.f : m;
     const float m2 = mm * kLog2e;
@@ -194,20 +172,18 @@ __global__ void __launch_bounds__(NT) lse_gather_kernel(
     }
     if (tid < ntail) s += ex2(fmaf(xt, kLog2e, -m2));
     s = warp_sum(s);
-    if (lane == 0) red[1][wid] = s;
-    __syncthreads();
-    s = warp_sum(lane < NT / 32 ? red[1][lane] : 0.f);
-    const float l2s = log2f(s);
+    if (NT > 32) {
+      if (lane == 0) red[1][wid] = s;
+      __syncthreads();
+      s = warp_sum(lane < NT / 32 ? red[1][lane] : 0.f);
+    }
     if (tid == 0) {
+      const float l2s = log2f(s);
       lse2[g] = m2 + l2s;
       mt[g] = -l2s;
     }
     float* er = em + (size_t)g * Lp;
-#pragma unroll
-    for (int j = 0; j < GMAX; ++j) {
-      const int k = tid + j * NT;
-      if (k <= L) er[k] = fmaf(gv[j], kLog2e, -m2);
-    }
+    for (int k = tid; k <= L; k += NT) er[k] = fmaf(gb[k], kLog2e, -m2);
     ++n;
   }
 }
@@ -217,36 +193,27 @@ template <typename T, int NT>
 static int launch_pass_a(const void* logits, int B, int Tfr, int V, const LossLayout& w,
                          unsigned char* ws, cudaStream_t st) {
   constexpr int N = Elems<T>::N;
-  constexpr int PER = 32 / N, GMAX = 8;
-  const size_t row_bytes = (size_t)V * sizeof(T);
-  const bool tma = (row_bytes % 16 == 0) && ((reinterpret_cast<uintptr_t>(logits) & 15) == 0);
-  const int stride = (int)align_up(row_bytes, 128);
-  int nstage, ctas_per_sm;
-  if (stride * 2 <= 100 * 1024) { ctas_per_sm = 2; nstage = (100 * 1024) / stride; }
-  else { ctas_per_sm = 1; nstage = (200 * 1024) / stride; }
-  if (nstage > 4) nstage = 4;
-  if (!tma) nstage = 1;
-  B2_REQUIRE(nstage >= 1, "ctc_loss: V=%d too large for the shared-memory row path", V);
-  const size_t smem = (size_t)nstage * stride;
+  constexpr int PER = 40 / N;
+  const size_t extra = align_up(sizeof(float) * 2 * (size_t)w.Lp, 128);
+  const RowLaunchCfg c = row_launch_cfg(logits, (size_t)V * sizeof(T), extra, NT, "B200CTC_A");
+  B2_REQUIRE((size_t)c.nstage * c.stride + extra <= 226 * 1024,
+             "ctc_loss: V=%d too large for the shared-memory row path", V);
+  const size_t smem = (size_t)c.nstage * c.stride + extra;
   const int64_t rows = (int64_t)B * Tfr;
-  int grid = sm_count() * ctas_per_sm * (NT <= 256 ? 1 : 1);
-  if (grid > rows) grid = (int)rows;
+  int64_t grid = (int64_t)sm_count() * c.ctas_per_sm;
+  if (grid > rows) grid = rows;
   auto* utt = reinterpret_cast<const UttInfo*>(ws + w.utt);
   auto* lab = reinterpret_cast<const int*>(ws + w.lab);
   auto* lse2 = reinterpret_cast<float*>(ws + w.lse2);
   auto* mt = reinterpret_cast<float*>(ws + w.mt);
   auto* em = reinterpret_cast<float*>(ws + w.em);
-  if (tma) {
-    auto k = lse_gather_kernel<T, NT, PER, GMAX, true>;
+  auto go = [&](auto k) {
     cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k<<<grid, NT, smem, st>>>(static_cast<const T*>(logits), B, Tfr, V, utt, lab, w.Lp, lse2, mt,
-                              em, nstage, stride);
-  } else {
-    auto k = lse_gather_kernel<T, NT, PER, GMAX, false>;
-    cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k<<<grid, NT, smem, st>>>(static_cast<const T*>(logits), B, Tfr, V, utt, lab, w.Lp, lse2, mt,
-                              em, nstage, stride);
-  }
+    k<<<(unsigned)grid, NT, smem, st>>>(static_cast<const T*>(logits), B, Tfr, V, utt, lab, w.Lp,
+                                        lse2, mt, em, c.nstage, c.stride);
+  };
+  if (c.tma) go(lse_gather_kernel<T, NT, PER, true>);
+  else go(lse_gather_kernel<T, NT, PER, false>);
   count_launch();
   return check_launch("ctc lse_gather");
 }
@@ -254,14 +221,12 @@ static int launch_pass_a(const void* logits, int B, int Tfr, int V, const LossLa
 template <typename T>
 static int dispatch_pass_a(const void* logits, int B, int Tfr, int V, const LossLayout& w,
                            unsigned char* ws, cudaStream_t st) {
-  constexpr int N = Elems<T>::N;
-  const int need_v = (V + 31) / 32;                    // threads so that NT*PER*N >= V (PER*N = 32)
-  const int need_l = (w.Lmax + 1 + 7) / 8;            // threads so that NT*GMAX >= L+1
-  const int need = need_v > need_l ? need_v : need_l;
+  const int need = (V + 39) / 40;  // threads so that NT*PER*N >= V (PER*N = 40)
+  if (need <= 128) return launch_pass_a<T, 128>(logits, B, Tfr, V, w, ws, st);
   if (need <= 256) return launch_pass_a<T, 256>(logits, B, Tfr, V, w, ws, st);
   if (need <= 512) return launch_pass_a<T, 512>(logits, B, Tfr, V, w, ws, st);
   if (need <= 1024) return launch_pass_a<T, 1024>(logits, B, Tfr, V, w, ws, st);
-  set_error("ctc_loss: V=%d / max_tgt_len=%d exceed the supported row size", V, w.Lmax);
+  set_error("ctc_loss: V=%d exceeds the supported row size", V);
   return B200CTC_ERR_ARG;
 }
 

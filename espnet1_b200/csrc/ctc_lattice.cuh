@@ -2,8 +2,10 @@
 // One CTA per (utterance, direction): blockIdx.y = 0 runs alpha forward in
 // time, 1 runs beta backward in time as "alpha on the reversed lattice".
 // The lattice row lives in shared memory (double buffered, one barrier per
-// frame); emissions are prefetched PF frames ahead into registers; every K
-// frames the row is re-centred on its maximum (shift recorded in fp64).
+// frame).  The emissions em[t][k] of the next frames are streamed into a
+// shared-memory ring by the TMA engine (1-D bulk copies of whole frame chunks,
+// completion on mbarriers) so the dependent chain never touches global memory;
+// every K frames the row is re-centred on its maximum (shift recorded in fp64).
 #pragma once
 #include "ctc_ws.cuh"
 
@@ -11,6 +13,8 @@ namespace b200ctc {
 
 constexpr int kMaxLattice = 8192;  // 2*L+1 <= 8192  (R <= 8 positions per thread)
 constexpr int kRenormEvery = 16;
+constexpr int kEmRing = 4;         // chunks of emission frames in flight
+constexpr int kHalo = 4;           // -inf cells in front of the row (keeps rows 16-B aligned)
 
 __device__ __forceinline__ float lse3_log2(float a0, float a1, float a2) {
   const float m = fmaxf(fmaxf(a0, a1), a2);
@@ -18,13 +22,16 @@ __device__ __forceinline__ float lse3_log2(float a0, float a1, float a2) {
   return ms + lg2(ex2(a0 - ms) + ex2(a1 - ms) + ex2(a2 - ms));
 }
 
-template <int R, int PF>
+template <int R>
 __global__ void __launch_bounds__(1024) lattice_kernel(
     UttInfo* __restrict__ utt, const int* __restrict__ lab, int Lp, const float* __restrict__ em,
     const float* __restrict__ mt, float* __restrict__ alpha, float* __restrict__ beta,
     double* __restrict__ offA, double* __restrict__ offB, int Tfr, int Sp, int zero_infinity,
-    float* __restrict__ nll) {
-  extern __shared__ float lsm[];
+    float* __restrict__ nll, int chunk) {
+  extern __shared__ __align__(128) float lsm[];
+  __shared__ __align__(8) uint64_t bars[kEmRing];
+  __shared__ double dred[32];
+  __shared__ float wmax[32];
   const int NT = blockDim.x;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, NW = NT >> 5;
   const int b = blockIdx.x, dir = blockIdx.y;
@@ -38,23 +45,43 @@ __global__ void __launch_bounds__(1024) lattice_kernel(
     }
     return;
   }
-  float* buf0 = lsm;                // [Sp + 4], cells 0,1 are the -inf halo
-  float* buf1 = lsm + Sp + 4;
-  float* wmax = lsm + 2 * (Sp + 4);  // [32]
-  __shared__ double dred[32];
+  const int rowlen = Sp + kHalo;
+  float* buf0 = lsm;
+  float* buf1 = lsm + rowlen;
+  float* ring = lsm + 2 * rowlen;  // [kEmRing][chunk * Lp]
+  const int chunk_elems = chunk * Lp;
   float* lat = (dir ? beta : alpha) + (size_t)b * Tfr * Sp;
   double* off = (dir ? offB : offA) + (size_t)b * Tfr;
   const float* emb = em + (size_t)b * Tfr * Lp;
   const int* lb = lab + (size_t)b * Lp;
+  const int nchunks = (Tb + chunk - 1) / chunk;
 
-  for (int i = tid; i < 2 * (Sp + 4); i += NT) lsm[i] = kNegInf;
+  // chunk c holds recursion steps [c*chunk, (c+1)*chunk): frames ascending for
+  // alpha, the mirrored (still contiguous) frame block for beta
+  auto issue_chunk = [&](int c) {
+    const int i0 = c * chunk;
+    const int n = (Tb - i0 < chunk) ? Tb - i0 : chunk;
+    const int f0 = dir ? Tb - i0 - n : i0;  // first frame of the block
+    const int slot = c % kEmRing;
+    const uint32_t bytes = (uint32_t)n * Lp * 4u;
+    mbar_expect_tx(&bars[slot], bytes);
+    bulk_g2s(ring + (size_t)slot * chunk_elems, emb + (size_t)f0 * Lp, bytes, &bars[slot]);
+  };
+  if (tid == 0) {
+    for (int i = 0; i < kEmRing; ++i) mbar_init(&bars[i], 1);
+    fence_mbar_init();
+  }
+  for (int i = tid; i < 2 * rowlen; i += NT) lsm[i] = kNegInf;
+  __syncthreads();
+  if (tid == 0)
+    for (int c = 0; c < kEmRing && c < nchunks; ++c) issue_chunk(c);
 
   // static description of this thread's lattice positions
   int s_of[R], k_of[R];
   bool act[R], skip[R];
 #pragma unroll
   for (int j = 0; j < R; ++j) {
-    const int sp = tid + j * NT;       // position in recursion order
+    const int sp = tid + j * NT;          // position in recursion order
     act[j] = sp < S;
     const int s = dir ? S - 1 - sp : sp;  // true lattice index
     s_of[j] = s;
@@ -68,64 +95,54 @@ __global__ void __launch_bounds__(1024) lattice_kernel(
     }
     skip[j] = sk;
   }
-  // emission prefetch ring
-  float pf[R][PF];
-#pragma unroll
-  for (int u = 0; u < PF; ++u) {
-    const int t = dir ? Tb - 1 - u : u;
-#pragma unroll
-    for (int j = 0; j < R; ++j)
-      pf[j][u] = (u < Tb && act[j]) ? emb[(size_t)t * Lp + k_of[j]] : 0.f;
-  }
-  __syncthreads();
 
   double a_run = 0.0;
-  for (int i0 = 0; i0 < Tb; i0 += PF) {
-#pragma unroll
-    for (int u = 0; u < PF; ++u) {
+  for (int c = 0; c < nchunks; ++c) {
+    const int i0 = c * chunk;
+    const int n = (Tb - i0 < chunk) ? Tb - i0 : chunk;
+    const int slot = c % kEmRing;
+    const float* ech = ring + (size_t)slot * chunk_elems;
+    mbar_wait(&bars[slot], (c / kEmRing) & 1);
+    for (int u = 0; u < n; ++u) {
       const int i = i0 + u;
-      if (i < Tb) {
-        const int t = dir ? Tb - 1 - i : i;
-        const float* cur = (i & 1) ? buf1 : buf0;
-        float* nxt = (i & 1) ? buf0 : buf1;
-        float c = 0.f;
-        if (i > 0 && (i % kRenormEvery) == 0) {  // apply the shift measured last frame
-          c = warp_max(lane < NW ? wmax[lane] : kNegInf);
-          if (!(c > kNegInf && c < -kNegInf)) c = 0.f;
-          a_run += (double)c;
-        }
-        float vmax = kNegInf;
-#pragma unroll
-        for (int j = 0; j < R; ++j) {
-          const float e = pf[j][u];
-          const int ip = i + PF;
-          if (ip < Tb && act[j]) {
-            const int tp = dir ? Tb - 1 - ip : ip;
-            pf[j][u] = emb[(size_t)tp * Lp + k_of[j]];
-          }
-          if (act[j]) {
-            const int sp = tid + j * NT;
-            float v;
-            if (i == 0) {
-              v = sp < 2 ? e : kNegInf;
-            } else {
-              const float a0 = cur[sp + 2], a1 = cur[sp + 1];
-              const float a2 = skip[j] ? cur[sp] : kNegInf;
-              v = lse3_log2(a0, a1, a2) + e - c;
-            }
-            nxt[sp + 2] = v;
-            lat[(size_t)t * Sp + s_of[j]] = v;
-            vmax = fmaxf(vmax, v);
-          }
-        }
-        if ((i % kRenormEvery) == kRenormEvery - 1) {  // measure for the next frame
-          vmax = warp_max(vmax);
-          if (lane == 0) wmax[wid] = vmax;
-        }
-        if (tid == 0) off[t] = a_run;
-        __syncthreads();
+      const int t = dir ? Tb - 1 - i : i;
+      const float* erow = ech + (size_t)(dir ? n - 1 - u : u) * Lp;
+      const float* cur = (i & 1) ? buf1 : buf0;
+      float* nxt = (i & 1) ? buf0 : buf1;
+      float cshift = 0.f;
+      if (i > 0 && (i % kRenormEvery) == 0) {  // apply the shift measured last frame
+        cshift = warp_max(lane < NW ? wmax[lane] : kNegInf);
+        if (!(cshift > kNegInf && cshift < -kNegInf)) cshift = 0.f;
+        a_run += (double)cshift;
       }
+      float vmax = kNegInf;
+#pragma unroll
+      for (int j = 0; j < R; ++j) {
+        if (act[j]) {
+          const int sp = tid + j * NT;
+          const float e = erow[k_of[j]];
+          float v;
+          if (i == 0) {
+            v = sp < 2 ? e : kNegInf;
+          } else {
+            const float a0 = cur[sp + kHalo], a1 = cur[sp + kHalo - 1];
+            const float a2 = skip[j] ? cur[sp + kHalo - 2] : kNegInf;
+            v = lse3_log2(a0, a1, a2) + (e - cshift);
+          }
+          nxt[sp + kHalo] = v;
+          lat[(size_t)t * Sp + s_of[j]] = v;
+          vmax = fmaxf(vmax, v);
+        }
+      }
+      if ((i % kRenormEvery) == kRenormEvery - 1) {  // measure for the next frame
+        vmax = warp_max(vmax);
+        if (lane == 0) wmax[wid] = vmax;
+      }
+      if (tid == 0) off[t] = a_run;
+      __syncthreads();
     }
+    // every thread is past its last read of this ring slot: refill it
+    if (tid == 0 && c + kEmRing < nchunks) issue_chunk(c + kEmRing);
   }
   if (dir != 0) return;
   // ---- alpha epilogue: log-likelihood ------------------------------------
@@ -140,8 +157,8 @@ __global__ void __launch_bounds__(1024) lattice_kernel(
     double msum = 0.0;
     for (int w2 = 0; w2 < NW; ++w2) msum += dred[w2];
     const float* fin = ((Tb - 1) & 1) ? buf0 : buf1;  // buffer written by the last frame
-    const double l1 = (double)fin[(S - 1) + 2];
-    const double l2 = S > 1 ? (double)fin[(S - 2) + 2] : (double)kNegInf;
+    const double l1 = (double)fin[(S - 1) + kHalo];
+    const double l2 = S > 1 ? (double)fin[(S - 2) + kHalo] : (double)kNegInf;
     const double m = fmax(l1, l2);
     double lam;
     if (m == (double)kNegInf) lam = m;
@@ -157,16 +174,33 @@ __global__ void __launch_bounds__(1024) lattice_kernel(
   }
 }
 
+// qt[b,t] = mt + offA + offB - aend - lam : the per-frame scalar of the occupancy
+// exponent (ctc_ws.cuh), combined in fp64 once so the gradient pass reads one float
+__global__ void __launch_bounds__(256) finalize_kernel(const UttInfo* __restrict__ utt,
+                                                       const float* __restrict__ mt,
+                                                       const double* __restrict__ offA,
+                                                       const double* __restrict__ offB,
+                                                       float* __restrict__ qt, int Tfr) {
+  const int b = blockIdx.y;
+  const int t = blockIdx.x * 256 + threadIdx.x;
+  if (t >= utt[b].T) return;
+  const size_t g = (size_t)b * Tfr + t;
+  qt[g] = (float)((double)mt[g] + offA[g] + offB[g] - utt[b].aend - utt[b].lam);
+}
+
 template <int R>
 static int launch_lattice_r(const LossLayout& w, unsigned char* ws, int Tfr, int zero_infinity,
                             int need_grad, float* nll, cudaStream_t st) {
-  constexpr int PF = R <= 2 ? 8 : (R <= 4 ? 4 : 2);
   const int Smax = 2 * w.Lmax + 1;
   int nt = (Smax + R - 1) / R;
   nt = (nt + 31) / 32 * 32;
   if (nt < 32) nt = 32;
-  const size_t smem = sizeof(float) * (2 * (size_t)(w.Sp + 4) + 32);
-  auto k = lattice_kernel<R, PF>;
+  int chunk = 8192 / (w.Lp * 4);
+  if (chunk < 1) chunk = 1;
+  if (chunk > 32) chunk = 32;
+  const size_t smem =
+      sizeof(float) * (2 * (size_t)(w.Sp + kHalo) + (size_t)kEmRing * chunk * w.Lp) + 128;
+  auto k = lattice_kernel<R>;
   if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   dim3 grid(w.B, need_grad ? 2 : 1);
   k<<<grid, nt, smem, st>>>(reinterpret_cast<UttInfo*>(ws + w.utt),
@@ -176,8 +210,16 @@ static int launch_lattice_r(const LossLayout& w, unsigned char* ws, int Tfr, int
                             reinterpret_cast<float*>(ws + w.alpha),
                             reinterpret_cast<float*>(ws + w.beta),
                             reinterpret_cast<double*>(ws + w.offA),
-                            reinterpret_cast<double*>(ws + w.offB), Tfr, w.Sp, zero_infinity, nll);
+                            reinterpret_cast<double*>(ws + w.offB), Tfr, w.Sp, zero_infinity, nll,
+                            chunk);
   count_launch();
+  if (need_grad && Tfr > 0) {
+    finalize_kernel<<<dim3((Tfr + 255) / 256, w.B), 256, 0, st>>>(
+        reinterpret_cast<const UttInfo*>(ws + w.utt), reinterpret_cast<const float*>(ws + w.mt),
+        reinterpret_cast<const double*>(ws + w.offA), reinterpret_cast<const double*>(ws + w.offB),
+        reinterpret_cast<float*>(ws + w.qt), Tfr);
+    count_launch();
+  }
   return check_launch("ctc lattice");
 }
 

@@ -35,7 +35,7 @@ struct UttInfo {
 
 struct LossLayout {
   int B, T, V, Lmax, Lp, Sp;
-  size_t lse2, mt, em, alpha, beta, offA, offB, utt, lab, dup, total;
+  size_t lse2, mt, qt, em, alpha, beta, offA, offB, utt, lab, dup, total;
 };
 
 inline LossLayout make_loss_layout(int B, int T, int V, int Lmax) {
@@ -51,6 +51,7 @@ inline LossLayout make_loss_layout(int B, int T, int V, int Lmax) {
   w.dup = take(4 * (size_t)B * w.Lp);
   w.lse2 = take(4 * BT);
   w.mt = take(4 * BT);
+  w.qt = take(4 * BT);
   w.offA = take(8 * BT);
   w.offB = take(8 * BT);
   w.em = take(4 * BT * w.Lp);
