@@ -1,10 +1,12 @@
-// CTC backward, row pass "B": the gradient w.r.t. the logits is produced in ONE
+// CTC gradient, row pass "B": the gradient w.r.t. the logits is produced in ONE
 // streaming pass - each (b,t) row is read once (TMA bulk copy into a shared
-// memory ring), softmax and the lattice occupancies are combined on chip and the
-// (B,T,V) gradient is written exactly once:
+// memory ring); its log-sum-exp, the soft-max and the lattice occupancies are
+// combined on chip and the (B,T,V) gradient is written exactly once:
 //     grad[b,t,v] = g_b * ( softmax(x)[v] - sum_{s: l_s = v} gamma_t(s) )
 // (= autograd of log_softmax + ctc_loss, espnet2/asr/ctc.py:54-55; the
-// analytically-zero term softmax * sum_v g_lp is dropped.)
+// analytically-zero term softmax * sum_v g_lp is dropped.)  The row's lse2 is
+// also written out: in the eager mode (b200ctc_loss_fwd_grad) this is the only
+// full read of the logits and the loss value is finished from it (nll_kernel).
 #include "rows_common.cuh"
 
 namespace b200ctc {
@@ -13,13 +15,16 @@ template <typename T, int NT, int PER, bool TMA>
 __global__ void __launch_bounds__(NT) grad_rows_kernel(
     const T* __restrict__ logits, T* __restrict__ grad, int B, int Tfr, int V, int blank,
     const UttInfo* __restrict__ utt, const int* __restrict__ lab, const int* __restrict__ dup,
-    int Lp, int Sp, const float* __restrict__ lse2, const float* __restrict__ qt,
+    int Lp, int Sp, int NWp, int wshift, float* __restrict__ lse2, const float* __restrict__ cmax,
     const float* __restrict__ alpha, const float* __restrict__ beta,
+    const int* __restrict__ offA, const int* __restrict__ offB,
     const float* __restrict__ gscale, int gstride, float gmul, int nstage, int stage_stride) {
   constexpr int N = Elems<T>::N;
+  constexpr int NWARP = NT / 32;
   extern __shared__ __align__(128) unsigned char dsm[];
   __shared__ __align__(8) uint64_t bars[kMaxRowStages];
   __shared__ float wp[32];
+  __shared__ float2 wms[2][32];  // per-warp (max, sum) of the row, double buffered
   unsigned char* stages = dsm;
   float* pbuf = reinterpret_cast<float*>(dsm + (size_t)nstage * stage_stride);  // [Lp]
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -54,17 +59,13 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
   uint32_t n = 0;
   RowCursor rc;
   rc.init(blockIdx.x, gridDim.x, Tfr);
-  // per-row scalars are fetched one row ahead (their latency hides behind the current row)
-  float l2_nx = rc.g < nrows ? lse2[rc.g] : 0.f;
-  float q_nx = rc.g < nrows ? qt[rc.g] : 0.f;
+  // the per-row constant is fetched one row ahead (its latency hides behind the current row)
+  float c_nx = rc.g < nrows ? cmax[rc.g] : 0.f;
   for (; rc.g < nrows; rc.next()) {
     const int b = rc.b, t = rc.t;
     const int64_t g = rc.g;
-    const float l2 = l2_nx, q = q_nx;
-    if (g + rc.stride < nrows) {
-      l2_nx = lse2[g + rc.stride];
-      q_nx = qt[g + rc.stride];
-    }
+    const float c2 = c_nx;
+    if (g + rc.stride < nrows) c_nx = cmax[g + rc.stride];
     const UttInfo u = utt[b];
     T* gr = grad + g * V;
     const bool al16 = (reinterpret_cast<uintptr_t>(gr) & 15) == 0;
@@ -82,20 +83,28 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
     }
     const int L = u.L, S = 2 * L + 1;
     float gb = gmul * (gscale ? gscale[(size_t)b * gstride] : 1.f);
-    float o_t = q;  // = mt + offA + offB - aend - lam  (finalize_kernel)
+    float qbase = -(float)u.lam;
     if (u.infinite) {  // inf loss kept (!zero_infinity): the reference's gradient is NaN
       gb = __int_as_float(0x7fc00000);
-      o_t = gb;
+      qbase = gb;
     }
     const float* al = alpha + (size_t)g * Sp;
     const float* be = beta + (size_t)g * Sp;
+    const int* oa = offA + (size_t)g * NWp;
+    const int* ob = offB + (size_t)g * NWp;
     const int* lb = lab + (size_t)b * Lp;
+    // log2 gamma_t(s) = alpha + beta - em + (FA_wA + FB_wB - aend) - lam   (ctc_ws.cuh)
+    auto lattice_term = [&](int s) {
+      const int sb = S - 1 - s;  // beta is stored in recursion order
+      const int fo = oa[s >> wshift] + ob[sb >> wshift] - u.aend;
+      return al[s] + be[sb] + ((float)fo + qbase);
+    };
     constexpr int SM = 3;  // lattice positions per thread whose loads are issued before the wait
     float ab[SM];
 #pragma unroll
     for (int j = 0; j < SM; ++j) {
       const int s = tid + j * NT;
-      ab[j] = s < S ? al[s] + be[s] : kNegInf;
+      ab[j] = s < S ? lattice_term(s) : kNegInf;
     }
     const unsigned char* stg;
     if (TMA) {
@@ -110,45 +119,88 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
       __syncthreads();
     }
     const T* xs = reinterpret_cast<const T*>(stg);
-    // ---- phase 1a: occupancies gamma_t(s) = 2^(alpha + beta - lp2(l_s) + o_t)
+    // ---- phase 0: whole row -> registers; thread-local max and sum of 2^(x2 - max)
+    float x[PER][N];
+    float m = kNegInf;
+#pragma unroll
+    for (int j = 0; j < PER; ++j) {
+      const int i = tid + j * NT;
+      if (i < nchunk) {
+        unpack16<T>(reinterpret_cast<const uint4*>(stg)[i], x[j]);
+#pragma unroll
+        for (int e = 0; e < N; ++e) m = fmaxf(m, x[j][e]);
+      }
+    }
+    float xt = kNegInf;
+    if (tid < ntail) {
+      xt = to_f32<T>(xs[nchunk * N + tid]);
+      m = fmaxf(m, xt);
+    }
+    m = warp_max(m);  // warp-level maximum keeps the later combine short
+    const float mw2 = ((m == kNegInf) ? 0.f : m) * kLog2e;
+    float sum = 0.f;
+#pragma unroll
+    for (int j = 0; j < PER; ++j) {
+      const int i = tid + j * NT;
+      if (i < nchunk) {
+#pragma unroll
+        for (int e = 0; e < N; ++e) {
+          x[j][e] = ex2(fmaf(x[j][e], kLog2e, -mw2));  // kept: reused for the output
+          sum += x[j][e];
+        }
+      }
+    }
+    if (tid < ntail) {
+      xt = ex2(fmaf(xt, kLog2e, -mw2));
+      sum += xt;
+    }
+    sum = warp_sum(sum);
+    if (lane == 0) wms[n & 1][wid] = make_float2(mw2, sum);
+    // ---- phase 1a: occupancies gamma_t(s) (independent of the row's normaliser)
     float blank_part = 0.f;
     for (int s0 = 0; s0 < S; s0 += NT * SM) {
 #pragma unroll
       for (int j = 0; j < SM; ++j) {
         const int s = s0 + tid + j * NT;
         if (s < S) {
-          const float abv = s0 == 0 ? ab[j] : al[s] + be[s];
+          const float abv = s0 == 0 ? ab[j] : lattice_term(s);
           const bool odd = s & 1;
           const int k = odd ? (s + 1) >> 1 : 0;
           const int v = odd ? lb[k] : blank;
-          const float lp2 = fmaf(to_f32<T>(xs[v]), kLog2e, -l2);
-          const float p = ex2(abv - lp2 + o_t);
+          const float em = fmaf(to_f32<T>(xs[v]), kLog2e, -c2);
+          const float p = ex2(abv - em);
           if (odd) pbuf[k] = p; else blank_part += p;
         }
       }
     }
     blank_part = warp_sum(blank_part);
     if (lane == 0) wp[wid] = blank_part;
+    __syncthreads();  // wms, pbuf, wp visible
+    // ---- row normaliser: combine the per-warp (max, sum) pairs
+    float M2 = kNegInf;
+#pragma unroll
+    for (int w2 = 0; w2 < NWARP; ++w2) M2 = fmaxf(M2, wms[n & 1][w2].x);
+    float tot = 0.f;
+#pragma unroll
+    for (int w2 = 0; w2 < NWARP; ++w2) tot += wms[n & 1][w2].y * ex2(wms[n & 1][w2].x - M2);
+    const float l2 = M2 + log2f(tot);
+    if (tid == 0) lse2[g] = l2;
+    const float scale = gb * ex2(mw2 - l2);  // g_b * 2^(warp max - lse2)
     // ---- phase 1b: dense part, g_b * softmax(x), straight from registers
 #pragma unroll
     for (int j = 0; j < PER; ++j) {
       const int i = tid + j * NT;
       if (i < nchunk) {
-        float x[N];
-        unpack16<T>(reinterpret_cast<const uint4*>(stg)[i], x);
 #pragma unroll
-        for (int e = 0; e < N; ++e) x[e] = gb * ex2(fmaf(x[e], kLog2e, -l2));
-        if (al16) store16<T>(gr + i * N, x);
+        for (int e = 0; e < N; ++e) x[j][e] *= scale;
+        if (al16) store16<T>(gr + i * N, x[j]);
         else
 #pragma unroll
-          for (int e = 0; e < N; ++e) gr[i * N + e] = from_f32<T>(x[e]);
+          for (int e = 0; e < N; ++e) gr[i * N + e] = from_f32<T>(x[j][e]);
       }
     }
-    if (tid < ntail) {
-      const int i = nchunk * N + tid;
-      gr[i] = from_f32<T>(gb * ex2(fmaf(to_f32<T>(xs[i]), kLog2e, -l2)));
-    }
-    __syncthreads();
+    if (tid < ntail) gr[nchunk * N + tid] = from_f32<T>(xt * scale);
+    __syncthreads();  // dense stores are ordered before the column fix-ups below
     // ---- phase 2: the <= L+1 columns that carry occupancy are overwritten by
     // their single owner thread (deterministic for repeated labels)
     const int* db = dup + (size_t)b * Lp;
@@ -164,7 +216,7 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
     }
     if (tid == NT - 1) {
       float acc = 0.f;
-      for (int w2 = 0; w2 < NT / 32; ++w2) acc += wp[w2];
+      for (int w2 = 0; w2 < NWARP; ++w2) acc += wp[w2];
       for (int nx = u.blank_head; nx != 0; nx = db[nx] & kDupMask) acc += pbuf[nx];
       const float sm = ex2(fmaf(to_f32<T>(xs[blank]), kLog2e, -l2));
       gr[blank] = from_f32<T>(gb * (sm - acc));
@@ -177,25 +229,28 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
 
 template <typename T, int NT>
 static int launch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, int blank,
-                         const LossLayout& w, const unsigned char* ws, const float* gscale,
+                         const LossLayout& w, unsigned char* ws, const float* gscale,
                          int gstride, float gmul, cudaStream_t st) {
   constexpr int PER = 40 / Elems<T>::N;
   const size_t extra = align_up(sizeof(float) * (size_t)w.Lp, 128);
   const RowLaunchCfg c = row_launch_cfg(logits, (size_t)V * sizeof(T), extra, NT, "B200CTC_B");
   B2_REQUIRE((size_t)c.nstage * c.stride + extra <= 226 * 1024,
-             "ctc_loss bwd: V=%d too large for the shared-memory row path", V);
+             "ctc_loss grad: V=%d too large for the shared-memory row path", V);
   const size_t smem = (size_t)c.nstage * c.stride + extra;
   const int64_t rows = (int64_t)B * Tfr;
   int64_t grid = (int64_t)sm_count() * c.ctas_per_sm;
   if (grid > rows) grid = rows;
+  int wshift = 0;
+  while ((1 << wshift) < 32 * w.R) ++wshift;
   auto go = [&](auto k) {
     cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     k<<<(unsigned)grid, NT, smem, st>>>(
         static_cast<const T*>(logits), static_cast<T*>(grad), B, Tfr, V, blank,
         reinterpret_cast<const UttInfo*>(ws + w.utt), reinterpret_cast<const int*>(ws + w.lab),
-        reinterpret_cast<const int*>(ws + w.dup), w.Lp, w.Sp,
-        reinterpret_cast<const float*>(ws + w.lse2), reinterpret_cast<const float*>(ws + w.qt),
+        reinterpret_cast<const int*>(ws + w.dup), w.Lp, w.Sp, w.NW, wshift,
+        reinterpret_cast<float*>(ws + w.lse2), reinterpret_cast<const float*>(ws + w.cmax),
         reinterpret_cast<const float*>(ws + w.alpha), reinterpret_cast<const float*>(ws + w.beta),
+        reinterpret_cast<const int*>(ws + w.offA), reinterpret_cast<const int*>(ws + w.offB),
         gscale, gstride, gmul, c.nstage, c.stride);
   };
   if (c.tma) go(grad_rows_kernel<T, NT, PER, true>);
@@ -206,15 +261,62 @@ static int launch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, 
 
 template <typename T>
 static int dispatch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, int blank,
-                           const LossLayout& w, const unsigned char* ws, const float* gscale,
+                           const LossLayout& w, unsigned char* ws, const float* gscale,
                            int gstride, float gmul, cudaStream_t st) {
   const int need = (V + 39) / 40;
   if (need <= 128) return launch_pass_b<T, 128>(logits, grad, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, st);
   if (need <= 256) return launch_pass_b<T, 256>(logits, grad, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, st);
   if (need <= 512) return launch_pass_b<T, 512>(logits, grad, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, st);
   if (need <= 1024) return launch_pass_b<T, 1024>(logits, grad, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, st);
-  set_error("ctc_loss bwd: V=%d exceeds the supported row size", V);
+  set_error("ctc_loss grad: V=%d exceeds the supported row size", V);
   return B200CTC_ERR_ARG;
+}
+
+int launch_grad_rows(const void* logits, int dtype, void* grad, int B, int T, int V, int blank,
+                     const LossLayout& w, unsigned char* ws, const float* gscale, int gstride,
+                     float gmul, cudaStream_t st) {
+  switch (dtype) {
+    case B200CTC_F32:
+      return dispatch_pass_b<float>(logits, grad, B, T, V, blank, w, ws, gscale, gstride, gmul, st);
+    case B200CTC_F16:
+      return dispatch_pass_b<__half>(logits, grad, B, T, V, blank, w, ws, gscale, gstride, gmul, st);
+    default:
+      return dispatch_pass_b<__nv_bfloat16>(logits, grad, B, T, V, blank, w, ws, gscale, gstride,
+                                            gmul, st);
+  }
+}
+
+// ---- lazy rescale of an eager gradient -------------------------------------
+// The eager forward baked `hint` into the gradient; when the real upstream
+// gradient equals the hint (loss.sum()/B with grad_output 1) every CTA reads
+// one scalar and exits - no pass over the (B,T,V) tensor.
+template <typename T>
+__global__ void __launch_bounds__(256) rescale_kernel(T* __restrict__ grad, int64_t per_utt,
+                                                      const float* __restrict__ gscale,
+                                                      int gstride, float hint) {
+  constexpr int N = Elems<T>::N;
+  const int b = blockIdx.y;
+  const float gv = gscale[(size_t)b * gstride];
+  if (gv == hint) return;
+  const float ratio = gv / hint;
+  T* base = grad + (size_t)b * per_utt;
+  const int64_t nvec = per_utt / N;
+  const bool al16 = (reinterpret_cast<uintptr_t>(base) & 15) == 0;
+  if (al16) {
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * 256) {
+      float f[N];
+      unpack16<T>(reinterpret_cast<const uint4*>(base)[i], f);
+#pragma unroll
+      for (int e = 0; e < N; ++e) f[e] *= ratio;
+      store16<T>(base + i * N, f);
+    }
+    for (int64_t i = nvec * N + (int64_t)blockIdx.x * 256 + threadIdx.x; i < per_utt;
+         i += (int64_t)gridDim.x * 256)
+      base[i] = from_f32<T>(to_f32<T>(base[i]) * ratio);
+  } else {
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < per_utt; i += (int64_t)gridDim.x * 256)
+      base[i] = from_f32<T>(to_f32<T>(base[i]) * ratio);
+  }
 }
 
 }  // namespace b200ctc
@@ -224,7 +326,7 @@ using namespace b200ctc;
 extern "C" int b200ctc_loss_bwd(const void* logits, int dtype, const int64_t* in_lens, int B, int T,
                                 int V, int max_tgt_len, int blank, int zero_infinity,
                                 const float* gscale, int gscale_stride, float gscale_mul,
-                                void* grad, const void* ws_, size_t ws_bytes,
+                                void* grad, void* ws_, size_t ws_bytes,
                                 b200ctc_stream_t stream) {
   (void)in_lens; (void)zero_infinity;  // lengths and the zeroed flags live in the workspace
   B2_REQUIRE(B >= 0 && T >= 0 && V > 0 && max_tgt_len >= 0, "loss_bwd: bad shape");
@@ -237,21 +339,46 @@ extern "C" int b200ctc_loss_bwd(const void* logits, int dtype, const int64_t* in
     set_error("loss_bwd: workspace %zu < required %zu bytes", ws_bytes, w.total);
     return B200CTC_ERR_WORKSPACE;
   }
-  const unsigned char* ws = static_cast<const unsigned char*>(ws_);
+  unsigned char* ws = static_cast<unsigned char*>(ws_);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  int rc;
   prof_mark(3, 0, st);
-  switch (dtype) {
-    case B200CTC_F32:
-      rc = dispatch_pass_b<float>(logits, grad, B, T, V, blank, w, ws, gscale, gscale_stride, gscale_mul, st);
-      break;
-    case B200CTC_F16:
-      rc = dispatch_pass_b<__half>(logits, grad, B, T, V, blank, w, ws, gscale, gscale_stride, gscale_mul, st);
-      break;
-    default:
-      rc = dispatch_pass_b<__nv_bfloat16>(logits, grad, B, T, V, blank, w, ws, gscale, gscale_stride, gscale_mul, st);
-      break;
-  }
+  const int rc = launch_grad_rows(logits, dtype, grad, B, T, V, blank, w, ws, gscale,
+                                  gscale_stride, gscale_mul, st);
   prof_mark(3, 1, st);
   return rc;
+}
+
+extern "C" int b200ctc_grad_rescale(void* grad, int dtype, const float* gscale, int gscale_stride,
+                                    float grad_hint, int B, int T, int V,
+                                    b200ctc_stream_t stream) {
+  B2_REQUIRE(B >= 0 && T >= 0 && V > 0, "grad_rescale: bad shape");
+  if (B == 0 || T == 0) return B200CTC_OK;
+  B2_REQUIRE(grad && gscale, "grad_rescale: null pointer");
+  B2_REQUIRE(dtype >= 0 && dtype <= 2, "grad_rescale: unknown dtype %d", dtype);
+  B2_REQUIRE(gscale_stride == 0 || gscale_stride == 1, "grad_rescale: gscale_stride must be 0 or 1");
+  B2_REQUIRE(grad_hint != 0.f && grad_hint == grad_hint, "grad_rescale: grad_hint must be non-zero");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int64_t per_utt = (int64_t)T * V;
+  int gx = (2 * sm_count() + B - 1) / B;
+  if (gx < 1) gx = 1;
+  dim3 grid(gx, B);
+  const float inv = grad_hint;
+  prof_mark(6, 0, st);
+  switch (dtype) {
+    case B200CTC_F32:
+      rescale_kernel<float><<<grid, 256, 0, st>>>(static_cast<float*>(grad), per_utt, gscale,
+                                                  gscale_stride, inv);
+      break;
+    case B200CTC_F16:
+      rescale_kernel<__half><<<grid, 256, 0, st>>>(static_cast<__half*>(grad), per_utt, gscale,
+                                                   gscale_stride, inv);
+      break;
+    default:
+      rescale_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(static_cast<__nv_bfloat16*>(grad),
+                                                          per_utt, gscale, gscale_stride, inv);
+      break;
+  }
+  prof_mark(6, 1, st);
+  count_launch();
+  return check_launch("ctc grad_rescale");
 }

@@ -10,16 +10,18 @@ namespace b200ctc {
 // ------------------------------------------------------------------ prep
 // int64 labels -> per-utterance int32 rows (k = 0 is the blank), duplicate
 // chains (so that repeated labels are accumulated deterministically by one
-// owner thread in the backward), clamped lengths.
-__global__ void __launch_bounds__(128) prep_kernel(const int64_t* __restrict__ targets,
-                                                   const int64_t* __restrict__ offs,
-                                                   const int64_t* __restrict__ in_lens,
-                                                   const int64_t* __restrict__ tgt_lens, int T,
-                                                   int V, int Lmax, int Lp, int blank,
-                                                   UttInfo* __restrict__ utt,
-                                                   int* __restrict__ lab, int* __restrict__ dup) {
+// owner thread in the backward), clamped lengths.  Labels are staged in shared
+// memory: the O(L^2) duplicate search then runs on broadcast LDS.
+__global__ void __launch_bounds__(1024) prep_kernel(const int64_t* __restrict__ targets,
+                                                    const int64_t* __restrict__ offs,
+                                                    const int64_t* __restrict__ in_lens,
+                                                    const int64_t* __restrict__ tgt_lens, int T,
+                                                    int V, int Lmax, int Lp, int blank,
+                                                    UttInfo* __restrict__ utt,
+                                                    int* __restrict__ lab, int* __restrict__ dup) {
+  extern __shared__ int slab[];  // [Lp]
   __shared__ int s_bad, s_head;
-  const int b = blockIdx.x;
+  const int b = blockIdx.x, NT = blockDim.x;
   long long L64 = tgt_lens[b], T64 = in_lens[b];
   const int L = (int)(L64 < 0 ? 0 : (L64 > Lmax ? Lmax : L64));
   const int Tb = (int)(T64 < 0 ? 0 : (T64 > T ? T : T64));
@@ -28,25 +30,26 @@ __global__ void __launch_bounds__(128) prep_kernel(const int64_t* __restrict__ t
   int* db = dup + (size_t)b * Lp;
   if (threadIdx.x == 0) { s_bad = 0; s_head = 0x7fffffff; }
   __syncthreads();
-  for (int k = threadIdx.x; k < Lp; k += 128) {
+  for (int k = threadIdx.x; k < Lp; k += NT) {
     int v = blank;
     if (k >= 1 && k <= L) {
       long long t = targets[base + k - 1];
       if (t < 0 || t >= V) { s_bad = 1; t = t < 0 ? 0 : V - 1; }
       v = (int)t;
     }
+    slab[k] = v;
     lb[k] = v;
   }
   __syncthreads();
-  for (int k = threadIdx.x; k < Lp; k += 128) {
+  for (int k = threadIdx.x; k < Lp; k += NT) {
     int code = 0;
     if (k >= 1 && k <= L) {
-      const int v = lb[k];
+      const int v = slab[k];
       bool first = (v != blank);
-      for (int j = 1; j < k && first; ++j) first = lb[j] != v;
+      for (int j = 1; j < k && first; ++j) first = slab[j] != v;
       int next = 0;
       for (int j = k + 1; j <= L; ++j)
-        if (lb[j] == v) { next = j; break; }
+        if (slab[j] == v) { next = j; break; }
       code = next | (first ? kDupFirst : 0);
       if (v == blank) atomicMin(&s_head, k);
     }
@@ -55,12 +58,85 @@ __global__ void __launch_bounds__(128) prep_kernel(const int64_t* __restrict__ t
   __syncthreads();
   if (threadIdx.x == 0) {
     UttInfo u;
-    u.lam = 0; u.aend = 0; u.msum = 0;
+    u.lam = 0; u.aend = 0;
     u.T = Tb; u.L = L; u.zeroed = 0; u.infinite = 0;
     u.blank_head = s_head == 0x7fffffff ? 0 : s_head;
-    u.bad_label = s_bad; u.pad[0] = u.pad[1] = 0;
+    u.bad_label = s_bad; u.pad = 0;
     utt[b] = u;
   }
+}
+
+// ------------------------------------------------- emission gather (sparse)
+// The lattice needs only the logits at the utterance's label columns (and the
+// blank): (L+1) of the V entries of every row, i.e. ~1/4 of the row's 32-byte
+// sectors at C2 instead of a full streaming read.  One warp per (b,t) row;
+// em[t][k] = logit[t][label_k]*log2(e) - c[t] with c[t] = max_k (ctc_ws.cuh).
+constexpr int kGatherWarps = 8;
+constexpr int kGatherRegs = 8;  // values kept in registers per lane (L+1 <= 256)
+
+template <typename T>
+__global__ void __launch_bounds__(kGatherWarps * 32) gather_kernel(
+    const T* __restrict__ logits, int Tfr, int V, const UttInfo* __restrict__ utt,
+    const int* __restrict__ lab, int Lp, float* __restrict__ em, float* __restrict__ cmax,
+    int frames_per_cta) {
+  extern __shared__ int slab[];  // [L+1] label columns of this utterance
+  const int b = blockIdx.y;
+  const int2 TL = *reinterpret_cast<const int2*>(&utt[b].T);
+  const int Tb = TL.x, L = TL.y;
+  const int t0 = blockIdx.x * frames_per_cta;
+  if (t0 >= Tb) return;
+  const int* lb = lab + (size_t)b * Lp;
+  for (int k = threadIdx.x; k <= L; k += blockDim.x) slab[k] = lb[k];
+  __syncthreads();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  int t1 = t0 + frames_per_cta;
+  if (t1 > Tb) t1 = Tb;
+  const bool in_regs = L + 1 <= 32 * kGatherRegs;
+  for (int t = t0 + wid; t < t1; t += kGatherWarps) {
+    const size_t g = (size_t)b * Tfr + t;
+    const T* row = logits + g * V;
+    float* er = em + g * Lp;
+    float v[kGatherRegs];
+    float m = kNegInf;
+    if (in_regs) {
+#pragma unroll
+      for (int j = 0; j < kGatherRegs; ++j) {
+        const int k = lane + 32 * j;
+        v[j] = kNegInf;
+        if (k <= L) v[j] = to_f32<T>(__ldg(row + slab[k])) * kLog2e;
+        m = fmaxf(m, v[j]);
+      }
+    } else {
+      for (int k = lane; k <= L; k += 32) m = fmaxf(m, to_f32<T>(__ldg(row + slab[k])) * kLog2e);
+    }
+    m = warp_max(m);
+    if (!(m > kNegInf && m < -kNegInf)) m = 0.f;  // all -inf / NaN rows: no centring
+    if (in_regs) {
+#pragma unroll
+      for (int j = 0; j < kGatherRegs; ++j) {
+        const int k = lane + 32 * j;
+        if (k <= L) er[k == 0 ? 0 : kEmLabel0 + k - 1] = v[j] - m;
+      }
+    } else {
+      for (int k = lane; k <= L; k += 32)
+        er[k == 0 ? 0 : kEmLabel0 + k - 1] = to_f32<T>(__ldg(row + slab[k])) * kLog2e - m;
+    }
+    if (lane == 0) cmax[g] = m;
+  }
+}
+
+template <typename T>
+static int launch_gather(const void* logits, int B, int Tfr, int V, const LossLayout& w,
+                         unsigned char* ws, cudaStream_t st) {
+  const int fpc = 2 * kGatherWarps;
+  dim3 grid((Tfr + fpc - 1) / fpc, B);
+  const size_t smem = sizeof(int) * (size_t)(w.Lmax + 1);
+  gather_kernel<T><<<grid, kGatherWarps * 32, smem, st>>>(
+      static_cast<const T*>(logits), Tfr, V, reinterpret_cast<const UttInfo*>(ws + w.utt),
+      reinterpret_cast<const int*>(ws + w.lab), w.Lp, reinterpret_cast<float*>(ws + w.em),
+      reinterpret_cast<float*>(ws + w.cmax), fpc);
+  count_launch();
+  return check_launch("ctc gather");
 }
 
 // --------------------------------------------------------- pass A (rows)
@@ -72,7 +148,7 @@ __global__ void __launch_bounds__(128) prep_kernel(const int64_t* __restrict__ t
 template <typename T, int NT, int PER, bool TMA>
 __global__ void __launch_bounds__(NT) lse_gather_kernel(
     const T* __restrict__ logits, int B, int Tfr, int V, const UttInfo* __restrict__ utt,
-    const int* __restrict__ lab, int Lp, float* __restrict__ lse2, float* __restrict__ mt,
+    const int* __restrict__ lab, int Lp, float* __restrict__ lse2, float* __restrict__ cmax,
     float* __restrict__ em, int nstage, int stage_stride) {
   constexpr int N = Elems<T>::N;
   extern __shared__ __align__(128) unsigned char dsm[];
@@ -178,12 +254,11 @@ __global__ void __launch_bounds__(NT) lse_gather_kernel(
       s = warp_sum(lane < NT / 32 ? red[1][lane] : 0.f);
     }
     if (tid == 0) {
-      const float l2s = log2f(s);
-      lse2[g] = m2 + l2s;
-      mt[g] = -l2s;
+      lse2[g] = m2 + log2f(s);
+      cmax[g] = m2;  // the per-frame constant of this mode is the row maximum
     }
     float* er = em + (size_t)g * Lp;
-    for (int k = tid; k <= L; k += NT) er[k] = fmaf(gb[k], kLog2e, -m2);
+    for (int k = tid; k <= L; k += NT) er[k == 0 ? 0 : kEmLabel0 + k - 1] = fmaf(gb[k], kLog2e, -m2);
     ++n;
   }
 }
@@ -205,12 +280,12 @@ static int launch_pass_a(const void* logits, int B, int Tfr, int V, const LossLa
   auto* utt = reinterpret_cast<const UttInfo*>(ws + w.utt);
   auto* lab = reinterpret_cast<const int*>(ws + w.lab);
   auto* lse2 = reinterpret_cast<float*>(ws + w.lse2);
-  auto* mt = reinterpret_cast<float*>(ws + w.mt);
+  auto* cmax = reinterpret_cast<float*>(ws + w.cmax);
   auto* em = reinterpret_cast<float*>(ws + w.em);
   auto go = [&](auto k) {
     cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     k<<<(unsigned)grid, NT, smem, st>>>(static_cast<const T*>(logits), B, Tfr, V, utt, lab, w.Lp,
-                                        lse2, mt, em, c.nstage, c.stride);
+                                        lse2, cmax, em, c.nstage, c.stride);
   };
   if (c.tma) go(lse_gather_kernel<T, NT, PER, true>);
   else go(lse_gather_kernel<T, NT, PER, false>);
@@ -239,36 +314,67 @@ extern "C" size_t b200ctc_loss_workspace_bytes(int B, int T, int V, int max_tgt_
   return make_loss_layout(B, T, V, max_tgt_len).total;
 }
 
+namespace b200ctc {
+
+static int check_loss_args(const char* who, const void* logits, int dtype, const int64_t* targets,
+                           const int64_t* tgt_offsets, const int64_t* in_lens,
+                           const int64_t* tgt_lens, int B, int T, int V, int max_tgt_len, int blank,
+                           const float* nll, const void* ws_, size_t ws_bytes, LossLayout* out) {
+  B2_REQUIRE(B >= 0 && T >= 0 && V > 0 && max_tgt_len >= 0, "%s: bad shape", who);
+  if (B == 0) return B200CTC_OK;
+  B2_REQUIRE(logits && tgt_offsets && in_lens && tgt_lens && nll && ws_, "%s: null pointer", who);
+  B2_REQUIRE(targets || max_tgt_len == 0, "%s: null targets", who);
+  B2_REQUIRE(blank >= 0 && blank < V, "%s: blank=%d outside [0,%d)", who, blank, V);
+  B2_REQUIRE(dtype >= 0 && dtype <= 2, "%s: unknown dtype %d", who, dtype);
+  B2_REQUIRE(2 * (int64_t)max_tgt_len + 1 <= kMaxLattice,
+             "%s: max_tgt_len=%d exceeds the supported lattice width %d", who, max_tgt_len,
+             kMaxLattice);
+  *out = make_loss_layout(B, T, V, max_tgt_len);
+  if (ws_bytes < out->total) {
+    set_error("%s: workspace %zu < required %zu bytes", who, ws_bytes, out->total);
+    return B200CTC_ERR_WORKSPACE;
+  }
+  B2_REQUIRE((reinterpret_cast<uintptr_t>(ws_) & 255) == 0, "%s: workspace must be 256-B aligned",
+             who);
+  return B200CTC_OK;
+}
+
+static int launch_prep(const LossLayout& w, unsigned char* ws, const int64_t* targets,
+                       const int64_t* tgt_offsets, const int64_t* in_lens, const int64_t* tgt_lens,
+                       int blank, cudaStream_t st) {
+  int nt = (w.Lmax + 1 + 31) / 32 * 32;
+  if (nt < 64) nt = 64;
+  if (nt > 1024) nt = 1024;
+  prof_mark(0, 0, st);
+  prep_kernel<<<w.B, nt, sizeof(int) * (size_t)w.Lp, st>>>(
+      targets, tgt_offsets, in_lens, tgt_lens, w.T, w.V, w.Lmax, w.Lp, blank,
+      reinterpret_cast<UttInfo*>(ws + w.utt), reinterpret_cast<int*>(ws + w.lab),
+      reinterpret_cast<int*>(ws + w.dup));
+  count_launch();
+  prof_mark(0, 1, st);
+  return check_launch("ctc prep");
+}
+
+// defined in ctc_bwd.cu
+int launch_grad_rows(const void* logits, int dtype, void* grad, int B, int T, int V, int blank,
+                     const LossLayout& w, unsigned char* ws, const float* gscale, int gstride,
+                     float gmul, cudaStream_t st);
+
+}  // namespace b200ctc
+
+// forward (deferred-gradient mode): row pass A (lse + emissions) -> lattice -> nll
 extern "C" int b200ctc_loss_fwd(const void* logits, int dtype, const int64_t* targets,
                                 const int64_t* tgt_offsets, const int64_t* in_lens,
                                 const int64_t* tgt_lens, int B, int T, int V, int max_tgt_len,
                                 int blank, int zero_infinity, int need_grad, float* nll, void* ws_,
                                 size_t ws_bytes, b200ctc_stream_t stream) {
-  B2_REQUIRE(B >= 0 && T >= 0 && V > 0 && max_tgt_len >= 0, "loss_fwd: bad shape");
-  if (B == 0) return B200CTC_OK;
-  B2_REQUIRE(logits && tgt_offsets && in_lens && tgt_lens && nll && ws_, "loss_fwd: null pointer");
-  B2_REQUIRE(targets || max_tgt_len == 0, "loss_fwd: null targets");
-  B2_REQUIRE(blank >= 0 && blank < V, "loss_fwd: blank=%d outside [0,%d)", blank, V);
-  B2_REQUIRE(dtype >= 0 && dtype <= 2, "loss_fwd: unknown dtype %d", dtype);
-  B2_REQUIRE(2 * (int64_t)max_tgt_len + 1 <= kMaxLattice,
-             "loss_fwd: max_tgt_len=%d exceeds the supported lattice width %d", max_tgt_len,
-             kMaxLattice);
-  const LossLayout w = make_loss_layout(B, T, V, max_tgt_len);
-  if (ws_bytes < w.total) {
-    set_error("loss_fwd: workspace %zu < required %zu bytes", ws_bytes, w.total);
-    return B200CTC_ERR_WORKSPACE;
-  }
-  B2_REQUIRE((reinterpret_cast<uintptr_t>(ws_) & 255) == 0, "loss_fwd: workspace must be 256-B aligned");
+  LossLayout w;
+  int rc = check_loss_args("loss_fwd", logits, dtype, targets, tgt_offsets, in_lens, tgt_lens, B, T,
+                           V, max_tgt_len, blank, nll, ws_, ws_bytes, &w);
+  if (rc || B == 0) return rc;
   unsigned char* ws = static_cast<unsigned char*>(ws_);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  auto* utt = reinterpret_cast<UttInfo*>(ws + w.utt);
-  prof_mark(0, 0, st);
-  prep_kernel<<<B, 128, 0, st>>>(targets, tgt_offsets, in_lens, tgt_lens, T, V, max_tgt_len, w.Lp,
-                                 blank, utt, reinterpret_cast<int*>(ws + w.lab),
-                                 reinterpret_cast<int*>(ws + w.dup));
-  count_launch();
-  prof_mark(0, 1, st);
-  int rc = check_launch("ctc prep");
+  rc = launch_prep(w, ws, targets, tgt_offsets, in_lens, tgt_lens, blank, st);
   if (rc) return rc;
   if (T > 0) {
     prof_mark(1, 0, st);
@@ -281,7 +387,49 @@ extern "C" int b200ctc_loss_fwd(const void* logits, int dtype, const int64_t* ta
     if (rc) return rc;
   }
   prof_mark(2, 0, st);
-  rc = launch_lattice(w, ws, T, zero_infinity, need_grad, nll, st);
+  rc = launch_lattice(w, ws, T, zero_infinity, need_grad, st);
   prof_mark(2, 1, st);
-  return rc;
+  if (rc) return rc;
+  return launch_nll(w, ws, T, zero_infinity, nll, st);
+}
+
+// forward + gradient in one call (eager mode): the logits are read ONCE in
+// full (row pass B); the lattice runs on a sparse gather of the label columns.
+extern "C" int b200ctc_loss_fwd_grad(const void* logits, int dtype, const int64_t* targets,
+                                     const int64_t* tgt_offsets, const int64_t* in_lens,
+                                     const int64_t* tgt_lens, int B, int T, int V,
+                                     int max_tgt_len, int blank, int zero_infinity,
+                                     float grad_hint, float* nll, void* grad, void* ws_,
+                                     size_t ws_bytes, b200ctc_stream_t stream) {
+  LossLayout w;
+  int rc = check_loss_args("loss_fwd_grad", logits, dtype, targets, tgt_offsets, in_lens, tgt_lens,
+                           B, T, V, max_tgt_len, blank, nll, ws_, ws_bytes, &w);
+  if (rc || B == 0) return rc;
+  B2_REQUIRE(grad || T == 0, "loss_fwd_grad: null grad");
+  B2_REQUIRE(grad_hint != 0.f && grad_hint == grad_hint, "loss_fwd_grad: grad_hint must be non-zero");
+  unsigned char* ws = static_cast<unsigned char*>(ws_);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  rc = launch_prep(w, ws, targets, tgt_offsets, in_lens, tgt_lens, blank, st);
+  if (rc) return rc;
+  if (T > 0) {
+    prof_mark(1, 0, st);
+    switch (dtype) {
+      case B200CTC_F32: rc = launch_gather<float>(logits, B, T, V, w, ws, st); break;
+      case B200CTC_F16: rc = launch_gather<__half>(logits, B, T, V, w, ws, st); break;
+      default: rc = launch_gather<__nv_bfloat16>(logits, B, T, V, w, ws, st); break;
+    }
+    prof_mark(1, 1, st);
+    if (rc) return rc;
+  }
+  prof_mark(2, 0, st);
+  rc = launch_lattice(w, ws, T, zero_infinity, 1, st);
+  prof_mark(2, 1, st);
+  if (rc) return rc;
+  if (T > 0) {
+    prof_mark(3, 0, st);
+    rc = launch_grad_rows(logits, dtype, grad, B, T, V, blank, w, ws, nullptr, 0, grad_hint, st);
+    prof_mark(3, 1, st);
+    if (rc) return rc;
+  }
+  return launch_nll(w, ws, T, zero_infinity, nll, st);
 }

@@ -1,48 +1,78 @@
-// Workspace layout shared by the CTC forward (lse/gather + lattice recursion)
-// and backward (fused gradient) kernels.
+// Workspace layout shared by the CTC loss kernels (emission gather / row pass A,
+// lattice recursion, gradient row pass B, nll finalize).
 //
 // All lattice quantities are in LOG2 units and NORMALISED so that no large
 // magnitudes are ever added in fp32 (the reference's fp32 log-space lattice
 // carries |alpha| ~ 4e3 at T=500,V=5000, i.e. ~3e-3 relative error in the
-// occupancies; see DESIGN.md "numerics"):
-//
-//   lp2[t][v]   = logit*log2(e) - lse2[t]                  (log2-probability)
-//   mt[t]       = max_v lp2[t][v] = -log2(sum_v 2^(y2-max)) (per-frame offset, <= 0)
-//   em[t][k]    = lp2[t][label_k] - mt[t]   (k = 0: blank, k = 1..L: labels)  <= 0
-//   alpha[t][s] = true log2-alpha - (sum_{tau<=t} mt[tau] + offA[t])
-//   beta [t][s] = true log2-beta  - (sum_{tau>=t} mt[tau] + offB[t])
-//
-// offA/offB are the cumulative renormalisation shifts (fp64), so that
-//   log2 gamma_t(s) = alpha + beta - em + (offA[t] + offB[t] - aend - lam)
-// involves only O(1..100) magnitudes.
+// occupancies; see DESIGN.md "numerics").  The recursion never needs the
+// soft-max normaliser: any per-frame constant cancels in the occupancies
+//   gamma_t(s) = alpha_t(s) beta_t(s) / (P * y_t(l_s)),
+// so the lattice runs on RAW logits gathered at the label columns only,
+//   y2[t][k]    = logit[t][label_k] * log2(e)           (k = 0: blank, 1..L: labels)
+//   c[t]        = a per-frame constant (max_k y2[t][k] from the gather kernel,
+//                 or the row maximum from row pass A)
+//   em[t][k]    = y2[t][k] - c[t]
+//   alpha[t][sp] = true log2-alpha~ - (sum_{tau<=t} c[tau] + FA_w[t])
+//   beta [t][sp] = true log2-beta~  - (sum_{tau>=t} c[tau] + FB_w[t])
+// where alpha~/beta~ are the recursions on the unnormalised scores 2^y2 and
+// FA_w/FB_w are INTEGER re-centring offsets kept per (frame, warp of the lattice
+// CTA): every warp re-centres its own slice on its own maximum, so no CTA-wide
+// reduction sits on the serial chain, and integer offsets combine exactly:
+//   log2 gamma_t(s) = alpha + beta - em + (FA_wA[t] + FB_wB[t] - aend) - lam
+//   log2 P          = lam + aend + sum_t (c[t] - lse2[t])
+// with lse2[t] the row's log2-sum-exp (row pass A, or row pass B in the eager
+// gradient mode).  beta is stored in recursion order: beta[t][sp], sp = S-1-s.
 #pragma once
+#include <stddef.h>
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace b200ctc {
 
 struct UttInfo {
-  double lam;    // log2-sum of the two final normalised alphas
-  double aend;   // offA at the last valid frame
-  double msum;   // sum_t mt[t] over valid frames
-  int T;         // clamped input length
-  int L;         // clamped target length
-  int zeroed;    // 1: loss was +inf and zero_infinity -> gradient is all zeros
-  int infinite;  // 1: loss is +inf (kept when !zero_infinity -> NaN gradient)
+  double lam;      // log2-sum of the two final normalised alphas
+  int T;           // clamped input length          (T, L are read as one int2)
+  int L;           // clamped target length
+  int aend;        // FA of the warp that owns position S-1 at the last valid frame
+  int zeroed;      // 1: loss was +inf and zero_infinity -> gradient is all zeros
+  int infinite;    // 1: loss is +inf (kept when !zero_infinity -> NaN gradient)
   int blank_head;  // first label position (1-based k) whose label == blank, 0 = none
   int bad_label;   // 1: some label was outside [0,V) and got clamped
-  int pad[2];
+  int pad;
 };
 
+static_assert(offsetof(UttInfo, T) % 8 == 0 && offsetof(UttInfo, L) == offsetof(UttInfo, T) + 4,
+              "UttInfo::{T,L} must form an aligned int2");
+
+constexpr int kEmLabel0 = 4;  // em row: [blank, -, -, -, label_1 .. label_L]
+
 struct LossLayout {
-  int B, T, V, Lmax, Lp, Sp;
-  size_t lse2, mt, qt, em, alpha, beta, offA, offB, utt, lab, dup, total;
+  int B, T, V, Lmax, Lp, Sp, R, NW;
+  size_t lse2, cmax, em, alpha, beta, offA, offB, utt, lab, dup, total;
 };
+
+// positions per thread of the lattice CTA (even); one warp covers 32*R positions
+// (at most 31 compute warps: the 32nd warp of the CTA is the TMA producer)
+inline int lattice_R(int Smax) {
+  if (const char* e = getenv("B200CTC_LAT_R")) {  // tuning sweeps only
+    const int r = atoi(e);
+    if ((r == 2 || r == 4 || r == 8 || r == 16) && Smax <= 31 * 32 * r) return r;
+  }
+  if (Smax <= 16 * 32 * 2) return 2;
+  if (Smax <= 31 * 32 * 4) return 4;
+  if (Smax <= 31 * 32 * 8) return 8;
+  return 16;
+}
 
 inline LossLayout make_loss_layout(int B, int T, int V, int Lmax) {
   LossLayout w;
   w.B = B; w.T = T; w.V = V; w.Lmax = Lmax;
-  w.Lp = (int)align_up((size_t)Lmax + 1, 4);
-  w.Sp = (int)align_up((size_t)2 * Lmax + 1, 4);
+  const int S = 2 * Lmax + 1;
+  w.Lp = kEmLabel0 + (int)align_up((size_t)(Lmax > 0 ? Lmax : 1), 4);
+  w.Sp = (int)align_up((size_t)S, 8);
+  w.R = lattice_R(S);
+  w.NW = (S + 32 * w.R - 1) / (32 * w.R);
   size_t o = 0;
   const size_t BT = (size_t)B * T;
   auto take = [&](size_t bytes) { size_t r = o; o = align_up(o + bytes, 256); return r; };
@@ -50,10 +80,9 @@ inline LossLayout make_loss_layout(int B, int T, int V, int Lmax) {
   w.lab = take(4 * (size_t)B * w.Lp);
   w.dup = take(4 * (size_t)B * w.Lp);
   w.lse2 = take(4 * BT);
-  w.mt = take(4 * BT);
-  w.qt = take(4 * BT);
-  w.offA = take(8 * BT);
-  w.offB = take(8 * BT);
+  w.cmax = take(4 * BT);
+  w.offA = take(4 * BT * w.NW);
+  w.offB = take(4 * BT * w.NW);
   w.em = take(4 * BT * w.Lp);
   w.alpha = take(4 * BT * w.Sp);
   w.beta = take(4 * BT * w.Sp);

@@ -1,7 +1,7 @@
 // Host-buffer entry point (bench.py `e2e`): logits arrive in HOST memory, the
 // loss (and optionally the gradient) go back to HOST memory.  Utterance chunks
-// are copied H2D on a copy stream while the previous chunk runs loss_fwd +
-// loss_bwd on the compute stream; gradient chunks return on a third stream.
+// are copied H2D on a copy stream while the previous chunk runs loss_fwd_grad
+// on the compute stream; gradient chunks return on a third stream.
 #include <mutex>
 #include <vector>
 
@@ -131,11 +131,9 @@ extern "C" int b200ctc_loss_fwd_bwd_host(const void* logits_host, int dtype,
                            utt_bytes * nb, cudaMemcpyHostToDevice, a.s_copy));
     CU_TRY(cudaEventRecord(a.ev[2 * c], a.s_copy));
     CU_TRY(cudaStreamWaitEvent(a.s_comp, a.ev[2 * c], 0));
-    rc = b200ctc_loss_fwd(dl, dtype, d_tgt, d_off + b0, d_il + b0, d_tl + b0, nb, T, V, (int)lmax,
-                          blank, zero_infinity, 1, d_nll + b0, a.ws, a.ws_cap, a.s_comp);
-    if (rc) break;
-    rc = b200ctc_loss_bwd(dl, dtype, d_il + b0, nb, T, V, (int)lmax, blank, zero_infinity, nullptr,
-                          0, gscale, dg, a.ws, a.ws_cap, a.s_comp);
+    rc = b200ctc_loss_fwd_grad(dl, dtype, d_tgt, d_off + b0, d_il + b0, d_tl + b0, nb, T, V,
+                               (int)lmax, blank, zero_infinity, gscale, d_nll + b0, dg, a.ws,
+                               a.ws_cap, a.s_comp);
     if (rc) break;
     if (grad_host) {
       CU_TRY(cudaEventRecord(a.ev[2 * c + 1], a.s_comp));

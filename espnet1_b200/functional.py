@@ -5,6 +5,7 @@ arithmetic step of the hot path runs in libb200ctc.so.
 """
 from __future__ import annotations
 
+import numpy as np
 import torch
 
 from . import _lib
@@ -74,13 +75,27 @@ def greedy_decode(logits: torch.Tensor, in_lens=None, blank: int = 0):
     return ids, lens
 
 
+def _upstream(g):
+    """(fp32 device vector, stride) describing the upstream gradient of nll (B,)."""
+    if g.stride(0) == 0 or g.numel() == 1:  # expanded scalar (loss.sum()/B)
+        return g.reshape(-1)[:1].to(torch.float32).contiguous(), 0
+    return g.to(torch.float32).contiguous(), 1
+
+
 class _CTCLossFn(torch.autograd.Function):
-    """nll (B,) fp32 = CTCLoss(reduction='none')(log_softmax(logits)); the
-    backward writes d/dlogits in one pass (no (T,B,V) log-prob tensor exists)."""
+    """nll (B,) fp32 = CTCLoss(reduction='none')(log_softmax(logits)).
+
+    eager mode (default when the logits need a gradient): forward computes the
+    loss AND d nll/d logits scaled by ``grad_hint`` in one call - the logits are
+    read in full once, the gradient is written once (no (T,B,V) log-prob tensor
+    ever exists); backward only rescales if the upstream gradient differs from
+    the hint (device-side check, no host sync).
+    deferred mode: forward keeps the lattices in a workspace, backward runs the
+    gradient row pass with the real upstream gradient."""
 
     @staticmethod
     def forward(ctx, logits, targets, tgt_offsets, in_lens, tgt_lens, max_tgt_len, blank,
-                zero_infinity):
+                zero_infinity, grad_hint, eager):
         require_cuda(logits, "CTC logits")
         x = logits.contiguous()
         B, T, V = x.shape
@@ -89,41 +104,66 @@ class _CTCLossFn(torch.autograd.Function):
         nbytes = lib().b200ctc_loss_workspace_bytes(B, T, V, max_tgt_len)
         ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
         nll = torch.empty(B, dtype=torch.float32, device=dev)
+        ctx.eager = bool(need_grad and eager and B > 0)
+        if ctx.eager:
+            grad = torch.empty_like(x)
+            check(lib().b200ctc_loss_fwd_grad(ptr(x), dtype_code(x), ptr(targets), ptr(tgt_offsets),
+                                              ptr(in_lens), ptr(tgt_lens), B, T, V, max_tgt_len,
+                                              blank, int(zero_infinity), grad_hint, ptr(nll),
+                                              ptr(grad), ptr(ws), nbytes, stream_ptr(dev)),
+                  "loss_fwd_grad")
+            ctx.grad_buf = grad
+            ctx.cfg = (B, T, V, grad_hint)
+            return nll
         check(lib().b200ctc_loss_fwd(ptr(x), dtype_code(x), ptr(targets), ptr(tgt_offsets),
                                      ptr(in_lens), ptr(tgt_lens), B, T, V, max_tgt_len, blank,
                                      int(zero_infinity), int(need_grad), ptr(nll), ptr(ws), nbytes,
                                      stream_ptr(dev)), "loss_fwd")
-        ctx.save_for_backward(x, in_lens, ws)
-        ctx.cfg = (B, T, V, max_tgt_len, blank, int(zero_infinity), nbytes)
+        if need_grad:
+            ctx.save_for_backward(x, in_lens, ws)
+            ctx.cfg = (B, T, V, max_tgt_len, blank, int(zero_infinity), nbytes)
         return nll
 
     @staticmethod
     def backward(ctx, g):
+        none9 = (None,) * 9
+        gs, stride = _upstream(g)
+        if ctx.eager:
+            grad = ctx.grad_buf
+            if grad is None:
+                raise RuntimeError(
+                    "the eager CTC gradient was already consumed by an earlier backward(); "
+                    "use ctc_loss(..., grad_mode='deferred') to backpropagate twice")
+            ctx.grad_buf = None
+            B, T, V, hint = ctx.cfg
+            check(lib().b200ctc_grad_rescale(ptr(grad), dtype_code(grad), ptr(gs), stride, hint,
+                                             B, T, V, stream_ptr(grad.device)), "grad_rescale")
+            return (grad,) + none9
         x, in_lens, ws = ctx.saved_tensors
         B, T, V, lmax, blank, zinf, nbytes = ctx.cfg
         grad = torch.empty_like(x)
-        if g.stride(0) == 0 or g.numel() == 1:  # expanded scalar (loss.sum()/B)
-            gs = g.reshape(-1)[:1].to(torch.float32).contiguous()
-            stride = 0
-        else:
-            gs = g.to(torch.float32).contiguous()
-            stride = 1
         check(lib().b200ctc_loss_bwd(ptr(x), dtype_code(x), ptr(in_lens), B, T, V, lmax, blank,
                                      zinf, ptr(gs), stride, 1.0, ptr(grad), ptr(ws), nbytes,
                                      stream_ptr(x.device)), "loss_bwd")
-        return grad, None, None, None, None, None, None, None
+        return (grad,) + none9
 
 
 def ctc_loss(logits, targets, in_lens, tgt_lens, blank: int = 0, zero_infinity: bool = True,
-             max_tgt_len: int | None = None, tgt_offsets=None) -> torch.Tensor:
+             max_tgt_len: int | None = None, tgt_offsets=None, grad_hint: float | None = None,
+             grad_mode: str = "eager") -> torch.Tensor:
     """Per-utterance CTC negative log-likelihood from LOGITS.
 
     logits (B,T,V) batch-major activations (fp32/fp16/bf16, CUDA); targets 1-D
     concatenated int64 labels; in_lens / tgt_lens (B,).  Equivalent to
     ``F.ctc_loss(logits.transpose(0,1).log_softmax(2), ..., reduction="none")``.
     ``max_tgt_len`` may be given to avoid a device->host sync.
+    ``grad_hint``: the upstream gradient the caller expects for every nll[b]
+    (default 1/B, i.e. ``nll.sum()/B`` as in espnet2/asr/ctc.py:56-60); any other
+    upstream gradient is still exact, it only costs one rescaling pass.
     """
     require_cuda(logits, "CTC logits")
+    if grad_mode not in ("eager", "deferred"):
+        raise ValueError(f"grad_mode must be 'eager' or 'deferred': {grad_mode}")
     dev = logits.device
     tl_dev = torch.as_tensor(tgt_lens).to(device=dev, dtype=torch.int64).contiguous()
     il_dev = torch.as_tensor(in_lens).to(device=dev, dtype=torch.int64).contiguous()
@@ -134,8 +174,11 @@ def ctc_loss(logits, targets, in_lens, tgt_lens, blank: int = 0, zero_infinity: 
     if tgt_offsets is None:
         tgt_offsets = torch.zeros(tl_dev.numel() + 1, dtype=torch.int64, device=dev)
         torch.cumsum(tl_dev, 0, out=tgt_offsets[1:])
+    if grad_hint is None:  # fp32 1/B exactly as torch's `x / B` backward produces it
+        grad_hint = float(np.float32(1.0) / np.float32(max(logits.shape[0], 1)))
     return _CTCLossFn.apply(logits, tg_dev, tgt_offsets, il_dev, tl_dev, int(max_tgt_len),
-                            int(blank), bool(zero_infinity))
+                            int(blank), bool(zero_infinity), float(grad_hint),
+                            grad_mode == "eager")
 
 
 def forced_align(lp: torch.Tensor, target: torch.Tensor, blank: int = 0) -> torch.Tensor:

@@ -48,8 +48,8 @@ const char* b200ctc_last_error(void);
 int64_t b200ctc_launch_count(void);
 void b200ctc_reset_launch_count(void);
 /* optional per-phase timing with CUDA events recorded on the caller's stream
- * around the library's own launches (phase ids: 0 prep, 1 lse_gather, 2 lattice,
- * 3 grad_rows, 4 prefix_step, 5 softmax family).  profile_read synchronises,
+ * around the library's own launches (phase ids: 0 prep, 1 emission gather / row
+ * pass A, 2 lattice, 3 grad_rows, 4 prefix_step, 5 softmax family, 6 rescale).  profile_read synchronises,
  * returns per-phase total milliseconds / launch counts and clears the log. */
 void b200ctc_profile_enable(int on);
 int b200ctc_profile_read(float* ms_total, int* counts, int n);
@@ -84,11 +84,22 @@ int b200ctc_greedy_decode(const void* x, const int64_t* in_lens, int B, int T,
  * logits: (B,T,V) batch-major pre-softmax activations (what ctc_lo emits,
  *   espnet2/asr/ctc.py:82), row stride V.  targets: 1-D concatenated labels
  *   (espnet2/asr/ctc.py:91) with tgt_offsets (B+1,) prefix sums.
- * fwd writes nll (B,) fp32 (0 where infeasible and zero_infinity) and keeps
- * the lattices in `ws`; bwd consumes `ws` and writes
- *   grad[b,t,v] = gscale_mul * gscale[b*gscale_stride] * d nll[b] / d logits[b,t,v]
- * (zeros for t >= in_lens[b]); gscale may be NULL (=1), gscale_stride is 0 for
- * a scalar upstream gradient, 1 for a per-utterance one.                      */
+ * Two ways to get the gradient:
+ *  - eager (training default): b200ctc_loss_fwd_grad computes nll AND
+ *      grad[b,t,v] = grad_hint * d nll[b] / d logits[b,t,v]   (zeros for t >= in_lens[b])
+ *    in one call.  The lattice runs on a sparse gather of the label columns, so
+ *    the (B,T,V) logits are read in full exactly once and the gradient is
+ *    written exactly once.  grad_hint is the upstream gradient the caller
+ *    expects (1/B for loss.sum()/B); b200ctc_grad_rescale later multiplies by
+ *    gscale[b*stride]/grad_hint and is a device-side no-op (every CTA reads one
+ *    scalar and exits) when the real upstream gradient equals the hint.
+ *  - deferred: b200ctc_loss_fwd(need_grad=1) keeps the lattices in `ws`
+ *    (one full read of the logits for the row log-sum-exp), b200ctc_loss_bwd
+ *    consumes `ws` and writes
+ *      grad[b,t,v] = gscale_mul * gscale[b*gscale_stride] * d nll[b] / d logits[b,t,v];
+ *    gscale may be NULL (=1), gscale_stride is 0 for a scalar upstream
+ *    gradient, 1 for a per-utterance one.
+ * fwd writes nll (B,) fp32 (0 where infeasible and zero_infinity).            */
 size_t b200ctc_loss_workspace_bytes(int B, int T, int V, int max_tgt_len);
 int b200ctc_loss_fwd(const void* logits, int dtype, const int64_t* targets,
                      const int64_t* tgt_offsets, const int64_t* in_lens,
@@ -98,8 +109,17 @@ int b200ctc_loss_fwd(const void* logits, int dtype, const int64_t* targets,
 int b200ctc_loss_bwd(const void* logits, int dtype, const int64_t* in_lens,
                      int B, int T, int V, int max_tgt_len, int blank,
                      int zero_infinity, const float* gscale, int gscale_stride,
-                     float gscale_mul, void* grad, const void* ws, size_t ws_bytes,
+                     float gscale_mul, void* grad, void* ws, size_t ws_bytes,
                      b200ctc_stream_t stream);
+int b200ctc_loss_fwd_grad(const void* logits, int dtype, const int64_t* targets,
+                          const int64_t* tgt_offsets, const int64_t* in_lens,
+                          const int64_t* tgt_lens, int B, int T, int V,
+                          int max_tgt_len, int blank, int zero_infinity,
+                          float grad_hint, float* nll, void* grad, void* ws,
+                          size_t ws_bytes, b200ctc_stream_t stream);
+int b200ctc_grad_rescale(void* grad, int dtype, const float* gscale,
+                         int gscale_stride, float grad_hint, int B, int T, int V,
+                         b200ctc_stream_t stream);
 /* forced alignment (espnet/nets/pytorch_backend/ctc.py:163-226): max-semiring
  * lattice with back-pointers for ONE utterance; lp (T,V) fp32 log-probs,
  * out_ids (T,) int64 = label emitted at each frame (tgt_len >= 1).            */

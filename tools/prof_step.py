@@ -17,6 +17,13 @@ dev = torch.device("cuda:0")
 logits, tg, il, tl = synth(cfg, 1234)
 x = logits.to(dev).requires_grad_(True)
 tg, il, tl = tg.to(dev), il.to(dev), tl.to(dev)
+import ctypes  # noqa: E402
+
+from espnet1_b200 import _lib  # noqa: E402
+
+L = _lib.lib()
+if os.environ.get("PHASES"):
+    L.b200ctc_profile_enable(1)
 ev = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
 for i in range(steps):
     ev[i].record()
@@ -26,3 +33,8 @@ for i in range(steps):
 ev[steps].record()
 torch.cuda.synchronize()
 print("ms per step:", [round(ev[i].elapsed_time(ev[i + 1]), 4) for i in range(steps)], "loss", float(nll.sum()) / cfg["B"])
+if os.environ.get("PHASES"):
+    pm, pc = (ctypes.c_float * 8)(), (ctypes.c_int * 8)()
+    L.b200ctc_profile_read(pm, pc, 8)
+    names = ["prep", "gather", "lattice", "grad_rows", "prefix", "softmax", "rescale", "-"]
+    print({n: round(pm[i] / pc[i], 4) for i, n in enumerate(names) if pc[i]})
