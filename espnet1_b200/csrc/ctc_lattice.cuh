@@ -7,8 +7,8 @@
 // The CTA is a SYSTOLIC ARRAY OF WARPS with no CTA-wide barrier on the serial
 // chain.  Thread i keeps R consecutive lattice positions in registers; inside a
 // warp the neighbour value it needs arrives by shuffle; between warps they
-// travel through a small shared-memory ring of 16-byte packets {-, a[-1], step
-// tag, frame offset} written by the last lane of warp w and read by warp
+// travel through a small shared-memory ring of 16-byte packets {a[-1], step tag,
+// frame offset, step tag} written by the last lane of warp w and read by warp
 // w+1 one step later.  The dependency is one-directional (position sp needs
 // sp-1, sp-2), so warp w+1 simply trails warp w by a step or two; a consumed
 // counter gives back-pressure on the ring.  Every warp re-centres its own slice
@@ -51,19 +51,256 @@ __device__ __forceinline__ void sts_volatile_i32(int* p, int v) {
   asm volatile("st.volatile.shared.s32 [%0], %1;" ::"r"(smem_u32(p)), "r"(v) : "memory");
 }
 
-// log2(2^a + 2^b), 2 MUFU; -inf safe
-__device__ __forceinline__ float lse2_log2(float a, float b) {
-  const float m = fmaxf(a, b), n = fminf(a, b);
-  const float ms = (m == kNegInf) ? 0.f : m;
-  return m + lg2(1.f + ex2(n - ms));
+// The lattice uses a FINITE log-zero so that the serial chain needs no -inf /
+// NaN guards: kLogZero absorbs every real increment (ulp(1e30) ~ 7e22), the
+// difference of two log-zeros is 0 (not NaN), and 2^(kLogZero - x) underflows to 0.
+constexpr float kLogZero = -1.0e30f;
+constexpr float kLogZeroTest = -1.0e29f;  // "is alive" threshold
+
+// log2(2^a + 2^b) + e : 2 MUFU, chain FADD -> EX2 -> FADD -> LG2 -> FADD
+__device__ __forceinline__ float lse2_fast(float a, float b, float e) {
+  const float me = fmaxf(a, b) + e;
+  return me + lg2(1.f + ex2(-fabsf(a - b)));
 }
-// log2(2^a + 2^b + 2^c), 3 MUFU (the largest term is exactly 1); -inf safe
-__device__ __forceinline__ float lse3_log2(float a, float b, float c) {
-  const float hi = fmaxf(a, b), lo = fminf(a, b);
-  const float m = fmaxf(hi, c), t = fminf(hi, c);
-  const float mid = fmaxf(lo, t), mn = fminf(lo, t);
-  const float ms = (m == kNegInf) ? 0.f : m;
-  return m + lg2(1.f + ex2(mid - ms) + ex2(mn - ms));
+// log2(2^a + 2^b + 2^c) + e : 4 MUFU but the shortest dependent chain
+__device__ __forceinline__ float lse3_fast(float a, float b, float c, float e) {
+  const float m = fmaxf(fmaxf(a, b), c);
+  const float s = ex2(a - m) + ex2(b - m) + ex2(c - m);
+  return (m + e) + lg2(s);
+}
+
+// raw 32-bit shared-memory addressing for the serial loop (no generic->shared
+// conversions or re-derived bases inside it)
+__device__ __forceinline__ float4 lds_v4_u32(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.volatile.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts_v4_u32(uint32_t addr, float4 v) {
+  asm volatile("st.volatile.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ int lds_i32_u32(uint32_t addr) {
+  int v;
+  asm volatile("ld.volatile.shared.s32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts_i32_u32(uint32_t addr, int v) {
+  asm volatile("st.volatile.shared.s32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ float lds_f32_u32(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+  return v;
+}
+// make a loop-invariant value opaque so that it is kept in a register instead
+// of being re-derived inside the serial loop
+__device__ __forceinline__ uint32_t pin(uint32_t v) {
+  asm volatile("mov.b32 %0, %0;" : "+r"(v));
+  return v;
+}
+
+struct LatticeArgs {
+  UttInfo* utt;
+  const int* lb;      // labels of this utterance (k = 0 blank)
+  float* lat;         // alpha or beta rows of this utterance, (Tfr, Sp)
+  int* off;           // offA or offB rows of this utterance, (Tfr, NWp)
+  uint32_t ring;      // shared: em ring base
+  uint32_t pkt;       // shared: packet ring base [NW][kPktRing] float4
+  uint32_t cons;      // shared: consumed[32]
+  uint64_t* full;
+  uint64_t* empty;
+  int Tb, L, Lp, Sp, NWp, chunk, nw_live, zero_infinity, b;
+};
+
+// One compute warp of the systolic lattice (see the file header).  This is the
+// serial chain of the whole loss: one warp per SM sub-partition with a single
+// step in flight, so every instruction costs issue latency.  Branch-free
+// arithmetic (finite kLogZero, step 0 is an ordinary step started from a virtual
+// alpha_{-1}(0) = log 1), compile-time direction, pointer-walking addressing,
+// and the upstream packet prefetched one step ahead.
+template <int R, bool STORE, int DIR>
+__device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int lane) {
+  const int Tb = A.Tb, L = A.L, S = 2 * L + 1, Lp = A.Lp;
+  const int sp0 = (w * 32 + lane) * R;  // first recursion position of this thread
+  // static description of this thread's positions: q even = blank, q odd = label
+  uint32_t jlab[R / 2];  // byte offset of the label emission inside an em row
+  bool skip[R / 2];      // may the path skip the blank in front of this label?
+  bool act[R];
+#pragma unroll
+  for (int q = 0; q < R; ++q) act[q] = sp0 + q < S;
+#pragma unroll
+  for (int h = 0; h < R / 2; ++h) {
+    const int sp = sp0 + 2 * h + 1;
+    const int s = DIR ? S - 1 - sp : sp;
+    const int k = (s + 1) >> 1;  // 1..L when active
+    bool sk = false;
+    if (sp < S) {
+      if (DIR == 0) sk = (k >= 2) && (A.lb[k] != A.lb[k - 1]);
+      else sk = (k + 1 <= L) && (A.lb[k] != A.lb[k + 1]);
+    }
+    skip[h] = sk;
+    jlab[h] = pin(4u * (uint32_t)(kEmLabel0 + ((sp < S) ? k - 1 : 0)));
+  }
+  const bool has_up = w > 0, has_down = w + 1 < A.nw_live;
+  const bool lane0 = lane == 0;
+  const bool pub = has_down && lane == 31;
+  const uint32_t pk_in = pin(A.pkt + (uint32_t)(has_up ? w - 1 : 0) * (kPktRing * 16u));
+  const uint32_t pk_out = pin(A.pkt + (uint32_t)w * (kPktRing * 16u));
+  const uint32_t cons_mine = pin(A.cons + 4u * (uint32_t)w);
+  const uint32_t cons_down = pin(A.cons + 4u * (uint32_t)(has_down ? w + 1 : w));
+  const uint32_t row_bytes = pin(4u * (uint32_t)Lp);
+  const uint32_t chunk_bytes = pin(4u * (uint32_t)(A.chunk * Lp));
+
+  // walking pointers (frames ascend for alpha, descend for beta)
+  const int t0 = DIR ? Tb - 1 : 0;
+  float* lat_p = nullptr;
+  int* off_p = nullptr;
+  if (STORE) {
+    lat_p = A.lat + (size_t)t0 * A.Sp + sp0;
+    off_p = A.off + (size_t)t0 * A.NWp + w;
+  }
+  const ptrdiff_t lat_step = DIR ? -(ptrdiff_t)A.Sp : (ptrdiff_t)A.Sp;
+  const ptrdiff_t off_step = DIR ? -(ptrdiff_t)A.NWp : (ptrdiff_t)A.NWp;
+  const bool store_ok = STORE && sp0 < A.Sp;
+  const bool store_off = STORE && lane0;
+
+  float a[R];
+#pragma unroll
+  for (int q = 0; q < R; ++q) a[q] = kLogZero;
+  if (sp0 == 0) a[0] = 0.f;  // virtual alpha_{-1}(0) = log 1
+  int F = 0;          // integer frame offset of a[] (ctc_ws.cuh)
+  int Dpend = 0;      // re-centring shift to apply at the next step
+  float shift = 0.f;  // = (float)Dpend
+  int cons_seen = 0;  // downstream warp's fetch count (cached)
+  // packet of step -1: the ring is initialised with tag -1 / kLogZero / F = 0
+  float4 pk = lds_v4_u32(pk_in + (kPktRing - 1) * 16u);
+  int i = 0;  // recursion step
+
+  // value of position sp0-1 after step i-1, expressed in MY frame (one neighbour
+  // value per thread: R is even, so sp0 is a blank and needs only sp0-1, and the
+  // label at sp0+1 takes its skip transition from sp0-1 as well)
+  auto fetch = [&]() {
+    float p1 = __shfl_up_sync(0xffffffffu, a[R - 1], 1);
+    if (has_up) {
+      // packet = {value, tag, frame offset, tag}: each 8-byte half validates itself,
+      // so the protocol does not depend on 16-byte shared stores being single-copy atomic
+      while (__float_as_int(pk.y) != i - 1 || __float_as_int(pk.w) != i - 1)
+        pk = lds_v4_u32(pk_in + ((uint32_t)(i - 1) & (kPktRing - 1)) * 16u);
+      const float up = pk.x + (float)(__float_as_int(pk.z) - F);
+      p1 = lane0 ? up : p1;
+      if (lane0) sts_i32_u32(cons_mine, i + 1);
+    } else {
+      p1 = lane0 ? kLogZero : p1;
+    }
+    return p1;
+  };
+
+  const int nchunks = (Tb + A.chunk - 1) / A.chunk;
+  for (int c = 0; c < nchunks; ++c) {
+    const int n = (Tb - c * A.chunk < A.chunk) ? Tb - c * A.chunk : A.chunk;
+    const int slot = c % kEmRing;
+    uint32_t erow = A.ring + (uint32_t)slot * chunk_bytes + (DIR ? (uint32_t)(n - 1) * row_bytes : 0u);
+    mbar_wait(&A.full[slot], (c / kEmRing) & 1);
+#pragma unroll 1
+    for (int u = 0; u < n; ++u) {
+      const float eb = lds_f32_u32(erow) - shift;
+      float el[R / 2];
+#pragma unroll
+      for (int h = 0; h < R / 2; ++h) el[h] = lds_f32_u32(erow + jlab[h]) - shift;
+      if (DIR) erow -= row_bytes; else erow += row_bytes;
+      const float p1 = fetch();
+      // prefetch the packet of THIS step (needed at the next one): the upstream
+      // warp runs a step or two ahead, so it is normally already there
+      if (has_up) pk = lds_v4_u32(pk_in + ((uint32_t)i & (kPktRing - 1)) * 16u);
+      float nw_[R];
+#pragma unroll
+      for (int q = 0; q < R; ++q) {
+        const float x0 = a[q];
+        const float x1 = q >= 1 ? a[q - 1] : p1;
+        float v;
+        if (q & 1) {
+          const float x2r = q >= 2 ? a[q - 2] : p1;
+          const float x2 = skip[q >> 1] ? x2r : kLogZero;
+          v = lse3_fast(x0, x1, x2, el[q >> 1]);
+        } else {
+          v = lse2_fast(x0, x1, eb);
+        }
+        nw_[q] = act[q] ? v : kLogZero;
+      }
+      F += Dpend;
+      Dpend = 0;
+      shift = 0.f;
+#pragma unroll
+      for (int q = 0; q < R; ++q) a[q] = nw_[q];
+      // hand the top position to the next warp; the slot's previous packet
+      // (step i-16) is read by the consumer's fetch of step i-15
+      if (has_down) {
+        while (cons_seen < i - (kPktRing - 2)) cons_seen = lds_i32_u32(cons_down);
+        if (pub)
+          sts_v4_u32(pk_out + ((uint32_t)i & (kPktRing - 1)) * 16u,
+                     make_float4(a[R - 1], __int_as_float(i), __int_as_float(F), __int_as_float(i)));
+      }
+      if (store_ok) {
+        if (R == 2) {
+          *reinterpret_cast<float2*>(lat_p) = make_float2(a[0], a[1]);
+        } else {
+#pragma unroll
+          for (int q = 0; q < R; q += 4)
+            *reinterpret_cast<float4*>(lat_p + q) = make_float4(a[q], a[q + 1], a[q + 2], a[q + 3]);
+        }
+      }
+      if (store_off) *off_p = F;
+      lat_p += lat_step;
+      off_p += off_step;
+      if ((i & (kRenormEvery - 1)) == kRenormEvery - 1) {
+        float m = a[0];
+#pragma unroll
+        for (int q = 1; q < R; ++q) m = fmaxf(m, a[q]);
+        m = warp_max(m);
+        // nothing alive yet: adopt the upstream warp's frame so that the first
+        // real values to arrive are already centred.  (Clamped: a pathological
+        // -1e10 "logzero" logit must not overflow the integer offsets.)
+        // The prefetched packet is NOT validated and a 128-bit LDS is served in
+        // quarter-warp phases, so lanes may hold different packets: take lane 0's
+        // (the frame offset must stay warp-uniform).
+        const int upF = __shfl_sync(0xffffffffu, __float_as_int(pk.z), 0);
+        Dpend = (m > kLogZeroTest) ? (int)rintf(fminf(fmaxf(m, -1048576.f), 1048576.f))
+                                   : (has_up ? upF - F : 0);
+        shift = (float)Dpend;
+      }
+      ++i;
+    }
+    __syncwarp();
+    if (lane0) mbar_arrive(&A.empty[slot]);
+  }
+
+  // ---- epilogue: log-likelihood from the last two positions (alpha only)
+  if (DIR != 0) return;
+  const float p1 = fetch();
+  const int q_own = (S - 1) % R;
+  if (sp0 + q_own == S - 1) {
+    float v1 = kLogZero, v2 = kLogZero;
+#pragma unroll
+    for (int q = 0; q < R; ++q) {
+      if (q == q_own) {
+        v1 = a[q];
+        v2 = q >= 1 ? a[q - 1] : p1;
+      }
+    }
+    if (S == 1) v2 = kLogZero;
+    const double l1 = (double)v1, l2 = (double)v2;
+    const double m = fmax(l1, l2);
+    const bool inf = !(m > (double)kLogZeroTest);
+    const double lam = inf ? (double)kNegInf : m + log2(exp2(l1 - m) + exp2(l2 - m));
+    A.utt[A.b].lam = lam;
+    A.utt[A.b].aend = F;
+    A.utt[A.b].infinite = inf;
+    A.utt[A.b].zeroed = inf && A.zero_infinity;
+  }
 }
 
 template <int R, bool STORE>
@@ -94,20 +331,20 @@ __global__ void __launch_bounds__(R == 2 ? 544 : (R <= 8 ? 1024 : 576)) lattice_
   float* ring = lsm;
   float4* pkt = reinterpret_cast<float4*>(lsm + (size_t)kEmRing * chunk_elems);  // [NW][kPktRing]
   const float* emb = em + (size_t)b * Tfr * Lp;
-  const int nchunks = (Tb + chunk - 1) / chunk;
 
   if (tid == 0) {
     for (int i = 0; i < kEmRing; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], nw_live); }
     fence_mbar_init();
   }
   for (int i = tid; i < NW * kPktRing; i += blockDim.x)
-    pkt[i] = make_float4(kNegInf, kNegInf, __int_as_float(-1), __int_as_float(0));
+    pkt[i] = make_float4(kLogZero, __int_as_float(-1), __int_as_float(0), __int_as_float(-1));
   if (tid < 32) consumed[tid] = 0;
   __syncthreads();
 
   // ------------------------------------------------------------ TMA producer warp
   if (wid == NW) {
     if (lane == 0) {
+      const int nchunks = (Tb + chunk - 1) / chunk;
       for (int c = 0; c < nchunks; ++c) {
         const int slot = c % kEmRing, round = c / kEmRing;
         if (round > 0) mbar_wait(&empty[slot], (round - 1) & 1);
@@ -123,176 +360,20 @@ __global__ void __launch_bounds__(R == 2 ? 544 : (R <= 8 ? 1024 : 576)) lattice_
   }
   if (wid >= nw_live) return;
 
-  // ------------------------------------------------------------ compute warps
-  const int w = wid;
-  const int sp0 = (w * 32 + lane) * R;  // first recursion position of this thread
-  const int* lb = lab + (size_t)b * Lp;
-  // static description of this thread's positions: q even = blank, q odd = label
-  int jlab[R / 2];     // index into the em row of the label emission
-  bool skip[R / 2];    // may the path skip the blank in front of this label?
-  bool act[R];
-#pragma unroll
-  for (int q = 0; q < R; ++q) act[q] = sp0 + q < S;
-#pragma unroll
-  for (int h = 0; h < R / 2; ++h) {
-    const int sp = sp0 + 2 * h + 1;
-    const int s = dir ? S - 1 - sp : sp;
-    const int k = (s + 1) >> 1;  // 1..L when active
-    bool sk = false;
-    if (sp < S) {
-      if (dir == 0) sk = (k >= 2) && (lb[k] != lb[k - 1]);
-      else sk = (k + 1 <= L) && (lb[k] != lb[k + 1]);
-    }
-    skip[h] = sk;
-    jlab[h] = kEmLabel0 + ((sp < S) ? k - 1 : 0);
-  }
-  float* lat = nullptr;
-  int* off = nullptr;
-  if (STORE) {
-    lat = (dir ? beta : alpha) + (size_t)b * Tfr * Sp + sp0;
-    off = (dir ? offB : offA) + (size_t)b * Tfr * NWp + w;
-  }
-  const bool store_ok = sp0 < Sp;
-  const float4* pk_in = pkt + (size_t)(w > 0 ? w - 1 : 0) * kPktRing;
-  float4* pk_out = pkt + (size_t)w * kPktRing;
-  const bool has_up = w > 0, has_down = w + 1 < nw_live;
-
-  float a[R];
-#pragma unroll
-  for (int q = 0; q < R; ++q) a[q] = kNegInf;
-  int F = 0;       // integer frame offset of a[] (ctc_ws.cuh)
-  int Dpend = 0;   // shift to apply at the next step
-  int upF = 0;     // frame offset carried by the last upstream packet
-  int cons_seen = 0;  // downstream warp's consumed count (cached)
-
-  // fetch the value of position sp0-1 at step `i-1`, expressed in MY frame.
-  // (R is even, so sp0 is a blank and needs only sp0-1; the label at sp0+1 takes
-  // its skip transition from sp0-1 as well: ONE neighbour value per thread.)
-  auto fetch = [&](int i) {
-    float p1 = __shfl_up_sync(0xffffffffu, a[R - 1], 1);
-    if (has_up) {
-      float4 pk;
-      do {
-        pk = lds_volatile_v4(&pk_in[(i - 1) % kPktRing]);
-      } while (__float_as_int(pk.z) != i - 1);
-      upF = __float_as_int(pk.w);
-      if (lane == 0) {
-        p1 = pk.y + (float)(upF - F);
-        sts_volatile_i32(&consumed[w], i);
-      }
-    } else if (lane == 0) {
-      p1 = kNegInf;
-    }
-    return p1;
-  };
-
-  for (int c = 0; c < nchunks; ++c) {
-    const int i0 = c * chunk;
-    const int n = (Tb - i0 < chunk) ? Tb - i0 : chunk;
-    const int slot = c % kEmRing;
-    const float* ech = ring + (size_t)slot * chunk_elems;
-    mbar_wait(&full[slot], (c / kEmRing) & 1);
-    for (int u = 0; u < n; ++u) {
-      const int i = i0 + u;
-      const int t = dir ? Tb - 1 - i : i;
-      const float* erow = ech + (size_t)(dir ? n - 1 - u : u) * Lp;
-      const float shift = (float)Dpend;
-      const float eb = erow[0] - shift;
-      float el[R / 2];
-#pragma unroll
-      for (int h = 0; h < R / 2; ++h) el[h] = erow[jlab[h]] - shift;
-      float nw_[R];
-      if (i == 0) {
-#pragma unroll
-        for (int q = 0; q < R; ++q) {
-          const float e = (q & 1) ? el[q >> 1] : eb;
-          nw_[q] = (sp0 + q < 2 && act[q]) ? e : kNegInf;
-        }
-      } else {
-        const float p1 = fetch(i);
-#pragma unroll
-        for (int q = 0; q < R; ++q) {
-          const float x0 = a[q];
-          const float x1 = q >= 1 ? a[q - 1] : p1;
-          float v;
-          if (q & 1) {
-            const float x2r = q >= 2 ? a[q - 2] : p1;
-            const float x2 = skip[q >> 1] ? x2r : kNegInf;
-            v = lse3_log2(x0, x1, x2) + el[q >> 1];
-          } else {
-            v = lse2_log2(x0, x1) + eb;
-          }
-          nw_[q] = act[q] ? v : kNegInf;
-        }
-      }
-      F += Dpend;
-      Dpend = 0;
-#pragma unroll
-      for (int q = 0; q < R; ++q) a[q] = nw_[q];
-      // hand the top two positions to the next warp
-      if (has_down) {
-        const int need = i - kPktRing + 1;  // the slot's previous packet must be consumed
-        if (need > cons_seen) {
-          do { cons_seen = lds_volatile_i32(&consumed[w + 1]); } while (cons_seen < need);
-        }
-        if (lane == 31)
-          sts_volatile_v4(&pk_out[i % kPktRing],
-                          make_float4(0.f, a[R - 1], __int_as_float(i), __int_as_float(F)));
-      }
-      if (STORE) {
-        if (store_ok) {
-          float* dst = lat + (size_t)t * Sp;
-          if (R == 2) {
-            *reinterpret_cast<float2*>(dst) = make_float2(a[0], a[1]);
-          } else {
-#pragma unroll
-            for (int q = 0; q < R; q += 4)
-              *reinterpret_cast<float4*>(dst + q) = make_float4(a[q], a[q + 1], a[q + 2], a[q + 3]);
-          }
-        }
-        if (lane == 0) off[(size_t)t * NWp] = F;
-      }
-      if ((i % kRenormEvery) == kRenormEvery - 1) {
-        float m = a[0];
-#pragma unroll
-        for (int q = 1; q < R; ++q) m = fmaxf(m, a[q]);
-        m = warp_max(m);
-        // all -inf: adopt the upstream warp's frame so that the first finite
-        // values to arrive are already centred
-        // (clamped: a pathological -1e10 "logzero" logit must not overflow the offsets)
-        Dpend = (m > kNegInf) ? (int)rintf(fminf(fmaxf(m, -1048576.f), 1048576.f))
-                              : (has_up ? upF - F : 0);
-      }
-    }
-    __syncwarp();
-    if (lane == 0) mbar_arrive(&empty[slot]);
-  }
-
-  // ---- epilogue: log-likelihood from the last two positions (alpha only)
-  if (dir != 0) return;
-  const float p1 = fetch(Tb);
-  const int q_own = (S - 1) % R;
-  if (sp0 + q_own == S - 1) {
-    float v1 = kNegInf, v2 = kNegInf;
-#pragma unroll
-    for (int q = 0; q < R; ++q) {
-      if (q == q_own) {
-        v1 = a[q];
-        v2 = q >= 1 ? a[q - 1] : p1;
-      }
-    }
-    if (S == 1) v2 = kNegInf;
-    const double l1 = (double)v1, l2 = (double)v2;
-    const double m = fmax(l1, l2);
-    double lam;
-    if (m == (double)kNegInf) lam = m;
-    else lam = m + log2(exp2(l1 - m) + exp2(l2 - m));
-    const bool inf = (lam == (double)kNegInf);
-    utt[b].lam = lam;
-    utt[b].aend = F;
-    utt[b].infinite = inf;
-    utt[b].zeroed = inf && zero_infinity;
-  }
+  LatticeArgs A;
+  A.utt = utt;
+  A.lb = lab + (size_t)b * Lp;
+  A.lat = (dir ? beta : alpha) + (size_t)b * Tfr * Sp;
+  A.off = (dir ? offB : offA) + (size_t)b * Tfr * NWp;
+  A.ring = smem_u32(ring);
+  A.pkt = smem_u32(pkt);
+  A.cons = smem_u32(consumed);
+  A.full = full;
+  A.empty = empty;
+  A.Tb = Tb; A.L = L; A.Lp = Lp; A.Sp = Sp; A.NWp = NWp; A.chunk = chunk;
+  A.nw_live = nw_live; A.zero_infinity = zero_infinity; A.b = b;
+  if (dir == 0) lattice_warp<R, STORE, 0>(A, wid, lane);
+  else lattice_warp<R, STORE, 1>(A, wid, lane);
 }
 
 // nll[b] = -ln2 * (lam + aend + sum_t (c[t] - lse2[t]))   (ctc_ws.cuh)
