@@ -2,6 +2,8 @@
 // vocabulary + gather of the lattice emissions, streamed through shared memory
 // by the TMA engine (1-D bulk copies, mbarrier ring), (3) alpha/beta lattice
 // recursion (ctc_lattice.cuh), one CTA per utterance and direction.
+#include <mutex>
+
 #include "ctc_lattice.cuh"
 #include "rows_common.cuh"
 
@@ -355,10 +357,38 @@ static int launch_prep(const LossLayout& w, unsigned char* ws, const int64_t* ta
   return check_launch("ctc prep");
 }
 
-// defined in ctc_bwd.cu
+// defined in ctc_bwd.cu / ctc_dense.cu
 int launch_grad_rows(const void* logits, int dtype, void* grad, int B, int T, int V, int blank,
                      const LossLayout& w, unsigned char* ws, const float* gscale, int gstride,
                      float gmul, cudaStream_t st);
+int launch_dense_rows(const void* logits, int dtype, void* grad, int B, int T, int V,
+                      const int64_t* in_lens, const LossLayout& w, unsigned char* ws, float gmul,
+                      cudaStream_t st);
+int launch_fixup(void* grad, int dtype, int B, int T, int V, int blank, const LossLayout& w,
+                 const unsigned char* ws, float gmul, cudaStream_t st);
+
+// internal low-priority stream (one per device) on which the dense row pass of
+// the eager mode overlaps the caller-stream gather + lattice chain
+static std::mutex g_side_mu;
+static cudaStream_t g_side[64] = {};
+
+static cudaStream_t side_stream() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  std::lock_guard<std::mutex> lk(g_side_mu);
+  if (!g_side[dev]) {
+    int lo = 0, hi = 0;
+    cudaDeviceGetStreamPriorityRange(&lo, &hi);  // lo = numerically largest = lowest priority
+    if (cudaStreamCreateWithPriority(&g_side[dev], cudaStreamNonBlocking, lo) != cudaSuccess)
+      g_side[dev] = nullptr;
+  }
+  return g_side[dev];
+}
+
+static bool eager_split_enabled() {
+  const char* e = getenv("B200CTC_EAGER_SPLIT");
+  return !(e && e[0] == '0');
+}
 
 }  // namespace b200ctc
 
@@ -409,9 +439,29 @@ extern "C" int b200ctc_loss_fwd_grad(const void* logits, int dtype, const int64_
   B2_REQUIRE(grad_hint != 0.f && grad_hint == grad_hint, "loss_fwd_grad: grad_hint must be non-zero");
   unsigned char* ws = static_cast<unsigned char*>(ws_);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  rc = launch_prep(w, ws, targets, tgt_offsets, in_lens, tgt_lens, blank, st);
-  if (rc) return rc;
-  if (T > 0) {
+  // fork: the dense row pass needs nothing from the chain below
+  const bool split = T > 0 && eager_split_enabled();
+  cudaStream_t sd = split ? side_stream() : nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  if (sd) {
+    if (cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming) != cudaSuccess) {
+      if (ev_fork) cudaEventDestroy(ev_fork);
+      ev_fork = ev_join = nullptr;
+      sd = nullptr;
+      cudaGetLastError();
+    }
+  }
+  if (sd) {
+    cudaEventRecord(ev_fork, st);
+    cudaStreamWaitEvent(sd, ev_fork, 0);
+    prof_mark(3, 0, sd);
+    rc = launch_dense_rows(logits, dtype, grad, B, T, V, in_lens, w, ws, grad_hint, sd);
+    prof_mark(3, 1, sd);
+    cudaEventRecord(ev_join, sd);
+  }
+  if (!rc) rc = launch_prep(w, ws, targets, tgt_offsets, in_lens, tgt_lens, blank, st);
+  if (!rc && T > 0) {
     prof_mark(1, 0, st);
     switch (dtype) {
       case B200CTC_F32: rc = launch_gather<float>(logits, B, T, V, w, ws, st); break;
@@ -419,16 +469,28 @@ extern "C" int b200ctc_loss_fwd_grad(const void* logits, int dtype, const int64_
       default: rc = launch_gather<__nv_bfloat16>(logits, B, T, V, w, ws, st); break;
     }
     prof_mark(1, 1, st);
-    if (rc) return rc;
   }
-  prof_mark(2, 0, st);
-  rc = launch_lattice(w, ws, T, zero_infinity, 1, st);
-  prof_mark(2, 1, st);
+  if (!rc) {
+    prof_mark(2, 0, st);
+    rc = launch_lattice(w, ws, T, zero_infinity, 1, st);
+    prof_mark(2, 1, st);
+  }
+  if (sd) {  // join (always, also on error: the caller's stream must cover the side work)
+    cudaStreamWaitEvent(st, ev_join, 0);
+    cudaEventDestroy(ev_fork);
+    cudaEventDestroy(ev_join);
+  }
   if (rc) return rc;
   if (T > 0) {
-    prof_mark(3, 0, st);
-    rc = launch_grad_rows(logits, dtype, grad, B, T, V, blank, w, ws, nullptr, 0, grad_hint, st);
-    prof_mark(3, 1, st);
+    if (sd) {
+      prof_mark(7, 0, st);
+      rc = launch_fixup(grad, dtype, B, T, V, blank, w, ws, grad_hint, st);
+      prof_mark(7, 1, st);
+    } else {
+      prof_mark(3, 0, st);
+      rc = launch_grad_rows(logits, dtype, grad, B, T, V, blank, w, ws, nullptr, 0, grad_hint, st);
+      prof_mark(3, 1, st);
+    }
     if (rc) return rc;
   }
   return launch_nll(w, ws, T, zero_infinity, nll, st);

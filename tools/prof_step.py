@@ -36,5 +36,5 @@ print("ms per step:", [round(ev[i].elapsed_time(ev[i + 1]), 4) for i in range(st
 if os.environ.get("PHASES"):
     pm, pc = (ctypes.c_float * 8)(), (ctypes.c_int * 8)()
     L.b200ctc_profile_read(pm, pc, 8)
-    names = ["prep", "gather", "lattice", "grad_rows", "prefix", "softmax", "rescale", "-"]
+    names = ["prep", "gather", "lattice", "grad_rows|dense", "prefix", "softmax", "rescale", "fixup"]
     print({n: round(pm[i] / pc[i], 4) for i, n in enumerate(names) if pc[i]})
