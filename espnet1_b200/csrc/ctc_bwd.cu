@@ -15,7 +15,7 @@ template <typename T, int NT, int PER, bool TMA>
 __global__ void __launch_bounds__(NT) grad_rows_kernel(
     const T* __restrict__ logits, T* __restrict__ grad, int B, int Tfr, int V, int blank,
     const UttInfo* __restrict__ utt, const int* __restrict__ lab, const int* __restrict__ dup,
-    int Lp, int Sp, int NWp, int wshift, float* __restrict__ lse2, const float* __restrict__ cmax,
+    int Lp, int Sp, int NWp, int NB, int wshift, float* __restrict__ lse2, const float* __restrict__ cmax,
     const float* __restrict__ alpha, const float* __restrict__ beta,
     const int* __restrict__ offA, const int* __restrict__ offB,
     const float* __restrict__ gscale, int gstride, float gmul, int nstage, int stage_stride) {
@@ -90,8 +90,9 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
     }
     const float* al = alpha + (size_t)g * Sp;
     const float* be = beta + (size_t)g * Sp;
-    const int* oa = offA + (size_t)g * NWp;
-    const int* ob = offB + (size_t)g * NWp;
+    // frame offsets: one per block of kRenormEvery recursion steps (t / T_b-1-t)
+    const int* oa = offA + ((size_t)b * NB + (t / kRenormEvery)) * NWp;
+    const int* ob = offB + ((size_t)b * NB + ((u.T - 1 - t) / kRenormEvery)) * NWp;
     const int* lb = lab + (size_t)b * Lp;
     // log2 gamma_t(s) = alpha + beta - em + (FA_wA + FB_wB - aend) - lam   (ctc_ws.cuh)
     auto lattice_term = [&](int s) {
@@ -247,7 +248,7 @@ static int launch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, 
     k<<<(unsigned)grid, NT, smem, st>>>(
         static_cast<const T*>(logits), static_cast<T*>(grad), B, Tfr, V, blank,
         reinterpret_cast<const UttInfo*>(ws + w.utt), reinterpret_cast<const int*>(ws + w.lab),
-        reinterpret_cast<const int*>(ws + w.dup), w.Lp, w.Sp, w.NW, wshift,
+        reinterpret_cast<const int*>(ws + w.dup), w.Lp, w.Sp, w.NW, w.NB, wshift,
         reinterpret_cast<float*>(ws + w.lse2), reinterpret_cast<const float*>(ws + w.cmax),
         reinterpret_cast<const float*>(ws + w.alpha), reinterpret_cast<const float*>(ws + w.beta),
         reinterpret_cast<const int*>(ws + w.offA), reinterpret_cast<const int*>(ws + w.offB),

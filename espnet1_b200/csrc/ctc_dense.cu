@@ -166,7 +166,7 @@ constexpr int kFixWarps = 4;
 template <typename T>
 __global__ void __launch_bounds__(kFixWarps * 32) fixup_kernel(
     T* __restrict__ grad, int B, int Tfr, int V, int blank, const UttInfo* __restrict__ utt,
-    const int* __restrict__ lab, const int* __restrict__ dup, int Lp, int Sp, int NWp, int wshift,
+    const int* __restrict__ lab, const int* __restrict__ dup, int Lp, int Sp, int NWp, int NB, int wshift,
     const float* __restrict__ lse2, const float* __restrict__ cmax, const float* __restrict__ em,
     const float* __restrict__ alpha, const float* __restrict__ beta,
     const int* __restrict__ offA, const int* __restrict__ offB, float gmul) {
@@ -188,8 +188,9 @@ __global__ void __launch_bounds__(kFixWarps * 32) fixup_kernel(
     const int L = u.L, S = 2 * L + 1;
     const float* al = alpha + (size_t)g * Sp;
     const float* be = beta + (size_t)g * Sp;
-    const int* oa = offA + (size_t)g * NWp;
-    const int* ob = offB + (size_t)g * NWp;
+    // frame offsets: one per block of kRenormEvery recursion steps (t / T_b-1-t)
+    const int* oa = offA + ((size_t)b * NB + (t / kRenormEvery)) * NWp;
+    const int* ob = offB + ((size_t)b * NB + ((u.T - 1 - t) / kRenormEvery)) * NWp;
     const float* er = em + (size_t)g * Lp;
     const int* lb = lab + (size_t)b * Lp;
     const int* db = dup + (size_t)b * Lp;
@@ -289,7 +290,7 @@ static int launch_fixup_t(void* grad, int B, int Tfr, int V, int blank, const Lo
   k<<<(unsigned)grid, kFixWarps * 32, smem, st>>>(
       static_cast<T*>(grad), B, Tfr, V, blank, reinterpret_cast<const UttInfo*>(ws + w.utt),
       reinterpret_cast<const int*>(ws + w.lab), reinterpret_cast<const int*>(ws + w.dup), w.Lp,
-      w.Sp, w.NW, wshift, reinterpret_cast<const float*>(ws + w.lse2),
+      w.Sp, w.NW, w.NB, wshift, reinterpret_cast<const float*>(ws + w.lse2),
       reinterpret_cast<const float*>(ws + w.cmax), reinterpret_cast<const float*>(ws + w.em),
       reinterpret_cast<const float*>(ws + w.alpha), reinterpret_cast<const float*>(ws + w.beta),
       reinterpret_cast<const int*>(ws + w.offA), reinterpret_cast<const int*>(ws + w.offB), gmul);

@@ -385,9 +385,13 @@ static cudaStream_t side_stream() {
   return g_side[dev];
 }
 
+// Split mode (dense rows on the side stream + sparse fix-up) is opt-in: measured on
+// B200 at C2 it loses to the fused row pass (profiles/README.md) because the
+// fix-up's partial-sector writes and the contention on the gather cost more than
+// the lattice latency they hide.
 static bool eager_split_enabled() {
   const char* e = getenv("B200CTC_EAGER_SPLIT");
-  return !(e && e[0] == '0');
+  return e && e[0] == '1';
 }
 
 }  // namespace b200ctc

@@ -6,49 +6,30 @@
 //
 // The CTA is a SYSTOLIC ARRAY OF WARPS with no CTA-wide barrier on the serial
 // chain.  Thread i keeps R consecutive lattice positions in registers; inside a
-// warp the neighbour value it needs arrives by shuffle; between warps they
-// travel through a small shared-memory ring of 16-byte packets {a[-1], step tag,
-// frame offset, step tag} written by the last lane of warp w and read by warp
-// w+1 one step later.  The dependency is one-directional (position sp needs
-// sp-1, sp-2), so warp w+1 simply trails warp w by a step or two; a consumed
-// counter gives back-pressure on the ring.  Every warp re-centres its own slice
-// on its own maximum every kRenormEvery frames with an INTEGER shift (exact to
-// combine, see ctc_ws.cuh), so there is no reduction across warps either.
-// The emissions em[t][k] are streamed into a shared-memory ring by a dedicated
-// producer warp with the TMA engine (1-D bulk copies of frame chunks, full /
-// empty mbarriers).
+// warp the one neighbour value it needs arrives by shuffle; between warps it
+// travels through a shared-memory ring written by the last lane of warp w and
+// read by warp w+1.  The dependency is one-directional (position sp needs
+// sp-1, sp-2), so warp w+1 simply runs one BLOCK of kBlk steps behind warp w:
+// all hand-shaking (ready / consumed counters, frame offsets) happens once per
+// block, and inside a block the steps are straight-line code - one LDS, one
+// STS and one SHFL per step beside the arithmetic.  Every warp re-centres its
+// own slice on its own maximum every kRenormEvery steps with an INTEGER shift
+// (exact to combine, see ctc_ws.cuh), so there is no reduction across warps
+// either.  The emissions em[t][k] are streamed into a shared-memory ring by a
+// dedicated producer warp with the TMA engine (1-D bulk copies of kBlk-frame
+// chunks, full / empty mbarriers).
 #pragma once
 #include "ctc_ws.cuh"
 
 namespace b200ctc {
 
 constexpr int kMaxLattice = 8192;  // 2*L+1 <= 8192  (R = 16, 16 warps + producer)
-constexpr int kRenormEvery = 16;
-constexpr int kEmRing = 4;    // chunks of emission frames in flight
-constexpr int kPktRing = 16;  // boundary packets in flight between adjacent warps
+constexpr int kValRing = 64;       // boundary values in flight between adjacent warps (steps)
+constexpr int kFRing = 2 * kValRing / kRenormEvery;  // frame offsets, one per renorm block
+constexpr int kMaxEmRing = 8;      // chunks of emission frames in flight
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ float4 lds_volatile_v4(const float4* p) {
-  float4 v;
-  asm volatile("ld.volatile.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
-               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
-               : "r"(smem_u32(p)));
-  return v;
-}
-__device__ __forceinline__ void sts_volatile_v4(float4* p, float4 v) {
-  asm volatile("st.volatile.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(smem_u32(p)), "f"(v.x),
-               "f"(v.y), "f"(v.z), "f"(v.w)
-               : "memory");
-}
-__device__ __forceinline__ int lds_volatile_i32(const int* p) {
-  int v;
-  asm volatile("ld.volatile.shared.s32 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)));
-  return v;
-}
-__device__ __forceinline__ void sts_volatile_i32(int* p, int v) {
-  asm volatile("st.volatile.shared.s32 [%0], %1;" ::"r"(smem_u32(p)), "r"(v) : "memory");
 }
 
 // The lattice uses a FINITE log-zero so that the serial chain needs no -inf /
@@ -78,10 +59,8 @@ __device__ __forceinline__ float4 lds_v4_u32(uint32_t addr) {
                : "r"(addr));
   return v;
 }
-__device__ __forceinline__ void sts_v4_u32(uint32_t addr, float4 v) {
-  asm volatile("st.volatile.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "f"(v.x), "f"(v.y),
-               "f"(v.z), "f"(v.w)
-               : "memory");
+__device__ __forceinline__ void sts_f32_u32(uint32_t addr, float v) {
+  asm volatile("st.volatile.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
 }
 __device__ __forceinline__ int lds_i32_u32(uint32_t addr) {
   int v;
@@ -90,6 +69,14 @@ __device__ __forceinline__ int lds_i32_u32(uint32_t addr) {
 }
 __device__ __forceinline__ void sts_i32_u32(uint32_t addr, int v) {
   asm volatile("st.volatile.shared.s32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ int lds_acquire_i32(uint32_t addr) {
+  int v;
+  asm volatile("ld.acquire.cta.shared.s32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sts_release_i32(uint32_t addr, int v) {
+  asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }
 __device__ __forceinline__ float lds_f32_u32(uint32_t addr) {
   float v;
@@ -107,23 +94,25 @@ struct LatticeArgs {
   UttInfo* utt;
   const int* lb;      // labels of this utterance (k = 0 blank)
   float* lat;         // alpha or beta rows of this utterance, (Tfr, Sp)
-  int* off;           // offA or offB rows of this utterance, (Tfr, NWp)
+  int* off;           // offA or offB of this utterance, (NB, NWp): one entry per renorm block
   uint32_t ring;      // shared: em ring base
-  uint32_t pkt;       // shared: packet ring base [NW][kPktRing] float4
-  uint32_t cons;      // shared: consumed[32]
+  uint32_t vals;      // shared: boundary values  [NW][kValRing] float
+  uint32_t fring;     // shared: frame offsets    [NW][kFRing]  int
+  uint32_t ready;     // shared: steps published  [NW] int
+  uint32_t cons;      // shared: steps consumed   [NW] int
   uint64_t* full;
   uint64_t* empty;
-  int Tb, L, Lp, Sp, NWp, chunk, nw_live, zero_infinity, b;
+  int Tb, L, Lp, Sp, NWp, nw_live, zero_infinity, b, nring;
 };
 
 // One compute warp of the systolic lattice (see the file header).  This is the
 // serial chain of the whole loss: one warp per SM sub-partition with a single
 // step in flight, so every instruction costs issue latency.  Branch-free
 // arithmetic (finite kLogZero, step 0 is an ordinary step started from a virtual
-// alpha_{-1}(0) = log 1), compile-time direction, pointer-walking addressing,
-// and the upstream packet prefetched one step ahead.
-template <int R, bool STORE, int DIR>
+// alpha_{-1}(0) = log 1), compile-time direction, blocks of K straight-line steps.
+template <int R, bool STORE, int DIR, int K>
 __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int lane) {
+  static_assert(K == 4 || K == 8, "block of 4 or 8 steps");
   const int Tb = A.Tb, L = A.L, S = 2 * L + 1, Lp = A.Lp;
   const int sp0 = (w * 32 + lane) * R;  // first recursion position of this thread
   // static description of this thread's positions: q even = blank, q odd = label
@@ -148,12 +137,17 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
   const bool has_up = w > 0, has_down = w + 1 < A.nw_live;
   const bool lane0 = lane == 0;
   const bool pub = has_down && lane == 31;
-  const uint32_t pk_in = pin(A.pkt + (uint32_t)(has_up ? w - 1 : 0) * (kPktRing * 16u));
-  const uint32_t pk_out = pin(A.pkt + (uint32_t)w * (kPktRing * 16u));
+  const int wu = has_up ? w - 1 : 0;
+  const uint32_t vals_in = pin(A.vals + (uint32_t)wu * (kValRing * 4u));
+  const uint32_t vals_out = pin(A.vals + (uint32_t)w * (kValRing * 4u));
+  const uint32_t fr_in = pin(A.fring + (uint32_t)wu * (kFRing * 4u));
+  const uint32_t fr_out = pin(A.fring + (uint32_t)w * (kFRing * 4u));
+  const uint32_t ready_in = pin(A.ready + 4u * (uint32_t)wu);
+  const uint32_t ready_out = pin(A.ready + 4u * (uint32_t)w);
   const uint32_t cons_mine = pin(A.cons + 4u * (uint32_t)w);
   const uint32_t cons_down = pin(A.cons + 4u * (uint32_t)(has_down ? w + 1 : w));
   const uint32_t row_bytes = pin(4u * (uint32_t)Lp);
-  const uint32_t chunk_bytes = pin(4u * (uint32_t)(A.chunk * Lp));
+  const uint32_t chunk_bytes = pin(4u * (uint32_t)(K * Lp));
 
   // walking pointers (frames ascend for alpha, descend for beta)
   const int t0 = DIR ? Tb - 1 : 0;
@@ -161,10 +155,9 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
   int* off_p = nullptr;
   if (STORE) {
     lat_p = A.lat + (size_t)t0 * A.Sp + sp0;
-    off_p = A.off + (size_t)t0 * A.NWp + w;
+    off_p = A.off + w;  // indexed by the renorm block of the RECURSION step, both directions
   }
   const ptrdiff_t lat_step = DIR ? -(ptrdiff_t)A.Sp : (ptrdiff_t)A.Sp;
-  const ptrdiff_t off_step = DIR ? -(ptrdiff_t)A.NWp : (ptrdiff_t)A.NWp;
   const bool store_ok = STORE && sp0 < A.Sp;
   const bool store_off = STORE && lane0;
 
@@ -172,107 +165,122 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
 #pragma unroll
   for (int q = 0; q < R; ++q) a[q] = kLogZero;
   if (sp0 == 0) a[0] = 0.f;  // virtual alpha_{-1}(0) = log 1
-  int F = 0;          // integer frame offset of a[] (ctc_ws.cuh)
-  int Dpend = 0;      // re-centring shift to apply at the next step
-  float shift = 0.f;  // = (float)Dpend
-  int cons_seen = 0;  // downstream warp's fetch count (cached)
-  // packet of step -1: the ring is initialised with tag -1 / kLogZero / F = 0
-  float4 pk = lds_v4_u32(pk_in + (kPktRing - 1) * 16u);
-  int i = 0;  // recursion step
+  int F = 0;       // integer frame offset of a[] (ctc_ws.cuh)
+  int Dpend = 0;   // re-centring shift measured at the end of the previous renorm block
+  int Fup = 0;     // upstream warp's current frame offset
+  int ready_seen = 0, cons_seen = 0;
 
-  // value of position sp0-1 after step i-1, expressed in MY frame (one neighbour
-  // value per thread: R is even, so sp0 is a blank and needs only sp0-1, and the
-  // label at sp0+1 takes its skip transition from sp0-1 as well)
-  auto fetch = [&]() {
-    float p1 = __shfl_up_sync(0xffffffffu, a[R - 1], 1);
-    if (has_up) {
-      // packet = {value, tag, frame offset, tag}: each 8-byte half validates itself,
-      // so the protocol does not depend on 16-byte shared stores being single-copy atomic
-      while (__float_as_int(pk.y) != i - 1 || __float_as_int(pk.w) != i - 1)
-        pk = lds_v4_u32(pk_in + ((uint32_t)(i - 1) & (kPktRing - 1)) * 16u);
-      const float up = pk.x + (float)(__float_as_int(pk.z) - F);
-      p1 = lane0 ? up : p1;
-      if (lane0) sts_i32_u32(cons_mine, i + 1);
-    } else {
-      p1 = lane0 ? kLogZero : p1;
-    }
-    return p1;
-  };
-
-  const int nchunks = (Tb + A.chunk - 1) / A.chunk;
-  for (int c = 0; c < nchunks; ++c) {
-    const int n = (Tb - c * A.chunk < A.chunk) ? Tb - c * A.chunk : A.chunk;
-    const int slot = c % kEmRing;
+  const int nblk = (Tb + K - 1) / K;
+  for (int c = 0; c < nblk; ++c) {
+    const int i0 = c * K;
+    const int n = (Tb - i0 < K) ? Tb - i0 : K;
+    const int slot = c % A.nring;
     uint32_t erow = A.ring + (uint32_t)slot * chunk_bytes + (DIR ? (uint32_t)(n - 1) * row_bytes : 0u);
-    mbar_wait(&A.full[slot], (c / kEmRing) & 1);
-#pragma unroll 1
-    for (int u = 0; u < n; ++u) {
-      const float eb = lds_f32_u32(erow) - shift;
-      float el[R / 2];
+    // ---------------- block prologue: all hand-shaking happens here, once per K steps
+    const bool renorm_apply = (i0 & (kRenormEvery - 1)) == 0;
+    const int D = renorm_apply ? Dpend : 0;
+    const float shift = (float)D;
+    float up[K];
 #pragma unroll
-      for (int h = 0; h < R / 2; ++h) el[h] = lds_f32_u32(erow + jlab[h]) - shift;
-      if (DIR) erow -= row_bytes; else erow += row_bytes;
-      const float p1 = fetch();
-      // prefetch the packet of THIS step (needed at the next one): the upstream
-      // warp runs a step or two ahead, so it is normally already there
-      if (has_up) pk = lds_v4_u32(pk_in + ((uint32_t)i & (kPktRing - 1)) * 16u);
-      float nw_[R];
-#pragma unroll
-      for (int q = 0; q < R; ++q) {
-        const float x0 = a[q];
-        const float x1 = q >= 1 ? a[q - 1] : p1;
-        float v;
-        if (q & 1) {
-          const float x2r = q >= 2 ? a[q - 2] : p1;
-          const float x2 = skip[q >> 1] ? x2r : kLogZero;
-          v = lse3_fast(x0, x1, x2, el[q >> 1]);
-        } else {
-          v = lse2_fast(x0, x1, eb);
-        }
-        nw_[q] = act[q] ? v : kLogZero;
+    for (int u = 0; u < K; ++u) up[u] = kLogZero;
+    float adj0 = 0.f, adj = 0.f;
+    if (has_up) {
+      // value of step j sits in slot (j+1) & 63: this block needs steps i0-1 .. i0+K-2
+      const int need = (i0 + K - 1 < Tb - 1) ? i0 + K - 1 : Tb - 1;
+      while (ready_seen < need) ready_seen = lds_acquire_i32(ready_in);
+      const uint32_t vb = vals_in + ((uint32_t)i0 & (kValRing - 1)) * 4u;
+      const float4 v0 = lds_v4_u32(vb);
+      up[0] = v0.x; up[1] = v0.y; up[2] = v0.z; up[3] = v0.w;
+      if (K == 8) {
+        const float4 v1 = lds_v4_u32(vb + 16u);
+        up[K - 4] = v1.x; up[K - 3] = v1.y; up[K - 2] = v1.z; up[K - 1] = v1.w;
       }
-      F += Dpend;
+      const int Fprev = lds_i32_u32(fr_in + (((uint32_t)((i0 - 1) >> 4)) & (kFRing - 1)) * 4u);
+      Fup = lds_i32_u32(fr_in + (((uint32_t)(i0 >> 4)) & (kFRing - 1)) * 4u);
+      adj0 = (float)(Fprev - F);     // step i0 still adds to my old frame (then -shift)
+      adj = (float)(Fup - (F + D));  // later steps of the block
+      if (lane0) sts_i32_u32(cons_mine, i0 + K);
+    }
+    if (has_down) {
+      // my slots of this block last held steps i0-64 ..: the consumer read them in the
+      // block that ended at step i0 + 2K - 64
+      const int needc = i0 + 2 * K - kValRing;
+      while (cons_seen < needc) cons_seen = lds_i32_u32(cons_down);
+    }
+    if (renorm_apply) {
+      F += D;
       Dpend = 0;
-      shift = 0.f;
-#pragma unroll
-      for (int q = 0; q < R; ++q) a[q] = nw_[q];
-      // hand the top position to the next warp; the slot's previous packet
-      // (step i-16) is read by the consumer's fetch of step i-15
-      if (has_down) {
-        while (cons_seen < i - (kPktRing - 2)) cons_seen = lds_i32_u32(cons_down);
-        if (pub)
-          sts_v4_u32(pk_out + ((uint32_t)i & (kPktRing - 1)) * 16u,
-                     make_float4(a[R - 1], __int_as_float(i), __int_as_float(F), __int_as_float(i)));
+      if (pub) sts_i32_u32(fr_out + (((uint32_t)(i0 >> 4)) & (kFRing - 1)) * 4u, F);
+      if (STORE) {
+        if (store_off) *off_p = F;
+        off_p += A.NWp;
       }
-      if (store_ok) {
-        if (R == 2) {
-          *reinterpret_cast<float2*>(lat_p) = make_float2(a[0], a[1]);
-        } else {
+    }
+    const uint32_t ob0 = vals_out + (((uint32_t)i0 & (kValRing - 1)) + 1u) * 4u;  // slots of steps i0..i0+K-2
+    const uint32_t ob1 = vals_out + ((uint32_t)(i0 + K) & (kValRing - 1)) * 4u;    // slot of step i0+K-1
+    mbar_wait(&A.full[slot], (c / A.nring) & 1);
+    // ---------------- K straight-line steps
 #pragma unroll
-          for (int q = 0; q < R; q += 4)
-            *reinterpret_cast<float4*>(lat_p + q) = make_float4(a[q], a[q + 1], a[q + 2], a[q + 3]);
+    for (int u = 0; u < K; ++u) {
+      if (u < n) {
+        float eb = lds_f32_u32(erow);
+        float el[R / 2];
+#pragma unroll
+        for (int h = 0; h < R / 2; ++h) el[h] = lds_f32_u32(erow + jlab[h]);
+        if (u == 0) {
+          eb -= shift;
+#pragma unroll
+          for (int h = 0; h < R / 2; ++h) el[h] -= shift;
         }
-      }
-      if (store_off) *off_p = F;
-      lat_p += lat_step;
-      off_p += off_step;
-      if ((i & (kRenormEvery - 1)) == kRenormEvery - 1) {
-        float m = a[0];
+        if (DIR) erow -= row_bytes; else erow += row_bytes;
+        // value of position sp0-1 after the previous step, in MY frame (one neighbour
+        // value per thread: R is even, so sp0 is a blank and needs only sp0-1, and the
+        // label at sp0+1 takes its skip transition from sp0-1 as well)
+        float p1 = __shfl_up_sync(0xffffffffu, a[R - 1], 1);
+        p1 = lane0 ? up[u] + (u == 0 ? adj0 : adj) : p1;
+        float nw_[R];
 #pragma unroll
-        for (int q = 1; q < R; ++q) m = fmaxf(m, a[q]);
-        m = warp_max(m);
-        // nothing alive yet: adopt the upstream warp's frame so that the first
-        // real values to arrive are already centred.  (Clamped: a pathological
-        // -1e10 "logzero" logit must not overflow the integer offsets.)
-        // The prefetched packet is NOT validated and a 128-bit LDS is served in
-        // quarter-warp phases, so lanes may hold different packets: take lane 0's
-        // (the frame offset must stay warp-uniform).
-        const int upF = __shfl_sync(0xffffffffu, __float_as_int(pk.z), 0);
-        Dpend = (m > kLogZeroTest) ? (int)rintf(fminf(fmaxf(m, -1048576.f), 1048576.f))
-                                   : (has_up ? upF - F : 0);
-        shift = (float)Dpend;
+        for (int q = 0; q < R; ++q) {
+          const float x0 = a[q];
+          const float x1 = q >= 1 ? a[q - 1] : p1;
+          float v;
+          if (q & 1) {
+            const float x2r = q >= 2 ? a[q - 2] : p1;
+            const float x2 = skip[q >> 1] ? x2r : kLogZero;
+            v = lse3_fast(x0, x1, x2, el[q >> 1]);
+          } else {
+            v = lse2_fast(x0, x1, eb);
+          }
+          nw_[q] = act[q] ? v : kLogZero;
+        }
+#pragma unroll
+        for (int q = 0; q < R; ++q) a[q] = nw_[q];
+        if (pub) sts_f32_u32(u == K - 1 ? ob1 : ob0 + 4u * u, a[R - 1]);
+        if (store_ok) {
+          if (R == 2) {
+            *reinterpret_cast<float2*>(lat_p) = make_float2(a[0], a[1]);
+          } else {
+#pragma unroll
+            for (int q = 0; q < R; q += 4)
+              *reinterpret_cast<float4*>(lat_p + q) = make_float4(a[q], a[q + 1], a[q + 2], a[q + 3]);
+          }
+        }
+        lat_p += lat_step;
       }
-      ++i;
+    }
+    // ---------------- block epilogue
+    if (pub) sts_release_i32(ready_out, i0 + n);
+    if ((i0 & (kRenormEvery - 1)) == kRenormEvery - K && n == K) {
+      float m = a[0];
+#pragma unroll
+      for (int q = 1; q < R; ++q) m = fmaxf(m, a[q]);
+      m = warp_max(m);
+      // nothing alive yet: adopt the upstream warp's frame so that the first real
+      // values to arrive are already centred.  (Clamped: a pathological -1e10
+      // "logzero" logit must not overflow the integer offsets.)  Fup came from a
+      // 4-byte broadcast LDS after the acquire, so it is warp-uniform.
+      Dpend = (m > kLogZeroTest) ? (int)rintf(fminf(fmaxf(m, -1048576.f), 1048576.f))
+                                 : (has_up ? Fup - F : 0);
     }
     __syncwarp();
     if (lane0) mbar_arrive(&A.empty[slot]);
@@ -280,7 +288,15 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
 
   // ---- epilogue: log-likelihood from the last two positions (alpha only)
   if (DIR != 0) return;
-  const float p1 = fetch();
+  float p1 = __shfl_up_sync(0xffffffffu, a[R - 1], 1);
+  if (has_up) {
+    while (ready_seen < Tb) ready_seen = lds_acquire_i32(ready_in);
+    const float v = lds_f32_u32(vals_in + ((uint32_t)Tb & (kValRing - 1)) * 4u);
+    const int Fl = lds_i32_u32(fr_in + (((uint32_t)((Tb - 1) >> 4)) & (kFRing - 1)) * 4u);
+    if (lane0) p1 = v + (float)(Fl - F);
+  } else if (lane0) {
+    p1 = kLogZero;
+  }
   const int q_own = (S - 1) % R;
   if (sp0 + q_own == S - 1) {
     float v1 = kLogZero, v2 = kLogZero;
@@ -303,15 +319,14 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
   }
 }
 
-template <int R, bool STORE>
+template <int R, bool STORE, int K>
 __global__ void __launch_bounds__(R == 2 ? 544 : (R <= 8 ? 1024 : 576)) lattice_kernel(
     UttInfo* __restrict__ utt, const int* __restrict__ lab, int Lp, const float* __restrict__ em,
     float* __restrict__ alpha, float* __restrict__ beta, int* __restrict__ offA,
-    int* __restrict__ offB, int Tfr, int Sp, int NWp, int zero_infinity, int chunk) {
+    int* __restrict__ offB, int Tfr, int Sp, int NWp, int NB, int zero_infinity, int nring) {
   static_assert(R % 2 == 0, "R must be even: even recursion positions are blanks");
-  extern __shared__ __align__(128) float lsm[];  // em ring [kEmRing][chunk*Lp], packet ring
-  __shared__ __align__(8) uint64_t full[kEmRing], empty[kEmRing];
-  __shared__ int consumed[32];
+  extern __shared__ __align__(128) float lsm[];  // em ring [nring][K*Lp] | vals | fring | ready | cons
+  __shared__ __align__(8) uint64_t full[kMaxEmRing], empty[kMaxEmRing];
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int NW = (blockDim.x >> 5) - 1;  // compute warps; warp NW is the TMA producer
   const int b = blockIdx.x, dir = blockIdx.y;
@@ -327,29 +342,31 @@ __global__ void __launch_bounds__(R == 2 ? 544 : (R <= 8 ? 1024 : 576)) lattice_
     return;
   }
   const int nw_live = (S + 32 * R - 1) / (32 * R);
-  const int chunk_elems = chunk * Lp;
+  const int chunk_elems = K * Lp;
   float* ring = lsm;
-  float4* pkt = reinterpret_cast<float4*>(lsm + (size_t)kEmRing * chunk_elems);  // [NW][kPktRing]
+  float* vals = lsm + (size_t)nring * chunk_elems;     // [NW][kValRing]
+  int* fring = reinterpret_cast<int*>(vals + (size_t)NW * kValRing);  // [NW][kFRing]
+  int* ready = fring + (size_t)NW * kFRing;            // [NW]
+  int* cons = ready + NW;                              // [NW]
   const float* emb = em + (size_t)b * Tfr * Lp;
 
   if (tid == 0) {
-    for (int i = 0; i < kEmRing; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], nw_live); }
+    for (int i = 0; i < nring; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], nw_live); }
     fence_mbar_init();
   }
-  for (int i = tid; i < NW * kPktRing; i += blockDim.x)
-    pkt[i] = make_float4(kLogZero, __int_as_float(-1), __int_as_float(0), __int_as_float(-1));
-  if (tid < 32) consumed[tid] = 0;
+  for (int i = tid; i < NW * kValRing; i += blockDim.x) vals[i] = kLogZero;
+  for (int i = tid; i < NW * (kFRing + 2); i += blockDim.x) fring[i] = 0;  // fring, ready, cons
   __syncthreads();
 
   // ------------------------------------------------------------ TMA producer warp
   if (wid == NW) {
     if (lane == 0) {
-      const int nchunks = (Tb + chunk - 1) / chunk;
+      const int nchunks = (Tb + K - 1) / K;
       for (int c = 0; c < nchunks; ++c) {
-        const int slot = c % kEmRing, round = c / kEmRing;
+        const int slot = c % nring, round = c / nring;
         if (round > 0) mbar_wait(&empty[slot], (round - 1) & 1);
-        const int i0 = c * chunk;
-        const int n = (Tb - i0 < chunk) ? Tb - i0 : chunk;
+        const int i0 = c * K;
+        const int n = (Tb - i0 < K) ? Tb - i0 : K;
         const int f0 = dir ? Tb - i0 - n : i0;  // first frame of the (contiguous) block
         const uint32_t bytes = (uint32_t)n * Lp * 4u;
         mbar_expect_tx(&full[slot], bytes);
@@ -364,16 +381,18 @@ __global__ void __launch_bounds__(R == 2 ? 544 : (R <= 8 ? 1024 : 576)) lattice_
   A.utt = utt;
   A.lb = lab + (size_t)b * Lp;
   A.lat = (dir ? beta : alpha) + (size_t)b * Tfr * Sp;
-  A.off = (dir ? offB : offA) + (size_t)b * Tfr * NWp;
+  A.off = (dir ? offB : offA) + (size_t)b * NB * NWp;
   A.ring = smem_u32(ring);
-  A.pkt = smem_u32(pkt);
-  A.cons = smem_u32(consumed);
+  A.vals = smem_u32(vals);
+  A.fring = smem_u32(fring);
+  A.ready = smem_u32(ready);
+  A.cons = smem_u32(cons);
   A.full = full;
   A.empty = empty;
-  A.Tb = Tb; A.L = L; A.Lp = Lp; A.Sp = Sp; A.NWp = NWp; A.chunk = chunk;
-  A.nw_live = nw_live; A.zero_infinity = zero_infinity; A.b = b;
-  if (dir == 0) lattice_warp<R, STORE, 0>(A, wid, lane);
-  else lattice_warp<R, STORE, 1>(A, wid, lane);
+  A.Tb = Tb; A.L = L; A.Lp = Lp; A.Sp = Sp; A.NWp = NWp;
+  A.nw_live = nw_live; A.zero_infinity = zero_infinity; A.b = b; A.nring = nring;
+  if (dir == 0) lattice_warp<R, STORE, 0, K>(A, wid, lane);
+  else lattice_warp<R, STORE, 1, K>(A, wid, lane);
 }
 
 // nll[b] = -ln2 * (lam + aend + sum_t (c[t] - lse2[t]))   (ctc_ws.cuh)
@@ -403,15 +422,10 @@ __global__ void __launch_bounds__(256) nll_kernel(const UttInfo* __restrict__ ut
   }
 }
 
-template <int R>
-static int launch_lattice_r(const LossLayout& w, unsigned char* ws, int Tfr, int zero_infinity,
-                            int both_dirs, cudaStream_t st) {
+template <int R, int K>
+static int launch_lattice_rk(const LossLayout& w, unsigned char* ws, int Tfr, int zero_infinity,
+                             int both_dirs, int nring, size_t smem, cudaStream_t st) {
   const int nt = (w.NW + 1) * 32;
-  int chunk = 8192 / (w.Lp * 4);
-  if (chunk < 1) chunk = 1;
-  if (chunk > 32) chunk = 32;
-  const size_t smem = sizeof(float) * (size_t)kEmRing * chunk * w.Lp +
-                      sizeof(float4) * (size_t)w.NW * kPktRing;
   dim3 grid(w.B, both_dirs ? 2 : 1);
   auto go = [&](auto k) {
     if (smem > 48 * 1024)
@@ -422,13 +436,32 @@ static int launch_lattice_r(const LossLayout& w, unsigned char* ws, int Tfr, int
                               reinterpret_cast<float*>(ws + w.alpha),
                               reinterpret_cast<float*>(ws + w.beta),
                               reinterpret_cast<int*>(ws + w.offA),
-                              reinterpret_cast<int*>(ws + w.offB), Tfr, w.Sp, w.NW, zero_infinity,
-                              chunk);
+                              reinterpret_cast<int*>(ws + w.offB), Tfr, w.Sp, w.NW, w.NB,
+                              zero_infinity, nring);
   };
-  if (both_dirs) go(lattice_kernel<R, true>);
-  else go(lattice_kernel<R, false>);
+  if (both_dirs) go(lattice_kernel<R, true, K>);
+  else go(lattice_kernel<R, false, K>);
   count_launch();
   return check_launch("ctc lattice");
+}
+
+template <int R>
+static int launch_lattice_r(const LossLayout& w, unsigned char* ws, int Tfr, int zero_infinity,
+                            int both_dirs, cudaStream_t st) {
+  // shared memory: em ring of nring chunks of K frames + the per-warp hand-off rings
+  const size_t fixed = (size_t)w.NW * (kValRing * 4 + kFRing * 4 + 8) + 256;
+  const size_t budget = 200 * 1024 - fixed;
+  const size_t frame = (size_t)w.Lp * 4;
+  int K = 8;
+  if (2 * 8 * frame > budget) K = 4;
+  B2_REQUIRE(2 * (size_t)K * frame <= budget, "ctc lattice: target too long for shared memory");
+  int nring = (int)(budget / (K * frame));
+  if (nring > kMaxEmRing) nring = kMaxEmRing;
+  // keep small cases small (several CTAs per SM): ~32 KB of emissions in flight is plenty
+  while (nring > 3 && (size_t)nring * K * frame > 32 * 1024) --nring;
+  const size_t smem = (size_t)nring * K * frame + fixed;
+  if (K == 8) return launch_lattice_rk<R, 8>(w, ws, Tfr, zero_infinity, both_dirs, nring, smem, st);
+  return launch_lattice_rk<R, 4>(w, ws, Tfr, zero_infinity, both_dirs, nring, smem, st);
 }
 
 static inline int launch_lattice(const LossLayout& w, unsigned char* ws, int Tfr, int zero_infinity,

@@ -15,8 +15,9 @@
 //   alpha[t][sp] = true log2-alpha~ - (sum_{tau<=t} c[tau] + FA_w[t])
 //   beta [t][sp] = true log2-beta~  - (sum_{tau>=t} c[tau] + FB_w[t])
 // where alpha~/beta~ are the recursions on the unnormalised scores 2^y2 and
-// FA_w/FB_w are INTEGER re-centring offsets kept per (frame, warp of the lattice
-// CTA): every warp re-centres its own slice on its own maximum, so no CTA-wide
+// FA_w/FB_w are INTEGER re-centring offsets kept per (block of kRenormEvery
+// recursion steps, warp of the lattice CTA; the recursion step of frame t is t
+// for alpha and T_b-1-t for beta): every warp re-centres its own slice on its own maximum, so no CTA-wide
 // reduction sits on the serial chain, and integer offsets combine exactly:
 //   log2 gamma_t(s) = alpha + beta - em + (FA_wA[t] + FB_wB[t] - aend) - lam
 //   log2 P          = lam + aend + sum_t (c[t] - lse2[t])
@@ -45,10 +46,11 @@ struct UttInfo {
 static_assert(offsetof(UttInfo, T) % 8 == 0 && offsetof(UttInfo, L) == offsetof(UttInfo, T) + 4,
               "UttInfo::{T,L} must form an aligned int2");
 
+constexpr int kRenormEvery = 16;  // lattice re-centring period (steps); one frame offset per block
 constexpr int kEmLabel0 = 4;  // em row: [blank, -, -, -, label_1 .. label_L]
 
 struct LossLayout {
-  int B, T, V, Lmax, Lp, Sp, R, NW;
+  int B, T, V, Lmax, Lp, Sp, R, NW, NB;
   size_t lse2, cmax, em, alpha, beta, offA, offB, utt, lab, dup, total;
 };
 
@@ -73,6 +75,7 @@ inline LossLayout make_loss_layout(int B, int T, int V, int Lmax) {
   w.Sp = (int)align_up((size_t)S, 8);
   w.R = lattice_R(S);
   w.NW = (S + 32 * w.R - 1) / (32 * w.R);
+  w.NB = (T + kRenormEvery - 1) / kRenormEvery;  // renorm blocks per utterance
   size_t o = 0;
   const size_t BT = (size_t)B * T;
   auto take = [&](size_t bytes) { size_t r = o; o = align_up(o + bytes, 256); return r; };
@@ -81,8 +84,8 @@ inline LossLayout make_loss_layout(int B, int T, int V, int Lmax) {
   w.dup = take(4 * (size_t)B * w.Lp);
   w.lse2 = take(4 * BT);
   w.cmax = take(4 * BT);
-  w.offA = take(4 * BT * w.NW);
-  w.offB = take(4 * BT * w.NW);
+  w.offA = take(4 * (size_t)B * w.NB * w.NW);
+  w.offB = take(4 * (size_t)B * w.NB * w.NW);
   w.em = take(4 * BT * w.Lp);
   w.alpha = take(4 * BT * w.Sp);
   w.beta = take(4 * BT * w.Sp);
