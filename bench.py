@@ -263,7 +263,7 @@ def run_gpu(args):
     pm = (ctypes.c_float * 8)()
     pc = (ctypes.c_int * 8)()
     L.b200ctc_profile_read(pm, pc, 8)
-    names = ["prep", "gather", "lattice", "dense_rows", "prefix", "softmax", "rescale", "fixup"]
+    names = ["prep", "gather", "lattice", "grad_rows", "prefix", "softmax", "rescale", "fixup"]
     phases = {n: (pm[i] / pc[i] if pc[i] else None) for i, n in enumerate(names)}
 
     # ---- e2e: host buffers through the C-ABI pipeline (H2D + compute + D2H of the loss)

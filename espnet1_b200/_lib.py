@@ -34,12 +34,13 @@ SIGNATURES = {
     "b200ctc_greedy_decode": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_int, _P, _P, _P]),
     "b200ctc_loss_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "b200ctc_loss_fwd": (c_int, [_P, c_int, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int,
-                                 c_int, c_int, _P, _P, c_size_t, _P]),
+                                 c_int, c_int, _P, _P, c_float, _P, c_size_t, _P]),
     "b200ctc_loss_bwd": (c_int, [_P, c_int, _P, c_int, c_int, c_int, c_int, c_int, c_int, _P,
                                  c_int, c_float, _P, _P, c_size_t, _P]),
     "b200ctc_loss_fwd_grad": (c_int, [_P, c_int, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int,
-                                      c_int, c_float, _P, _P, _P, c_size_t, _P]),
-    "b200ctc_grad_rescale": (c_int, [_P, c_int, _P, c_int, c_float, c_int, c_int, c_int, _P]),
+                                      c_int, c_float, _P, _P, c_float, _P, _P, c_size_t, _P]),
+    "b200ctc_grad_rescale": (c_int, [_P, c_int, _P, c_int, c_float, c_float, c_int, c_int, c_int,
+                                     _P]),
     "b200ctc_align_workspace_bytes": (c_size_t, [c_int, c_int]),
     "b200ctc_forced_align": (c_int, [_P, _P, c_int, c_int, c_int, c_int, _P, _P, c_size_t, _P]),
     "b200ctc_prefix_pad": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_float, _P]),

@@ -294,10 +294,10 @@ int launch_grad_rows(const void* logits, int dtype, void* grad, int B, int T, in
 template <typename T>
 __global__ void __launch_bounds__(256) rescale_kernel(T* __restrict__ grad, int64_t per_utt,
                                                       const float* __restrict__ gscale,
-                                                      int gstride, float hint) {
+                                                      int gstride, float gmul, float hint) {
   constexpr int N = Elems<T>::N;
   const int b = blockIdx.y;
-  const float gv = gscale[(size_t)b * gstride];
+  const float gv = gscale[(size_t)b * gstride] * gmul;
   if (gv == hint) return;
   const float ratio = gv / hint;
   T* base = grad + (size_t)b * per_utt;
@@ -350,7 +350,7 @@ extern "C" int b200ctc_loss_bwd(const void* logits, int dtype, const int64_t* in
 }
 
 extern "C" int b200ctc_grad_rescale(void* grad, int dtype, const float* gscale, int gscale_stride,
-                                    float grad_hint, int B, int T, int V,
+                                    float gscale_mul, float grad_hint, int B, int T, int V,
                                     b200ctc_stream_t stream) {
   B2_REQUIRE(B >= 0 && T >= 0 && V > 0, "grad_rescale: bad shape");
   if (B == 0 || T == 0) return B200CTC_OK;
@@ -368,15 +368,15 @@ extern "C" int b200ctc_grad_rescale(void* grad, int dtype, const float* gscale, 
   switch (dtype) {
     case B200CTC_F32:
       rescale_kernel<float><<<grid, 256, 0, st>>>(static_cast<float*>(grad), per_utt, gscale,
-                                                  gscale_stride, inv);
+                                                  gscale_stride, gscale_mul, inv);
       break;
     case B200CTC_F16:
       rescale_kernel<__half><<<grid, 256, 0, st>>>(static_cast<__half*>(grad), per_utt, gscale,
-                                                   gscale_stride, inv);
+                                                   gscale_stride, gscale_mul, inv);
       break;
     default:
       rescale_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(static_cast<__nv_bfloat16*>(grad),
-                                                          per_utt, gscale, gscale_stride, inv);
+                                                          per_utt, gscale, gscale_stride, gscale_mul, inv);
       break;
   }
   prof_mark(6, 1, st);

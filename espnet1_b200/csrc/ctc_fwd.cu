@@ -20,18 +20,32 @@ __global__ void __launch_bounds__(1024) prep_kernel(const int64_t* __restrict__ 
                                                     const int64_t* __restrict__ tgt_lens, int T,
                                                     int V, int Lmax, int Lp, int blank,
                                                     UttInfo* __restrict__ utt,
-                                                    int* __restrict__ lab, int* __restrict__ dup) {
+                                                    int* __restrict__ lab, int* __restrict__ dup,
+                                                    int* __restrict__ counter) {
   extern __shared__ int slab[];  // [Lp]
   __shared__ int s_bad, s_head;
+  __shared__ long long s_base;
   const int b = blockIdx.x, NT = blockDim.x;
+  if (b == 0 && threadIdx.x == 0) *counter = 0;  // nll_kernel's "last CTA" ticket
   long long L64 = tgt_lens[b], T64 = in_lens[b];
   const int L = (int)(L64 < 0 ? 0 : (L64 > Lmax ? Lmax : L64));
   const int Tb = (int)(T64 < 0 ? 0 : (T64 > T ? T : T64));
-  const int64_t base = offs[b];
   int* lb = lab + (size_t)b * Lp;
   int* db = dup + (size_t)b * Lp;
-  if (threadIdx.x == 0) { s_bad = 0; s_head = 0x7fffffff; }
+  if (threadIdx.x == 0) { s_bad = 0; s_head = 0x7fffffff; s_base = 0; }
   __syncthreads();
+  if (offs) {
+    if (threadIdx.x == 0) s_base = offs[b];
+  } else {  // offsets not given: prefix sum of the (non-negative) target lengths
+    long long part = 0;
+    for (int i = threadIdx.x; i < b; i += NT) part += tgt_lens[i] < 0 ? 0 : tgt_lens[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+    if ((threadIdx.x & 31) == 0 && part) atomicAdd(reinterpret_cast<unsigned long long*>(&s_base),
+                                                   (unsigned long long)part);
+  }
+  __syncthreads();
+  const int64_t base = s_base;
   for (int k = threadIdx.x; k < Lp; k += NT) {
     int v = blank;
     if (k >= 1 && k <= L) {
@@ -324,7 +338,8 @@ static int check_loss_args(const char* who, const void* logits, int dtype, const
                            const float* nll, const void* ws_, size_t ws_bytes, LossLayout* out) {
   B2_REQUIRE(B >= 0 && T >= 0 && V > 0 && max_tgt_len >= 0, "%s: bad shape", who);
   if (B == 0) return B200CTC_OK;
-  B2_REQUIRE(logits && tgt_offsets && in_lens && tgt_lens && nll && ws_, "%s: null pointer", who);
+  (void)tgt_offsets;  // may be NULL: prep_kernel then prefix-sums tgt_lens itself
+  B2_REQUIRE(logits && in_lens && tgt_lens && nll && ws_, "%s: null pointer", who);
   B2_REQUIRE(targets || max_tgt_len == 0, "%s: null targets", who);
   B2_REQUIRE(blank >= 0 && blank < V, "%s: blank=%d outside [0,%d)", who, blank, V);
   B2_REQUIRE(dtype >= 0 && dtype <= 2, "%s: unknown dtype %d", who, dtype);
@@ -351,7 +366,7 @@ static int launch_prep(const LossLayout& w, unsigned char* ws, const int64_t* ta
   prep_kernel<<<w.B, nt, sizeof(int) * (size_t)w.Lp, st>>>(
       targets, tgt_offsets, in_lens, tgt_lens, w.T, w.V, w.Lmax, w.Lp, blank,
       reinterpret_cast<UttInfo*>(ws + w.utt), reinterpret_cast<int*>(ws + w.lab),
-      reinterpret_cast<int*>(ws + w.dup));
+      reinterpret_cast<int*>(ws + w.dup), reinterpret_cast<int*>(ws + w.counter));
   count_launch();
   prof_mark(0, 1, st);
   return check_launch("ctc prep");
@@ -400,8 +415,9 @@ static bool eager_split_enabled() {
 extern "C" int b200ctc_loss_fwd(const void* logits, int dtype, const int64_t* targets,
                                 const int64_t* tgt_offsets, const int64_t* in_lens,
                                 const int64_t* tgt_lens, int B, int T, int V, int max_tgt_len,
-                                int blank, int zero_infinity, int need_grad, float* nll, void* ws_,
-                                size_t ws_bytes, b200ctc_stream_t stream) {
+                                int blank, int zero_infinity, int need_grad, float* nll,
+                                float* loss_out, float loss_scale, void* ws_, size_t ws_bytes,
+                                b200ctc_stream_t stream) {
   LossLayout w;
   int rc = check_loss_args("loss_fwd", logits, dtype, targets, tgt_offsets, in_lens, tgt_lens, B, T,
                            V, max_tgt_len, blank, nll, ws_, ws_bytes, &w);
@@ -424,7 +440,7 @@ extern "C" int b200ctc_loss_fwd(const void* logits, int dtype, const int64_t* ta
   rc = launch_lattice(w, ws, T, zero_infinity, need_grad, st);
   prof_mark(2, 1, st);
   if (rc) return rc;
-  return launch_nll(w, ws, T, zero_infinity, nll, st);
+  return launch_nll(w, ws, T, zero_infinity, nll, loss_out, loss_scale, st);
 }
 
 // forward + gradient in one call (eager mode): the logits are read ONCE in
@@ -433,8 +449,9 @@ extern "C" int b200ctc_loss_fwd_grad(const void* logits, int dtype, const int64_
                                      const int64_t* tgt_offsets, const int64_t* in_lens,
                                      const int64_t* tgt_lens, int B, int T, int V,
                                      int max_tgt_len, int blank, int zero_infinity,
-                                     float grad_hint, float* nll, void* grad, void* ws_,
-                                     size_t ws_bytes, b200ctc_stream_t stream) {
+                                     float grad_hint, float* nll, float* loss_out,
+                                     float loss_scale, void* grad, void* ws_, size_t ws_bytes,
+                                     b200ctc_stream_t stream) {
   LossLayout w;
   int rc = check_loss_args("loss_fwd_grad", logits, dtype, targets, tgt_offsets, in_lens, tgt_lens,
                            B, T, V, max_tgt_len, blank, nll, ws_, ws_bytes, &w);
@@ -465,7 +482,13 @@ extern "C" int b200ctc_loss_fwd_grad(const void* logits, int dtype, const int64_
     cudaEventRecord(ev_join, sd);
   }
   if (!rc) rc = launch_prep(w, ws, targets, tgt_offsets, in_lens, tgt_lens, blank, st);
-  if (!rc && T > 0) {
+  // B200CTC_FUSED_GATHER=1: the lattice's own producer warps gather the label
+  // columns.  Opt-in: alpha and beta CTAs each fetch every frame, and the doubled
+  // sparse-sector traffic (HBM serves 32-byte sectors at ~1/3 of streaming speed)
+  // costs as much as the stand-alone gather kernel saves (profiles/README.md).
+  const char* fg = getenv("B200CTC_FUSED_GATHER");
+  const bool fused_gather = T > 0 && !sd && fg && fg[0] == '1';
+  if (!rc && T > 0 && !fused_gather) {
     prof_mark(1, 0, st);
     switch (dtype) {
       case B200CTC_F32: rc = launch_gather<float>(logits, B, T, V, w, ws, st); break;
@@ -475,8 +498,9 @@ extern "C" int b200ctc_loss_fwd_grad(const void* logits, int dtype, const int64_
     prof_mark(1, 1, st);
   }
   if (!rc) {
+    GatherSrc gsrc{logits, reinterpret_cast<float*>(ws + w.cmax), dtype, V};
     prof_mark(2, 0, st);
-    rc = launch_lattice(w, ws, T, zero_infinity, 1, st);
+    rc = launch_lattice(w, ws, T, zero_infinity, 1, st, fused_gather ? &gsrc : nullptr);
     prof_mark(2, 1, st);
   }
   if (sd) {  // join (always, also on error: the caller's stream must cover the side work)
@@ -497,5 +521,5 @@ extern "C" int b200ctc_loss_fwd_grad(const void* logits, int dtype, const int64_
     }
     if (rc) return rc;
   }
-  return launch_nll(w, ws, T, zero_infinity, nll, st);
+  return launch_nll(w, ws, T, zero_infinity, nll, loss_out, loss_scale, st);
 }

@@ -319,16 +319,44 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
   }
 }
 
-template <int R, bool STORE, int K>
-__global__ void __launch_bounds__(R == 2 ? 544 : (R <= 8 ? 1024 : 576)) lattice_kernel(
+struct GatherSrc {      // GATHER mode: the producer warps read the logits directly
+  const void* logits;   // (B, Tfr, V)
+  float* cmax;          // (B, Tfr) per-frame constant, written by the alpha CTA
+  int dtype, V;
+};
+
+constexpr int kGatherProducers = 4;  // producer warps in GATHER mode (alternating chunks)
+constexpr int kGatherTile = 5;       // label columns per lane and pass (160 per warp)
+
+template <typename T, int K>
+__device__ __forceinline__ void gather_tile(const void* logits, size_t row_first, int n, int V,
+                                            const int (&col)[kGatherTile],
+                                            float (&v)[K][kGatherTile]) {
+  const T* base = static_cast<const T*>(logits);
+  T raw[K][kGatherTile];
+#pragma unroll
+  for (int f = 0; f < K; ++f) {
+    const T* row = base + (row_first + (f < n ? f : n - 1)) * (size_t)V;
+#pragma unroll
+    for (int j = 0; j < kGatherTile; ++j) raw[f][j] = __ldg(row + (col[j] >= 0 ? col[j] : 0));
+  }
+#pragma unroll
+  for (int f = 0; f < K; ++f)
+#pragma unroll
+    for (int j = 0; j < kGatherTile; ++j) v[f][j] = to_f32<T>(raw[f][j]) * kLog2e;
+}
+
+template <int R, bool STORE, int K, bool GATHER>
+__global__ void __launch_bounds__(R == 2 || R == 16 ? 640 : 1024, 1) lattice_kernel(
     UttInfo* __restrict__ utt, const int* __restrict__ lab, int Lp, const float* __restrict__ em,
-    float* __restrict__ alpha, float* __restrict__ beta, int* __restrict__ offA,
+    GatherSrc gs, float* __restrict__ alpha, float* __restrict__ beta, int* __restrict__ offA,
     int* __restrict__ offB, int Tfr, int Sp, int NWp, int NB, int zero_infinity, int nring) {
   static_assert(R % 2 == 0, "R must be even: even recursion positions are blanks");
   extern __shared__ __align__(128) float lsm[];  // em ring [nring][K*Lp] | vals | fring | ready | cons
   __shared__ __align__(8) uint64_t full[kMaxEmRing], empty[kMaxEmRing];
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  const int NW = (blockDim.x >> 5) - 1;  // compute warps; warp NW is the TMA producer
+  // compute warps 0..NW-1; then the producer warp(s): one TMA issuer, or the gather warps
+  const int NW = (blockDim.x >> 5) - (GATHER ? kGatherProducers : 1);
   const int b = blockIdx.x, dir = blockIdx.y;
   const int Tb = utt[b].T, L = utt[b].L, S = 2 * L + 1;
   if (Tb == 0) {
@@ -351,27 +379,87 @@ __global__ void __launch_bounds__(R == 2 ? 544 : (R <= 8 ? 1024 : 576)) lattice_
   const float* emb = em + (size_t)b * Tfr * Lp;
 
   if (tid == 0) {
-    for (int i = 0; i < nring; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], nw_live); }
+    for (int i = 0; i < nring; ++i) {
+      mbar_init(&full[i], GATHER ? 32 : 1);
+      mbar_init(&empty[i], nw_live);
+    }
     fence_mbar_init();
   }
   for (int i = tid; i < NW * kValRing; i += blockDim.x) vals[i] = kLogZero;
   for (int i = tid; i < NW * (kFRing + 2); i += blockDim.x) fring[i] = 0;  // fring, ready, cons
   __syncthreads();
 
-  // ------------------------------------------------------------ TMA producer warp
-  if (wid == NW) {
-    if (lane == 0) {
-      const int nchunks = (Tb + K - 1) / K;
-      for (int c = 0; c < nchunks; ++c) {
-        const int slot = c % nring, round = c / nring;
-        if (round > 0) mbar_wait(&empty[slot], (round - 1) & 1);
-        const int i0 = c * K;
-        const int n = (Tb - i0 < K) ? Tb - i0 : K;
-        const int f0 = dir ? Tb - i0 - n : i0;  // first frame of the (contiguous) block
-        const uint32_t bytes = (uint32_t)n * Lp * 4u;
-        mbar_expect_tx(&full[slot], bytes);
-        bulk_g2s(ring + (size_t)slot * chunk_elems, emb + (size_t)f0 * Lp, bytes, &full[slot]);
+  // ------------------------------------------------------------ producer warp(s)
+  if (wid >= NW) {
+    const int nchunks = (Tb + K - 1) / K;
+    if (!GATHER) {
+      // TMA: the emissions were gathered into `em` by an earlier kernel
+      if (lane == 0) {
+        for (int c = 0; c < nchunks; ++c) {
+          const int slot = c % nring, round = c / nring;
+          if (round > 0) mbar_wait(&empty[slot], (round - 1) & 1);
+          const int i0 = c * K;
+          const int n = (Tb - i0 < K) ? Tb - i0 : K;
+          const int f0 = dir ? Tb - i0 - n : i0;  // first frame of the (contiguous) block
+          const uint32_t bytes = (uint32_t)n * Lp * 4u;
+          mbar_expect_tx(&full[slot], bytes);
+          bulk_g2s(ring + (size_t)slot * chunk_elems, emb + (size_t)f0 * Lp, bytes, &full[slot]);
+        }
       }
+      return;
+    }
+    // GATHER: read the label columns of the logits straight into the ring.  The
+    // lattice is latency-bound and leaves HBM idle, so the sparse gather (L+1
+    // scattered sectors per frame, issued K frames x kGatherTile columns deep) costs
+    // no extra time.  Per-frame constant c[t] = the blank's score (any constant
+    // cancels, ctc_ws.cuh), so one shuffle replaces a reduction.
+    const int* lb = lab + (size_t)b * Lp;
+    const size_t row0 = (size_t)b * Tfr;
+    const int ntiles = (L + 1 + 32 * kGatherTile - 1) / (32 * kGatherTile);
+    for (int c = wid - NW; c < nchunks; c += kGatherProducers) {
+      const int slot = c % nring, round = c / nring;
+      if (round > 0) mbar_wait(&empty[slot], (round - 1) & 1);
+      const int i0 = c * K;
+      const int n = (Tb - i0 < K) ? Tb - i0 : K;
+      const int f0 = dir ? Tb - i0 - n : i0;
+      float* dst = ring + (size_t)slot * chunk_elems;
+      float cf[K];
+      for (int tile = 0; tile < ntiles; ++tile) {
+        int col[kGatherTile];
+#pragma unroll
+        for (int j = 0; j < kGatherTile; ++j) {
+          const int k = (tile * kGatherTile + j) * 32 + lane;
+          col[j] = k <= L ? lb[k] : -1;
+        }
+        // K x kGatherTile independent loads in flight per lane: unconditional, with
+        // clamped (always valid) addresses, so that nothing serialises them
+        float v[K][kGatherTile];
+        if (gs.dtype == B200CTC_F32)
+          gather_tile<float, K>(gs.logits, row0 + f0, n, gs.V, col, v);
+        else if (gs.dtype == B200CTC_F16)
+          gather_tile<__half, K>(gs.logits, row0 + f0, n, gs.V, col, v);
+        else
+          gather_tile<__nv_bfloat16, K>(gs.logits, row0 + f0, n, gs.V, col, v);
+        if (tile == 0) {
+#pragma unroll
+          for (int f = 0; f < K; ++f) {
+            float c0 = __shfl_sync(0xffffffffu, v[f][0], 0);  // k = 0: the blank
+            if (!(c0 > kNegInf && c0 < -kNegInf)) c0 = 0.f;   // -inf / NaN blank: no centring
+            cf[f] = c0;
+            if (dir == 0 && lane == 0 && f < n) gs.cmax[row0 + f0 + f] = c0;
+          }
+        }
+#pragma unroll
+        for (int f = 0; f < K; ++f) {
+#pragma unroll
+          for (int j = 0; j < kGatherTile; ++j) {
+            const int k = (tile * kGatherTile + j) * 32 + lane;
+            if (f < n && col[j] >= 0)
+              dst[(size_t)f * Lp + (k == 0 ? 0 : kEmLabel0 + k - 1)] = v[f][j] - cf[f];
+          }
+        }
+      }
+      mbar_arrive(&full[slot]);  // 32 arrivals (release) complete the phase
     }
     return;
   }
@@ -396,11 +484,17 @@ __global__ void __launch_bounds__(R == 2 ? 544 : (R <= 8 ? 1024 : 576)) lattice_
 }
 
 // nll[b] = -ln2 * (lam + aend + sum_t (c[t] - lse2[t]))   (ctc_ws.cuh)
+// Optionally the CTA that finishes last also writes the batch reduction
+// loss_out[0] = loss_scale * sum_b nll[b] (fixed summation order: deterministic),
+// i.e. espnet2/asr/ctc.py:56-60 `loss.sum() / size` without further launches.
 __global__ void __launch_bounds__(256) nll_kernel(const UttInfo* __restrict__ utt,
                                                   const float* __restrict__ cmax,
                                                   const float* __restrict__ lse2, int Tfr,
-                                                  int zero_infinity, float* __restrict__ nll) {
+                                                  int zero_infinity, float* __restrict__ nll,
+                                                  float* __restrict__ loss_out, float loss_scale,
+                                                  int* __restrict__ counter) {
   __shared__ double dred[8];
+  __shared__ int s_last;
   const int b = blockIdx.x, tid = threadIdx.x;
   const UttInfo u = utt[b];
   double part = 0.0;
@@ -419,35 +513,59 @@ __global__ void __launch_bounds__(256) nll_kernel(const UttInfo* __restrict__ ut
     if (u.infinite) v = zero_infinity ? 0.f : -kNegInf;
     else v = (float)(-(u.lam + (double)u.aend + tot) * 0.6931471805599453);
     nll[b] = v;
+    s_last = 0;
+    if (loss_out) {
+      __threadfence();
+      s_last = atomicAdd(counter, 1) == (int)gridDim.x - 1;
+    }
+  }
+  if (!loss_out) return;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  double acc = 0.0;
+  for (int i = tid; i < (int)gridDim.x; i += 256) acc += (double)__ldcg(nll + i);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((tid & 31) == 0) dred[tid >> 5] = acc;
+  __syncthreads();
+  if (tid == 0) {
+    double tot = 0.0;
+    for (int i = 0; i < 8; ++i) tot += dred[i];
+    loss_out[0] = (float)(tot * (double)loss_scale);
+    *counter = 0;  // ready for the next call on this workspace
   }
 }
 
 template <int R, int K>
 static int launch_lattice_rk(const LossLayout& w, unsigned char* ws, int Tfr, int zero_infinity,
-                             int both_dirs, int nring, size_t smem, cudaStream_t st) {
-  const int nt = (w.NW + 1) * 32;
+                             int both_dirs, int nring, size_t smem, const GatherSrc* gsrc,
+                             cudaStream_t st) {
+  const int nt = (w.NW + (gsrc ? kGatherProducers : 1)) * 32;
+  GatherSrc gs = gsrc ? *gsrc : GatherSrc{nullptr, nullptr, 0, 0};
   dim3 grid(w.B, both_dirs ? 2 : 1);
   auto go = [&](auto k) {
     if (smem > 48 * 1024)
       cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     k<<<grid, nt, smem, st>>>(reinterpret_cast<UttInfo*>(ws + w.utt),
                               reinterpret_cast<const int*>(ws + w.lab), w.Lp,
-                              reinterpret_cast<const float*>(ws + w.em),
+                              reinterpret_cast<const float*>(ws + w.em), gs,
                               reinterpret_cast<float*>(ws + w.alpha),
                               reinterpret_cast<float*>(ws + w.beta),
                               reinterpret_cast<int*>(ws + w.offA),
                               reinterpret_cast<int*>(ws + w.offB), Tfr, w.Sp, w.NW, w.NB,
                               zero_infinity, nring);
   };
-  if (both_dirs) go(lattice_kernel<R, true, K>);
-  else go(lattice_kernel<R, false, K>);
+  if (gsrc) go(lattice_kernel<R, true, K, true>);  // eager gradient mode only
+  else if (both_dirs) go(lattice_kernel<R, true, K, false>);
+  else go(lattice_kernel<R, false, K, false>);
   count_launch();
   return check_launch("ctc lattice");
 }
 
 template <int R>
 static int launch_lattice_r(const LossLayout& w, unsigned char* ws, int Tfr, int zero_infinity,
-                            int both_dirs, cudaStream_t st) {
+                            int both_dirs, const GatherSrc* gsrc, cudaStream_t st) {
   // shared memory: em ring of nring chunks of K frames + the per-warp hand-off rings
   const size_t fixed = (size_t)w.NW * (kValRing * 4 + kFRing * 4 + 8) + 256;
   const size_t budget = 200 * 1024 - fixed;
@@ -460,26 +578,28 @@ static int launch_lattice_r(const LossLayout& w, unsigned char* ws, int Tfr, int
   // keep small cases small (several CTAs per SM): ~32 KB of emissions in flight is plenty
   while (nring > 3 && (size_t)nring * K * frame > 32 * 1024) --nring;
   const size_t smem = (size_t)nring * K * frame + fixed;
-  if (K == 8) return launch_lattice_rk<R, 8>(w, ws, Tfr, zero_infinity, both_dirs, nring, smem, st);
-  return launch_lattice_rk<R, 4>(w, ws, Tfr, zero_infinity, both_dirs, nring, smem, st);
+  if (K == 8)
+    return launch_lattice_rk<R, 8>(w, ws, Tfr, zero_infinity, both_dirs, nring, smem, gsrc, st);
+  return launch_lattice_rk<R, 4>(w, ws, Tfr, zero_infinity, both_dirs, nring, smem, gsrc, st);
 }
 
 static inline int launch_lattice(const LossLayout& w, unsigned char* ws, int Tfr, int zero_infinity,
-                                 int both_dirs, cudaStream_t st) {
+                                 int both_dirs, cudaStream_t st, const GatherSrc* gsrc = nullptr) {
   switch (w.R) {
-    case 2: return launch_lattice_r<2>(w, ws, Tfr, zero_infinity, both_dirs, st);
-    case 4: return launch_lattice_r<4>(w, ws, Tfr, zero_infinity, both_dirs, st);
-    case 8: return launch_lattice_r<8>(w, ws, Tfr, zero_infinity, both_dirs, st);
-    default: return launch_lattice_r<16>(w, ws, Tfr, zero_infinity, both_dirs, st);
+    case 2: return launch_lattice_r<2>(w, ws, Tfr, zero_infinity, both_dirs, gsrc, st);
+    case 4: return launch_lattice_r<4>(w, ws, Tfr, zero_infinity, both_dirs, gsrc, st);
+    case 8: return launch_lattice_r<8>(w, ws, Tfr, zero_infinity, both_dirs, gsrc, st);
+    default: return launch_lattice_r<16>(w, ws, Tfr, zero_infinity, both_dirs, gsrc, st);
   }
 }
 
-static inline int launch_nll(const LossLayout& w, const unsigned char* ws, int Tfr,
-                             int zero_infinity, float* nll, cudaStream_t st) {
+static inline int launch_nll(const LossLayout& w, unsigned char* ws, int Tfr, int zero_infinity,
+                             float* nll, float* loss_out, float loss_scale, cudaStream_t st) {
   nll_kernel<<<w.B, 256, 0, st>>>(reinterpret_cast<const UttInfo*>(ws + w.utt),
                                   reinterpret_cast<const float*>(ws + w.cmax),
                                   reinterpret_cast<const float*>(ws + w.lse2), Tfr, zero_infinity,
-                                  nll);
+                                  nll, loss_out, loss_scale,
+                                  reinterpret_cast<int*>(ws + w.counter));
   count_launch();
   return check_launch("ctc nll");
 }

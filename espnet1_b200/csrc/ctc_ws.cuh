@@ -51,19 +51,19 @@ constexpr int kEmLabel0 = 4;  // em row: [blank, -, -, -, label_1 .. label_L]
 
 struct LossLayout {
   int B, T, V, Lmax, Lp, Sp, R, NW, NB;
-  size_t lse2, cmax, em, alpha, beta, offA, offB, utt, lab, dup, total;
+  size_t lse2, cmax, em, alpha, beta, offA, offB, utt, lab, dup, counter, total;
 };
 
 // positions per thread of the lattice CTA (even); one warp covers 32*R positions
-// (at most 31 compute warps: the 32nd warp of the CTA is the TMA producer)
+// (at most 28 compute warps: the CTA also holds one TMA or four gather producer warps)
 inline int lattice_R(int Smax) {
   if (const char* e = getenv("B200CTC_LAT_R")) {  // tuning sweeps only
     const int r = atoi(e);
-    if ((r == 2 || r == 4 || r == 8 || r == 16) && Smax <= 31 * 32 * r) return r;
+    if ((r == 2 || r == 4 || r == 8 || r == 16) && Smax <= 28 * 32 * r) return r;
   }
   if (Smax <= 16 * 32 * 2) return 2;
-  if (Smax <= 31 * 32 * 4) return 4;
-  if (Smax <= 31 * 32 * 8) return 8;
+  if (Smax <= 28 * 32 * 4) return 4;
+  if (Smax <= 28 * 32 * 8) return 8;
   return 16;
 }
 
@@ -79,6 +79,7 @@ inline LossLayout make_loss_layout(int B, int T, int V, int Lmax) {
   size_t o = 0;
   const size_t BT = (size_t)B * T;
   auto take = [&](size_t bytes) { size_t r = o; o = align_up(o + bytes, 256); return r; };
+  w.counter = take(sizeof(int));  // "last CTA reduces" ticket of nll_kernel (zeroed by prep)
   w.utt = take(sizeof(UttInfo) * (size_t)B);
   w.lab = take(4 * (size_t)B * w.Lp);
   w.dup = take(4 * (size_t)B * w.Lp);

@@ -132,8 +132,8 @@ extern "C" int b200ctc_loss_fwd_bwd_host(const void* logits_host, int dtype,
     CU_TRY(cudaEventRecord(a.ev[2 * c], a.s_copy));
     CU_TRY(cudaStreamWaitEvent(a.s_comp, a.ev[2 * c], 0));
     rc = b200ctc_loss_fwd_grad(dl, dtype, d_tgt, d_off + b0, d_il + b0, d_tl + b0, nb, T, V,
-                               (int)lmax, blank, zero_infinity, gscale, d_nll + b0, dg, a.ws,
-                               a.ws_cap, a.s_comp);
+                               (int)lmax, blank, zero_infinity, gscale, d_nll + b0, nullptr, 0.f,
+                               dg, a.ws, a.ws_cap, a.s_comp);
     if (rc) break;
     if (grad_host) {
       CU_TRY(cudaEventRecord(a.ev[2 * c + 1], a.s_comp));

@@ -62,8 +62,10 @@ static inline RowLaunchCfg row_launch_cfg(const void* base, size_t row_bytes, si
   c.tma = (row_bytes % 16 == 0) && ((reinterpret_cast<uintptr_t>(base) & 15) == 0);
   c.stride = (int)align_up(row_bytes, 128);
   const size_t budget = 220 * 1024;  // of the 227 KB an SM can hand to CTAs
-  int want_ctas = nt <= 128 ? 5 : (nt <= 256 ? 3 : 1);
-  int want_stages = 2;
+  // measured on B200 (tools/sweep_rows.py, C2): many single-stage CTAs beat fewer
+  // double-buffered ones - the other CTAs of the SM are the pipeline
+  int want_ctas = nt <= 128 ? 6 : (nt <= 256 ? 3 : 1);
+  int want_stages = nt <= 128 ? 1 : 2;
   char name[64];
   snprintf(name, sizeof(name), "%s_CTAS", env_prefix);
   if (const char* e = getenv(name)) want_ctas = atoi(e);

@@ -44,11 +44,13 @@ class CTC(torch.nn.Module):
         """(T,B,V) activations -> loss / B; summed over the batch iff reduce
         (the reference folds that sum into CTCLoss(reduction="sum"), :37-40)."""
         logits = th_pred.transpose(0, 1)
+        size = th_pred.size(1)
+        if self.reduce:  # sum()/B comes out of the loss kernels themselves
+            return B.ctc_loss(logits, th_target, th_ilen, th_olen, blank=0, zero_infinity=True,
+                              max_tgt_len=max_tgt_len, reduce_scale=B._f32_recip(size))
         nll = B.ctc_loss(logits, th_target, th_ilen, th_olen, blank=0, zero_infinity=True,
                          max_tgt_len=max_tgt_len)
-        if self.reduce:
-            nll = nll.sum()
-        return nll / th_pred.size(1)
+        return nll / size
 
     def forward(self, hs_pad, hlens, ys_pad):
         """CTC forward

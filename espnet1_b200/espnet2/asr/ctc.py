@@ -62,9 +62,11 @@ class CTC(torch.nn.Module):
 
     # same call convention as torch.nn.CTCLoss(reduction="none") but fed with
     # batch-major LOGITS: log-softmax is fused into the loss kernels.
-    def _builtin_ctc_loss(self, logits_btv, th_target, th_ilen, th_olen, max_tgt_len=None):
+    def _builtin_ctc_loss(self, logits_btv, th_target, th_ilen, th_olen, max_tgt_len=None,
+                          reduce_scale=None):
         return B.ctc_loss(logits_btv, th_target, th_ilen, th_olen, blank=0,
-                          zero_infinity=self.zero_infinity, max_tgt_len=max_tgt_len)
+                          zero_infinity=self.zero_infinity, max_tgt_len=max_tgt_len,
+                          reduce_scale=reduce_scale)
 
     def loss_fn(self, th_pred, th_target, th_ilen, th_olen, max_tgt_len=None) -> torch.Tensor:
         """th_pred is (T, B, V) like the reference (:52); a transposed view of a
@@ -72,13 +74,12 @@ class CTC(torch.nn.Module):
         if self.ctc_type != "builtin":
             raise NotImplementedError
         logits = th_pred.transpose(0, 1)  # (B, T, V); contiguous when th_pred was a view
-        loss = self.ctc_loss(logits, th_target, th_ilen, th_olen, max_tgt_len)
         size = th_pred.size(1)
         if self.reduce:
-            loss = loss.sum() / size  # batch-size average (:58-60)
-        else:
-            loss = loss / size
-        return loss
+            # batch-size average (:58-60): sum()/size comes out of the loss kernels
+            return self.ctc_loss(logits, th_target, th_ilen, th_olen, max_tgt_len,
+                                 reduce_scale=B._f32_recip(size))
+        return self.ctc_loss(logits, th_target, th_ilen, th_olen, max_tgt_len) / size
 
     def forward(self, hs_pad, hlens, ys_pad, ys_lens):
         """Calculate CTC loss.

@@ -77,13 +77,15 @@ def greedy_decode(logits: torch.Tensor, in_lens=None, blank: int = 0):
 
 def _upstream(g):
     """(fp32 device vector, stride) describing the upstream gradient of nll (B,)."""
-    if g.stride(0) == 0 or g.numel() == 1:  # expanded scalar (loss.sum()/B)
+    if g.dim() == 0 or g.numel() == 1 or g.stride(0) == 0:  # scalar / expanded scalar
         return g.reshape(-1)[:1].to(torch.float32).contiguous(), 0
     return g.to(torch.float32).contiguous(), 1
 
 
 class _CTCLossFn(torch.autograd.Function):
-    """nll (B,) fp32 = CTCLoss(reduction='none')(log_softmax(logits)).
+    """nll (B,) fp32 = CTCLoss(reduction='none')(log_softmax(logits)); with
+    ``reduce_scale`` the scalar ``reduce_scale * nll.sum()`` instead (written by
+    the same launches).
 
     eager mode (default when the logits need a gradient): forward computes the
     loss AND d nll/d logits scaled by ``grad_hint`` in one call - the logits are
@@ -95,7 +97,7 @@ class _CTCLossFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, logits, targets, tgt_offsets, in_lens, tgt_lens, max_tgt_len, blank,
-                zero_infinity, grad_hint, eager):
+                zero_infinity, grad_hint, eager, reduce_scale):
         require_cuda(logits, "CTC logits")
         x = logits.contiguous()
         B, T, V = x.shape
@@ -104,29 +106,34 @@ class _CTCLossFn(torch.autograd.Function):
         nbytes = lib().b200ctc_loss_workspace_bytes(B, T, V, max_tgt_len)
         ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
         nll = torch.empty(B, dtype=torch.float32, device=dev)
+        reduced = reduce_scale is not None
+        loss = torch.zeros((), dtype=torch.float32, device=dev) if (reduced and B == 0) else (
+            torch.empty((), dtype=torch.float32, device=dev) if reduced else None)
+        scale = float(reduce_scale) if reduced else 0.0
         ctx.eager = bool(need_grad and eager and B > 0)
+        ctx.gmul = float(reduce_scale) if reduced else 1.0
         if ctx.eager:
             grad = torch.empty_like(x)
             check(lib().b200ctc_loss_fwd_grad(ptr(x), dtype_code(x), ptr(targets), ptr(tgt_offsets),
                                               ptr(in_lens), ptr(tgt_lens), B, T, V, max_tgt_len,
                                               blank, int(zero_infinity), grad_hint, ptr(nll),
-                                              ptr(grad), ptr(ws), nbytes, stream_ptr(dev)),
-                  "loss_fwd_grad")
+                                              ptr(loss), scale, ptr(grad), ptr(ws), nbytes,
+                                              stream_ptr(dev)), "loss_fwd_grad")
             ctx.grad_buf = grad
             ctx.cfg = (B, T, V, grad_hint)
-            return nll
+            return loss if reduced else nll
         check(lib().b200ctc_loss_fwd(ptr(x), dtype_code(x), ptr(targets), ptr(tgt_offsets),
                                      ptr(in_lens), ptr(tgt_lens), B, T, V, max_tgt_len, blank,
-                                     int(zero_infinity), int(need_grad), ptr(nll), ptr(ws), nbytes,
-                                     stream_ptr(dev)), "loss_fwd")
+                                     int(zero_infinity), int(need_grad), ptr(nll), ptr(loss), scale,
+                                     ptr(ws), nbytes, stream_ptr(dev)), "loss_fwd")
         if need_grad:
             ctx.save_for_backward(x, in_lens, ws)
             ctx.cfg = (B, T, V, max_tgt_len, blank, int(zero_infinity), nbytes)
-        return nll
+        return loss if reduced else nll
 
     @staticmethod
     def backward(ctx, g):
-        none9 = (None,) * 9
+        none10 = (None,) * 10
         gs, stride = _upstream(g)
         if ctx.eager:
             grad = ctx.grad_buf
@@ -136,30 +143,38 @@ class _CTCLossFn(torch.autograd.Function):
                     "use ctc_loss(..., grad_mode='deferred') to backpropagate twice")
             ctx.grad_buf = None
             B, T, V, hint = ctx.cfg
-            check(lib().b200ctc_grad_rescale(ptr(grad), dtype_code(grad), ptr(gs), stride, hint,
-                                             B, T, V, stream_ptr(grad.device)), "grad_rescale")
-            return (grad,) + none9
+            check(lib().b200ctc_grad_rescale(ptr(grad), dtype_code(grad), ptr(gs), stride, ctx.gmul,
+                                             hint, B, T, V, stream_ptr(grad.device)),
+                  "grad_rescale")
+            return (grad,) + none10
         x, in_lens, ws = ctx.saved_tensors
         B, T, V, lmax, blank, zinf, nbytes = ctx.cfg
         grad = torch.empty_like(x)
         check(lib().b200ctc_loss_bwd(ptr(x), dtype_code(x), ptr(in_lens), B, T, V, lmax, blank,
-                                     zinf, ptr(gs), stride, 1.0, ptr(grad), ptr(ws), nbytes,
+                                     zinf, ptr(gs), stride, ctx.gmul, ptr(grad), ptr(ws), nbytes,
                                      stream_ptr(x.device)), "loss_bwd")
-        return (grad,) + none9
+        return (grad,) + none10
+
+
+def _f32_recip(n: int) -> float:
+    """fp32 1/n exactly as torch's `x / n` produces it."""
+    return float(np.float32(1.0) / np.float32(max(n, 1)))
 
 
 def ctc_loss(logits, targets, in_lens, tgt_lens, blank: int = 0, zero_infinity: bool = True,
              max_tgt_len: int | None = None, tgt_offsets=None, grad_hint: float | None = None,
-             grad_mode: str = "eager") -> torch.Tensor:
+             grad_mode: str = "eager", reduce_scale: float | None = None) -> torch.Tensor:
     """Per-utterance CTC negative log-likelihood from LOGITS.
 
     logits (B,T,V) batch-major activations (fp32/fp16/bf16, CUDA); targets 1-D
     concatenated int64 labels; in_lens / tgt_lens (B,).  Equivalent to
     ``F.ctc_loss(logits.transpose(0,1).log_softmax(2), ..., reduction="none")``.
     ``max_tgt_len`` may be given to avoid a device->host sync.
+    ``reduce_scale``: return the scalar ``reduce_scale * nll.sum()`` instead of
+    the (B,) vector (``1/B`` gives espnet2/asr/ctc.py:56-60) with no extra launch.
     ``grad_hint``: the upstream gradient the caller expects for every nll[b]
-    (default 1/B, i.e. ``nll.sum()/B`` as in espnet2/asr/ctc.py:56-60); any other
-    upstream gradient is still exact, it only costs one rescaling pass.
+    (default 1/B, i.e. ``nll.sum()/B``); any other upstream gradient is still
+    exact, it only costs one rescaling pass.
     """
     require_cuda(logits, "CTC logits")
     if grad_mode not in ("eager", "deferred"):
@@ -171,14 +186,12 @@ def ctc_loss(logits, targets, in_lens, tgt_lens, blank: int = 0, zero_infinity: 
     if max_tgt_len is None:
         src = tgt_lens if not (isinstance(tgt_lens, torch.Tensor) and tgt_lens.is_cuda) else tl_dev
         max_tgt_len = int(torch.as_tensor(src).max()) if tl_dev.numel() else 0
-    if tgt_offsets is None:
-        tgt_offsets = torch.zeros(tl_dev.numel() + 1, dtype=torch.int64, device=dev)
-        torch.cumsum(tl_dev, 0, out=tgt_offsets[1:])
-    if grad_hint is None:  # fp32 1/B exactly as torch's `x / B` backward produces it
-        grad_hint = float(np.float32(1.0) / np.float32(max(logits.shape[0], 1)))
+    if grad_hint is None:
+        grad_hint = float(reduce_scale) if reduce_scale is not None else _f32_recip(logits.shape[0])
     return _CTCLossFn.apply(logits, tg_dev, tgt_offsets, il_dev, tl_dev, int(max_tgt_len),
                             int(blank), bool(zero_infinity), float(grad_hint),
-                            grad_mode == "eager")
+                            grad_mode == "eager",
+                            None if reduce_scale is None else float(reduce_scale))
 
 
 def forced_align(lp: torch.Tensor, target: torch.Tensor, blank: int = 0) -> torch.Tensor:

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define B200CTC_ABI_VERSION 1
+#define B200CTC_ABI_VERSION 2
 
 #define B200CTC_OK 0
 #define B200CTC_ERR_ARG (-1)     /* bad argument (null pointer, size, dtype) */
@@ -99,13 +99,17 @@ int b200ctc_greedy_decode(const void* x, const int64_t* in_lens, int B, int T,
  *      grad[b,t,v] = gscale_mul * gscale[b*gscale_stride] * d nll[b] / d logits[b,t,v];
  *    gscale may be NULL (=1), gscale_stride is 0 for a scalar upstream
  *    gradient, 1 for a per-utterance one.
- * fwd writes nll (B,) fp32 (0 where infeasible and zero_infinity).            */
+ * fwd writes nll (B,) fp32 (0 where infeasible and zero_infinity).  tgt_offsets
+ * may be NULL (the library prefix-sums tgt_lens itself).  loss_out may be NULL;
+ * otherwise loss_out[0] = loss_scale * sum_b nll[b] is written by the same
+ * launches (espnet2/asr/ctc.py:56-60 `loss.sum() / size` with loss_scale = 1/B). */
 size_t b200ctc_loss_workspace_bytes(int B, int T, int V, int max_tgt_len);
 int b200ctc_loss_fwd(const void* logits, int dtype, const int64_t* targets,
                      const int64_t* tgt_offsets, const int64_t* in_lens,
                      const int64_t* tgt_lens, int B, int T, int V,
                      int max_tgt_len, int blank, int zero_infinity, int need_grad,
-                     float* nll, void* ws, size_t ws_bytes, b200ctc_stream_t stream);
+                     float* nll, float* loss_out, float loss_scale, void* ws,
+                     size_t ws_bytes, b200ctc_stream_t stream);
 int b200ctc_loss_bwd(const void* logits, int dtype, const int64_t* in_lens,
                      int B, int T, int V, int max_tgt_len, int blank,
                      int zero_infinity, const float* gscale, int gscale_stride,
@@ -115,11 +119,13 @@ int b200ctc_loss_fwd_grad(const void* logits, int dtype, const int64_t* targets,
                           const int64_t* tgt_offsets, const int64_t* in_lens,
                           const int64_t* tgt_lens, int B, int T, int V,
                           int max_tgt_len, int blank, int zero_infinity,
-                          float grad_hint, float* nll, void* grad, void* ws,
-                          size_t ws_bytes, b200ctc_stream_t stream);
+                          float grad_hint, float* nll, float* loss_out,
+                          float loss_scale, void* grad, void* ws, size_t ws_bytes,
+                          b200ctc_stream_t stream);
+/* grad *= gscale[b*gscale_stride] * gscale_mul / grad_hint (no-op when equal)  */
 int b200ctc_grad_rescale(void* grad, int dtype, const float* gscale,
-                         int gscale_stride, float grad_hint, int B, int T, int V,
-                         b200ctc_stream_t stream);
+                         int gscale_stride, float gscale_mul, float grad_hint,
+                         int B, int T, int V, b200ctc_stream_t stream);
 /* forced alignment (espnet/nets/pytorch_backend/ctc.py:163-226): max-semiring
  * lattice with back-pointers for ONE utterance; lp (T,V) fp32 log-probs,
  * out_ids (T,) int64 = label emitted at each frame (tgt_len >= 1).            */

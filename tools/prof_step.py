@@ -28,11 +28,11 @@ for i in range(steps):
         L.b200ctc_profile_enable(1)
     ev[i].record()
     x.grad = None
-    nll = F.ctc_loss(x, tg, il, tl, max_tgt_len=cfg["lmax"])
-    (nll.sum() / cfg["B"]).backward()
+    nll = F.ctc_loss(x, tg, il, tl, max_tgt_len=cfg["lmax"], reduce_scale=1.0 / cfg["B"])
+    nll.backward()
 ev[steps].record()
 torch.cuda.synchronize()
-print("ms per step:", [round(ev[i].elapsed_time(ev[i + 1]), 4) for i in range(steps)], "loss", float(nll.sum()) / cfg["B"])
+print("ms per step:", [round(ev[i].elapsed_time(ev[i + 1]), 4) for i in range(steps)], "loss", float(nll.detach()))
 if os.environ.get("PHASES"):
     pm, pc = (ctypes.c_float * 8)(), (ctypes.c_int * 8)()
     L.b200ctc_profile_read(pm, pc, 8)
