@@ -12,145 +12,181 @@ namespace b200ctc {
 // ------------------------------------------------------------------ prep
 // int64 labels -> per-utterance int32 rows (k = 0 is the blank), duplicate
 // chains (so that repeated labels are accumulated deterministically by one
-// owner thread in the backward), clamped lengths.  Labels are staged in shared
-// memory: the O(L^2) duplicate search then runs on broadcast LDS.
-__global__ void __launch_bounds__(1024) prep_kernel(const int64_t* __restrict__ targets,
-                                                    const int64_t* __restrict__ offs,
-                                                    const int64_t* __restrict__ in_lens,
-                                                    const int64_t* __restrict__ tgt_lens, int T,
-                                                    int V, int Lmax, int Lp, int blank,
-                                                    UttInfo* __restrict__ utt,
-                                                    int* __restrict__ lab, int* __restrict__ dup,
-                                                    int* __restrict__ counter) {
-  extern __shared__ int slab[];  // [Lp]
+// owner thread in the gradient pass), clamped lengths.  Labels are staged in
+// shared memory: the O(L^2) duplicate search then runs on broadcast LDS.
+// Executed by a whole CTA; `publish` = also write lab/dup/utt for the later
+// kernels (one CTA per utterance does, the others only need `slab`).
+struct PrepArgs {
+  const int64_t* targets;
+  const int64_t* offs;  // may be NULL: prefix sum of tgt_lens
+  const int64_t* in_lens;
+  const int64_t* tgt_lens;
+  int T, V, Lmax, Lp, blank;
+  UttInfo* utt;
+  int* lab;
+  int* dup;
+  int* counter;
+};
+
+__device__ __forceinline__ void prep_utterance(const PrepArgs& P, int b, int* slab, bool publish,
+                                               int& Tb_out, int& L_out) {
   __shared__ int s_bad, s_head;
   __shared__ long long s_base;
-  const int b = blockIdx.x, NT = blockDim.x;
-  if (b == 0 && threadIdx.x == 0) *counter = 0;  // nll_kernel's "last CTA" ticket
-  long long L64 = tgt_lens[b], T64 = in_lens[b];
-  const int L = (int)(L64 < 0 ? 0 : (L64 > Lmax ? Lmax : L64));
-  const int Tb = (int)(T64 < 0 ? 0 : (T64 > T ? T : T64));
-  int* lb = lab + (size_t)b * Lp;
-  int* db = dup + (size_t)b * Lp;
-  if (threadIdx.x == 0) { s_bad = 0; s_head = 0x7fffffff; s_base = 0; }
+  const int NT = blockDim.x, tid = threadIdx.x;
+  if (publish && b == 0 && tid == 0) *P.counter = 0;  // nll_kernel's "last CTA" ticket
+  const long long L64 = P.tgt_lens[b], T64 = P.in_lens[b];
+  const int L = (int)(L64 < 0 ? 0 : (L64 > P.Lmax ? P.Lmax : L64));
+  const int Tb = (int)(T64 < 0 ? 0 : (T64 > P.T ? P.T : T64));
+  Tb_out = Tb;
+  L_out = L;
+  if (tid == 0) { s_bad = 0; s_head = 0x7fffffff; s_base = 0; }
   __syncthreads();
-  if (offs) {
-    if (threadIdx.x == 0) s_base = offs[b];
-  } else {  // offsets not given: prefix sum of the (non-negative) target lengths
+  if (P.offs) {
+    if (tid == 0) s_base = P.offs[b];
+  } else {
     long long part = 0;
-    for (int i = threadIdx.x; i < b; i += NT) part += tgt_lens[i] < 0 ? 0 : tgt_lens[i];
+    for (int i = tid; i < b; i += NT) part += P.tgt_lens[i] < 0 ? 0 : P.tgt_lens[i];
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-    if ((threadIdx.x & 31) == 0 && part) atomicAdd(reinterpret_cast<unsigned long long*>(&s_base),
-                                                   (unsigned long long)part);
+    if ((tid & 31) == 0 && part)
+      atomicAdd(reinterpret_cast<unsigned long long*>(&s_base), (unsigned long long)part);
   }
   __syncthreads();
   const int64_t base = s_base;
-  for (int k = threadIdx.x; k < Lp; k += NT) {
-    int v = blank;
+  int* lb = P.lab + (size_t)b * P.Lp;
+  for (int k = tid; k < P.Lp; k += NT) {
+    int v = P.blank;
     if (k >= 1 && k <= L) {
-      long long t = targets[base + k - 1];
-      if (t < 0 || t >= V) { s_bad = 1; t = t < 0 ? 0 : V - 1; }
+      long long t = P.targets[base + k - 1];
+      if (t < 0 || t >= P.V) { s_bad = 1; t = t < 0 ? 0 : P.V - 1; }
       v = (int)t;
     }
     slab[k] = v;
-    lb[k] = v;
+    if (publish) lb[k] = v;
   }
   __syncthreads();
-  for (int k = threadIdx.x; k < Lp; k += NT) {
+  if (!publish) return;
+  int* db = P.dup + (size_t)b * P.Lp;
+  for (int k = tid; k < P.Lp; k += NT) {
     int code = 0;
     if (k >= 1 && k <= L) {
       const int v = slab[k];
-      bool first = (v != blank);
+      bool first = (v != P.blank);
       for (int j = 1; j < k && first; ++j) first = slab[j] != v;
       int next = 0;
       for (int j = k + 1; j <= L; ++j)
         if (slab[j] == v) { next = j; break; }
       code = next | (first ? kDupFirst : 0);
-      if (v == blank) atomicMin(&s_head, k);
+      if (v == P.blank) atomicMin(&s_head, k);
     }
     db[k] = code;
   }
   __syncthreads();
-  if (threadIdx.x == 0) {
+  if (tid == 0) {
     UttInfo u;
     u.lam = 0; u.aend = 0;
     u.T = Tb; u.L = L; u.zeroed = 0; u.infinite = 0;
     u.blank_head = s_head == 0x7fffffff ? 0 : s_head;
     u.bad_label = s_bad; u.pad = 0;
-    utt[b] = u;
+    P.utt[b] = u;
   }
+}
+
+__global__ void __launch_bounds__(1024) prep_kernel(PrepArgs P) {
+  extern __shared__ int slab[];  // [Lp]
+  int Tb, L;
+  prep_utterance(P, blockIdx.x, slab, true, Tb, L);
 }
 
 // ------------------------------------------------- emission gather (sparse)
 // The lattice needs only the logits at the utterance's label columns (and the
 // blank): (L+1) of the V entries of every row, i.e. ~1/4 of the row's 32-byte
-// sectors at C2 instead of a full streaming read.  One warp per (b,t) row;
+// sectors at C2 instead of a full streaming read.  A warp handles kGatherRows
+// (b,t) rows at once (all their loads in flight together);
 // em[t][k] = logit[t][label_k]*log2(e) - c[t] with c[t] = max_k (ctc_ws.cuh).
+// The label preparation is fused in: every CTA stages its utterance's labels
+// itself, and the first CTA of each utterance publishes lab/dup/utt.
 constexpr int kGatherWarps = 8;
-constexpr int kGatherRegs = 8;  // values kept in registers per lane (L+1 <= 256)
+constexpr int kGatherRows = 4;   // rows per warp in flight
+constexpr int kGatherRegs = 8;   // values kept in registers per lane and row (L+1 <= 256)
 
 template <typename T>
 __global__ void __launch_bounds__(kGatherWarps * 32) gather_kernel(
-    const T* __restrict__ logits, int Tfr, int V, const UttInfo* __restrict__ utt,
-    const int* __restrict__ lab, int Lp, float* __restrict__ em, float* __restrict__ cmax,
-    int frames_per_cta) {
-  extern __shared__ int slab[];  // [L+1] label columns of this utterance
+    const T* __restrict__ logits, PrepArgs P, float* __restrict__ em, float* __restrict__ cmax) {
+  extern __shared__ int slab[];  // [Lp] label columns of this utterance
   const int b = blockIdx.y;
-  const int2 TL = *reinterpret_cast<const int2*>(&utt[b].T);
-  const int Tb = TL.x, L = TL.y;
-  const int t0 = blockIdx.x * frames_per_cta;
-  if (t0 >= Tb) return;
-  const int* lb = lab + (size_t)b * Lp;
-  for (int k = threadIdx.x; k <= L; k += blockDim.x) slab[k] = lb[k];
-  __syncthreads();
+  int Tb, L;
+  prep_utterance(P, b, slab, blockIdx.x == 0, Tb, L);
+  const int Tfr = P.T, V = P.V, Lp = P.Lp;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  int t1 = t0 + frames_per_cta;
-  if (t1 > Tb) t1 = Tb;
+  constexpr int kFramesPerCta = kGatherWarps * kGatherRows;
+  const int t0 = blockIdx.x * kFramesPerCta + wid * kGatherRows;
+  if (t0 >= Tb) return;
+  const int nr = Tb - t0 < kGatherRows ? Tb - t0 : kGatherRows;
+  const size_t g0 = (size_t)b * Tfr + t0;
   const bool in_regs = L + 1 <= 32 * kGatherRegs;
-  for (int t = t0 + wid; t < t1; t += kGatherWarps) {
-    const size_t g = (size_t)b * Tfr + t;
-    const T* row = logits + g * V;
-    float* er = em + g * Lp;
-    float v[kGatherRegs];
-    float m = kNegInf;
-    if (in_regs) {
+  float m[kGatherRows];
 #pragma unroll
-      for (int j = 0; j < kGatherRegs; ++j) {
-        const int k = lane + 32 * j;
-        v[j] = kNegInf;
-        if (k <= L) v[j] = to_f32<T>(__ldg(row + slab[k])) * kLog2e;
-        m = fmaxf(m, v[j]);
+  for (int r = 0; r < kGatherRows; ++r) m[r] = kNegInf;
+  if (in_regs) {
+    float v[kGatherRows][kGatherRegs];
+#pragma unroll
+    for (int j = 0; j < kGatherRegs; ++j) {
+      const int k = lane + 32 * j;
+      const int col = slab[k <= L ? k : 0];
+#pragma unroll
+      for (int r = 0; r < kGatherRows; ++r) {  // clamped row: always a valid address
+        const T* row = logits + (g0 + (r < nr ? r : nr - 1)) * V;
+        v[r][j] = (j == 0 || k <= L) ? to_f32<T>(__ldg(row + col)) * kLog2e : kNegInf;
       }
-    } else {
-      for (int k = lane; k <= L; k += 32) m = fmaxf(m, to_f32<T>(__ldg(row + slab[k])) * kLog2e);
     }
-    m = warp_max(m);
-    if (!(m > kNegInf && m < -kNegInf)) m = 0.f;  // all -inf / NaN rows: no centring
-    if (in_regs) {
 #pragma unroll
-      for (int j = 0; j < kGatherRegs; ++j) {
-        const int k = lane + 32 * j;
-        if (k <= L) er[k == 0 ? 0 : kEmLabel0 + k - 1] = v[j] - m;
+    for (int r = 0; r < kGatherRows; ++r) {
+#pragma unroll
+      for (int j = 0; j < kGatherRegs; ++j) m[r] = fmaxf(m[r], (lane + 32 * j <= L) ? v[r][j] : kNegInf);
+      m[r] = warp_max(m[r]);
+      if (!(m[r] > kNegInf && m[r] < -kNegInf)) m[r] = 0.f;  // all -inf / NaN rows: no centring
+    }
+#pragma unroll
+    for (int r = 0; r < kGatherRows; ++r) {
+      if (r < nr) {
+        float* er = em + (g0 + r) * Lp;
+#pragma unroll
+        for (int j = 0; j < kGatherRegs; ++j) {
+          const int k = lane + 32 * j;
+          if (k <= L) er[k == 0 ? 0 : kEmLabel0 + k - 1] = v[r][j] - m[r];
+        }
+        if (lane == 0) cmax[g0 + r] = m[r];
       }
-    } else {
+    }
+  } else {
+    for (int r = 0; r < nr; ++r) {
+      const T* row = logits + (g0 + r) * V;
+      float mm = kNegInf;
+      for (int k = lane; k <= L; k += 32) mm = fmaxf(mm, to_f32<T>(__ldg(row + slab[k])) * kLog2e);
+      mm = warp_max(mm);
+      if (!(mm > kNegInf && mm < -kNegInf)) mm = 0.f;
+      float* er = em + (g0 + r) * Lp;
       for (int k = lane; k <= L; k += 32)
-        er[k == 0 ? 0 : kEmLabel0 + k - 1] = to_f32<T>(__ldg(row + slab[k])) * kLog2e - m;
+        er[k == 0 ? 0 : kEmLabel0 + k - 1] = to_f32<T>(__ldg(row + slab[k])) * kLog2e - mm;
+      if (lane == 0) cmax[g0 + r] = mm;
     }
-    if (lane == 0) cmax[g] = m;
   }
 }
 
 template <typename T>
-static int launch_gather(const void* logits, int B, int Tfr, int V, const LossLayout& w,
+static int launch_gather(const void* logits, const PrepArgs& P, int B, const LossLayout& w,
                          unsigned char* ws, cudaStream_t st) {
-  const int fpc = 2 * kGatherWarps;
-  dim3 grid((Tfr + fpc - 1) / fpc, B);
-  const size_t smem = sizeof(int) * (size_t)(w.Lmax + 1);
-  gather_kernel<T><<<grid, kGatherWarps * 32, smem, st>>>(
-      static_cast<const T*>(logits), Tfr, V, reinterpret_cast<const UttInfo*>(ws + w.utt),
-      reinterpret_cast<const int*>(ws + w.lab), w.Lp, reinterpret_cast<float*>(ws + w.em),
-      reinterpret_cast<float*>(ws + w.cmax), fpc);
+  constexpr int fpc = kGatherWarps * kGatherRows;
+  int gx = (P.T + fpc - 1) / fpc;
+  if (gx < 1) gx = 1;  // the first CTA of every utterance also publishes the label prep
+  dim3 grid(gx, B);
+  const size_t smem = sizeof(int) * (size_t)w.Lp;
+  auto k = gather_kernel<T>;
+  if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  k<<<grid, kGatherWarps * 32, smem, st>>>(static_cast<const T*>(logits), P,
+                                           reinterpret_cast<float*>(ws + w.em),
+                                           reinterpret_cast<float*>(ws + w.cmax));
   count_launch();
   return check_launch("ctc gather");
 }
@@ -356,17 +392,25 @@ static int check_loss_args(const char* who, const void* logits, int dtype, const
   return B200CTC_OK;
 }
 
-static int launch_prep(const LossLayout& w, unsigned char* ws, const int64_t* targets,
-                       const int64_t* tgt_offsets, const int64_t* in_lens, const int64_t* tgt_lens,
-                       int blank, cudaStream_t st) {
+static PrepArgs make_prep_args(const LossLayout& w, unsigned char* ws, const int64_t* targets,
+                               const int64_t* tgt_offsets, const int64_t* in_lens,
+                               const int64_t* tgt_lens, int blank) {
+  PrepArgs P;
+  P.targets = targets; P.offs = tgt_offsets; P.in_lens = in_lens; P.tgt_lens = tgt_lens;
+  P.T = w.T; P.V = w.V; P.Lmax = w.Lmax; P.Lp = w.Lp; P.blank = blank;
+  P.utt = reinterpret_cast<UttInfo*>(ws + w.utt);
+  P.lab = reinterpret_cast<int*>(ws + w.lab);
+  P.dup = reinterpret_cast<int*>(ws + w.dup);
+  P.counter = reinterpret_cast<int*>(ws + w.counter);
+  return P;
+}
+
+static int launch_prep(const LossLayout& w, const PrepArgs& P, cudaStream_t st) {
   int nt = (w.Lmax + 1 + 31) / 32 * 32;
   if (nt < 64) nt = 64;
   if (nt > 1024) nt = 1024;
   prof_mark(0, 0, st);
-  prep_kernel<<<w.B, nt, sizeof(int) * (size_t)w.Lp, st>>>(
-      targets, tgt_offsets, in_lens, tgt_lens, w.T, w.V, w.Lmax, w.Lp, blank,
-      reinterpret_cast<UttInfo*>(ws + w.utt), reinterpret_cast<int*>(ws + w.lab),
-      reinterpret_cast<int*>(ws + w.dup), reinterpret_cast<int*>(ws + w.counter));
+  prep_kernel<<<w.B, nt, sizeof(int) * (size_t)w.Lp, st>>>(P);
   count_launch();
   prof_mark(0, 1, st);
   return check_launch("ctc prep");
@@ -424,7 +468,8 @@ extern "C" int b200ctc_loss_fwd(const void* logits, int dtype, const int64_t* ta
   if (rc || B == 0) return rc;
   unsigned char* ws = static_cast<unsigned char*>(ws_);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  rc = launch_prep(w, ws, targets, tgt_offsets, in_lens, tgt_lens, blank, st);
+  const PrepArgs P = make_prep_args(w, ws, targets, tgt_offsets, in_lens, tgt_lens, blank);
+  rc = launch_prep(w, P, st);
   if (rc) return rc;
   if (T > 0) {
     prof_mark(1, 0, st);
@@ -481,19 +526,20 @@ extern "C" int b200ctc_loss_fwd_grad(const void* logits, int dtype, const int64_
     prof_mark(3, 1, sd);
     cudaEventRecord(ev_join, sd);
   }
-  if (!rc) rc = launch_prep(w, ws, targets, tgt_offsets, in_lens, tgt_lens, blank, st);
+  const PrepArgs P = make_prep_args(w, ws, targets, tgt_offsets, in_lens, tgt_lens, blank);
   // B200CTC_FUSED_GATHER=1: the lattice's own producer warps gather the label
   // columns.  Opt-in: alpha and beta CTAs each fetch every frame, and the doubled
   // sparse-sector traffic (HBM serves 32-byte sectors at ~1/3 of streaming speed)
   // costs as much as the stand-alone gather kernel saves (profiles/README.md).
   const char* fg = getenv("B200CTC_FUSED_GATHER");
   const bool fused_gather = T > 0 && !sd && fg && fg[0] == '1';
-  if (!rc && T > 0 && !fused_gather) {
+  if (!rc && fused_gather) rc = launch_prep(w, P, st);
+  if (!rc && !fused_gather) {  // gather kernel with the label prep fused in
     prof_mark(1, 0, st);
     switch (dtype) {
-      case B200CTC_F32: rc = launch_gather<float>(logits, B, T, V, w, ws, st); break;
-      case B200CTC_F16: rc = launch_gather<__half>(logits, B, T, V, w, ws, st); break;
-      default: rc = launch_gather<__nv_bfloat16>(logits, B, T, V, w, ws, st); break;
+      case B200CTC_F32: rc = launch_gather<float>(logits, P, B, w, ws, st); break;
+      case B200CTC_F16: rc = launch_gather<__half>(logits, P, B, w, ws, st); break;
+      default: rc = launch_gather<__nv_bfloat16>(logits, P, B, w, ws, st); break;
     }
     prof_mark(1, 1, st);
   }
