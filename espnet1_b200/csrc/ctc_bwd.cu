@@ -46,15 +46,17 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
       pc.next();
     }
   };
+  griddep_launch();  // PDL: nll_kernel may queue up behind this grid
   if (TMA) {
     if (tid == 0) {
       for (int i = 0; i < nstage; ++i) mbar_init(&bars[i], 1);
       fence_mbar_init();
     }
     __syncthreads();
-    if (tid == 0)
-      for (int i = 0; i < nstage; ++i) issue_next();
   }
+  griddep_wait();  // utt / lattices / cmax come from the previous kernels
+  if (TMA && tid == 0)
+    for (int i = 0; i < nstage; ++i) issue_next();
 
   uint32_t n = 0;
   RowCursor rc;
@@ -245,7 +247,10 @@ static int launch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, 
   while ((1 << wshift) < 32 * w.R) ++wshift;
   auto go = [&](auto k) {
     cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k<<<(unsigned)grid, NT, smem, st>>>(
+    launch_pdl(
+        // (no PDL here: a persistent grid must not become resident piecemeal beside
+        //  the still-running lattice - late CTAs would form a second wave)
+        k, dim3((unsigned)grid), dim3(NT), smem, st, false,
         static_cast<const T*>(logits), static_cast<T*>(grad), B, Tfr, V, blank,
         reinterpret_cast<const UttInfo*>(ws + w.utt), reinterpret_cast<const int*>(ws + w.lab),
         reinterpret_cast<const int*>(ws + w.dup), w.Lp, w.Sp, w.NW, w.NB, wshift,

@@ -114,6 +114,7 @@ template <typename T>
 __global__ void __launch_bounds__(kGatherWarps * 32) gather_kernel(
     const T* __restrict__ logits, PrepArgs P, float* __restrict__ em, float* __restrict__ cmax) {
   extern __shared__ int slab[];  // [Lp] label columns of this utterance
+  griddep_launch();  // the lattice CTAs may become resident and set up meanwhile
   const int b = blockIdx.y;
   int Tb, L;
   prep_utterance(P, b, slab, blockIdx.x == 0, Tb, L);

@@ -358,6 +358,8 @@ __global__ void __launch_bounds__(R == 2 || R == 16 ? 640 : 1024, 1) lattice_ker
   // compute warps 0..NW-1; then the producer warp(s): one TMA issuer, or the gather warps
   const int NW = (blockDim.x >> 5) - (GATHER ? kGatherProducers : 1);
   const int b = blockIdx.x, dir = blockIdx.y;
+  griddep_launch();  // PDL: let the gradient row pass become resident behind us
+  griddep_wait();    // utt / lab / em come from the previous kernel
   const int Tb = utt[b].T, L = utt[b].L, S = 2 * L + 1;
   if (Tb == 0) {
     if (dir == 0 && tid == 0) {
@@ -496,6 +498,7 @@ __global__ void __launch_bounds__(256) nll_kernel(const UttInfo* __restrict__ ut
   __shared__ double dred[8];
   __shared__ int s_last;
   const int b = blockIdx.x, tid = threadIdx.x;
+  griddep_wait();
   const UttInfo u = utt[b];
   double part = 0.0;
   for (int t = tid; t < u.T; t += 256) {
@@ -547,14 +550,12 @@ static int launch_lattice_rk(const LossLayout& w, unsigned char* ws, int Tfr, in
   auto go = [&](auto k) {
     if (smem > 48 * 1024)
       cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k<<<grid, nt, smem, st>>>(reinterpret_cast<UttInfo*>(ws + w.utt),
-                              reinterpret_cast<const int*>(ws + w.lab), w.Lp,
-                              reinterpret_cast<const float*>(ws + w.em), gs,
-                              reinterpret_cast<float*>(ws + w.alpha),
-                              reinterpret_cast<float*>(ws + w.beta),
-                              reinterpret_cast<int*>(ws + w.offA),
-                              reinterpret_cast<int*>(ws + w.offB), Tfr, w.Sp, w.NW, w.NB,
-                              zero_infinity, nring);
+    launch_pdl(k, grid, dim3(nt), smem, st, true, reinterpret_cast<UttInfo*>(ws + w.utt),
+               reinterpret_cast<const int*>(ws + w.lab), w.Lp,
+               reinterpret_cast<const float*>(ws + w.em), gs,
+               reinterpret_cast<float*>(ws + w.alpha), reinterpret_cast<float*>(ws + w.beta),
+               reinterpret_cast<int*>(ws + w.offA), reinterpret_cast<int*>(ws + w.offB), Tfr, w.Sp,
+               w.NW, w.NB, zero_infinity, nring);
   };
   if (gsrc) go(lattice_kernel<R, true, K, true>);  // eager gradient mode only
   else if (both_dirs) go(lattice_kernel<R, true, K, false>);
@@ -595,11 +596,11 @@ static inline int launch_lattice(const LossLayout& w, unsigned char* ws, int Tfr
 
 static inline int launch_nll(const LossLayout& w, unsigned char* ws, int Tfr, int zero_infinity,
                              float* nll, float* loss_out, float loss_scale, cudaStream_t st) {
-  nll_kernel<<<w.B, 256, 0, st>>>(reinterpret_cast<const UttInfo*>(ws + w.utt),
-                                  reinterpret_cast<const float*>(ws + w.cmax),
-                                  reinterpret_cast<const float*>(ws + w.lse2), Tfr, zero_infinity,
-                                  nll, loss_out, loss_scale,
-                                  reinterpret_cast<int*>(ws + w.counter));
+  launch_pdl(nll_kernel, dim3(w.B), dim3(256), 0, st, true,
+             reinterpret_cast<const UttInfo*>(ws + w.utt),
+             reinterpret_cast<const float*>(ws + w.cmax),
+             reinterpret_cast<const float*>(ws + w.lse2), Tfr, zero_infinity, nll, loss_out,
+             loss_scale, reinterpret_cast<int*>(ws + w.counter));
   count_launch();
   return check_launch("ctc nll");
 }
