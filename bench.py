@@ -56,6 +56,17 @@ def peaks():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, per launch, from the
+    committed `ncu --set full` capture (profiles/grad_rows_traffic.json); None if absent."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "grad_rows_traffic.json")) as f:
+            d = json.load(f)
+        return float(d["dram_bytes_read"]) + float(d["dram_bytes_write"])
+    except Exception:
+        return None
+
+
 class ClockSampler(threading.Thread):
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
@@ -256,10 +267,14 @@ def run_gpu(args):
     sampler = ClockSampler(local)
     sampler.start()
     _lib.reset_launch_count()
-    L.b200ctc_profile_enable(1)
     ms = time_region(step, args.steps, dist_on, dev)
-    L.b200ctc_profile_enable(0)
     launches = _lib.launch_count() * world
+    # per-kernel durations: the same steps again with CUDA events recorded around every
+    # library launch on its own stream (kept out of the headline region: the extra
+    # event records cost ~25 us per step)
+    L.b200ctc_profile_enable(1)
+    time_region(step, max(3, min(args.steps, 20)), dist_on, dev)
+    L.b200ctc_profile_enable(0)
     pm = (ctypes.c_float * 8)()
     pc = (ctypes.c_int * 8)()
     L.b200ctc_profile_read(pm, pc, 8)
@@ -313,10 +328,11 @@ def run_gpu(args):
         "roofline": {"bound": "hbm", "kernel": "grad_rows_kernel (pass B: softmax - occupancy, written once)",
                      "achieved": alg / (gr_ms * 1e-3) / 1e9 if gr_ms else None, "peak": peak,
                      "unit": "GB/s", "frac": (alg / (gr_ms * 1e-3) / 1e9 / peak) if gr_ms else None,
-                     "traffic": None, "peak_source": peak_src,
+                     "traffic": ncu_traffic(), "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg,
-                     "note": "achieved = SURVEY 8(d) algorithmic bytes of the whole fwd+bwd step / "
-                             "duration of the dominant kernel; 'step' below divides by the whole step"},
+                     "note": "grad_rows_kernel's own algorithmic bytes = read logits + write grad + "
+                             "read alpha,beta = 4*B*T*(2V+2S), the SURVEY 8(d) figure; 'roofline_step' "
+                             "divides the same bytes by the whole step"},
         "roofline_step": {"achieved": alg / (ms * 1e-3) / 1e9, "frac": alg / (ms * 1e-3) / 1e9 / peak,
                           "frac_of_8TBps_nominal": alg / (ms * 1e-3) / 8e12},
         "kernel_ms": phases,
