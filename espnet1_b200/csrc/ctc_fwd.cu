@@ -528,14 +528,7 @@ extern "C" int b200ctc_loss_fwd_grad(const void* logits, int dtype, const int64_
     cudaEventRecord(ev_join, sd);
   }
   const PrepArgs P = make_prep_args(w, ws, targets, tgt_offsets, in_lens, tgt_lens, blank);
-  // B200CTC_FUSED_GATHER=1: the lattice's own producer warps gather the label
-  // columns.  Opt-in: alpha and beta CTAs each fetch every frame, and the doubled
-  // sparse-sector traffic (HBM serves 32-byte sectors at ~1/3 of streaming speed)
-  // costs as much as the stand-alone gather kernel saves (profiles/README.md).
-  const char* fg = getenv("B200CTC_FUSED_GATHER");
-  const bool fused_gather = T > 0 && !sd && fg && fg[0] == '1';
-  if (!rc && fused_gather) rc = launch_prep(w, P, st);
-  if (!rc && !fused_gather) {  // gather kernel with the label prep fused in
+  if (!rc) {  // gather kernel with the label prep fused in
     prof_mark(1, 0, st);
     switch (dtype) {
       case B200CTC_F32: rc = launch_gather<float>(logits, P, B, w, ws, st); break;
@@ -545,9 +538,8 @@ extern "C" int b200ctc_loss_fwd_grad(const void* logits, int dtype, const int64_
     prof_mark(1, 1, st);
   }
   if (!rc) {
-    GatherSrc gsrc{logits, reinterpret_cast<float*>(ws + w.cmax), dtype, V};
     prof_mark(2, 0, st);
-    rc = launch_lattice(w, ws, T, zero_infinity, 1, st, fused_gather ? &gsrc : nullptr);
+    rc = launch_lattice(w, ws, T, zero_infinity, 1, st);
     prof_mark(2, 1, st);
   }
   if (sd) {  // join (always, also on error: the caller's stream must cover the side work)

@@ -26,7 +26,7 @@ namespace b200ctc {
 constexpr int kMaxLattice = 8192;  // 2*L+1 <= 8192  (R = 16, 16 warps + producer)
 constexpr int kValRing = 64;       // boundary values in flight between adjacent warps (steps)
 constexpr int kFRing = 2 * kValRing / kRenormEvery;  // frame offsets, one per renorm block
-constexpr int kMaxEmRing = 8;      // chunks of emission frames in flight
+constexpr int kMaxEmRing = 20;     // chunks of emission frames in flight
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -48,6 +48,15 @@ __device__ __forceinline__ float lse3_fast(float a, float b, float c, float e) {
   const float m = fmaxf(fmaxf(a, b), c);
   const float s = ex2(a - m) + ex2(b - m) + ex2(c - m);
   return (m + e) + lg2(s);
+}
+
+// same with 3 MUFU (the largest term is exactly 1): for wide lattices, which are
+// MUFU-throughput-bound rather than latency-bound
+__device__ __forceinline__ float lse3_lean(float a, float b, float c, float e) {
+  const float hi = fmaxf(a, b), lo = fminf(a, b);
+  const float m = fmaxf(hi, c), t = fminf(hi, c);
+  const float mid = fmaxf(lo, t), mn = fminf(lo, t);
+  return (m + e) + lg2(1.f + ex2(mid - m) + ex2(mn - m));
 }
 
 // raw 32-bit shared-memory addressing for the serial loop (no generic->shared
@@ -83,6 +92,28 @@ __device__ __forceinline__ float lds_f32_u32(uint32_t addr) {
   asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
   return v;
 }
+// emission ring reads: ordered after the mbarrier wait (volatile asm), plain ld.shared
+__device__ __forceinline__ float lds_em(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void mbar_wait_u32(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_u32(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
 // make a loop-invariant value opaque so that it is kept in a register instead
 // of being re-derived inside the serial loop
 __device__ __forceinline__ uint32_t pin(uint32_t v) {
@@ -100,39 +131,47 @@ struct LatticeArgs {
   uint32_t fring;     // shared: frame offsets    [NW][kFRing]  int
   uint32_t ready;     // shared: steps published  [NW] int
   uint32_t cons;      // shared: steps consumed   [NW] int
-  uint64_t* full;
-  uint64_t* empty;
+  uint32_t full;      // shared: full[kMaxEmRing] mbarriers, then empty[kMaxEmRing]
   int Tb, L, Lp, Sp, NWp, nw_live, zero_infinity, b, nring;
 };
 
 // One compute warp of the systolic lattice (see the file header).  This is the
 // serial chain of the whole loss: one warp per SM sub-partition with a single
-// step in flight, so every instruction costs issue latency.  Branch-free
-// arithmetic (finite kLogZero, step 0 is an ordinary step started from a virtual
-// alpha_{-1}(0) = log 1), compile-time direction, blocks of K straight-line steps.
+// step in flight, so every instruction on the chain costs its full latency and
+// everything else is moved off it:
+//  * branch-free arithmetic (finite kLogZero; step 0 is an ordinary step started
+//    from a virtual alpha_{-1}(0) = log 1; positions beyond the lattice compute
+//    finite don't-care values and are masked only where they could be observed:
+//    the re-centring maximum and the final read-out),
+//  * compile-time direction, full blocks of K steps as straight-line code with the
+//    block's emissions and upstream boundary values already in registers,
+//  * all hand-shaking once per block, ring slots by increment (no div / mod).
 template <int R, bool STORE, int DIR, int K>
 __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int lane) {
   static_assert(K == 4 || K == 8, "block of 4 or 8 steps");
+  constexpr bool kPre = R <= 4;  // whole block's emissions preloaded into registers
   const int Tb = A.Tb, L = A.L, S = 2 * L + 1, Lp = A.Lp;
   const int sp0 = (w * 32 + lane) * R;  // first recursion position of this thread
   // static description of this thread's positions: q even = blank, q odd = label
   uint32_t jlab[R / 2];  // byte offset of the label emission inside an em row
   bool skip[R / 2];      // may the path skip the blank in front of this label?
-  bool act[R];
+  {
+    int la[R / 2], ln[R / 2];
+    bool ok[R / 2];
 #pragma unroll
-  for (int q = 0; q < R; ++q) act[q] = sp0 + q < S;
-#pragma unroll
-  for (int h = 0; h < R / 2; ++h) {
-    const int sp = sp0 + 2 * h + 1;
-    const int s = DIR ? S - 1 - sp : sp;
-    const int k = (s + 1) >> 1;  // 1..L when active
-    bool sk = false;
-    if (sp < S) {
-      if (DIR == 0) sk = (k >= 2) && (A.lb[k] != A.lb[k - 1]);
-      else sk = (k + 1 <= L) && (A.lb[k] != A.lb[k + 1]);
+    for (int h = 0; h < R / 2; ++h) {  // unconditional clamped loads: one global latency in all
+      const int sp = sp0 + 2 * h + 1;
+      const int s = DIR ? S - 1 - sp : sp;
+      const int k = (s + 1) >> 1;  // 1..L when active
+      const int kn = DIR ? k + 1 : k - 1;
+      const bool valid = sp < S;
+      ok[h] = valid && (DIR ? kn <= L : kn >= 1);
+      la[h] = A.lb[valid ? k : 0];
+      ln[h] = A.lb[ok[h] ? kn : 0];
+      jlab[h] = pin(valid ? 4u * (uint32_t)(kEmLabel0 + k - 1) : 0u);  // dead: the blank column
     }
-    skip[h] = sk;
-    jlab[h] = pin(4u * (uint32_t)(kEmLabel0 + ((sp < S) ? k - 1 : 0)));
+#pragma unroll
+    for (int h = 0; h < R / 2; ++h) skip[h] = ok[h] && la[h] != ln[h];
   }
   const bool has_up = w > 0, has_down = w + 1 < A.nw_live;
   const bool lane0 = lane == 0;
@@ -148,6 +187,7 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
   const uint32_t cons_down = pin(A.cons + 4u * (uint32_t)(has_down ? w + 1 : w));
   const uint32_t row_bytes = pin(4u * (uint32_t)Lp);
   const uint32_t chunk_bytes = pin(4u * (uint32_t)(K * Lp));
+  const uint32_t bar_end = pin(A.full + 8u * (uint32_t)A.nring);
 
   // walking pointers (frames ascend for alpha, descend for beta)
   const int t0 = DIR ? Tb - 1 : 0;
@@ -167,39 +207,63 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
   if (sp0 == 0) a[0] = 0.f;  // virtual alpha_{-1}(0) = log 1
   int F = 0;       // integer frame offset of a[] (ctc_ws.cuh)
   int Dpend = 0;   // re-centring shift measured at the end of the previous renorm block
-  int Fup = 0;     // upstream warp's current frame offset
+  int Fup = 0;     // upstream warp's frame offset in the current renorm block
+  float adj = 0.f; // Fup - F: upstream frame -> my frame
   int ready_seen = 0, cons_seen = 0;
+  uint32_t slot_addr = A.ring, full_addr = A.full, phase = 0;
 
-  const int nblk = (Tb + K - 1) / K;
-  for (int c = 0; c < nblk; ++c) {
-    const int i0 = c * K;
+  // one recursion step: emissions eb (blank) / el[] (labels), p1 = value of position
+  // sp0-1 after the previous step in MY frame (one neighbour value per thread: R is
+  // even, so sp0 is a blank and needs only sp0-1, and the label at sp0+1 takes its
+  // skip transition from sp0-1 as well); the new a[R-1] goes to slot `out`.
+  auto step = [&](float eb, const float (&el)[R / 2], float upv, uint32_t out) {
+    float p1 = __shfl_up_sync(0xffffffffu, a[R - 1], 1);
+    p1 = lane0 ? upv : p1;
+    float nw_[R];
+#pragma unroll
+    for (int q = 0; q < R; ++q) {
+      const float x0 = a[q];
+      const float x1 = q >= 1 ? a[q - 1] : p1;
+      if (q & 1) {
+        const float x2r = q >= 2 ? a[q - 2] : p1;
+        const float x2 = skip[q >> 1] ? x2r : kLogZero;
+        nw_[q] = R >= 8 ? lse3_lean(x0, x1, x2, el[q >> 1]) : lse3_fast(x0, x1, x2, el[q >> 1]);
+      } else {
+        nw_[q] = lse2_fast(x0, x1, eb);
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < R; ++q) a[q] = nw_[q];
+    if (pub) sts_f32_u32(out, a[R - 1]);
+    if (store_ok) {
+      if (R == 2) {
+        *reinterpret_cast<float2*>(lat_p) = make_float2(a[0], a[1]);
+      } else {
+#pragma unroll
+        for (int q = 0; q < R; q += 4)
+          *reinterpret_cast<float4*>(lat_p + q) = make_float4(a[q], a[q + 1], a[q + 2], a[q + 3]);
+      }
+    }
+    lat_p += lat_step;
+  };
+
+  for (int i0 = 0; i0 < Tb; i0 += K) {
     const int n = (Tb - i0 < K) ? Tb - i0 : K;
-    const int slot = c % A.nring;
-    uint32_t erow = A.ring + (uint32_t)slot * chunk_bytes + (DIR ? (uint32_t)(n - 1) * row_bytes : 0u);
     // ---------------- block prologue: all hand-shaking happens here, once per K steps
-    const bool renorm_apply = (i0 & (kRenormEvery - 1)) == 0;
-    const int D = renorm_apply ? Dpend : 0;
-    const float shift = (float)D;
+    const uint32_t vb = vals_in + ((uint32_t)i0 & (kValRing - 1)) * 4u;
     float up[K];
 #pragma unroll
     for (int u = 0; u < K; ++u) up[u] = kLogZero;
-    float adj0 = 0.f, adj = 0.f;
     if (has_up) {
       // value of step j sits in slot (j+1) & 63: this block needs steps i0-1 .. i0+K-2
       const int need = (i0 + K - 1 < Tb - 1) ? i0 + K - 1 : Tb - 1;
       while (ready_seen < need) ready_seen = lds_acquire_i32(ready_in);
-      const uint32_t vb = vals_in + ((uint32_t)i0 & (kValRing - 1)) * 4u;
       const float4 v0 = lds_v4_u32(vb);
       up[0] = v0.x; up[1] = v0.y; up[2] = v0.z; up[3] = v0.w;
       if (K == 8) {
         const float4 v1 = lds_v4_u32(vb + 16u);
         up[K - 4] = v1.x; up[K - 3] = v1.y; up[K - 2] = v1.z; up[K - 1] = v1.w;
       }
-      const int Fprev = lds_i32_u32(fr_in + (((uint32_t)((i0 - 1) >> 4)) & (kFRing - 1)) * 4u);
-      Fup = lds_i32_u32(fr_in + (((uint32_t)(i0 >> 4)) & (kFRing - 1)) * 4u);
-      adj0 = (float)(Fprev - F);     // step i0 still adds to my old frame (then -shift)
-      adj = (float)(Fup - (F + D));  // later steps of the block
-      if (lane0) sts_i32_u32(cons_mine, i0 + K);
     }
     if (has_down) {
       // my slots of this block last held steps i0-64 ..: the consumer read them in the
@@ -207,73 +271,92 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
       const int needc = i0 + 2 * K - kValRing;
       while (cons_seen < needc) cons_seen = lds_i32_u32(cons_down);
     }
-    if (renorm_apply) {
-      F += D;
+    float shift = 0.f, adj0 = adj;
+    if ((i0 & (kRenormEvery - 1)) == 0) {  // first block of a renorm block: apply the shift
+      const int D = Dpend;
       Dpend = 0;
+      shift = (float)D;
+      if (has_up) {
+        const int Fprev = lds_i32_u32(fr_in + (((uint32_t)((i0 - 1) >> 4)) & (kFRing - 1)) * 4u);
+        Fup = lds_i32_u32(fr_in + (((uint32_t)(i0 >> 4)) & (kFRing - 1)) * 4u);
+        adj0 = (float)(Fprev - F);     // step i0 still adds to my old frame (then -shift)
+        adj = (float)(Fup - (F + D));  // all later steps of the renorm block
+      }
+      F += D;
       if (pub) sts_i32_u32(fr_out + (((uint32_t)(i0 >> 4)) & (kFRing - 1)) * 4u, F);
       if (STORE) {
         if (store_off) *off_p = F;
         off_p += A.NWp;
       }
     }
-    const uint32_t ob0 = vals_out + (((uint32_t)i0 & (kValRing - 1)) + 1u) * 4u;  // slots of steps i0..i0+K-2
-    const uint32_t ob1 = vals_out + ((uint32_t)(i0 + K) & (kValRing - 1)) * 4u;    // slot of step i0+K-1
-    mbar_wait(&A.full[slot], (c / A.nring) & 1);
-    // ---------------- K straight-line steps
+    if (has_up && lane0) sts_i32_u32(cons_mine, i0 + K);  // up[] and the frame offsets are read
+    const uint32_t ob0 = vals_out + (((uint32_t)i0 & (kValRing - 1)) + 1u) * 4u;  // steps i0..i0+K-2
+    const uint32_t ob1 = vals_out + ((uint32_t)(i0 + K) & (kValRing - 1)) * 4u;    // step i0+K-1
+    mbar_wait_u32(full_addr, phase);
+    if (n == K) {
+      // ---------------- K straight-line steps
+      uint32_t erow = slot_addr + (DIR ? (uint32_t)(K - 1) * row_bytes : 0u);
+      float ebv[kPre ? K : 1], elv[kPre ? K : 1][R / 2];
+      if (kPre) {
 #pragma unroll
-    for (int u = 0; u < K; ++u) {
-      if (u < n) {
-        float eb = lds_f32_u32(erow);
-        float el[R / 2];
+        for (int u = 0; u < K; ++u) {
+          ebv[u] = lds_em(erow);
 #pragma unroll
-        for (int h = 0; h < R / 2; ++h) el[h] = lds_f32_u32(erow + jlab[h]);
+          for (int h = 0; h < R / 2; ++h) elv[u][h] = lds_em(erow + jlab[h]);
+          if (DIR) erow -= row_bytes; else erow += row_bytes;
+        }
+        __syncwarp();
+        if (lane0) mbar_arrive_u32(full_addr + 8u * kMaxEmRing);  // empty[slot]: values are in registers
+      }
+#pragma unroll
+      for (int u = 0; u < K; ++u) {
+        float eb, el[R / 2];
+        if (kPre) {
+          eb = ebv[u];
+#pragma unroll
+          for (int h = 0; h < R / 2; ++h) el[h] = elv[u][h];
+        } else {
+          eb = lds_em(erow);
+#pragma unroll
+          for (int h = 0; h < R / 2; ++h) el[h] = lds_em(erow + jlab[h]);
+          if (DIR) erow -= row_bytes; else erow += row_bytes;
+        }
         if (u == 0) {
           eb -= shift;
 #pragma unroll
           for (int h = 0; h < R / 2; ++h) el[h] -= shift;
         }
-        if (DIR) erow -= row_bytes; else erow += row_bytes;
-        // value of position sp0-1 after the previous step, in MY frame (one neighbour
-        // value per thread: R is even, so sp0 is a blank and needs only sp0-1, and the
-        // label at sp0+1 takes its skip transition from sp0-1 as well)
-        float p1 = __shfl_up_sync(0xffffffffu, a[R - 1], 1);
-        p1 = lane0 ? up[u] + (u == 0 ? adj0 : adj) : p1;
-        float nw_[R];
-#pragma unroll
-        for (int q = 0; q < R; ++q) {
-          const float x0 = a[q];
-          const float x1 = q >= 1 ? a[q - 1] : p1;
-          float v;
-          if (q & 1) {
-            const float x2r = q >= 2 ? a[q - 2] : p1;
-            const float x2 = skip[q >> 1] ? x2r : kLogZero;
-            v = lse3_fast(x0, x1, x2, el[q >> 1]);
-          } else {
-            v = lse2_fast(x0, x1, eb);
-          }
-          nw_[q] = act[q] ? v : kLogZero;
-        }
-#pragma unroll
-        for (int q = 0; q < R; ++q) a[q] = nw_[q];
-        if (pub) sts_f32_u32(u == K - 1 ? ob1 : ob0 + 4u * u, a[R - 1]);
-        if (store_ok) {
-          if (R == 2) {
-            *reinterpret_cast<float2*>(lat_p) = make_float2(a[0], a[1]);
-          } else {
-#pragma unroll
-            for (int q = 0; q < R; q += 4)
-              *reinterpret_cast<float4*>(lat_p + q) = make_float4(a[q], a[q + 1], a[q + 2], a[q + 3]);
-          }
-        }
-        lat_p += lat_step;
+        step(eb, el, up[u] + (u == 0 ? adj0 : adj), u == K - 1 ? ob1 : ob0 + 4u * u);
       }
+      if (!kPre) {
+        __syncwarp();
+        if (lane0) mbar_arrive_u32(full_addr + 8u * kMaxEmRing);
+      }
+    } else {
+      // ---------------- the last, partial block (at most once per utterance)
+      uint32_t erow = slot_addr + (DIR ? (uint32_t)(n - 1) * row_bytes : 0u);
+#pragma unroll 1
+      for (int u = 0; u < n; ++u) {
+        float eb = lds_em(erow), el[R / 2];
+#pragma unroll
+        for (int h = 0; h < R / 2; ++h) el[h] = lds_em(erow + jlab[h]);
+        if (DIR) erow -= row_bytes; else erow += row_bytes;
+        const float sh = u == 0 ? shift : 0.f;
+        eb -= sh;
+#pragma unroll
+        for (int h = 0; h < R / 2; ++h) el[h] -= sh;
+        const float upv = has_up ? lds_f32_u32(vb + 4u * u) + (u == 0 ? adj0 : adj) : kLogZero;
+        step(eb, el, upv, ob0 + 4u * u);  // u <= K-2: no wrap
+      }
+      __syncwarp();
+      if (lane0) mbar_arrive_u32(full_addr + 8u * kMaxEmRing);
     }
     // ---------------- block epilogue
     if (pub) sts_release_i32(ready_out, i0 + n);
     if ((i0 & (kRenormEvery - 1)) == kRenormEvery - K && n == K) {
-      float m = a[0];
+      float m = kLogZero;
 #pragma unroll
-      for (int q = 1; q < R; ++q) m = fmaxf(m, a[q]);
+      for (int q = 0; q < R; ++q) m = fmaxf(m, sp0 + q < S ? a[q] : kLogZero);
       m = warp_max(m);
       // nothing alive yet: adopt the upstream warp's frame so that the first real
       // values to arrive are already centred.  (Clamped: a pathological -1e10
@@ -282,8 +365,9 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
       Dpend = (m > kLogZeroTest) ? (int)rintf(fminf(fmaxf(m, -1048576.f), 1048576.f))
                                  : (has_up ? Fup - F : 0);
     }
-    __syncwarp();
-    if (lane0) mbar_arrive(&A.empty[slot]);
+    slot_addr += chunk_bytes;
+    full_addr += 8u;
+    if (full_addr == bar_end) { slot_addr = A.ring; full_addr = A.full; phase ^= 1u; }
   }
 
   // ---- epilogue: log-likelihood from the last two positions (alpha only)
@@ -319,44 +403,18 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
   }
 }
 
-struct GatherSrc {      // GATHER mode: the producer warps read the logits directly
-  const void* logits;   // (B, Tfr, V)
-  float* cmax;          // (B, Tfr) per-frame constant, written by the alpha CTA
-  int dtype, V;
-};
-
-constexpr int kGatherProducers = 4;  // producer warps in GATHER mode (alternating chunks)
-constexpr int kGatherTile = 5;       // label columns per lane and pass (160 per warp)
-
-template <typename T, int K>
-__device__ __forceinline__ void gather_tile(const void* logits, size_t row_first, int n, int V,
-                                            const int (&col)[kGatherTile],
-                                            float (&v)[K][kGatherTile]) {
-  const T* base = static_cast<const T*>(logits);
-  T raw[K][kGatherTile];
-#pragma unroll
-  for (int f = 0; f < K; ++f) {
-    const T* row = base + (row_first + (f < n ? f : n - 1)) * (size_t)V;
-#pragma unroll
-    for (int j = 0; j < kGatherTile; ++j) raw[f][j] = __ldg(row + (col[j] >= 0 ? col[j] : 0));
-  }
-#pragma unroll
-  for (int f = 0; f < K; ++f)
-#pragma unroll
-    for (int j = 0; j < kGatherTile; ++j) v[f][j] = to_f32<T>(raw[f][j]) * kLog2e;
-}
-
-template <int R, bool STORE, int K, bool GATHER>
-__global__ void __launch_bounds__(R == 2 || R == 16 ? 640 : 1024, 1) lattice_kernel(
+template <int R, bool STORE, int K>
+__global__ void __launch_bounds__(544, 1) lattice_kernel(
     UttInfo* __restrict__ utt, const int* __restrict__ lab, int Lp, const float* __restrict__ em,
-    GatherSrc gs, float* __restrict__ alpha, float* __restrict__ beta, int* __restrict__ offA,
+    float* __restrict__ alpha, float* __restrict__ beta, int* __restrict__ offA,
     int* __restrict__ offB, int Tfr, int Sp, int NWp, int NB, int zero_infinity, int nring) {
   static_assert(R % 2 == 0, "R must be even: even recursion positions are blanks");
   extern __shared__ __align__(128) float lsm[];  // em ring [nring][K*Lp] | vals | fring | ready | cons
-  __shared__ __align__(8) uint64_t full[kMaxEmRing], empty[kMaxEmRing];
+  __shared__ __align__(8) uint64_t bars[2 * kMaxEmRing];  // full[], empty[]
+  uint64_t* const full = bars;
+  uint64_t* const empty = bars + kMaxEmRing;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  // compute warps 0..NW-1; then the producer warp(s): one TMA issuer, or the gather warps
-  const int NW = (blockDim.x >> 5) - (GATHER ? kGatherProducers : 1);
+  const int NW = (blockDim.x >> 5) - 1;  // compute warps; warp NW is the TMA producer
   const int b = blockIdx.x, dir = blockIdx.y;
   griddep_launch();  // PDL: let the gradient row pass become resident behind us
   griddep_wait();    // utt / lab / em come from the previous kernel
@@ -381,87 +439,27 @@ __global__ void __launch_bounds__(R == 2 || R == 16 ? 640 : 1024, 1) lattice_ker
   const float* emb = em + (size_t)b * Tfr * Lp;
 
   if (tid == 0) {
-    for (int i = 0; i < nring; ++i) {
-      mbar_init(&full[i], GATHER ? 32 : 1);
-      mbar_init(&empty[i], nw_live);
-    }
+    for (int i = 0; i < nring; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], nw_live); }
     fence_mbar_init();
   }
   for (int i = tid; i < NW * kValRing; i += blockDim.x) vals[i] = kLogZero;
   for (int i = tid; i < NW * (kFRing + 2); i += blockDim.x) fring[i] = 0;  // fring, ready, cons
   __syncthreads();
 
-  // ------------------------------------------------------------ producer warp(s)
-  if (wid >= NW) {
-    const int nchunks = (Tb + K - 1) / K;
-    if (!GATHER) {
-      // TMA: the emissions were gathered into `em` by an earlier kernel
-      if (lane == 0) {
-        for (int c = 0; c < nchunks; ++c) {
-          const int slot = c % nring, round = c / nring;
-          if (round > 0) mbar_wait(&empty[slot], (round - 1) & 1);
-          const int i0 = c * K;
-          const int n = (Tb - i0 < K) ? Tb - i0 : K;
-          const int f0 = dir ? Tb - i0 - n : i0;  // first frame of the (contiguous) block
-          const uint32_t bytes = (uint32_t)n * Lp * 4u;
-          mbar_expect_tx(&full[slot], bytes);
-          bulk_g2s(ring + (size_t)slot * chunk_elems, emb + (size_t)f0 * Lp, bytes, &full[slot]);
-        }
+  // ------------------------------------------------------------ TMA producer warp
+  if (wid == NW) {
+    if (lane == 0) {
+      const int nchunks = (Tb + K - 1) / K;
+      for (int c = 0; c < nchunks; ++c) {
+        const int slot = c % nring, round = c / nring;
+        if (round > 0) mbar_wait(&empty[slot], (round - 1) & 1);
+        const int i0 = c * K;
+        const int n = (Tb - i0 < K) ? Tb - i0 : K;
+        const int f0 = dir ? Tb - i0 - n : i0;  // first frame of the (contiguous) block
+        const uint32_t bytes = (uint32_t)n * Lp * 4u;
+        mbar_expect_tx(&full[slot], bytes);
+        bulk_g2s(ring + (size_t)slot * chunk_elems, emb + (size_t)f0 * Lp, bytes, &full[slot]);
       }
-      return;
-    }
-    // GATHER: read the label columns of the logits straight into the ring.  The
-    // lattice is latency-bound and leaves HBM idle, so the sparse gather (L+1
-    // scattered sectors per frame, issued K frames x kGatherTile columns deep) costs
-    // no extra time.  Per-frame constant c[t] = the blank's score (any constant
-    // cancels, ctc_ws.cuh), so one shuffle replaces a reduction.
-    const int* lb = lab + (size_t)b * Lp;
-    const size_t row0 = (size_t)b * Tfr;
-    const int ntiles = (L + 1 + 32 * kGatherTile - 1) / (32 * kGatherTile);
-    for (int c = wid - NW; c < nchunks; c += kGatherProducers) {
-      const int slot = c % nring, round = c / nring;
-      if (round > 0) mbar_wait(&empty[slot], (round - 1) & 1);
-      const int i0 = c * K;
-      const int n = (Tb - i0 < K) ? Tb - i0 : K;
-      const int f0 = dir ? Tb - i0 - n : i0;
-      float* dst = ring + (size_t)slot * chunk_elems;
-      float cf[K];
-      for (int tile = 0; tile < ntiles; ++tile) {
-        int col[kGatherTile];
-#pragma unroll
-        for (int j = 0; j < kGatherTile; ++j) {
-          const int k = (tile * kGatherTile + j) * 32 + lane;
-          col[j] = k <= L ? lb[k] : -1;
-        }
-        // K x kGatherTile independent loads in flight per lane: unconditional, with
-        // clamped (always valid) addresses, so that nothing serialises them
-        float v[K][kGatherTile];
-        if (gs.dtype == B200CTC_F32)
-          gather_tile<float, K>(gs.logits, row0 + f0, n, gs.V, col, v);
-        else if (gs.dtype == B200CTC_F16)
-          gather_tile<__half, K>(gs.logits, row0 + f0, n, gs.V, col, v);
-        else
-          gather_tile<__nv_bfloat16, K>(gs.logits, row0 + f0, n, gs.V, col, v);
-        if (tile == 0) {
-#pragma unroll
-          for (int f = 0; f < K; ++f) {
-            float c0 = __shfl_sync(0xffffffffu, v[f][0], 0);  // k = 0: the blank
-            if (!(c0 > kNegInf && c0 < -kNegInf)) c0 = 0.f;   // -inf / NaN blank: no centring
-            cf[f] = c0;
-            if (dir == 0 && lane == 0 && f < n) gs.cmax[row0 + f0 + f] = c0;
-          }
-        }
-#pragma unroll
-        for (int f = 0; f < K; ++f) {
-#pragma unroll
-          for (int j = 0; j < kGatherTile; ++j) {
-            const int k = (tile * kGatherTile + j) * 32 + lane;
-            if (f < n && col[j] >= 0)
-              dst[(size_t)f * Lp + (k == 0 ? 0 : kEmLabel0 + k - 1)] = v[f][j] - cf[f];
-          }
-        }
-      }
-      mbar_arrive(&full[slot]);  // 32 arrivals (release) complete the phase
     }
     return;
   }
@@ -477,8 +475,7 @@ __global__ void __launch_bounds__(R == 2 || R == 16 ? 640 : 1024, 1) lattice_ker
   A.fring = smem_u32(fring);
   A.ready = smem_u32(ready);
   A.cons = smem_u32(cons);
-  A.full = full;
-  A.empty = empty;
+  A.full = smem_u32(full);
   A.Tb = Tb; A.L = L; A.Lp = Lp; A.Sp = Sp; A.NWp = NWp;
   A.nw_live = nw_live; A.zero_infinity = zero_infinity; A.b = b; A.nring = nring;
   if (dir == 0) lattice_warp<R, STORE, 0, K>(A, wid, lane);
@@ -542,55 +539,54 @@ __global__ void __launch_bounds__(256) nll_kernel(const UttInfo* __restrict__ ut
 
 template <int R, int K>
 static int launch_lattice_rk(const LossLayout& w, unsigned char* ws, int Tfr, int zero_infinity,
-                             int both_dirs, int nring, size_t smem, const GatherSrc* gsrc,
-                             cudaStream_t st) {
-  const int nt = (w.NW + (gsrc ? kGatherProducers : 1)) * 32;
-  GatherSrc gs = gsrc ? *gsrc : GatherSrc{nullptr, nullptr, 0, 0};
+                             int both_dirs, int nring, size_t smem, cudaStream_t st) {
+  const int nt = (w.NW + 1) * 32;  // + the TMA producer warp
   dim3 grid(w.B, both_dirs ? 2 : 1);
   auto go = [&](auto k) {
     if (smem > 48 * 1024)
       cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     launch_pdl(k, grid, dim3(nt), smem, st, true, reinterpret_cast<UttInfo*>(ws + w.utt),
                reinterpret_cast<const int*>(ws + w.lab), w.Lp,
-               reinterpret_cast<const float*>(ws + w.em), gs,
-               reinterpret_cast<float*>(ws + w.alpha), reinterpret_cast<float*>(ws + w.beta),
-               reinterpret_cast<int*>(ws + w.offA), reinterpret_cast<int*>(ws + w.offB), Tfr, w.Sp,
-               w.NW, w.NB, zero_infinity, nring);
+               reinterpret_cast<const float*>(ws + w.em), reinterpret_cast<float*>(ws + w.alpha),
+               reinterpret_cast<float*>(ws + w.beta), reinterpret_cast<int*>(ws + w.offA),
+               reinterpret_cast<int*>(ws + w.offB), Tfr, w.Sp, w.NW, w.NB, zero_infinity, nring);
   };
-  if (gsrc) go(lattice_kernel<R, true, K, true>);  // eager gradient mode only
-  else if (both_dirs) go(lattice_kernel<R, true, K, false>);
-  else go(lattice_kernel<R, false, K, false>);
+  if (both_dirs) go(lattice_kernel<R, true, K>);
+  else go(lattice_kernel<R, false, K>);
   count_launch();
   return check_launch("ctc lattice");
 }
 
 template <int R>
 static int launch_lattice_r(const LossLayout& w, unsigned char* ws, int Tfr, int zero_infinity,
-                            int both_dirs, const GatherSrc* gsrc, cudaStream_t st) {
-  // shared memory: em ring of nring chunks of K frames + the per-warp hand-off rings
+                            int both_dirs, cudaStream_t st) {
+  // shared memory: em ring of nring chunks of K frames + the per-warp hand-off rings.
+  // Warp w+1 runs one block behind warp w, so the ring must span NW+1 blocks or the
+  // first warp stalls on the last one (make_loss_layout picks R accordingly).
+  B2_REQUIRE(w.NW <= 16, "ctc lattice: target too long (more than 16 warps of 32 positions/thread)");
   const size_t fixed = (size_t)w.NW * (kValRing * 4 + kFRing * 4 + 8) + 256;
-  const size_t budget = 200 * 1024 - fixed;
+  const size_t budget = kLatticeSmemBudget - fixed;
   const size_t frame = (size_t)w.Lp * 4;
   int K = 8;
-  if (2 * 8 * frame > budget) K = 4;
+  if ((size_t)(w.NW + 1) * 8 * frame > budget) K = 4;
   B2_REQUIRE(2 * (size_t)K * frame <= budget, "ctc lattice: target too long for shared memory");
   int nring = (int)(budget / (K * frame));
   if (nring > kMaxEmRing) nring = kMaxEmRing;
-  // keep small cases small (several CTAs per SM): ~32 KB of emissions in flight is plenty
-  while (nring > 3 && (size_t)nring * K * frame > 32 * 1024) --nring;
+  // keep small cases small: ~32 KB of emissions in flight is plenty
+  while (nring > w.NW + 2 && nring > 3 && (size_t)nring * K * frame > 32 * 1024) --nring;
   const size_t smem = (size_t)nring * K * frame + fixed;
-  if (K == 8)
-    return launch_lattice_rk<R, 8>(w, ws, Tfr, zero_infinity, both_dirs, nring, smem, gsrc, st);
-  return launch_lattice_rk<R, 4>(w, ws, Tfr, zero_infinity, both_dirs, nring, smem, gsrc, st);
+  if (K == 8) return launch_lattice_rk<R, 8>(w, ws, Tfr, zero_infinity, both_dirs, nring, smem, st);
+  return launch_lattice_rk<R, 4>(w, ws, Tfr, zero_infinity, both_dirs, nring, smem, st);
 }
 
 static inline int launch_lattice(const LossLayout& w, unsigned char* ws, int Tfr, int zero_infinity,
-                                 int both_dirs, cudaStream_t st, const GatherSrc* gsrc = nullptr) {
+                                 int both_dirs, cudaStream_t st) {
   switch (w.R) {
-    case 2: return launch_lattice_r<2>(w, ws, Tfr, zero_infinity, both_dirs, gsrc, st);
-    case 4: return launch_lattice_r<4>(w, ws, Tfr, zero_infinity, both_dirs, gsrc, st);
-    case 8: return launch_lattice_r<8>(w, ws, Tfr, zero_infinity, both_dirs, gsrc, st);
-    default: return launch_lattice_r<16>(w, ws, Tfr, zero_infinity, both_dirs, gsrc, st);
+    case 2: return launch_lattice_r<2>(w, ws, Tfr, zero_infinity, both_dirs, st);
+    case 4: return launch_lattice_r<4>(w, ws, Tfr, zero_infinity, both_dirs, st);
+    case 8: return launch_lattice_r<8>(w, ws, Tfr, zero_infinity, both_dirs, st);
+    case 16: return launch_lattice_r<16>(w, ws, Tfr, zero_infinity, both_dirs, st);
+    default: return launch_lattice_r<32>(w, ws, Tfr, zero_infinity, both_dirs, st);
   }
 }
 

@@ -54,17 +54,23 @@ struct LossLayout {
   size_t lse2, cmax, em, alpha, beta, offA, offB, utt, lab, dup, counter, total;
 };
 
-// positions per thread of the lattice CTA (even); one warp covers 32*R positions
-// (at most 28 compute warps: the CTA also holds one TMA or four gather producer warps)
-inline int lattice_R(int Smax) {
+// positions per thread of the lattice CTA (even); one warp covers 32*R positions.
+// Warp w+1 of the systolic lattice trails warp w by one block of K >= 4 steps, and
+// all warps read one shared ring of emission chunks (K frames of Lp floats): the
+// ring must span NW+1 blocks.  R is the smallest value (<= 16 warps) that fits.
+constexpr size_t kLatticeSmemBudget = 200 * 1024;
+inline int lattice_R(int Smax, int Lp) {
   if (const char* e = getenv("B200CTC_LAT_R")) {  // tuning sweeps only
     const int r = atoi(e);
-    if ((r == 2 || r == 4 || r == 8 || r == 16) && Smax <= 28 * 32 * r) return r;
+    if ((r == 2 || r == 4 || r == 8 || r == 16 || r == 32) && Smax <= 16 * 32 * r) return r;
   }
-  if (Smax <= 16 * 32 * 2) return 2;
-  if (Smax <= 28 * 32 * 4) return 4;
-  if (Smax <= 28 * 32 * 8) return 8;
-  return 16;
+  for (int r = 2; r <= 16; r *= 2) {
+    const int nw = (Smax + 32 * r - 1) / (32 * r);
+    if (nw > 16) continue;
+    const size_t fixed = (size_t)nw * 300 + 256;
+    if ((size_t)(nw + 1) * 4 * Lp * 4 + fixed <= kLatticeSmemBudget) return r;
+  }
+  return 32;
 }
 
 inline LossLayout make_loss_layout(int B, int T, int V, int Lmax) {
@@ -73,7 +79,7 @@ inline LossLayout make_loss_layout(int B, int T, int V, int Lmax) {
   const int S = 2 * Lmax + 1;
   w.Lp = kEmLabel0 + (int)align_up((size_t)(Lmax > 0 ? Lmax : 1), 4);
   w.Sp = (int)align_up((size_t)S, 8);
-  w.R = lattice_R(S);
+  w.R = lattice_R(S, w.Lp);
   w.NW = (S + 32 * w.R - 1) / (32 * w.R);
   w.NB = (T + kRenormEvery - 1) / kRenormEvery;  // renorm blocks per utterance
   size_t o = 0;

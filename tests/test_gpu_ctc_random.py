@@ -148,3 +148,84 @@ def test_greedy_decode_matches_oracle():
         assert lens[b].item() == len(want)
         assert ids[b, : len(want)].tolist() == want
         assert torch.all(ids[b, len(want):] == -1)
+
+
+def _ref(logits, tg, il, tl):
+    return espnet_cpu.logits_loss_and_grad(logits, tg, il, tl)  # grad of nll.sum()/B
+
+
+@pytest.mark.parametrize("mode", ["eager", "deferred"])
+def test_grad_modes_agree_with_reference(mode):
+    """grad_mode: the forward-time gradient and the backward-time row pass are the same numbers."""
+    from espnet1_b200 import functional as F
+
+    logits, tg, il, tl = make_case(6, 90, 700, 5, 30, seed=31)
+    ref_nll, ref_g = _ref(logits, tg, il, tl)
+    x = logits.to(DEV).requires_grad_(True)
+    nll = F.ctc_loss(x, tg, il, tl, grad_mode=mode)
+    (nll.sum() / 6).backward()
+    np.testing.assert_allclose(nll.detach().cpu().numpy(), ref_nll.numpy(), rtol=1e-5)
+    np.testing.assert_allclose(x.grad.cpu().numpy(), ref_g.numpy(), rtol=0, atol=1e-4)
+
+
+def test_reduce_scale_scalar_loss_and_upstream_scalar():
+    """reduce_scale: the batch reduction of espnet2/asr/ctc.py:56-60 inside the nll kernel;
+    an upstream gradient that is not the hint (loss * 0.3) costs one rescale and stays exact."""
+    from espnet1_b200 import functional as F
+
+    logits, tg, il, tl = make_case(7, 70, 400, 3, 20, seed=32)
+    ref_nll, ref_g = _ref(logits, tg, il, tl)
+    x = logits.to(DEV).requires_grad_(True)
+    loss = F.ctc_loss(x, tg, il, tl, reduce_scale=F._f32_recip(7))
+    assert loss.dim() == 0
+    np.testing.assert_allclose(loss.item(), ref_nll.sum().item() / 7, rtol=1e-5)
+    loss.backward()
+    np.testing.assert_allclose(x.grad.cpu().numpy(), ref_g.numpy(), rtol=0, atol=1e-4)
+    x2 = logits.to(DEV).requires_grad_(True)
+    (F.ctc_loss(x2, tg, il, tl, reduce_scale=F._f32_recip(7)) * 0.3).backward()
+    np.testing.assert_allclose(x2.grad.cpu().numpy(), 0.3 * ref_g.numpy(), rtol=0, atol=1e-4)
+
+
+def test_wrong_hint_is_still_exact():
+    from espnet1_b200 import functional as F
+
+    logits, tg, il, tl = make_case(4, 50, 120, 3, 12, seed=33)
+    _, ref_g = _ref(logits, tg, il, tl)
+    x = logits.to(DEV).requires_grad_(True)
+    F.ctc_loss(x, tg, il, tl, grad_hint=123.0).sum().backward()  # upstream gradient is 1 per utterance
+    np.testing.assert_allclose(x.grad.cpu().numpy(), 4 * ref_g.numpy(), rtol=0, atol=4e-4)
+
+
+def test_explicit_target_offsets_match_prefix_sum():
+    from espnet1_b200 import functional as F
+
+    logits, tg, il, tl = make_case(5, 40, 64, 2, 9, seed=34)
+    off = (torch.cumsum(tl, 0) - tl).to(DEV)
+    a = F.ctc_loss(logits.to(DEV), tg, il, tl)
+    b = F.ctc_loss(logits.to(DEV), tg, il, tl, tgt_offsets=off)
+    assert torch.equal(a, b)
+
+
+def test_eager_gradient_cannot_be_consumed_twice():
+    from espnet1_b200 import functional as F
+
+    logits, tg, il, tl = make_case(2, 30, 20, 2, 5, seed=35)
+    x = logits.to(DEV).requires_grad_(True)
+    loss = F.ctc_loss(x, tg, il, tl).sum()
+    loss.backward(retain_graph=True)
+    with pytest.raises(RuntimeError):
+        loss.backward()
+
+
+@pytest.mark.parametrize("T,lmin,lmax", [
+    (300, 250, 290),    # 581 positions: 10 warps of 2/thread
+    (700, 500, 600),    # 1201 positions: 10 warps of 4/thread
+    (1500, 900, 1000),  # 2001 positions: 8/thread or 16/thread, 4-frame emission chunks
+])
+def test_medium_lattices_pick_consistent_layouts(T, lmin, lmax):
+    """Every (positions/thread, frames/chunk, ring depth) choice gives the same numbers."""
+    logits, tg, il, tl = make_case(3, T, 96, lmin, lmax, seed=T, ragged=True)
+    n64, g64 = espnet_cpu.logits_loss_and_grad(logits.double(), tg, il, tl)
+    nll, g = run_cuda(logits, tg, il, tl)
+    np.testing.assert_allclose(nll.numpy(), n64.numpy(), rtol=1e-5)
+    assert (g.double() - g64).abs().max().item() < 1e-3
