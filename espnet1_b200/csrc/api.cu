@@ -45,8 +45,6 @@ void prof_mark(int phase, int end, cudaStream_t st) {
   g_ev[phase][end ? 1 : 0].push_back(e);
 }
 
-bool prof_enabled() { return g_prof; }
-
 int sm_count() {
   static thread_local int cached_dev = -1, cached = 0;
   int dev = 0;

@@ -20,7 +20,6 @@ int sm_count();
 // 4 prefix_step, 5 softmax family
 constexpr int kProfPhases = 8;
 void prof_mark(int phase, int end, cudaStream_t st);
-bool prof_enabled();
 
 template <typename... KArgs, typename... Args>
 static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,

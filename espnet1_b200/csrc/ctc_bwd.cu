@@ -12,25 +12,19 @@
 namespace b200ctc {
 
 template <typename T, int NT, int PER, bool TMA>
-__global__ void __launch_bounds__(NT, NT <= 128 ? 6 : 1) grad_rows_kernel(
+__global__ void __launch_bounds__(NT) grad_rows_kernel(
     const T* __restrict__ logits, T* __restrict__ grad, int B, int Tfr, int V, int blank,
     const UttInfo* __restrict__ utt, const int* __restrict__ lab, const int* __restrict__ dup,
     int Lp, int Sp, int NWp, int NB, int wshift, float* __restrict__ lse2, const float* __restrict__ cmax,
     const float* __restrict__ alpha, const float* __restrict__ beta,
     const int* __restrict__ offA, const int* __restrict__ offB,
-    const float* __restrict__ gscale, int gstride, float gmul, int nstage, int stage_stride,
-    int64_t row0, int* __restrict__ queue) {
-  // rows [row0, B*Tfr): B is the END utterance of this wave (row0 = first utterance * Tfr).
-  // Rows are handed out DYNAMICALLY (queue[0] = next row, queue[kMaxWaves] = CTAs done):
-  // in the wave pipeline this grid shares the SMs with the lattice CTAs of later waves,
-  // so some of its CTAs become resident late - they must find work left, not a fixed share.
+    const float* __restrict__ gscale, int gstride, float gmul, int nstage, int stage_stride) {
   constexpr int N = Elems<T>::N;
   constexpr int NWARP = NT / 32;
   extern __shared__ __align__(128) unsigned char dsm[];
   __shared__ __align__(8) uint64_t bars[kMaxRowStages];
   __shared__ float wp[32];
   __shared__ float2 wms[2][32];  // per-warp (max, sum) of the row, double buffered
-  __shared__ int64_t s_row[kMaxRowStages];  // the row each stage holds (or will hold); -1 = none left
   unsigned char* stages = dsm;
   float* pbuf = reinterpret_cast<float*>(dsm + (size_t)nstage * stage_stride);  // [Lp]
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -39,19 +33,17 @@ __global__ void __launch_bounds__(NT, NT <= 128 ? 6 : 1) grad_rows_kernel(
   const int nchunk = V / N;
   const int ntail = V - nchunk * N;
 
-  // thread 0 only: claim the next row / publish it as the content of a stage and start its copy
-  auto claim = [&]() -> int64_t {
-    const int64_t r = row0 + atomicAdd(queue, 1);
-    return r < nrows ? r : -1;
-  };
-  auto has_data = [&](int64_t g) {  // padded frames / zeroed utterances only get zeros written
-    const int b = (int)((uint32_t)g / (uint32_t)Tfr), t = (int)g - b * Tfr;  // B*T < 2^31
-    return t < utt[b].T && !utt[b].zeroed;
-  };
-  auto start_copy = [&](int st, int64_t g) {
-    if (TMA && g >= 0 && has_data(g)) {
+  RowCursor pc;
+  pc.init(blockIdx.x, gridDim.x, Tfr);
+  uint32_t np = 0;
+  auto issue_next = [&]() {
+    while (pc.g < nrows && (pc.t >= utt[pc.b].T || utt[pc.b].zeroed)) pc.next();
+    if (pc.g < nrows) {
+      const int st = np % nstage;
       mbar_expect_tx(&bars[st], row_bytes);
-      bulk_g2s(stages + (size_t)st * stage_stride, logits + g * V, row_bytes, &bars[st]);
+      bulk_g2s(stages + (size_t)st * stage_stride, logits + pc.g * V, row_bytes, &bars[st]);
+      ++np;
+      pc.next();
     }
   };
   griddep_launch();  // PDL: nll_kernel may queue up behind this grid
@@ -63,23 +55,19 @@ __global__ void __launch_bounds__(NT, NT <= 128 ? 6 : 1) grad_rows_kernel(
     __syncthreads();
   }
   griddep_wait();  // utt / lattices / cmax come from the previous kernels
-  if (tid == 0)
-    for (int i = 0; i < nstage; ++i) {
-      const int64_t g = claim();
-      s_row[i] = g;
-      start_copy(i, g);
-    }
-  __syncthreads();
+  if (TMA && tid == 0)
+    for (int i = 0; i < nstage; ++i) issue_next();
 
-  uint32_t n = 0;        // rows of this CTA that carried data (wms / pbuf double buffering)
-  uint32_t phases = 0;   // mbarrier parity per stage
-  for (int st = 0;; st = (st + 1 == nstage) ? 0 : st + 1) {
-    const int64_t g = s_row[st];
-    if (g < 0) break;
-    int64_t g_next = -1;
-    if (tid == 0) g_next = claim();  // refills this stage below; the atomic's latency hides behind the row
-    const int b = (int)((uint32_t)g / (uint32_t)Tfr), t = (int)g - b * Tfr;
-    const float c2 = cmax[g];
+  uint32_t n = 0;
+  RowCursor rc;
+  rc.init(blockIdx.x, gridDim.x, Tfr);
+  // the per-row constant is fetched one row ahead (its latency hides behind the current row)
+  float c_nx = rc.g < nrows ? cmax[rc.g] : 0.f;
+  for (; rc.g < nrows; rc.next()) {
+    const int b = rc.b, t = rc.t;
+    const int64_t g = rc.g;
+    const float c2 = c_nx;
+    if (g + rc.stride < nrows) c_nx = cmax[g + rc.stride];
     const UttInfo u = utt[b];
     T* gr = grad + g * V;
     const bool al16 = (reinterpret_cast<uintptr_t>(gr) & 15) == 0;
@@ -93,12 +81,6 @@ __global__ void __launch_bounds__(NT, NT <= 128 ? 6 : 1) grad_rows_kernel(
       } else {
         for (int i = tid; i < V; i += NT) gr[i] = from_f32<T>(0.f);
       }
-      __syncthreads();  // every thread has read s_row[st]
-      if (tid == 0) {
-        s_row[st] = g_next;
-        start_copy(st, g_next);
-      }
-      __syncthreads();
       continue;
     }
     const int L = u.L, S = 2 * L + 1;
@@ -129,9 +111,9 @@ __global__ void __launch_bounds__(NT, NT <= 128 ? 6 : 1) grad_rows_kernel(
     }
     const unsigned char* stg;
     if (TMA) {
+      const int st = n % nstage;
       stg = stages + (size_t)st * stage_stride;
-      mbar_wait(&bars[st], (phases >> st) & 1u);
-      phases ^= 1u << st;
+      mbar_wait(&bars[st], (n / nstage) & 1);
     } else {
       stg = stages;
       const T* src = logits + g * V;
@@ -242,29 +224,23 @@ __global__ void __launch_bounds__(NT, NT <= 128 ? 6 : 1) grad_rows_kernel(
       const float sm = ex2(fmaf(to_f32<T>(xs[blank]), kLog2e, -l2));
       gr[blank] = from_f32<T>(gb * (sm - acc));
     }
-    if (tid == 0) s_row[st] = g_next;  // (all threads read s_row[st] before the barriers above)
     __syncthreads();  // stage, pbuf and wp are free again
-    if (tid == 0) start_copy(st, g_next);
+    if (TMA && tid == 0) issue_next();
     ++n;
-  }
-  // the last CTA to leave re-arms the queue for the next launch on this workspace
-  if (tid == 0 && atomicAdd(queue + kMaxWaves, 1) == (int)gridDim.x - 1) {
-    queue[0] = 0;
-    queue[kMaxWaves] = 0;
   }
 }
 
 template <typename T, int NT>
-static int launch_pass_b(const void* logits, void* grad, int b0, int nb, int Tfr, int V, int blank,
+static int launch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, int blank,
                          const LossLayout& w, unsigned char* ws, const float* gscale,
-                         int gstride, float gmul, cudaStream_t st, int wave) {
+                         int gstride, float gmul, cudaStream_t st) {
   constexpr int PER = 40 / Elems<T>::N;
   const size_t extra = align_up(sizeof(float) * (size_t)w.Lp, 128);
   const RowLaunchCfg c = row_launch_cfg(logits, (size_t)V * sizeof(T), extra, NT, "B200CTC_B");
   B2_REQUIRE((size_t)c.nstage * c.stride + extra <= 226 * 1024,
              "ctc_loss grad: V=%d too large for the shared-memory row path", V);
   const size_t smem = (size_t)c.nstage * c.stride + extra;
-  const int64_t rows = (int64_t)nb * Tfr;
+  const int64_t rows = (int64_t)B * Tfr;
   int64_t grid = (int64_t)sm_count() * c.ctas_per_sm;
   if (grid > rows) grid = rows;
   int wshift = 0;
@@ -275,14 +251,13 @@ static int launch_pass_b(const void* logits, void* grad, int b0, int nb, int Tfr
         // (no PDL here: a persistent grid must not become resident piecemeal beside
         //  the still-running lattice - late CTAs would form a second wave)
         k, dim3((unsigned)grid), dim3(NT), smem, st, false,
-        static_cast<const T*>(logits), static_cast<T*>(grad), b0 + nb, Tfr, V, blank,
+        static_cast<const T*>(logits), static_cast<T*>(grad), B, Tfr, V, blank,
         reinterpret_cast<const UttInfo*>(ws + w.utt), reinterpret_cast<const int*>(ws + w.lab),
         reinterpret_cast<const int*>(ws + w.dup), w.Lp, w.Sp, w.NW, w.NB, wshift,
         reinterpret_cast<float*>(ws + w.lse2), reinterpret_cast<const float*>(ws + w.cmax),
         reinterpret_cast<const float*>(ws + w.alpha), reinterpret_cast<const float*>(ws + w.beta),
         reinterpret_cast<const int*>(ws + w.offA), reinterpret_cast<const int*>(ws + w.offB),
-        gscale, gstride, gmul, c.nstage, c.stride, (int64_t)b0 * Tfr,
-        reinterpret_cast<int*>(ws + w.counter) + 1 + wave);
+        gscale, gstride, gmul, c.nstage, c.stride);
   };
   if (c.tma) go(grad_rows_kernel<T, NT, PER, true>);
   else go(grad_rows_kernel<T, NT, PER, false>);
@@ -291,34 +266,29 @@ static int launch_pass_b(const void* logits, void* grad, int b0, int nb, int Tfr
 }
 
 template <typename T>
-static int dispatch_pass_b(const void* logits, void* grad, int b0, int B, int Tfr, int V, int blank,
+static int dispatch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, int blank,
                            const LossLayout& w, unsigned char* ws, const float* gscale,
-                           int gstride, float gmul, cudaStream_t st, int wave) {
+                           int gstride, float gmul, cudaStream_t st) {
   const int need = (V + 39) / 40;
-  if (need <= 128) return launch_pass_b<T, 128>(logits, grad, b0, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, st, wave);
-  if (need <= 256) return launch_pass_b<T, 256>(logits, grad, b0, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, st, wave);
-  if (need <= 512) return launch_pass_b<T, 512>(logits, grad, b0, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, st, wave);
-  if (need <= 1024) return launch_pass_b<T, 1024>(logits, grad, b0, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, st, wave);
+  if (need <= 128) return launch_pass_b<T, 128>(logits, grad, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, st);
+  if (need <= 256) return launch_pass_b<T, 256>(logits, grad, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, st);
+  if (need <= 512) return launch_pass_b<T, 512>(logits, grad, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, st);
+  if (need <= 1024) return launch_pass_b<T, 1024>(logits, grad, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, st);
   set_error("ctc_loss grad: V=%d exceeds the supported row size", V);
   return B200CTC_ERR_ARG;
 }
 
 int launch_grad_rows(const void* logits, int dtype, void* grad, int B, int T, int V, int blank,
                      const LossLayout& w, unsigned char* ws, const float* gscale, int gstride,
-                     float gmul, cudaStream_t st, int b0, int nb, int wave) {
-  if (nb < 0) nb = B - b0;  // utterances [b0, b0 + nb); wave = which row queue of the workspace
-  if (nb <= 0) return B200CTC_OK;
-  B = nb;
+                     float gmul, cudaStream_t st) {
   switch (dtype) {
     case B200CTC_F32:
-      return dispatch_pass_b<float>(logits, grad, b0, B, T, V, blank, w, ws, gscale, gstride, gmul, st,
-                                    wave);
+      return dispatch_pass_b<float>(logits, grad, B, T, V, blank, w, ws, gscale, gstride, gmul, st);
     case B200CTC_F16:
-      return dispatch_pass_b<__half>(logits, grad, b0, B, T, V, blank, w, ws, gscale, gstride, gmul, st,
-                                     wave);
+      return dispatch_pass_b<__half>(logits, grad, B, T, V, blank, w, ws, gscale, gstride, gmul, st);
     default:
-      return dispatch_pass_b<__nv_bfloat16>(logits, grad, b0, B, T, V, blank, w, ws, gscale, gstride,
-                                            gmul, st, wave);
+      return dispatch_pass_b<__nv_bfloat16>(logits, grad, B, T, V, blank, w, ws, gscale, gstride,
+                                            gmul, st);
   }
 }
 
@@ -379,7 +349,7 @@ extern "C" int b200ctc_loss_bwd(const void* logits, int dtype, const int64_t* in
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   prof_mark(3, 0, st);
   const int rc = launch_grad_rows(logits, dtype, grad, B, T, V, blank, w, ws, gscale,
-                                  gscale_stride, gscale_mul, st, 0, -1, 0);
+                                  gscale_stride, gscale_mul, st);
   prof_mark(3, 1, st);
   return rc;
 }

@@ -2,7 +2,6 @@
 // vocabulary + gather of the lattice emissions, streamed through shared memory
 // by the TMA engine (1-D bulk copies, mbarrier ring), (3) alpha/beta lattice
 // recursion (ctc_lattice.cuh), one CTA per utterance and direction.
-#include <cstdio>
 #include <mutex>
 
 #include "ctc_lattice.cuh"
@@ -34,8 +33,7 @@ __device__ __forceinline__ void prep_utterance(const PrepArgs& P, int b, int* sl
   __shared__ int s_bad, s_head;
   __shared__ long long s_base;
   const int NT = blockDim.x, tid = threadIdx.x;
-  // nll_kernel's "last CTA" ticket + the row queues of the gradient pass (ctc_ws.cuh)
-  if (publish && b == 0 && tid < kCounterInts) P.counter[tid] = 0;
+  if (publish && b == 0 && tid == 0) *P.counter = 0;  // nll_kernel's "last CTA" ticket
   const long long L64 = P.tgt_lens[b], T64 = P.in_lens[b];
   const int L = (int)(L64 < 0 ? 0 : (L64 > P.Lmax ? P.Lmax : L64));
   const int Tb = (int)(T64 < 0 ? 0 : (T64 > P.T ? P.T : T64));
@@ -114,11 +112,10 @@ constexpr int kGatherRegs = 8;   // values kept in registers per lane and row (L
 
 template <typename T>
 __global__ void __launch_bounds__(kGatherWarps * 32) gather_kernel(
-    const T* __restrict__ logits, PrepArgs P, float* __restrict__ em, float* __restrict__ cmax,
-    int b0) {
+    const T* __restrict__ logits, PrepArgs P, float* __restrict__ em, float* __restrict__ cmax) {
   extern __shared__ int slab[];  // [Lp] label columns of this utterance
   griddep_launch();  // the lattice CTAs may become resident and set up meanwhile
-  const int b = b0 + blockIdx.y;  // b0: first utterance of this wave
+  const int b = blockIdx.y;
   int Tb, L;
   prep_utterance(P, b, slab, blockIdx.x == 0, Tb, L);
   const int Tfr = P.T, V = P.V, Lp = P.Lp;
@@ -179,18 +176,18 @@ __global__ void __launch_bounds__(kGatherWarps * 32) gather_kernel(
 }
 
 template <typename T>
-static int launch_gather(const void* logits, const PrepArgs& P, int b0, int nb, const LossLayout& w,
+static int launch_gather(const void* logits, const PrepArgs& P, int B, const LossLayout& w,
                          unsigned char* ws, cudaStream_t st) {
   constexpr int fpc = kGatherWarps * kGatherRows;
   int gx = (P.T + fpc - 1) / fpc;
   if (gx < 1) gx = 1;  // the first CTA of every utterance also publishes the label prep
-  dim3 grid(gx, nb);
+  dim3 grid(gx, B);
   const size_t smem = sizeof(int) * (size_t)w.Lp;
   auto k = gather_kernel<T>;
   if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   k<<<grid, kGatherWarps * 32, smem, st>>>(static_cast<const T*>(logits), P,
                                            reinterpret_cast<float*>(ws + w.em),
-                                           reinterpret_cast<float*>(ws + w.cmax), b0);
+                                           reinterpret_cast<float*>(ws + w.cmax));
   count_launch();
   return check_launch("ctc gather");
 }
@@ -386,7 +383,6 @@ static int check_loss_args(const char* who, const void* logits, int dtype, const
   B2_REQUIRE(2 * (int64_t)max_tgt_len + 1 <= kMaxLattice,
              "%s: max_tgt_len=%d exceeds the supported lattice width %d", who, max_tgt_len,
              kMaxLattice);
-  B2_REQUIRE((int64_t)B * T < (int64_t)1 << 31, "%s: B*T must be below 2^31 rows", who);
   *out = make_loss_layout(B, T, V, max_tgt_len);
   if (ws_bytes < out->total) {
     set_error("%s: workspace %zu < required %zu bytes", who, ws_bytes, out->total);
@@ -424,7 +420,7 @@ static int launch_prep(const LossLayout& w, const PrepArgs& P, cudaStream_t st) 
 // defined in ctc_bwd.cu / ctc_dense.cu
 int launch_grad_rows(const void* logits, int dtype, void* grad, int B, int T, int V, int blank,
                      const LossLayout& w, unsigned char* ws, const float* gscale, int gstride,
-                     float gmul, cudaStream_t st, int b0 = 0, int nb = -1, int wave = 0);
+                     float gmul, cudaStream_t st);
 int launch_dense_rows(const void* logits, int dtype, void* grad, int B, int T, int V,
                       const int64_t* in_lens, const LossLayout& w, unsigned char* ws, float gmul,
                       cudaStream_t st);
@@ -456,58 +452,6 @@ static cudaStream_t side_stream() {
 static bool eager_split_enabled() {
   const char* e = getenv("B200CTC_EAGER_SPLIT");
   return e && e[0] == '1';
-}
-
-// ---- waves --------------------------------------------------------------------
-// The eager step is a chain  gather (HBM-bound, sparse) -> lattice (latency-bound:
-// T dependent steps, a few warps per utterance, no HBM traffic) -> gradient rows
-// (HBM-bound, streaming).  Run on the whole batch at once, the lattice leaves HBM
-// idle for its whole duration.  The batch is therefore cut into `waves` of
-// utterances: all gathers and then all row passes run back to back on the caller's
-// stream (the "bandwidth" stream), while the lattice of every wave runs on its own
-// high-priority internal stream as soon as its gather is done - i.e. beside the
-// gathers of the later waves and the row passes of the earlier ones.  Plain stream
-// order + events: no kernel ever waits on another kernel's progress.
-struct WavePool {
-  cudaStream_t lat[kMaxWaves];
-  cudaEvent_t ev_g[kMaxWaves], ev_l[kMaxWaves];
-  bool ok = false;
-};
-static std::mutex g_wave_mu;  // also serialises the enqueue (the events are shared)
-static WavePool* g_waves[64] = {};
-
-static WavePool* wave_pool() {  // call with g_wave_mu held
-  int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
-  if (!g_waves[dev]) {
-    WavePool* p = new WavePool();
-    int lo = 0, hi = 0;
-    cudaDeviceGetStreamPriorityRange(&lo, &hi);  // hi = numerically smallest = highest priority
-    p->ok = true;
-    for (int i = 0; i < kMaxWaves && p->ok; ++i) {
-      p->ok = cudaStreamCreateWithPriority(&p->lat[i], cudaStreamNonBlocking, hi) == cudaSuccess &&
-              cudaEventCreateWithFlags(&p->ev_g[i], cudaEventDisableTiming) == cudaSuccess &&
-              cudaEventCreateWithFlags(&p->ev_l[i], cudaEventDisableTiming) == cudaSuccess;
-    }
-    if (!p->ok) cudaGetLastError();
-    g_waves[dev] = p;
-  }
-  return g_waves[dev]->ok ? g_waves[dev] : nullptr;
-}
-
-// waves for a (B,T,V) step: enough utterances per wave to fill the machine's SMs
-// with lattice CTAs is not needed (the lattice is latency-bound), but every wave
-// costs three launches, so small problems stay in one piece.
-static int pick_waves(int B, int T, int V, size_t elt) {
-  if (const char* e = getenv("B200CTC_WAVES")) {  // tuning sweeps only
-    const int n = atoi(e);
-    if (n >= 1) return n < kMaxWaves ? (n < B ? n : (B > 0 ? B : 1)) : kMaxWaves;
-  }
-  if (prof_enabled()) return 1;  // per-phase timings want the phases back to back
-  const double bytes = (double)B * T * V * elt;
-  if (B >= 16 && bytes >= 256e6) return 4;
-  if (B >= 8 && bytes >= 64e6) return 2;
-  return 1;
 }
 
 }  // namespace b200ctc
@@ -584,80 +528,13 @@ extern "C" int b200ctc_loss_fwd_grad(const void* logits, int dtype, const int64_
     cudaEventRecord(ev_join, sd);
   }
   const PrepArgs P = make_prep_args(w, ws, targets, tgt_offsets, in_lens, tgt_lens, blank);
-  auto gather = [&](int b0, int nb) {  // gather kernel with the label prep fused in
-    switch (dtype) {
-      case B200CTC_F32: return launch_gather<float>(logits, P, b0, nb, w, ws, st);
-      case B200CTC_F16: return launch_gather<__half>(logits, P, b0, nb, w, ws, st);
-      default: return launch_gather<__nv_bfloat16>(logits, P, b0, nb, w, ws, st);
-    }
-  };
-  const size_t elt = dtype == B200CTC_F32 ? 4 : 2;
-  const int nwave = (sd || T == 0) ? 1 : pick_waves(B, T, V, elt);
-  if (nwave > 1 && !rc) {
-    std::lock_guard<std::mutex> lk(g_wave_mu);
-    WavePool* wp = wave_pool();
-    if (wp) {
-      int b0s[kMaxWaves + 1];
-      for (int i = 0; i <= nwave; ++i) b0s[i] = (int)((int64_t)B * i / nwave);
-      int launched = 0;
-      static const int dbg = [] { const char* e = getenv("B200CTC_WAVE_DBG"); return e ? atoi(e) : 0; }();
-      // B200CTC_WAVE_DBG bit 2: print the device timeline of this call (debugging only: it
-      // synchronises the stream)
-      cudaEvent_t tr[3][kMaxWaves][2] = {};
-      const bool trace = (dbg & 4) != 0;
-      auto mark = [&](int k, int i, int e, cudaStream_t s) {
-        if (!trace) return;
-        cudaEventCreate(&tr[k][i][e]);
-        cudaEventRecord(tr[k][i][e], s);
-      };
-      for (int i = 0; i < nwave && !rc; ++i) {  // gathers back to back; lattices fan out
-        const int b0 = b0s[i], nb = b0s[i + 1] - b0s[i];
-        mark(0, i, 0, st);
-        rc = gather(b0, nb);
-        mark(0, i, 1, st);
-        if (rc) break;
-        cudaEventRecord(wp->ev_g[i], st);
-        cudaStream_t ls = wp->lat[(dbg & 1) ? 0 : i];
-        cudaStreamWaitEvent(ls, wp->ev_g[i], 0);
-        mark(1, i, 0, ls);
-        rc = launch_lattice(w, ws, T, zero_infinity, 1, ls, b0, nb);
-        mark(1, i, 1, ls);
-        cudaEventRecord(wp->ev_l[i], ls);  // also on error: the join below must cover it
-        launched = i + 1;
-      }
-      if (dbg & 2)
-        for (int i = 0; i < launched; ++i) cudaStreamWaitEvent(st, wp->ev_l[i], 0);
-      for (int i = 0; i < launched; ++i) {  // row passes back to back, each behind its lattice
-        cudaStreamWaitEvent(st, wp->ev_l[i], 0);
-        mark(2, i, 0, st);
-        if (!rc)
-          rc = launch_grad_rows(logits, dtype, grad, B, T, V, blank, w, ws, nullptr, 0, grad_hint, st,
-                                b0s[i], b0s[i + 1] - b0s[i], i);
-        mark(2, i, 1, st);
-      }
-      if (trace) {
-        cudaStreamSynchronize(st);
-        static const char* names[3] = {"gather", "lattice", "rows"};
-        for (int k = 0; k < 3; ++k)
-          for (int i = 0; i < launched; ++i) {
-            float a = 0.f, b = 0.f;
-            cudaEventElapsedTime(&a, tr[0][0][0], tr[k][i][0]);
-            cudaEventElapsedTime(&b, tr[0][0][0], tr[k][i][1]);
-            fprintf(stderr, "[wave trace] %-7s %d: %7.1f -> %7.1f us\n", names[k], i, a * 1e3f, b * 1e3f);
-          }
-        for (int k = 0; k < 3; ++k)
-          for (int i = 0; i < launched; ++i) {
-            cudaEventDestroy(tr[k][i][0]);
-            cudaEventDestroy(tr[k][i][1]);
-          }
-      }
-      if (rc) return rc;
-      return launch_nll(w, ws, T, zero_infinity, nll, loss_out, loss_scale, st);
-    }
-  }
-  if (!rc) {
+  if (!rc) {  // gather kernel with the label prep fused in
     prof_mark(1, 0, st);
-    rc = gather(0, B);
+    switch (dtype) {
+      case B200CTC_F32: rc = launch_gather<float>(logits, P, B, w, ws, st); break;
+      case B200CTC_F16: rc = launch_gather<__half>(logits, P, B, w, ws, st); break;
+      default: rc = launch_gather<__nv_bfloat16>(logits, P, B, w, ws, st); break;
+    }
     prof_mark(1, 1, st);
   }
   if (!rc) {

@@ -89,7 +89,7 @@ __device__ __forceinline__ void sts_release_i32(uint32_t addr, int v) {
 }
 __device__ __forceinline__ float lds_f32_u32(uint32_t addr) {
   float v;
-  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
   return v;
 }
 // emission ring reads: ordered after the mbarrier wait (volatile asm), plain ld.shared
@@ -407,7 +407,7 @@ template <int R, bool STORE, int K>
 __global__ void __launch_bounds__(544, 1) lattice_kernel(
     UttInfo* __restrict__ utt, const int* __restrict__ lab, int Lp, const float* __restrict__ em,
     float* __restrict__ alpha, float* __restrict__ beta, int* __restrict__ offA,
-    int* __restrict__ offB, int Tfr, int Sp, int NWp, int NB, int zero_infinity, int nring, int b0) {
+    int* __restrict__ offB, int Tfr, int Sp, int NWp, int NB, int zero_infinity, int nring) {
   static_assert(R % 2 == 0, "R must be even: even recursion positions are blanks");
   extern __shared__ __align__(128) float lsm[];  // em ring [nring][K*Lp] | vals | fring | ready | cons
   __shared__ __align__(8) uint64_t bars[2 * kMaxEmRing];  // full[], empty[]
@@ -415,7 +415,7 @@ __global__ void __launch_bounds__(544, 1) lattice_kernel(
   uint64_t* const empty = bars + kMaxEmRing;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int NW = (blockDim.x >> 5) - 1;  // compute warps; warp NW is the TMA producer
-  const int b = b0 + blockIdx.x, dir = blockIdx.y;  // b0: first utterance of this wave
+  const int b = blockIdx.x, dir = blockIdx.y;
   griddep_launch();  // PDL: let the gradient row pass become resident behind us
   griddep_wait();    // utt / lab / em come from the previous kernel
   const int Tb = utt[b].T, L = utt[b].L, S = 2 * L + 1;
@@ -539,10 +539,9 @@ __global__ void __launch_bounds__(256) nll_kernel(const UttInfo* __restrict__ ut
 
 template <int R, int K>
 static int launch_lattice_rk(const LossLayout& w, unsigned char* ws, int Tfr, int zero_infinity,
-                             int both_dirs, int nring, size_t smem, cudaStream_t st, int b0,
-                             int nb) {
+                             int both_dirs, int nring, size_t smem, cudaStream_t st) {
   const int nt = (w.NW + 1) * 32;  // + the TMA producer warp
-  dim3 grid(nb, both_dirs ? 2 : 1);
+  dim3 grid(w.B, both_dirs ? 2 : 1);
   auto go = [&](auto k) {
     if (smem > 48 * 1024)
       cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -550,7 +549,7 @@ static int launch_lattice_rk(const LossLayout& w, unsigned char* ws, int Tfr, in
                reinterpret_cast<const int*>(ws + w.lab), w.Lp,
                reinterpret_cast<const float*>(ws + w.em), reinterpret_cast<float*>(ws + w.alpha),
                reinterpret_cast<float*>(ws + w.beta), reinterpret_cast<int*>(ws + w.offA),
-               reinterpret_cast<int*>(ws + w.offB), Tfr, w.Sp, w.NW, w.NB, zero_infinity, nring, b0);
+               reinterpret_cast<int*>(ws + w.offB), Tfr, w.Sp, w.NW, w.NB, zero_infinity, nring);
   };
   if (both_dirs) go(lattice_kernel<R, true, K>);
   else go(lattice_kernel<R, false, K>);
@@ -560,7 +559,7 @@ static int launch_lattice_rk(const LossLayout& w, unsigned char* ws, int Tfr, in
 
 template <int R>
 static int launch_lattice_r(const LossLayout& w, unsigned char* ws, int Tfr, int zero_infinity,
-                            int both_dirs, cudaStream_t st, int b0, int nb) {
+                            int both_dirs, cudaStream_t st) {
   // shared memory: em ring of nring chunks of K frames + the per-warp hand-off rings.
   // Warp w+1 runs one block behind warp w, so the ring must span NW+1 blocks or the
   // first warp stalls on the last one (make_loss_layout picks R accordingly).
@@ -576,21 +575,18 @@ static int launch_lattice_r(const LossLayout& w, unsigned char* ws, int Tfr, int
   // keep small cases small: ~32 KB of emissions in flight is plenty
   while (nring > w.NW + 2 && nring > 3 && (size_t)nring * K * frame > 32 * 1024) --nring;
   const size_t smem = (size_t)nring * K * frame + fixed;
-  if (K == 8)
-    return launch_lattice_rk<R, 8>(w, ws, Tfr, zero_infinity, both_dirs, nring, smem, st, b0, nb);
-  return launch_lattice_rk<R, 4>(w, ws, Tfr, zero_infinity, both_dirs, nring, smem, st, b0, nb);
+  if (K == 8) return launch_lattice_rk<R, 8>(w, ws, Tfr, zero_infinity, both_dirs, nring, smem, st);
+  return launch_lattice_rk<R, 4>(w, ws, Tfr, zero_infinity, both_dirs, nring, smem, st);
 }
 
 static inline int launch_lattice(const LossLayout& w, unsigned char* ws, int Tfr, int zero_infinity,
-                                 int both_dirs, cudaStream_t st, int b0 = 0, int nb = -1) {
-  if (nb < 0) nb = w.B - b0;  // utterances [b0, b0 + nb)
-  if (nb <= 0) return B200CTC_OK;
+                                 int both_dirs, cudaStream_t st) {
   switch (w.R) {
-    case 2: return launch_lattice_r<2>(w, ws, Tfr, zero_infinity, both_dirs, st, b0, nb);
-    case 4: return launch_lattice_r<4>(w, ws, Tfr, zero_infinity, both_dirs, st, b0, nb);
-    case 8: return launch_lattice_r<8>(w, ws, Tfr, zero_infinity, both_dirs, st, b0, nb);
-    case 16: return launch_lattice_r<16>(w, ws, Tfr, zero_infinity, both_dirs, st, b0, nb);
-    default: return launch_lattice_r<32>(w, ws, Tfr, zero_infinity, both_dirs, st, b0, nb);
+    case 2: return launch_lattice_r<2>(w, ws, Tfr, zero_infinity, both_dirs, st);
+    case 4: return launch_lattice_r<4>(w, ws, Tfr, zero_infinity, both_dirs, st);
+    case 8: return launch_lattice_r<8>(w, ws, Tfr, zero_infinity, both_dirs, st);
+    case 16: return launch_lattice_r<16>(w, ws, Tfr, zero_infinity, both_dirs, st);
+    default: return launch_lattice_r<32>(w, ws, Tfr, zero_infinity, both_dirs, st);
   }
 }
 

@@ -46,8 +46,6 @@ struct UttInfo {
 static_assert(offsetof(UttInfo, T) % 8 == 0 && offsetof(UttInfo, L) == offsetof(UttInfo, T) + 4,
               "UttInfo::{T,L} must form an aligned int2");
 
-constexpr int kMaxWaves = 8;                     // batch slices pipelined by the eager step (ctc_fwd.cu)
-constexpr int kCounterInts = 1 + 2 * kMaxWaves;  // nll ticket | next row per wave | CTAs done per wave
 constexpr int kRenormEvery = 16;  // lattice re-centring period (steps); one frame offset per block
 constexpr int kEmLabel0 = 4;  // em row: [blank, -, -, -, label_1 .. label_L]
 
@@ -87,7 +85,7 @@ inline LossLayout make_loss_layout(int B, int T, int V, int Lmax) {
   size_t o = 0;
   const size_t BT = (size_t)B * T;
   auto take = [&](size_t bytes) { size_t r = o; o = align_up(o + bytes, 256); return r; };
-  w.counter = take(sizeof(int) * kCounterInts);  // tickets and row queues (zeroed by prep)
+  w.counter = take(sizeof(int));  // "last CTA reduces" ticket of nll_kernel (zeroed by prep)
   w.utt = take(sizeof(UttInfo) * (size_t)B);
   w.lab = take(4 * (size_t)B * w.Lp);
   w.dup = take(4 * (size_t)B * w.Lp);

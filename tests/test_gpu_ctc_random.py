@@ -229,3 +229,35 @@ def test_medium_lattices_pick_consistent_layouts(T, lmin, lmax):
     nll, g = run_cuda(logits, tg, il, tl)
     np.testing.assert_allclose(nll.numpy(), n64.numpy(), rtol=1e-5)
     assert (g.double() - g64).abs().max().item() < 1e-3
+
+
+def test_concurrent_streams_are_bit_identical():
+    """Two steps running side by side on two streams (their kernels share SMs) give exactly the
+    serial results, whatever the offset between them.  (The lattice's shared-memory rings are
+    timing-sensitive by construction: an emission slot released before its queued loads had
+    executed once corrupted steps that shared an SM with busy neighbours.)"""
+    from espnet1_b200 import functional as F
+
+    cases = [make_case(40, 300, 2000, 60, 120, seed=s) for s in (41, 42)]
+    xs = [c[0].to(DEV) for c in cases]
+
+    def step(i):
+        x = xs[i].clone().requires_grad_(True)
+        nll = F.ctc_loss(x, *cases[i][1:], max_tgt_len=120)
+        (nll.sum() / 40).backward()
+        return nll.detach(), x.grad
+
+    ref = [step(0), step(1)]
+    torch.cuda.synchronize()
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    for rep in range(24):
+        out = [None, None]
+        for i in (0, 1):
+            streams[i].wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(streams[i]):
+                if i == 1:  # sweep the offset: the gather of one step meets the lattice of the other
+                    torch.cuda._sleep(1 + rep * 12000)
+                out[i] = step(i)
+        torch.cuda.synchronize()
+        for i in (0, 1):
+            assert torch.equal(out[i][0], ref[i][0]) and torch.equal(out[i][1], ref[i][1])
