@@ -114,6 +114,13 @@ __device__ __forceinline__ void mbar_wait_u32(uint32_t bar, uint32_t parity) {
 __device__ __forceinline__ void mbar_arrive_u32(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
+__device__ __forceinline__ void stg_v2(float* p, float x, float y) {
+  asm volatile("st.global.v2.f32 [%0], {%1,%2};" ::"l"(p), "f"(x), "f"(y) : "memory");
+}
+__device__ __forceinline__ void stg_v4(float* p, float x, float y, float z, float w) {
+  asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(x), "f"(y), "f"(z), "f"(w)
+               : "memory");
+}
 // make a loop-invariant value opaque so that it is kept in a register instead
 // of being re-derived inside the serial loop
 __device__ __forceinline__ uint32_t pin(uint32_t v) {
@@ -148,7 +155,8 @@ struct LatticeArgs {
 //  * all hand-shaking once per block, ring slots by increment (no div / mod).
 template <int R, bool STORE, int DIR, int K>
 __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int lane) {
-  static_assert(K == 4 || K == 8, "block of 4 or 8 steps");
+  static_assert(K == 4 || K == 8 || K == 16, "block of 4, 8 or 16 steps");
+  static_assert(kRenormEvery % K == 0 && kValRing >= 4 * K, "block size vs renorm period / ring");
   constexpr bool kPre = R <= 4;  // whole block's emissions preloaded into registers
   const int Tb = A.Tb, L = A.L, S = 2 * L + 1, Lp = A.Lp;
   const int sp0 = (w * 32 + lane) * R;  // first recursion position of this thread
@@ -235,13 +243,14 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
 #pragma unroll
     for (int q = 0; q < R; ++q) a[q] = nw_[q];
     if (pub) sts_f32_u32(out, a[R - 1]);
+    // (asm stores: they stay inside their step.  Left to the scheduler they sink to the end
+    //  of the block and queue up behind one another on a single address register pair.)
     if (store_ok) {
       if (R == 2) {
-        *reinterpret_cast<float2*>(lat_p) = make_float2(a[0], a[1]);
+        stg_v2(lat_p, a[0], a[1]);
       } else {
 #pragma unroll
-        for (int q = 0; q < R; q += 4)
-          *reinterpret_cast<float4*>(lat_p + q) = make_float4(a[q], a[q + 1], a[q + 2], a[q + 3]);
+        for (int q = 0; q < R; q += 4) stg_v4(lat_p + q, a[q], a[q + 1], a[q + 2], a[q + 3]);
       }
     }
     lat_p += lat_step;
@@ -254,16 +263,28 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
     float up[K];
 #pragma unroll
     for (int u = 0; u < K; ++u) up[u] = kLogZero;
+    const bool apply = (i0 & (kRenormEvery - 1)) == 0;  // first block of a renorm block
+    int Fprev = 0;
     if (has_up) {
-      // value of step j sits in slot (j+1) & 63: this block needs steps i0-1 .. i0+K-2
+      // value of step j sits in slot (j+1) & 63: this block needs steps i0-1 .. i0+K-2.
+      // The flag load and the data loads are issued back to back (shared-memory loads of
+      // a warp execute in order): if the flag then says "published", the data is good and
+      // the common case costs one shared-memory round trip; otherwise poll and reload.
       const int need = (i0 + K - 1 < Tb - 1) ? i0 + K - 1 : Tb - 1;
-      while (ready_seen < need) ready_seen = lds_acquire_i32(ready_in);
-      const float4 v0 = lds_v4_u32(vb);
-      up[0] = v0.x; up[1] = v0.y; up[2] = v0.z; up[3] = v0.w;
-      if (K == 8) {
-        const float4 v1 = lds_v4_u32(vb + 16u);
-        up[K - 4] = v1.x; up[K - 3] = v1.y; up[K - 2] = v1.z; up[K - 1] = v1.w;
-      }
+      bool first = true;
+      do {
+        if (!first || ready_seen < need) ready_seen = lds_acquire_i32(ready_in);
+        first = false;
+#pragma unroll
+        for (int j = 0; j < K; j += 4) {
+          const float4 v = lds_v4_u32(vb + 4u * j);
+          up[j] = v.x; up[j + 1] = v.y; up[j + 2] = v.z; up[j + 3] = v.w;
+        }
+        if (apply) {
+          Fprev = lds_i32_u32(fr_in + (((uint32_t)((i0 - 1) >> 4)) & (kFRing - 1)) * 4u);
+          Fup = lds_i32_u32(fr_in + (((uint32_t)(i0 >> 4)) & (kFRing - 1)) * 4u);
+        }
+      } while (ready_seen < need);
     }
     if (has_down) {
       // my slots of this block last held steps i0-64 ..: the consumer read them in the
@@ -272,13 +293,11 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
       while (cons_seen < needc) cons_seen = lds_i32_u32(cons_down);
     }
     float shift = 0.f, adj0 = adj;
-    if ((i0 & (kRenormEvery - 1)) == 0) {  // first block of a renorm block: apply the shift
+    if (apply) {  // apply the shift measured at the end of the previous renorm block
       const int D = Dpend;
       Dpend = 0;
       shift = (float)D;
       if (has_up) {
-        const int Fprev = lds_i32_u32(fr_in + (((uint32_t)((i0 - 1) >> 4)) & (kFRing - 1)) * 4u);
-        Fup = lds_i32_u32(fr_in + (((uint32_t)(i0 >> 4)) & (kFRing - 1)) * 4u);
         adj0 = (float)(Fprev - F);     // step i0 still adds to my old frame (then -shift)
         adj = (float)(Fup - (F + D));  // all later steps of the renorm block
       }
@@ -357,13 +376,15 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
       float m = kLogZero;
 #pragma unroll
       for (int q = 0; q < R; ++q) m = fmaxf(m, sp0 + q < S ? a[q] : kLogZero);
-      m = warp_max(m);
+      // the shift is an integer anyway: round first, then ONE integer warp reduction
+      // (REDUX) instead of a five-deep shuffle chain.  -2^30 stands for "nothing alive".
+      constexpr float kDead = -1073741824.f;
+      const int mi = __reduce_max_sync(0xffffffffu, __float2int_rn(fminf(fmaxf(m, kDead), 1048576.f)));
       // nothing alive yet: adopt the upstream warp's frame so that the first real
       // values to arrive are already centred.  (Clamped: a pathological -1e10
       // "logzero" logit must not overflow the integer offsets.)  Fup came from a
       // 4-byte broadcast LDS after the acquire, so it is warp-uniform.
-      Dpend = (m > kLogZeroTest) ? (int)rintf(fminf(fmaxf(m, -1048576.f), 1048576.f))
-                                 : (has_up ? Fup - F : 0);
+      Dpend = (mi > (int)kDead) ? (mi < -1048576 ? -1048576 : mi) : (has_up ? Fup - F : 0);
     }
     slot_addr += chunk_bytes;
     full_addr += 8u;
@@ -404,7 +425,7 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
 }
 
 template <int R, bool STORE, int K>
-__global__ void __launch_bounds__(544, 1) lattice_kernel(
+__global__ void __launch_bounds__(K == 16 ? 288 : 544, 1) lattice_kernel(
     UttInfo* __restrict__ utt, const int* __restrict__ lab, int Lp, const float* __restrict__ em,
     float* __restrict__ alpha, float* __restrict__ beta, int* __restrict__ offA,
     int* __restrict__ offB, int Tfr, int Sp, int NWp, int NB, int zero_infinity, int nring) {
@@ -569,12 +590,21 @@ static int launch_lattice_r(const LossLayout& w, unsigned char* ws, int Tfr, int
   const size_t frame = (size_t)w.Lp * 4;
   int K = 8;
   if ((size_t)(w.NW + 1) * 8 * frame > budget) K = 4;
+  // short lattices: 16-step blocks halve the per-block hand-shaking (needs the registers
+  // of a <= 8-warp CTA; the pipeline skew between the warps grows to 16 steps)
+  static const int k16 = [] { const char* e = getenv("B200CTC_LAT_K16"); return e ? atoi(e) : 1; }();
+  if (k16 && R <= 4 && w.NW <= 8 && (size_t)(w.NW + 3) * 16 * frame <= budget) K = 16;
   B2_REQUIRE(2 * (size_t)K * frame <= budget, "ctc lattice: target too long for shared memory");
   int nring = (int)(budget / (K * frame));
   if (nring > kMaxEmRing) nring = kMaxEmRing;
   // keep small cases small: ~32 KB of emissions in flight is plenty
-  while (nring > w.NW + 2 && nring > 3 && (size_t)nring * K * frame > 32 * 1024) --nring;
+  static const int slack = [] { const char* e = getenv("B200CTC_LAT_SLACK"); return e ? atoi(e) : 2; }();
+  while (nring > w.NW + slack && nring > 3 && (size_t)nring * K * frame > 32 * 1024) --nring;
   const size_t smem = (size_t)nring * K * frame + fixed;
+  if (K == 16) {
+    if constexpr (R <= 4)
+      return launch_lattice_rk<R, 16>(w, ws, Tfr, zero_infinity, both_dirs, nring, smem, st);
+  }
   if (K == 8) return launch_lattice_rk<R, 8>(w, ws, Tfr, zero_infinity, both_dirs, nring, smem, st);
   return launch_lattice_rk<R, 4>(w, ws, Tfr, zero_infinity, both_dirs, nring, smem, st);
 }
