@@ -250,15 +250,13 @@ def run_gpu(args):
     x = host_logits.to(dev).requires_grad_(True)
     tg, il, tl = tg_h.to(dev), il_h.to(dev), tl_h.to(dev)
     module = CTC(V, 8).to(dev)
-    wbuf = torch.zeros(2, device=dev)
+    from espnet1_b200.sharded import reduce_sharded_mean
 
     def step():
         x.grad = None
         loss = module.loss_fn(x.transpose(0, 1), tg, il, tl, max_tgt_len=cfg["lmax"])
         if dist_on:  # [sum_b nll_b, B_local] -> global batch-weighted loss (2 floats over NCCL)
-            wbuf[0] = loss.detach() * B
-            wbuf[1] = B
-            dist.all_reduce(wbuf)
+            reduce_sharded_mean(loss, B)
         loss.backward()
         return loss
 

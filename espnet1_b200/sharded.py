@@ -22,10 +22,42 @@ def shard_range(n_items: int, rank: int, world: int):
     return lo, lo + base + (1 if rank < rem else 0)
 
 
+_CONST: dict = {}
+
+
+def _pack_consts(n_local: int, device: torch.device):
+    """Persistent [n, 0] and [0, n] device tensors: packing must not touch the host
+    (a Python scalar written into a CUDA tensor is a synchronous pageable H2D copy,
+    which stalls the launch queue of a 0.4 ms step)."""
+    key = (int(n_local), str(device))
+    c = _CONST.get(key)
+    if c is None:
+        c = (torch.tensor([float(n_local), 0.0], device=device),
+             torch.tensor([0.0, float(n_local)], device=device))
+        _CONST[key] = c
+    return c
+
+
 def pack_local(nll_local: torch.Tensor) -> torch.Tensor:
     """[sum of local per-utterance losses, local weight (= utterance count)]."""
-    return torch.stack([nll_local.float().sum(),
-                        torch.tensor(float(nll_local.numel()), device=nll_local.device)])
+    n = nll_local.numel()
+    scale, offs = _pack_consts(n, nll_local.device)
+    return torch.addcmul(offs, scale, nll_local.float().sum() / max(n, 1))
+
+
+def pack_local_mean(loss_mean: torch.Tensor, n_local: int) -> torch.Tensor:
+    """Same pair from the rank-local batch mean that ``CTC.forward`` returns
+    (espnet2/asr/ctc.py:56-60): [mean * n, n] in one launch, no host round trip."""
+    scale, offs = _pack_consts(n_local, loss_mean.device)
+    return torch.addcmul(offs, scale, loss_mean.detach().float())
+
+
+def reduce_sharded_mean(loss_mean: torch.Tensor, n_local: int, group=None):
+    """Global batch-weighted loss from the rank-local means (see reduce_sharded_loss)."""
+    buf = pack_local_mean(loss_mean, n_local)
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group)
+    return buf[0] / buf[1], buf[1]
 
 
 def reduce_sharded_loss(nll_local: torch.Tensor, group=None):
