@@ -39,6 +39,14 @@ SIGNATURES = {
                                  c_int, c_float, _P, _P, c_size_t, _P]),
     "b200ctc_loss_fwd_grad": (c_int, [_P, c_int, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int,
                                       c_int, c_float, _P, _P, c_float, _P, _P, c_size_t, _P]),
+    "b200ctc_loss_fwd_grad_sharded": (c_int, [_P, c_int, _P, _P, _P, _P, c_int, c_int, c_int, c_int,
+                                              c_int, c_int, c_float, _P, _P, c_float, _P, _P,
+                                              c_size_t, _P, _P, _P]),
+    "b200ctc_peer_create": (c_int, [c_int, c_int, _P, _P]),
+    "b200ctc_peer_connect": (c_int, [_P, _P]),
+    "b200ctc_peer_destroy": (c_int, [_P]),
+    "b200ctc_peer_error": (c_int, [_P]),
+    "b200ctc_peer_exchange": (c_int, [_P, _P, _P, _P]),
     "b200ctc_grad_rescale": (c_int, [_P, c_int, _P, c_int, c_float, c_float, c_int, c_int, c_int,
                                      _P]),
     "b200ctc_align_workspace_bytes": (c_size_t, [c_int, c_int]),

@@ -491,13 +491,22 @@ extern "C" int b200ctc_loss_fwd(const void* logits, int dtype, const int64_t* ta
 
 // forward + gradient in one call (eager mode): the logits are read ONCE in
 // full (row pass B); the lattice runs on a sparse gather of the label columns.
-extern "C" int b200ctc_loss_fwd_grad(const void* logits, int dtype, const int64_t* targets,
-                                     const int64_t* tgt_offsets, const int64_t* in_lens,
-                                     const int64_t* tgt_lens, int B, int T, int V,
-                                     int max_tgt_len, int blank, int zero_infinity,
-                                     float grad_hint, float* nll, float* loss_out,
-                                     float loss_scale, void* grad, void* ws_, size_t ws_bytes,
-                                     b200ctc_stream_t stream) {
+// peer != NULL: the batch-sharded variant - the kernel that finishes the loss also
+// all-reduces {sum of losses, utterance count} over the ranks through peer memory.
+static int loss_fwd_grad_impl(const void* logits, int dtype, const int64_t* targets,
+                              const int64_t* tgt_offsets, const int64_t* in_lens,
+                              const int64_t* tgt_lens, int B, int T, int V, int max_tgt_len,
+                              int blank, int zero_infinity, float grad_hint, float* nll,
+                              float* loss_out, float loss_scale, void* grad, void* ws_,
+                              size_t ws_bytes, b200ctc_stream_t stream, b200ctc_peer* peer,
+                              float* global_out) {
+  PeerDev pd{nullptr, 0, 0};
+  if (peer) {
+    B2_REQUIRE(peer->connected, "loss_fwd_grad_sharded: peer handle is not connected");
+    B2_REQUIRE(global_out, "loss_fwd_grad_sharded: null global_out");
+    B2_REQUIRE(B > 0, "loss_fwd_grad_sharded: a rank without utterances must call b200ctc_peer_exchange");
+    pd = PeerDev{peer->d_bufs, peer->world, peer->rank};
+  }
   LossLayout w;
   int rc = check_loss_args("loss_fwd_grad", logits, dtype, targets, tgt_offsets, in_lens, tgt_lens,
                            B, T, V, max_tgt_len, blank, nll, ws_, ws_bytes, &w);
@@ -560,5 +569,31 @@ extern "C" int b200ctc_loss_fwd_grad(const void* logits, int dtype, const int64_
     }
     if (rc) return rc;
   }
-  return launch_nll(w, ws, T, zero_infinity, nll, loss_out, loss_scale, st);
+  return launch_nll(w, ws, T, zero_infinity, nll, loss_out, loss_scale, st, pd, global_out);
+}
+
+extern "C" int b200ctc_loss_fwd_grad(const void* logits, int dtype, const int64_t* targets,
+                                     const int64_t* tgt_offsets, const int64_t* in_lens,
+                                     const int64_t* tgt_lens, int B, int T, int V,
+                                     int max_tgt_len, int blank, int zero_infinity,
+                                     float grad_hint, float* nll, float* loss_out,
+                                     float loss_scale, void* grad, void* ws, size_t ws_bytes,
+                                     b200ctc_stream_t stream) {
+  return loss_fwd_grad_impl(logits, dtype, targets, tgt_offsets, in_lens, tgt_lens, B, T, V,
+                            max_tgt_len, blank, zero_infinity, grad_hint, nll, loss_out, loss_scale,
+                            grad, ws, ws_bytes, stream, nullptr, nullptr);
+}
+
+extern "C" int b200ctc_loss_fwd_grad_sharded(const void* logits, int dtype, const int64_t* targets,
+                                             const int64_t* tgt_offsets, const int64_t* in_lens,
+                                             const int64_t* tgt_lens, int B, int T, int V,
+                                             int max_tgt_len, int blank, int zero_infinity,
+                                             float grad_hint, float* nll, float* loss_out,
+                                             float loss_scale, void* grad, void* ws,
+                                             size_t ws_bytes, b200ctc_peer* peer,
+                                             float* global_out, b200ctc_stream_t stream) {
+  B2_REQUIRE(peer, "loss_fwd_grad_sharded: null peer handle");
+  return loss_fwd_grad_impl(logits, dtype, targets, tgt_offsets, in_lens, tgt_lens, B, T, V,
+                            max_tgt_len, blank, zero_infinity, grad_hint, nll, loss_out, loss_scale,
+                            grad, ws, ws_bytes, stream, peer, global_out);
 }

@@ -20,6 +20,7 @@
 // chunks, full / empty mbarriers).
 #pragma once
 #include "ctc_ws.cuh"
+#include "peer.cuh"
 
 namespace b200ctc {
 
@@ -512,7 +513,8 @@ __global__ void __launch_bounds__(256) nll_kernel(const UttInfo* __restrict__ ut
                                                   const float* __restrict__ lse2, int Tfr,
                                                   int zero_infinity, float* __restrict__ nll,
                                                   float* __restrict__ loss_out, float loss_scale,
-                                                  int* __restrict__ counter) {
+                                                  int* __restrict__ counter, PeerDev peer,
+                                                  float* __restrict__ global_out) {
   __shared__ double dred[8];
   __shared__ int s_last;
   const int b = blockIdx.x, tid = threadIdx.x;
@@ -535,12 +537,12 @@ __global__ void __launch_bounds__(256) nll_kernel(const UttInfo* __restrict__ ut
     else v = (float)(-(u.lam + (double)u.aend + tot) * 0.6931471805599453);
     nll[b] = v;
     s_last = 0;
-    if (loss_out) {
+    if (loss_out || peer.bufs) {
       __threadfence();
       s_last = atomicAdd(counter, 1) == (int)gridDim.x - 1;
     }
   }
-  if (!loss_out) return;
+  if (!loss_out && !peer.bufs) return;
   __syncthreads();
   if (!s_last) return;
   __threadfence();
@@ -553,9 +555,15 @@ __global__ void __launch_bounds__(256) nll_kernel(const UttInfo* __restrict__ ut
   if (tid == 0) {
     double tot = 0.0;
     for (int i = 0; i < 8; ++i) tot += dred[i];
-    loss_out[0] = (float)(tot * (double)loss_scale);
+    if (loss_out) loss_out[0] = (float)(tot * (double)loss_scale);
+    dred[0] = tot;
     *counter = 0;  // ready for the next call on this workspace
   }
+  if (!peer.bufs) return;
+  // sharded training: the all-reduce of {sum of losses, utterance count} over the ranks
+  // is the tail of this kernel (peer.cuh) - pushed to the peers through NVLink, no launch
+  __syncthreads();
+  if (tid < 32) peer_exchange_warp(peer, (float)dred[0], (float)gridDim.x, global_out);
 }
 
 template <int R, int K>
@@ -621,12 +629,13 @@ static inline int launch_lattice(const LossLayout& w, unsigned char* ws, int Tfr
 }
 
 static inline int launch_nll(const LossLayout& w, unsigned char* ws, int Tfr, int zero_infinity,
-                             float* nll, float* loss_out, float loss_scale, cudaStream_t st) {
+                             float* nll, float* loss_out, float loss_scale, cudaStream_t st,
+                             PeerDev peer = PeerDev{nullptr, 0, 0}, float* global_out = nullptr) {
   launch_pdl(nll_kernel, dim3(w.B), dim3(256), 0, st, true,
              reinterpret_cast<const UttInfo*>(ws + w.utt),
              reinterpret_cast<const float*>(ws + w.cmax),
              reinterpret_cast<const float*>(ws + w.lse2), Tfr, zero_infinity, nll, loss_out,
-             loss_scale, reinterpret_cast<int*>(ws + w.counter));
+             loss_scale, reinterpret_cast<int*>(ws + w.counter), peer, global_out);
   count_launch();
   return check_launch("ctc nll");
 }

@@ -59,6 +59,10 @@ class CTC(torch.nn.Module):
             raise ValueError(f'ctc_type must be "builtin" or "gtnctc": {self.ctc_type}')
 
         self.reduce = reduce
+        # batch-sharded training: set to a sharded.PeerLossExchange and every loss_fn call also
+        # leaves the global batch-weighted loss of all ranks in `loss_exchange.out`
+        # (the all-reduce of trainer.py:604-613, fused into the loss kernel)
+        self.loss_exchange = None
 
     # same call convention as torch.nn.CTCLoss(reduction="none") but fed with
     # batch-major LOGITS: log-softmax is fused into the loss kernels.
@@ -66,7 +70,7 @@ class CTC(torch.nn.Module):
                           reduce_scale=None):
         return B.ctc_loss(logits_btv, th_target, th_ilen, th_olen, blank=0,
                           zero_infinity=self.zero_infinity, max_tgt_len=max_tgt_len,
-                          reduce_scale=reduce_scale)
+                          reduce_scale=reduce_scale, peer=self.loss_exchange)
 
     def loss_fn(self, th_pred, th_target, th_ilen, th_olen, max_tgt_len=None) -> torch.Tensor:
         """th_pred is (T, B, V) like the reference (:52); a transposed view of a

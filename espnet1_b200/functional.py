@@ -97,7 +97,7 @@ class _CTCLossFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, logits, targets, tgt_offsets, in_lens, tgt_lens, max_tgt_len, blank,
-                zero_infinity, grad_hint, eager, reduce_scale):
+                zero_infinity, grad_hint, eager, reduce_scale, peer=None):
         require_cuda(logits, "CTC logits")
         x = logits.contiguous()
         B, T, V = x.shape
@@ -112,13 +112,23 @@ class _CTCLossFn(torch.autograd.Function):
         scale = float(reduce_scale) if reduced else 0.0
         ctx.eager = bool(need_grad and eager and B > 0)
         ctx.gmul = float(reduce_scale) if reduced else 1.0
+        if peer is not None and not (ctx.eager):
+            raise RuntimeError("the fused sharded-loss exchange needs the eager gradient mode, logits "
+                               "that require a gradient and at least one utterance on every rank")
         if ctx.eager:
             grad = torch.empty_like(x)
-            check(lib().b200ctc_loss_fwd_grad(ptr(x), dtype_code(x), ptr(targets), ptr(tgt_offsets),
-                                              ptr(in_lens), ptr(tgt_lens), B, T, V, max_tgt_len,
-                                              blank, int(zero_infinity), grad_hint, ptr(nll),
-                                              ptr(loss), scale, ptr(grad), ptr(ws), nbytes,
-                                              stream_ptr(dev)), "loss_fwd_grad")
+            if peer is not None:  # sharded: the loss kernel also all-reduces {sum, B} over the ranks
+                check(lib().b200ctc_loss_fwd_grad_sharded(
+                    ptr(x), dtype_code(x), ptr(targets), ptr(tgt_offsets), ptr(in_lens),
+                    ptr(tgt_lens), B, T, V, max_tgt_len, blank, int(zero_infinity), grad_hint,
+                    ptr(nll), ptr(loss), scale, ptr(grad), ptr(ws), nbytes, peer.handle,
+                    ptr(peer.out), stream_ptr(dev)), "loss_fwd_grad_sharded")
+            else:
+                check(lib().b200ctc_loss_fwd_grad(ptr(x), dtype_code(x), ptr(targets),
+                                                  ptr(tgt_offsets), ptr(in_lens), ptr(tgt_lens), B, T,
+                                                  V, max_tgt_len, blank, int(zero_infinity), grad_hint,
+                                                  ptr(nll), ptr(loss), scale, ptr(grad), ptr(ws),
+                                                  nbytes, stream_ptr(dev)), "loss_fwd_grad")
             ctx.grad_buf = grad
             ctx.cfg = (B, T, V, grad_hint)
             return loss if reduced else nll
@@ -133,7 +143,7 @@ class _CTCLossFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g):
-        none10 = (None,) * 10
+        none10 = (None,) * 11
         gs, stride = _upstream(g)
         if ctx.eager:
             grad = ctx.grad_buf
@@ -163,7 +173,8 @@ def _f32_recip(n: int) -> float:
 
 def ctc_loss(logits, targets, in_lens, tgt_lens, blank: int = 0, zero_infinity: bool = True,
              max_tgt_len: int | None = None, tgt_offsets=None, grad_hint: float | None = None,
-             grad_mode: str = "eager", reduce_scale: float | None = None) -> torch.Tensor:
+             grad_mode: str = "eager", reduce_scale: float | None = None,
+             peer=None) -> torch.Tensor:
     """Per-utterance CTC negative log-likelihood from LOGITS.
 
     logits (B,T,V) batch-major activations (fp32/fp16/bf16, CUDA); targets 1-D
@@ -175,6 +186,9 @@ def ctc_loss(logits, targets, in_lens, tgt_lens, blank: int = 0, zero_infinity: 
     ``grad_hint``: the upstream gradient the caller expects for every nll[b]
     (default 1/B, i.e. ``nll.sum()/B``); any other upstream gradient is still
     exact, it only costs one rescaling pass.
+    ``peer``: a ``sharded.PeerLossExchange``; the kernel that finishes the loss then also
+    all-reduces [sum of losses, utterance count] over the data-parallel ranks through
+    NVLink peer memory and leaves [global mean loss, total count] in ``peer.out``.
     """
     require_cuda(logits, "CTC logits")
     if grad_mode not in ("eager", "deferred"):
@@ -191,7 +205,7 @@ def ctc_loss(logits, targets, in_lens, tgt_lens, blank: int = 0, zero_infinity: 
     return _CTCLossFn.apply(logits, tg_dev, tgt_offsets, il_dev, tl_dev, int(max_tgt_len),
                             int(blank), bool(zero_infinity), float(grad_hint),
                             grad_mode == "eager",
-                            None if reduce_scale is None else float(reduce_scale))
+                            None if reduce_scale is None else float(reduce_scale), peer)
 
 
 def forced_align(lp: torch.Tensor, target: torch.Tensor, blank: int = 0) -> torch.Tensor:

@@ -72,6 +72,69 @@ def reduce_sharded_loss(nll_local: torch.Tensor, group=None):
     return buf[0] / buf[1], buf[1]
 
 
+class PeerLossExchange:
+    """The sharded-loss all-reduce as the tail of the loss kernel (csrc/peer.cuh).
+
+    One per process and process group.  Construction is collective: every rank
+    creates a small exchange buffer on its GPU, the cudaIpc handles are
+    all-gathered through ``torch.distributed`` (plumbing) and mapped.  After
+    ``F.ctc_loss(..., peer=ex)`` (or ``CTC.loss_exchange = ex``) the two floats
+    ``ex.out`` = [global batch-weighted mean loss, total utterance count] are valid
+    on the stream of that call, identical on all ranks - the numbers of
+    ``reduce_sharded_loss`` without a collective launch or any host work.
+    """
+
+    def __init__(self, group=None, device=None):
+        import ctypes
+
+        from ._lib import check, lib
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else device
+        handle = ctypes.c_void_p()
+        raw = (ctypes.c_ubyte * 64)()
+        with torch.cuda.device(self.device):
+            check(lib().b200ctc_peer_create(self.world, self.rank, ctypes.byref(handle), raw),
+                  "peer_create")
+            self.handle = handle
+            mine = bytes(raw)
+            if self.world > 1:
+                gathered = [None] * self.world
+                dist.all_gather_object(gathered, mine, group=group)
+                blob = b"".join(gathered)
+            else:
+                blob = mine
+            buf = (ctypes.c_ubyte * len(blob)).from_buffer_copy(blob)
+            check(lib().b200ctc_peer_connect(self.handle, buf), "peer_connect")
+        self.out = torch.zeros(2, dtype=torch.float32, device=self.device)
+        if self.world > 1:
+            dist.barrier(group=group)  # every rank has mapped every buffer before the first push
+
+    def exchange(self, pair: torch.Tensor) -> torch.Tensor:
+        """Stand-alone collective on a device pair [sum, weight] (ranks without utterances)."""
+        from ._lib import check, lib, ptr, stream_ptr
+        pair = pair.to(device=self.device, dtype=torch.float32).contiguous()
+        check(lib().b200ctc_peer_exchange(self.handle, ptr(pair), ptr(self.out),
+                                          stream_ptr(self.device)), "peer_exchange")
+        return self.out
+
+    def timed_out(self) -> bool:
+        from ._lib import lib
+        return lib().b200ctc_peer_error(self.handle) != 0
+
+    def close(self):
+        from ._lib import lib
+        if getattr(self, "handle", None) is not None:
+            lib().b200ctc_peer_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):  # pragma: no cover - best effort
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
+
+
 def ddp_loss_for_backward(nll_local: torch.Tensor, group=None) -> torch.Tensor:
     """Loss whose backward reproduces the reference's DDP scaling: local mean
     times ``weight_local/weight_total * world_size`` (trainer.py:614-617), to be

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define B200CTC_ABI_VERSION 2
+#define B200CTC_ABI_VERSION 3
 
 #define B200CTC_OK 0
 #define B200CTC_ERR_ARG (-1)     /* bad argument (null pointer, size, dtype) */
@@ -122,6 +122,39 @@ int b200ctc_loss_fwd_grad(const void* logits, int dtype, const int64_t* targets,
                           float grad_hint, float* nll, float* loss_out,
                           float loss_scale, void* grad, void* ws, size_t ws_bytes,
                           b200ctc_stream_t stream);
+/* ---- (e) batch-sharded training: the loss all-reduce fused into the loss kernel
+ * replaces the per-step all-reduce of {loss*weight, weight} over the data-
+ * parallel ranks, espnet2/train/trainer.py:604-613 with
+ * espnet2/torch_utils/recursive_op.py:8-47 (one process per GPU, one node).
+ * A b200ctc_peer_t owns a small exchange buffer on the current device;
+ * peer_create returns its 64-byte cudaIpc handle, the caller all-gathers the
+ * handles of all ranks (any transport: torch.distributed, MPI, a file) and
+ * peer_connect maps them.  b200ctc_loss_fwd_grad_sharded is loss_fwd_grad whose
+ * final kernel ALSO pushes this rank's {sum_b nll_b, B} to every peer through
+ * NVLink peer stores, waits for theirs and writes
+ *   global_out[0] = sum_r sum_b nll / sum_r B_r ,  global_out[1] = sum_r B_r
+ * (bit-identical on all ranks: summed in rank order).  Collective semantics:
+ * every rank must make the same sequence of exchange calls; a rank with no
+ * utterances calls b200ctc_peer_exchange({0,0}).  A peer that does not show up
+ * within 5 s yields NaN and sets the sticky flag read by b200ctc_peer_error.  */
+typedef struct b200ctc_peer b200ctc_peer_t;
+int b200ctc_peer_create(int world, int rank, b200ctc_peer_t** out,
+                        unsigned char* handle_out /* 64 bytes */);
+int b200ctc_peer_connect(b200ctc_peer_t* peer,
+                         const unsigned char* all_handles /* world*64 bytes, rank order */);
+int b200ctc_peer_destroy(b200ctc_peer_t* peer);
+int b200ctc_peer_error(b200ctc_peer_t* peer); /* synchronises; 1 = a peer timed out */
+/* stand-alone exchange of a device pair {sum, weight} (same collective)       */
+int b200ctc_peer_exchange(b200ctc_peer_t* peer, const float* local_pair,
+                          float* global_out, b200ctc_stream_t stream);
+int b200ctc_loss_fwd_grad_sharded(const void* logits, int dtype, const int64_t* targets,
+                                  const int64_t* tgt_offsets, const int64_t* in_lens,
+                                  const int64_t* tgt_lens, int B, int T, int V,
+                                  int max_tgt_len, int blank, int zero_infinity,
+                                  float grad_hint, float* nll, float* loss_out,
+                                  float loss_scale, void* grad, void* ws,
+                                  size_t ws_bytes, b200ctc_peer_t* peer,
+                                  float* global_out, b200ctc_stream_t stream);
 /* grad *= gscale[b*gscale_stride] * gscale_mul / grad_hint (no-op when equal)  */
 int b200ctc_grad_rescale(void* grad, int dtype, const float* gscale,
                          int gscale_stride, float gscale_mul, float grad_hint,

@@ -49,7 +49,10 @@ def timeit(fn, n=30):
     return (time.perf_counter() - t0) / n * 1e3, cpu_issue * 1e3
 
 
-for mode, name in [(0, "no dist ops"), (1, "pack only"), (2, "pack + all_reduce")]:
+from espnet1_b200.sharded import PeerLossExchange
+ex = PeerLossExchange()
+for mode, name in [(0, "no dist ops"), (1, "pack only"), (2, "pack + all_reduce"), (3, "fused peer exchange")]:
+    m.loss_exchange = ex if mode == 3 else None
     ms, issue = timeit(lambda: step(mode))
     if rank == 0:
         print(f"{name:22s}: {ms:.3f} ms/step (CPU issue {issue:.3f} ms)", flush=True)
