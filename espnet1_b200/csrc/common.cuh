@@ -20,10 +20,16 @@ int sm_count();
 // 4 prefix_step, 5 softmax family
 constexpr int kProfPhases = 8;
 void prof_mark(int phase, int end, cudaStream_t st);
+// where a kernel fires griddepcontrol.launch_dependents (tuning: B200CTC_PDL_MODE):
+// 0 = at its start, 1 = at its end, 2 = never (implicit at completion)
+static inline int pdl_mode() {
+  static const int m = [] { const char* e = getenv("B200CTC_PDL_MODE"); return e ? atoi(e) : 2; }();
+  return m;
+}
 
 template <typename... KArgs, typename... Args>
 static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
-                                     cudaStream_t st, bool pdl, Args&&... args) {
+                                     cudaStream_t st, int pdl_bit, Args&&... args) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = block;
@@ -33,11 +39,14 @@ static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 b
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  // Opt-in (B200CTC_PDL=1).  Measured on B200 at C2: early-resident lattice CTAs are
-  // placed wherever the gather leaves room, several per SM, and the latency-bound
-  // recursion then shares issue slots: 0.495 ms/step with PDL vs 0.418 without.
-  static const int pdl_mask = [] { const char* e = getenv("B200CTC_PDL"); return e ? atoi(e) : 0; }();
-  cfg.numAttrs = (pdl && pdl_mask) ? 1 : 0;
+  // Programmatic stream serialisation on the lattice (bit 0), the gradient row pass
+  // (bit 1) and nll (bit 2).  Measured on B200 at C2 (profiles/README.md): with the
+  // trigger at the START of the primary, early-resident lattice CTAs land several per SM
+  // beside the running gather and the latency-bound recursion shares issue slots
+  // (0.405 ms/step); with the trigger at the end, or never (implicit at completion, the
+  // default), the kernel boundaries just get cheaper: 0.386 vs 0.393 ms without.
+  static const int pdl_mask = [] { const char* e = getenv("B200CTC_PDL"); return e ? atoi(e) : 7; }();
+  cfg.numAttrs = (pdl_bit >= 0 && ((pdl_mask >> pdl_bit) & 1)) ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 

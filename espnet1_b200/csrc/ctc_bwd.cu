@@ -18,7 +18,8 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
     int Lp, int Sp, int NWp, int NB, int wshift, float* __restrict__ lse2, const float* __restrict__ cmax,
     const float* __restrict__ alpha, const float* __restrict__ beta,
     const int* __restrict__ offA, const int* __restrict__ offB,
-    const float* __restrict__ gscale, int gstride, float gmul, int nstage, int stage_stride) {
+    const float* __restrict__ gscale, int gstride, float gmul, int nstage, int stage_stride,
+    int pdl) {
   constexpr int N = Elems<T>::N;
   constexpr int NWARP = NT / 32;
   extern __shared__ __align__(128) unsigned char dsm[];
@@ -46,7 +47,7 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
       pc.next();
     }
   };
-  griddep_launch();  // PDL: nll_kernel may queue up behind this grid
+  if (pdl == 0) griddep_launch();  // PDL: nll_kernel may queue up behind this grid
   if (TMA) {
     if (tid == 0) {
       for (int i = 0; i < nstage; ++i) mbar_init(&bars[i], 1);
@@ -228,6 +229,7 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
     if (TMA && tid == 0) issue_next();
     ++n;
   }
+  if (pdl == 1) griddep_launch();
 }
 
 template <typename T, int NT>
@@ -250,14 +252,14 @@ static int launch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, 
     launch_pdl(
         // (no PDL here: a persistent grid must not become resident piecemeal beside
         //  the still-running lattice - late CTAs would form a second wave)
-        k, dim3((unsigned)grid), dim3(NT), smem, st, false,
+        k, dim3((unsigned)grid), dim3(NT), smem, st, 1,
         static_cast<const T*>(logits), static_cast<T*>(grad), B, Tfr, V, blank,
         reinterpret_cast<const UttInfo*>(ws + w.utt), reinterpret_cast<const int*>(ws + w.lab),
         reinterpret_cast<const int*>(ws + w.dup), w.Lp, w.Sp, w.NW, w.NB, wshift,
         reinterpret_cast<float*>(ws + w.lse2), reinterpret_cast<const float*>(ws + w.cmax),
         reinterpret_cast<const float*>(ws + w.alpha), reinterpret_cast<const float*>(ws + w.beta),
         reinterpret_cast<const int*>(ws + w.offA), reinterpret_cast<const int*>(ws + w.offB),
-        gscale, gstride, gmul, c.nstage, c.stride);
+        gscale, gstride, gmul, c.nstage, c.stride, pdl_mode());
   };
   if (c.tma) go(grad_rows_kernel<T, NT, PER, true>);
   else go(grad_rows_kernel<T, NT, PER, false>);

@@ -112,9 +112,14 @@ constexpr int kGatherRegs = 8;   // values kept in registers per lane and row (L
 
 template <typename T>
 __global__ void __launch_bounds__(kGatherWarps * 32) gather_kernel(
-    const T* __restrict__ logits, PrepArgs P, float* __restrict__ em, float* __restrict__ cmax) {
+    const T* __restrict__ logits, PrepArgs P, float* __restrict__ em, float* __restrict__ cmax,
+    int pdl) {
   extern __shared__ int slab[];  // [Lp] label columns of this utterance
-  griddep_launch();  // the lattice CTAs may become resident and set up meanwhile
+  if (pdl == 0) griddep_launch();  // the lattice CTAs may become resident and set up meanwhile
+  struct AtExit {  // every return path below fires the end-of-kernel trigger
+    int pdl;
+    __device__ ~AtExit() { if (pdl == 1) griddep_launch(); }
+  } at_exit{pdl};
   const int b = blockIdx.y;
   int Tb, L;
   prep_utterance(P, b, slab, blockIdx.x == 0, Tb, L);
@@ -187,7 +192,7 @@ static int launch_gather(const void* logits, const PrepArgs& P, int B, const Los
   if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   k<<<grid, kGatherWarps * 32, smem, st>>>(static_cast<const T*>(logits), P,
                                            reinterpret_cast<float*>(ws + w.em),
-                                           reinterpret_cast<float*>(ws + w.cmax));
+                                           reinterpret_cast<float*>(ws + w.cmax), pdl_mode());
   count_launch();
   return check_launch("ctc gather");
 }

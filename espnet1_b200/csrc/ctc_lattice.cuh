@@ -429,7 +429,7 @@ template <int R, bool STORE, int K>
 __global__ void __launch_bounds__(K == 16 ? 288 : 544, 1) lattice_kernel(
     UttInfo* __restrict__ utt, const int* __restrict__ lab, int Lp, const float* __restrict__ em,
     float* __restrict__ alpha, float* __restrict__ beta, int* __restrict__ offA,
-    int* __restrict__ offB, int Tfr, int Sp, int NWp, int NB, int zero_infinity, int nring) {
+    int* __restrict__ offB, int Tfr, int Sp, int NWp, int NB, int zero_infinity, int nring, int pdl) {
   static_assert(R % 2 == 0, "R must be even: even recursion positions are blanks");
   extern __shared__ __align__(128) float lsm[];  // em ring [nring][K*Lp] | vals | fring | ready | cons
   __shared__ __align__(8) uint64_t bars[2 * kMaxEmRing];  // full[], empty[]
@@ -438,8 +438,8 @@ __global__ void __launch_bounds__(K == 16 ? 288 : 544, 1) lattice_kernel(
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int NW = (blockDim.x >> 5) - 1;  // compute warps; warp NW is the TMA producer
   const int b = blockIdx.x, dir = blockIdx.y;
-  griddep_launch();  // PDL: let the gradient row pass become resident behind us
-  griddep_wait();    // utt / lab / em come from the previous kernel
+  if (pdl == 0) griddep_launch();  // PDL: let the gradient row pass become resident behind us
+  griddep_wait();                  // utt / lab / em come from the previous kernel
   const int Tb = utt[b].T, L = utt[b].L, S = 2 * L + 1;
   if (Tb == 0) {
     if (dir == 0 && tid == 0) {
@@ -502,6 +502,7 @@ __global__ void __launch_bounds__(K == 16 ? 288 : 544, 1) lattice_kernel(
   A.nw_live = nw_live; A.zero_infinity = zero_infinity; A.b = b; A.nring = nring;
   if (dir == 0) lattice_warp<R, STORE, 0, K>(A, wid, lane);
   else lattice_warp<R, STORE, 1, K>(A, wid, lane);
+  if (pdl == 1 && wid == nw_live - 1) griddep_launch();  // the last warp of the pipeline is done
 }
 
 // nll[b] = -ln2 * (lam + aend + sum_t (c[t] - lse2[t]))   (ctc_ws.cuh)
@@ -574,11 +575,12 @@ static int launch_lattice_rk(const LossLayout& w, unsigned char* ws, int Tfr, in
   auto go = [&](auto k) {
     if (smem > 48 * 1024)
       cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    launch_pdl(k, grid, dim3(nt), smem, st, true, reinterpret_cast<UttInfo*>(ws + w.utt),
+    launch_pdl(k, grid, dim3(nt), smem, st, 0, reinterpret_cast<UttInfo*>(ws + w.utt),
                reinterpret_cast<const int*>(ws + w.lab), w.Lp,
                reinterpret_cast<const float*>(ws + w.em), reinterpret_cast<float*>(ws + w.alpha),
                reinterpret_cast<float*>(ws + w.beta), reinterpret_cast<int*>(ws + w.offA),
-               reinterpret_cast<int*>(ws + w.offB), Tfr, w.Sp, w.NW, w.NB, zero_infinity, nring);
+               reinterpret_cast<int*>(ws + w.offB), Tfr, w.Sp, w.NW, w.NB, zero_infinity, nring,
+               pdl_mode());
   };
   if (both_dirs) go(lattice_kernel<R, true, K>);
   else go(lattice_kernel<R, false, K>);
@@ -631,7 +633,7 @@ static inline int launch_lattice(const LossLayout& w, unsigned char* ws, int Tfr
 static inline int launch_nll(const LossLayout& w, unsigned char* ws, int Tfr, int zero_infinity,
                              float* nll, float* loss_out, float loss_scale, cudaStream_t st,
                              PeerDev peer = PeerDev{nullptr, 0, 0}, float* global_out = nullptr) {
-  launch_pdl(nll_kernel, dim3(w.B), dim3(256), 0, st, true,
+  launch_pdl(nll_kernel, dim3(w.B), dim3(256), 0, st, 2,
              reinterpret_cast<const UttInfo*>(ws + w.utt),
              reinterpret_cast<const float*>(ws + w.cmax),
              reinterpret_cast<const float*>(ws + w.lse2), Tfr, zero_infinity, nll, loss_out,
