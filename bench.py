@@ -186,20 +186,23 @@ def bench_prefix(dev, steps=20):
                                          ("fullvocab_margin20", None, 20, 3, 0)):
         sc = CTCPrefixScoreTH(lpz.clone().to(dev), xl, 0, V - 1, margin=margin)
         pre = [inputs(i, snum, margin, dev) for i in range(n + 1)]
-        y = [[V - 1] * 1 for _ in range(B * W)]
-        state, ms = None, []
-        for i in range(n + 1):
-            part, att, best = pre[i]
-            yy = [[V - 1] * (i + 1) for _ in range(B * W)]
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            _, st5 = sc(yy, state, part, att)
-            state = sc.index_select_state(st5, best)
+        # prefixes as a device tensor, as BatchBeamSearch passes them (batch_beam_search.py:
+        # hyp.yseq); steps are issued back to back and timed as one region (CUDA events),
+        # the way a beam search issues them - only the margin>0 window read-back syncs
+        ys = [torch.full((B * W, i + 1), V - 1, dtype=torch.int64, device=dev) for i in range(n + 1)]
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for rep in range(2):  # first pass: warm-up (the caching allocator grows its pools)
+            state = None
+            for i in range(n + 1):
+                part, att, best = pre[i]
+                if i == 1 and rep == 1:
+                    e0.record()
+                _, st5 = sc(ys[i], state, part, att)
+                state = sc.index_select_state(st5, best)
+                del st5
             e1.record()
             torch.cuda.synchronize(dev)
-            if i > 0:
-                ms.append(e0.elapsed_time(e1))
-            del st5
+        ms = [e0.elapsed_time(e1) / n] * n
         entry = {"gpu_ms_per_step": sum(ms) / len(ms), "gpu_steps_per_s": 1e3 * len(ms) / sum(ms)}
         if n_cpu:
             ora = PrefixOracle(lpz.clone(), xl, 0, V - 1, margin)

@@ -54,7 +54,8 @@ SIGNATURES = {
     "b200ctc_prefix_pad": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_float, _P]),
     "b200ctc_prefix_init_state": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, c_float, _P, _P]),
     "b200ctc_prefix_window": (c_int, [_P, c_int, c_int, _P, _P]),
-    "b200ctc_prefix_step": (c_int, [_P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int,
+    "b200ctc_prefix_transpose": (c_int, [_P, _P, c_int, c_int, c_int, _P]),
+    "b200ctc_prefix_step": (c_int, [_P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int,
                                     c_int, c_int, c_int, c_int, c_int, c_float, _P, _P, _P, _P,
                                     _P, _P]),
     "b200ctc_prefix_select": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int,

@@ -3,7 +3,14 @@
 // reference (:156-161, ~6 kernel launches per frame there) runs inside ONE
 // kernel launch per beam step; psi is accumulated on the fly.
 // Arithmetic follows the reference formulas in fp32 with its finite log-zero
-// (-1e10, sticky under fp32 addition) and torch.logsumexp's max-shift form.
+// (-1e10, sticky under fp32 addition) in the max-shift form m + log(1 + e^-|a-b|).
+//
+// The step is a dependent chain of T log-sum-exps per thread (latency-bound: ~60 cycles
+// per frame), so everything else is kept off it: the frame's inputs (x_t[k], x_t[blank],
+// phi_{t-1}) are fetched kPF frames ahead into registers, and with a pre-beam
+// (snum << V) x_t[k] comes from a TIME-CONTIGUOUS copy of the posteriors (B,V,T) made
+// once per utterance batch - one cache line then serves 32 frames of a thread instead
+// of one.  Full-vocabulary scoring reads the (B,T,V) rows directly (coalesced over k).
 #include "common.cuh"
 
 namespace b200ctc {
@@ -11,6 +18,26 @@ namespace b200ctc {
 __device__ __forceinline__ float lse2f(float a, float b) {
   const float m = fmaxf(a, b);
   return m + logf(expf(a - m) + expf(b - m));
+}
+// same value up to rounding on the MUFU units (ex2 / lg2): 2 transcendental ops per call
+__device__ __forceinline__ float lse2_mufu(float a, float b) {
+  return fmaxf(a, b) + __logf(1.f + __expf(-fabsf(a - b)));
+}
+
+// (B,T,V) -> (B,V,T) tiled transpose (32x32 tiles through shared memory)
+__global__ void __launch_bounds__(256) prefix_transpose_kernel(const float* __restrict__ in,
+                                                               float* __restrict__ out, int T,
+                                                               int V) {
+  __shared__ float tile[32][33];
+  const int b = blockIdx.z, v0 = blockIdx.x * 32, t0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 8 rows per pass
+  const float* src = in + (size_t)b * T * V;
+  float* dst = out + (size_t)b * V * T;
+  for (int r = ty; r < 32; r += 8)
+    if (t0 + r < T && v0 + tx < V) tile[r][tx] = src[(size_t)(t0 + r) * V + v0 + tx];
+  __syncthreads();
+  for (int r = ty; r < 32; r += 8)
+    if (v0 + r < V && t0 + tx < T) dst[(size_t)(v0 + r) * T + t0 + tx] = tile[tx][r];
 }
 
 // frames t >= xlens[b]: every label logzero, blank 0   (:47-50)
@@ -51,16 +78,25 @@ __global__ void __launch_bounds__(32) prefix_init_kernel(const float* __restrict
 }
 
 // f_arg[h] = sum_t att_w[h,t] * t ; min / max over h   (:145-147)
-__global__ void __launch_bounds__(256) prefix_window_kernel(const float* __restrict__ att_w,
-                                                            int n_bh, int T,
-                                                            float* __restrict__ minmax) {
-  __shared__ float smin[8], smax[8];
+// one warp per hypothesis row, 32 warps; a row's loads are all in flight before the
+// (fixed-order) accumulation starts
+constexpr int kWinWarps = 32;
+__global__ void __launch_bounds__(kWinWarps * 32) prefix_window_kernel(
+    const float* __restrict__ att_w, int n_bh, int T, float* __restrict__ minmax) {
+  __shared__ float smin[kWinWarps], smax[kWinWarps];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   float lo = -kNegInf, hi = kNegInf;
-  for (int h = wid; h < n_bh; h += 8) {
+  for (int h = wid; h < n_bh; h += kWinWarps) {
     const float* row = att_w + (size_t)h * T;
     float acc = 0.f;
-    for (int t = lane; t < T; t += 32) acc = fmaf(row[t], (float)t, acc);
+    for (int t0 = lane; t0 < T; t0 += 32 * 16) {
+      float v[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) v[j] = (t0 + 32 * j < T) ? __ldg(row + t0 + 32 * j) : 0.f;
+#pragma unroll
+      for (int j = 0; j < 16; ++j)
+        if (t0 + 32 * j < T) acc = fmaf(v[j], (float)(t0 + 32 * j), acc);
+    }
     acc = warp_sum(acc);
     lo = fminf(lo, acc);
     hi = fmaxf(hi, acc);
@@ -68,7 +104,7 @@ __global__ void __launch_bounds__(256) prefix_window_kernel(const float* __restr
   if (lane == 0) { smin[wid] = lo; smax[wid] = hi; }
   __syncthreads();
   if (threadIdx.x == 0) {
-    for (int i = 1; i < 8; ++i) { lo = fminf(lo, smin[i]); hi = fmaxf(hi, smax[i]); }
+    for (int i = 1; i < kWinWarps; ++i) { lo = fminf(lo, smin[i]); hi = fmaxf(hi, smax[i]); }
     minmax[0] = lo;
     minmax[1] = hi;
   }
@@ -99,53 +135,81 @@ __global__ void __launch_bounds__(256) prefix_fill_kernel(
   idmap[i] = -1;
 }
 
+constexpr int kPF = 16;  // frames fetched ahead of the recursion
+
+// TC: lp_t is the time-contiguous copy (B,V,T); else lp rows (B,T,V) are read directly
+template <bool TC>
 __global__ void __launch_bounds__(128) prefix_step_kernel(
-    const float* __restrict__ lp, const float* __restrict__ r_prev, const float* __restrict__ rsum,
-    const float* __restrict__ s_prev, const int64_t* __restrict__ last_ids,
-    const int64_t* __restrict__ scoring_ids, const int64_t* __restrict__ end_frames, int n_bh,
-    int n_hyps, int T, int V, int snum, int out_len, int start, int end, int blank, int eos,
-    float logzero, float* __restrict__ r, float* __restrict__ log_psi, float* __restrict__ scores,
-    int64_t* __restrict__ idmap) {
+    const float* __restrict__ lp, const float* __restrict__ lp_t, const float* __restrict__ r_prev,
+    const float* __restrict__ rsum, const float* __restrict__ s_prev,
+    const int64_t* __restrict__ last_ids, const int64_t* __restrict__ scoring_ids,
+    const int64_t* __restrict__ end_frames, int n_bh, int n_hyps, int T, int V, int snum,
+    int out_len, int start, int end, int blank, int eos, float logzero, float* __restrict__ r,
+    float* __restrict__ log_psi, float* __restrict__ scores, int64_t* __restrict__ idmap) {
   const size_t idx = (size_t)blockIdx.x * 128 + threadIdx.x;
   if (idx >= (size_t)n_bh * snum) return;
   const int h = (int)(idx / snum);
   const int b = h / n_hyps;
   const int k = scoring_ids ? (int)scoring_ids[idx] : (int)(idx - (size_t)h * snum);
   const bool same = (k == (int)last_ids[h]);
-  const float* xk = lp + (size_t)b * T * V + k;       // stride V over frames
-  const float* xb = lp + (size_t)b * T * V + blank;
-  const size_t plane = (size_t)n_bh * snum;           // one (t, n|b) plane of r
+  // per-frame input streams: x_t[k], x_t[blank], phi_{t-1} (= r^b_prev if k repeats the
+  // last label, else logsumexp(r^n_prev, r^b_prev), :132-141) with their strides over t
+  const float* xk = TC ? lp_t + ((size_t)b * V + k) * T : lp + (size_t)b * T * V + k;
+  const float* xb = TC ? lp_t + ((size_t)b * V + blank) * T : lp + (size_t)b * T * V + blank;
+  const size_t xs = TC ? 1 : (size_t)V;
+  const float* ph = same ? r_prev + n_bh + h : rsum + h;
+  const size_t phs = same ? 2 * (size_t)n_bh : (size_t)n_bh;
+  const size_t plane = (size_t)n_bh * snum;  // one (t, n|b) plane of r
   float* rout = r + idx;
   // frames before the window stay logzero; r^n_0 = x_0[k] for the empty prefix (:129-130)
   float rn = logzero, rb = logzero;
   for (int t = 0; t < start; ++t) {
     const float v0 = (t == 0 && out_len == 0) ? xk[0] : logzero;
-    rout[((size_t)t * 2 + 0) * plane] = v0;
-    rout[((size_t)t * 2 + 1) * plane] = logzero;
+    __stcs(rout + ((size_t)t * 2 + 0) * plane, v0);
+    __stcs(rout + ((size_t)t * 2 + 1) * plane, logzero);
     if (t == start - 1) rn = v0;
   }
-  // psi = logsumexp({phi_{t-1} + x_t[k]}_{t in window} U {r^n_{start-1}})  (:164-179)
+  // psi = logsumexp({phi_{t-1} + x_t[k]}_{t in window} U {r^n_{start-1}})  (:164-179),
+  // accumulated on line as (running max pm, sum ps of e^(term - pm))
   float pm = rn, ps = 1.f;
-  for (int t = start; t < end; ++t) {
-    const float x_k = xk[(size_t)t * V];
-    const float x_b = xb[(size_t)t * V];
-    const float phi = same ? r_prev[((size_t)(t - 1) * 2 + 1) * n_bh + h]
-                           : rsum[(size_t)(t - 1) * n_bh + h];
-    const float rn_new = lse2f(rn, phi) + x_k;
-    const float rb_new = lse2f(rn, rb) + x_b;
-    const float term = phi + x_k;
-    if (term > pm) { ps = ps * expf(pm - term) + 1.f; pm = term; }
-    else ps += expf(term - pm);
-    rout[((size_t)t * 2 + 0) * plane] = rn_new;
-    rout[((size_t)t * 2 + 1) * plane] = rb_new;
-    rn = rn_new;
-    rb = rb_new;
+  float cx[kPF], cb[kPF], cp[kPF];
+  auto fetch = [&](int t0) {  // clamped: always a valid address, values beyond `end` unused
+#pragma unroll
+    for (int j = 0; j < kPF; ++j) {
+      const int t = (t0 + j < end) ? t0 + j : end - 1;
+      cx[j] = __ldg(xk + (size_t)t * xs);
+      cb[j] = __ldg(xb + (size_t)t * xs);
+      cp[j] = __ldg(ph + (size_t)(t - 1) * phs);
+    }
+  };
+  if (start < end) fetch(start);
+  for (int t0 = start; t0 < end; t0 += kPF) {
+    float x_k[kPF], x_b[kPF], phi[kPF];
+#pragma unroll
+    for (int j = 0; j < kPF; ++j) { x_k[j] = cx[j]; x_b[j] = cb[j]; phi[j] = cp[j]; }
+    if (t0 + kPF < end) fetch(t0 + kPF);  // next group: in flight while this one is computed
+#pragma unroll
+    for (int j = 0; j < kPF; ++j) {
+      const int t = t0 + j;
+      if (t < end) {
+        const float rn_new = lse2_mufu(rn, phi[j]) + x_k[j];
+        const float rb_new = lse2_mufu(rn, rb) + x_b[j];
+        const float term = phi[j] + x_k[j];
+        const float m2 = fmaxf(pm, term);
+        ps = ps * __expf(pm - m2) + __expf(term - m2);
+        pm = m2;
+        __stcs(rout + ((size_t)t * 2 + 0) * plane, rn_new);
+        __stcs(rout + ((size_t)t * 2 + 1) * plane, rb_new);
+        rn = rn_new;
+        rb = rb_new;
+      }
+    }
   }
   for (int t = end; t < T; ++t) {
-    rout[((size_t)t * 2 + 0) * plane] = logzero;
-    rout[((size_t)t * 2 + 1) * plane] = logzero;
+    __stcs(rout + ((size_t)t * 2 + 0) * plane, logzero);
+    __stcs(rout + ((size_t)t * 2 + 1) * plane, logzero);
   }
-  float psi = pm + logf(ps);
+  float psi = pm + __logf(ps);
   const size_t o = (size_t)h * V + k;
   if (scoring_ids) {
     idmap[o] = (int64_t)(idx - (size_t)h * snum);
@@ -221,12 +285,26 @@ extern "C" int b200ctc_prefix_init_state(const float* lp, int B, int T, int V, i
 extern "C" int b200ctc_prefix_window(const float* att_w, int n_bh, int T, float* minmax,
                                      b200ctc_stream_t stream) {
   B2_REQUIRE(att_w && minmax && n_bh > 0 && T > 0, "prefix_window: bad argument");
-  prefix_window_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(att_w, n_bh, T, minmax);
+  prefix_window_kernel<<<1, kWinWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(att_w, n_bh, T,
+                                                                                    minmax);
   count_launch();
   return check_launch("prefix_window");
 }
 
-extern "C" int b200ctc_prefix_step(const float* lp, const float* r_prev, const float* s_prev,
+extern "C" int b200ctc_prefix_transpose(const float* lp, float* lp_t, int B, int T, int V,
+                                        b200ctc_stream_t stream) {
+  B2_REQUIRE(lp && lp_t, "prefix_transpose: null pointer");
+  B2_REQUIRE(B >= 0 && T >= 0 && V > 0, "prefix_transpose: bad shape");
+  if (B == 0 || T == 0) return B200CTC_OK;
+  B2_REQUIRE(B <= 65535 && (T + 31) / 32 <= 65535, "prefix_transpose: shape too large");
+  prefix_transpose_kernel<<<dim3((V + 31) / 32, (T + 31) / 32, B), 256, 0,
+                            static_cast<cudaStream_t>(stream)>>>(lp, lp_t, T, V);
+  count_launch();
+  return check_launch("prefix_transpose");
+}
+
+extern "C" int b200ctc_prefix_step(const float* lp, const float* lp_t, const float* r_prev,
+                                   const float* s_prev,
                                    const int64_t* last_ids, const int64_t* scoring_ids,
                                    const int64_t* end_frames, int B, int n_hyps, int T, int V,
                                    int snum, int out_len, int start, int end, int blank, int eos,
@@ -249,9 +327,15 @@ extern "C" int b200ctc_prefix_step(const float* lp, const float* r_prev, const f
         rsum_ws, s_prev, end_frames, n_bh, n_hyps, V, blank, eos, logzero, log_psi, scores, idmap);
     count_launch();
   }
-  prefix_step_kernel<<<blocks((size_t)n_bh * snum, 128), 128, 0, st>>>(
-      lp, r_prev, rsum_ws, s_prev, last_ids, scoring_ids, end_frames, n_bh, n_hyps, T, V, snum,
-      out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap);
+  // the time-contiguous copy pays off when few of the V columns are touched per hypothesis
+  if (lp_t && scoring_ids)
+    prefix_step_kernel<true><<<blocks((size_t)n_bh * snum, 128), 128, 0, st>>>(
+        lp, lp_t, r_prev, rsum_ws, s_prev, last_ids, scoring_ids, end_frames, n_bh, n_hyps, T, V,
+        snum, out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap);
+  else
+    prefix_step_kernel<false><<<blocks((size_t)n_bh * snum, 128), 128, 0, st>>>(
+        lp, lp_t, r_prev, rsum_ws, s_prev, last_ids, scoring_ids, end_frames, n_bh, n_hyps, T, V,
+        snum, out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap);
   count_launch();
   prof_mark(4, 1, st);
   return check_launch("prefix_step");

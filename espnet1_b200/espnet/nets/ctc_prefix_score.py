@@ -60,6 +60,15 @@ class CTCPrefixScoreTH(object):
             if not inplace:  # keep the reference's side effect on the caller's tensor (:47-50)
                 x.copy_(lp.to(x.dtype))
         self._lp = lp
+        self._lp_t = None  # (B, V, T) time-contiguous copy, made on the first pre-beam step
+
+    def _time_contiguous(self):
+        if self._lp_t is None:
+            B, T, V = self._lp.shape
+            self._lp_t = torch.empty(B, V, T, dtype=torch.float32, device=self.device)
+            check(lib().b200ctc_prefix_transpose(ptr(self._lp), ptr(self._lp_t), B, T, V,
+                                                 stream_ptr(self.device)), "prefix_transpose")
+        return self._lp_t
 
     @property
     def x(self):
@@ -131,7 +140,8 @@ class CTCPrefixScoreTH(object):
         log_psi = torch.empty(n_bh, V, dtype=torch.float32, device=dev)
         scores = torch.empty(n_bh, V, dtype=torch.float32, device=dev)
         rsum = torch.empty(T, n_bh, dtype=torch.float32, device=dev)
-        check(lib().b200ctc_prefix_step(ptr(self._lp), ptr(r_prev), ptr(s_prev), ptr(last_ids),
+        lp_t = self._time_contiguous() if ids is not None else None
+        check(lib().b200ctc_prefix_step(ptr(self._lp), ptr(lp_t), ptr(r_prev), ptr(s_prev), ptr(last_ids),
                                         ptr(ids), ptr(self._end_frames_dev), self.batch, n_hyps,
                                         T, V, snum, output_length, start, end, self.blank,
                                         self.eos, self.logzero, ptr(r), ptr(log_psi), ptr(scores),
@@ -175,6 +185,7 @@ class CTCPrefixScoreTH(object):
             new = x.to(torch.float32).contiguous().clone()
             new[:, : old.shape[1]] = old  # keep the already-scored prefix (:238)
             self._lp = new
+            self._lp_t = None
             self.input_length = x.size(1)
             self.end_frames = torch.as_tensor([x.size(1)]) - 1
             self._xlens_dev = torch.full((self.batch,), x.size(1), dtype=torch.int64,

@@ -182,12 +182,19 @@ int b200ctc_prefix_init_state(const float* lp, int B, int T, int V, int n_hyps,
  * minmax[0]=min_h f_arg, minmax[1]=max_h f_arg (fp32).                        */
 int b200ctc_prefix_window(const float* att_w, int n_bh, int T, float* minmax,
                           b200ctc_stream_t stream);
+/* time-contiguous copy of the padded posteriors: lp (B,T,V) -> lp_t (B,V,T).
+ * Made once per utterance batch (after prefix_pad); lets a pre-beam scoring
+ * step read one cache line per 32 frames of a candidate instead of one each. */
+int b200ctc_prefix_transpose(const float* lp, float* lp_t, int B, int T, int V,
+                             b200ctc_stream_t stream);
 /* one scoring step (__call__, :68-187) over frames [start,end).
+ *  lp (B,T,V) ; lp_t (B,V,T) from prefix_transpose or NULL ;
  *  r_prev (T,2,n_bh) ; s_prev (n_bh,V) or NULL (=0) ; last_ids (n_bh) ;
  *  scoring_ids (n_bh,snum) or NULL (then snum must equal V) ;
  *  outputs: r (T,2,n_bh,snum), log_psi (n_bh,V), scores (n_bh,V),
  *  idmap (n_bh,V) int64 (-1 = not scored; NULL iff scoring_ids is NULL).      */
-int b200ctc_prefix_step(const float* lp, const float* r_prev, const float* s_prev,
+int b200ctc_prefix_step(const float* lp, const float* lp_t, const float* r_prev,
+                        const float* s_prev,
                         const int64_t* last_ids, const int64_t* scoring_ids,
                         const int64_t* end_frames, int B, int n_hyps, int T, int V,
                         int snum, int out_len, int start, int end, int blank,
