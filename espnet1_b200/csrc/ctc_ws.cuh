@@ -58,7 +58,7 @@ struct LossLayout {
 // Warp w+1 of the systolic lattice trails warp w by one block of K >= 4 steps, and
 // all warps read one shared ring of emission chunks (K frames of Lp floats): the
 // ring must span NW+1 blocks.  R is the smallest value (<= 16 warps) that fits.
-constexpr size_t kLatticeSmemBudget = 200 * 1024;
+constexpr size_t kLatticeSmemBudget = 222 * 1024;  // of the 227 KB an SM can hand to one CTA
 inline int lattice_R(int Smax, int Lp) {
   if (const char* e = getenv("B200CTC_LAT_R")) {  // tuning sweeps only
     const int r = atoi(e);
