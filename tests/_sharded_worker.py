@@ -38,6 +38,24 @@ for it in range(6):
     assert all(torch.equal(v, allv[0]) for v in allv), allv
     assert abs(float(got[1]) - float(wt)) < 0.5, (got, wt)
     assert abs(float(got[0]) - float(want)) <= 2e-6 * abs(float(want)), (got, want)
+# the G-rank reduced loss equals the one-process loss over the whole batch
+from espnet1_b200.sharded import shard_range  # noqa: E402
+
+g = torch.Generator().manual_seed(4242)
+Bg, T, V = 4 * world + 3, 60, 80  # not divisible by the world size: ragged shards
+xg = torch.randn(Bg, T, V, generator=g) * 2
+tlg = torch.randint(3, 12, (Bg,), generator=g)
+ilg = torch.randint(40, T + 1, (Bg,), generator=g)
+offs = torch.cumsum(tlg, 0) - tlg
+tgg = torch.randint(1, V, (int(tlg.sum()),), generator=g)
+lo, hi = shard_range(Bg, rank, world)
+xs = xg[lo:hi].to(dev).requires_grad_(True)
+tgs = tgg[int(offs[lo]):int(offs[hi - 1] + tlg[hi - 1])]
+F.ctc_loss(xs, tgs, ilg[lo:hi], tlg[lo:hi], reduce_scale=F._f32_recip(hi - lo), peer=ex)
+with torch.no_grad():
+    whole = F.ctc_loss(xg.to(dev), tgg, ilg, tlg).double().mean()
+assert abs(float(ex.out[0]) - float(whole)) <= 1e-6 * abs(float(whole)), (ex.out, whole)
+assert float(ex.out[1]) == Bg
 # a rank without utterances joins through the stand-alone call
 pair = torch.tensor([float(rank + 1), 1.0], device=dev)
 out = ex.exchange(pair).clone()
