@@ -225,6 +225,24 @@ def bench_prefix(dev, steps=20):
     return out
 
 
+def bench_softmax_family(x, dev, iters=10):
+    """log_softmax / softmax / argmax over the vocabulary on the C2 logits
+    (640 MB fp32), HBM-bound streaming: algorithmic bytes 2*4*rows*V (argmax: 4*rows*V)."""
+    from espnet1_b200 import functional as F
+
+    peak = peaks()[0]
+    nbytes = x.numel() * x.element_size()
+    out = {}
+    for name, fn, traffic in (("log_softmax", F.log_softmax, 2 * nbytes), ("softmax", F.softmax, 2 * nbytes),
+                              ("argmax", F.argmax, nbytes)):
+        for _ in range(3):
+            y = fn(x)
+        del y
+        ms = time_region(lambda: fn(x), iters, False, dev)
+        out[name] = {"ms": ms, "GB_per_s": traffic / ms / 1e6, "frac_of_measured_peak": traffic / ms / 1e6 / peak}
+    return out
+
+
 def run_gpu(args):
     import ctypes
 
@@ -378,6 +396,7 @@ def run_gpu(args):
         line["torch_cuda_library_ms_per_step"] = time_region(torch_step, 10, False, dev)
         del xr
         line["prefix_score"] = bench_prefix(dev)
+        line["softmax_family"] = bench_softmax_family(x.detach(), dev)
     print(json.dumps(line), flush=True)
     if dist_on:
         dist.destroy_process_group()
