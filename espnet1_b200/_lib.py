@@ -60,6 +60,10 @@ SIGNATURES = {
                                     _P, _P]),
     "b200ctc_prefix_select": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int,
                                       _P, _P, _P]),
+    "b200ctc_beam_prebeam": (c_int, [_P, _P, _P, c_int, c_int64, c_int, c_int, _P, _P]),
+    "b200ctc_beam_select": (c_int, [_P, _P, _P, c_int, _P, _P, _P, c_int64, c_int, _P, _P, c_int,
+                                    c_int, c_int, c_int, c_int, c_int, _P, _P, _P, _P, _P, c_int64,
+                                    _P, _P]),
     "b200ctc_loss_fwd_bwd_host": (c_int, [_P, c_int, _P, _P, _P, c_int, c_int, c_int, c_int,
                                           c_int, c_float, _P, _P, POINTER(c_void_p), c_int]),
     "b200ctc_host_pipeline_release": (None, []),

@@ -94,6 +94,30 @@ class CTCPrefixScorer(BatchPartialScorerInterface):
         )
         return self.impl(y, batch_state, ids)
 
+    # ---- batched-state API (used by ..batch_beam_search) ----
+    # The state never becomes n_beam Python tuples: it stays the (r (T,2,n_bh), s (n_bh,V),
+    # f_min, f_max) tuple CTCPrefixScoreTH itself consumes (ctc_prefix_score.py:68-96), for
+    # U utterances x beam_size slots, and pruning is ONE index_select_state gather
+    # (ctc_prefix_score.py:189-220) instead of n_beam select_state slices (:40-63).
+    def batch_init_state_multi(self, xs: torch.Tensor, xlens):
+        """Initial state for U utterances ``xs (U, Tmax, D)`` decoded together."""
+        logp = self.ctc.log_softmax(xs).detach()
+        self.impl = CTCPrefixScoreTH(logp, torch.as_tensor(xlens), 0, self.eos)
+        return None
+
+    def batch_score_partial_batched(self, y, ids, state):
+        """``batch_score_partial`` on the batched state; returns (scores (n_bh,V), state5)."""
+        return self.impl(y, state, ids)
+
+    def batch_select_state(self, state, best_ids):
+        """Prune with flat ids ``best_ids (U, beam)`` over (slots x vocabulary)."""
+        return self.impl.index_select_state(state, best_ids)
+
+    def slot_state(self, state, i):
+        """The per-hypothesis view ``select_state`` would have returned for slot ``i``."""
+        r, s, f_min, f_max = state
+        return r[:, :, i], s[i], f_min, f_max
+
     # ---- streaming (:128-157) -------------------------------------------
     def extend_prob(self, x: torch.Tensor):
         """Extend probs for streaming decoding (Eq. 14 of arXiv:2006.14941)."""

@@ -225,3 +225,51 @@ def forced_align(lp: torch.Tensor, target: torch.Tensor, blank: int = 0) -> torc
 
 launch_count = _lib.launch_count
 reset_launch_count = _lib.reset_launch_count
+
+
+# ---- beam pruning (espnet/nets/batch_beam_search.py:206-283) ----------
+def _score_args(mats, weights):
+    """host-side pointer / stride / weight arrays of the (n, V) fp32 score matrices"""
+    import ctypes
+
+    K = len(mats)
+    for m in mats:
+        require_cuda(m, "beam score matrix")
+        if m.dtype != torch.float32 or m.dim() != 2:
+            raise TypeError("beam score matrices must be 2-D fp32")
+    ptrs = (ctypes.c_void_p * K)(*[m.data_ptr() for m in mats])
+    strides = (ctypes.c_int64 * (2 * K))(*[s for m in mats for s in m.stride()])
+    ws = (ctypes.c_float * K)(*[float(w) for w in weights])
+    return ptrs, strides, ws, K
+
+
+def beam_prebeam(mats, weights, k: int) -> torch.Tensor:
+    """Top-k token ids (n, k) of every row of ``sum_q weights[q] * mats[q]`` (pre-beam)."""
+    ptrs, strides, ws, K = _score_args(mats, weights)
+    n, V = mats[0].shape
+    out = torch.empty(n, k, dtype=torch.int64, device=mats[0].device)
+    check(lib().b200ctc_beam_prebeam(ptrs, strides, ws, K, n, V, k, ptr(out),
+                                     stream_ptr(out.device)), "beam_prebeam")
+    return out
+
+
+def beam_select(mats, weights, run_score, cum_in, yseq_in, cur_len, active, maxlen, step_i,
+                U: int, W: int, k: int, eos: int, yseq_out):
+    """One fused pruning step (include/b200ctc.h ``b200ctc_beam_select``).
+
+    Returns (out_val (U,k), out_flat (U,k) int64, out_run (U,k), cum_out (K,U*k),
+    pack (3+K,U,k)); ``yseq_out`` (a preallocated int64 buffer) receives the new prefixes."""
+    ptrs, strides, ws, K = _score_args(mats, weights)
+    n, V = mats[0].shape
+    dev = mats[0].device
+    out_val = torch.empty(U, k, dtype=torch.float32, device=dev)
+    out_flat = torch.empty(U, k, dtype=torch.int64, device=dev)
+    out_run = torch.empty(U, k, dtype=torch.float32, device=dev)
+    cum_out = torch.empty(K, U * k, dtype=torch.float32, device=dev)
+    pack = torch.empty(3 + K, U, k, dtype=torch.float32, device=dev)
+    check(lib().b200ctc_beam_select(ptrs, strides, ws, K, ptr(run_score), ptr(cum_in), ptr(yseq_in),
+                                    yseq_in.stride(0), cur_len, ptr(active), ptr(maxlen), step_i,
+                                    U, W, V, k, eos, ptr(out_val), ptr(out_flat), ptr(out_run),
+                                    ptr(cum_out), ptr(yseq_out), yseq_out.stride(0), ptr(pack),
+                                    stream_ptr(dev)), "beam_select")
+    return out_val, out_flat, out_run, cum_out, pack

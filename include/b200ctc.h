@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define B200CTC_ABI_VERSION 3
+#define B200CTC_ABI_VERSION 4
 
 #define B200CTC_OK 0
 #define B200CTC_ERR_ARG (-1)     /* bad argument (null pointer, size, dtype) */
@@ -206,6 +206,45 @@ int b200ctc_prefix_select(const float* r, const float* log_psi,
                           const int64_t* idmap, const int64_t* best_ids, int B,
                           int n_hyps, int W, int T, int V, int snum, float* r_new,
                           float* s_new, b200ctc_stream_t stream);
+
+/* ---- (f1) beam pruning of the label-synchronous search --------------------
+ * replaces the per-step glue of BatchBeamSearch.search
+ * (espnet/nets/batch_beam_search.py:206-283) after the scorers have run.
+ * Score matrices: K <= B200CTC_BEAM_MAX_SCORERS fp32 matrices of (n, V), given
+ * as a HOST array of device pointers `score_ptrs[K]`, HOST `strides[2K]`
+ * (row, column stride in elements; 0 = broadcast) and HOST `weights[K]`.
+ *   w[h,v] = ((0 + weights[0]*s_0[h,v]) + weights[1]*s_1[h,v]) + ...   (:217-241,
+ *   the reference's fp32 operation order; separate multiply and add)          */
+#define B200CTC_BEAM_MAX_SCORERS 8
+/* pre-beam (:228-234): out_ids (n_rows, k) int64 = top-k tokens of every row of w,
+ * sorted by descending score (ties: lower token id first); k <= 64, V <= 65536. */
+int b200ctc_beam_prebeam(const float* const* score_ptrs_host,
+                         const int64_t* strides_host, const float* weights_host,
+                         int K, int64_t n_rows, int V, int k, int64_t* out_ids,
+                         b200ctc_stream_t stream);
+/* one pruning step for U utterances x W beam slots (n = U*W rows), one CTA per
+ * utterance: top-k over the utterance's W*V entries of w + run_score[h]
+ * (batch_beam(), :98-118; k <= 64, W*V <= 65536), then for winner j of utterance u
+ * (prev = flat / V, tok = flat % V, row = u*W + prev, o = u*k + j):
+ *   out_val[o]  = w + run                  (the new hypothesis score, :258)
+ *   out_flat[o] = prev*V + tok             (what index_select_state expects)
+ *   out_run[o]  = out_val, or -inf if tok == eos, the utterance is inactive
+ *                 (active[u] == 0) or this is its last position
+ *                 (maxlen[u]-1 == step_i): the slot takes no further part (:318-347)
+ *   cum_out[q][o] = cum_in[q][row] + s_q[row, tok]   (merge_scores, :260-266)
+ *   yseq_out[o, :cur_len+1] = yseq_in[row, :cur_len] ++ tok   (append_token, :259)
+ *   pack (3+K, U, k) fp32 = {out_val, prev, tok, cum_out[0..K)}: the one record the
+ *                 host reads per step (ended hypotheses, end detection).
+ * run_score, active, maxlen may be NULL.                                      */
+int b200ctc_beam_select(const float* const* score_ptrs_host,
+                        const int64_t* strides_host, const float* weights_host, int K,
+                        const float* run_score, const float* cum_in,
+                        const int64_t* yseq_in, int64_t yseq_in_stride, int cur_len,
+                        const unsigned char* active, const int* maxlen, int step_i,
+                        int U, int W, int V, int k, int eos, float* out_val,
+                        int64_t* out_flat, float* out_run, float* cum_out,
+                        int64_t* yseq_out, int64_t yseq_out_stride, float* pack,
+                        b200ctc_stream_t stream);
 
 /* ---- host-buffer pipeline (bench.py `e2e`) --------------------------------
  * Same arithmetic as loss_fwd + loss_bwd, but logits/targets/lengths are HOST

@@ -57,6 +57,22 @@ class OracleCTCPrefixScorer:
             return r[:, :, i, col], s, f_min, f_max
         return None if state is None else state[i]
 
+    # -- batched-state API of the product scorer (espnet1_b200 .../scorers/ctc.py), so the
+    #    host logic of the device-resident beam search can be checked on CPU --------------
+    def batch_init_state_multi(self, xs, xlens):
+        self.impl = PrefixOracle(self.ctc.log_softmax(xs), torch.as_tensor(xlens), 0, self.eos)
+        return None
+
+    def batch_score_partial_batched(self, y, ids, state):
+        return self.impl.score(y, state, ids)
+
+    def batch_select_state(self, state, best_ids):
+        return self.impl.select(state, best_ids)
+
+    def slot_state(self, state, i):
+        r, s, f_min, f_max = state
+        return r[:, :, i], s[i], f_min, f_max
+
     def extend_prob(self, x):
         self.impl.extend_prob(self.ctc.log_softmax(x.unsqueeze(0)))
 

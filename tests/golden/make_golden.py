@@ -272,6 +272,47 @@ def make_beam():
     print("wrote beam_nbest.json")
 
 
+def make_beam_multi():
+    """n-best lists of the REAL BatchBeamSearch, one utterance at a time, for
+    a ragged batch of utterances; the device-resident engine must reproduce them both one
+    by one and decoded together (forward_batch)."""
+    res, arrays = {}, {}
+    cases = [
+        # name, lengths, V, beam, weights, pre_beam_key, seed
+        ("multi_joint_v60", [36, 29, 22, 36], 60, 4, {"ctc": 0.4, "decoder": 0.6, "length_bonus": 0.3},
+         "full", 211),
+        ("multi_ctc_v30", [24, 17, 24], 30, 3, {"ctc": 1.0, "length_bonus": 0.5}, None, 212),
+        ("multi_joint_v300", [50, 41], 300, 6, {"ctc": 0.3, "decoder": 0.7, "length_bonus": 0.4},
+         "decoder", 213),
+    ]
+    for name, lens, V, beam, weights, key, seed in cases:
+        g = torch.Generator().manual_seed(seed)
+        Tm = max(lens)
+        xs = torch.randn(len(lens), Tm, V, generator=g) * 3
+        table = torch.log_softmax(torch.randn(V, V, generator=g) * 2, dim=1)
+        arrays[f"{name}__xs"] = xs.numpy()
+        arrays[f"{name}__table"] = table.numpy()
+        eos = V - 1
+        entry = {"lens": lens, "V": V, "beam_size": beam, "weights": weights, "pre_beam_key": key,
+                 "sos": eos, "eos": eos, "nbest": []}
+        for u, T in enumerate(lens):
+            scorers = {"ctc": CTCPrefixScorer(_StubCTC(), eos), "length_bonus": LengthBonus(V)}
+            if "decoder" in weights:
+                scorers["decoder"] = _Table(table)
+            bs = BatchBeamSearch(scorers=scorers, weights=weights, beam_size=beam, vocab_size=V,
+                                 sos=eos, eos=eos, pre_beam_score_key=key)
+            with torch.no_grad():
+                nbest = bs(x=xs[u, :T].clone(), maxlenratio=0.0, minlenratio=0.0)
+            entry["nbest"].append([{"yseq": [int(v) for v in h.yseq], "score": float(h.score),
+                                    "scores": {k: float(v) for k, v in h.scores.items()}}
+                                   for h in nbest])
+        res[name] = entry
+    save("beam_multi_inputs.npz", arrays)
+    with open(os.path.join(HERE, "beam_multi_nbest.json"), "w") as f:
+        json.dump(res, f, indent=1)
+    print("wrote beam_multi_nbest.json")
+
+
 def make_streaming():
     """extend_prob / extend_state (ctc_prefix_score.py:222-269) through the
     CTCPrefixScorer adapter the way batch_beam_search_online.py:306-309 does."""
@@ -304,8 +345,13 @@ def make_streaming():
 
 if __name__ == "__main__":
     torch.set_num_threads(1)
+    if len(sys.argv) > 1:  # regenerate selected fixtures only: make_golden.py make_beam_multi ...
+        for fn in sys.argv[1:]:
+            globals()[fn]()
+        sys.exit(0)
     make_ctc_module()
     make_ctc_c1()
     make_prefix()
     make_beam()
+    make_beam_multi()
     make_streaming()

@@ -1,0 +1,73 @@
+#!/usr/bin/env python3
+"""Beam-search glue timing at C3 widths: beam 10, V=5000, T=500,
+joint CTC + bigram-table decoder + length bonus, pre-beam 15 ("full").
+  engine_batch32 : BatchBeamSearch.forward_batch, 32 utterances together
+  engine_single  : BatchBeamSearch.forward, one utterance at a time
+  listglue_single: the reference's per-hypothesis glue (oracle/beam_harness.py restates
+                   batch_beam_search.py:206-283) around the SAME CUDA scorer
+Fixed number of positions (maxlenratio < 0) so that the three do equal work."""
+import json
+import os
+import sys
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from espnet1_b200 import functional as F  # noqa: E402
+from espnet1_b200.espnet.nets.batch_beam_search import BatchBeamSearch  # noqa: E402
+from espnet1_b200.espnet.nets.scorers.ctc import CTCPrefixScorer  # noqa: E402
+from espnet1_b200.espnet.nets.scorers.length_bonus import LengthBonus  # noqa: E402
+from oracle import beam_harness  # noqa: E402
+from oracle.scorer_port import TableScorer  # noqa: E402
+
+
+D = 256  # encoder output size: x (T, D) -> ctc_lo -> (T, V), as espnet2/asr/ctc.py:109-117
+
+
+def main():
+    dev = "cuda:0"
+    U, W, V, T, POS = 32, 10, 5000, 500, int(os.environ.get("POS", "30"))
+    g = torch.Generator().manual_seed(5)
+    from espnet1_b200.espnet2.asr.ctc import CTC
+
+    xs = torch.randn(U, T, D, generator=g).to(dev)
+    ctc = CTC(V, D).to(dev)
+    with torch.no_grad():
+        ctc.ctc_lo.weight.mul_(8.0)  # peaky-ish posteriors
+    lens = [T] * U
+    table = torch.log_softmax(torch.randn(V, V, generator=g) * 2, dim=1).to(dev)
+    eos = V - 1
+    weights = {"ctc": 0.3, "decoder": 0.7, "length_bonus": 0.2}
+
+    def scorers():
+        return {"ctc": CTCPrefixScorer(ctc, eos), "decoder": TableScorer(table), "length_bonus": LengthBonus(V)}
+
+    bs = BatchBeamSearch(scorers(), weights, W, V, eos, eos, pre_beam_score_key="full")
+    out = {}
+    with torch.no_grad():
+        for name, fn, n_utt in (
+            ("engine_batch32", lambda: bs.forward_batch(xs.clone(), lens, maxlenratio=-POS), U),
+            ("engine_single", lambda: [bs(xs[u].clone(), maxlenratio=-POS) for u in range(4)], 4),
+            ("listglue_single", lambda: [beam_harness.batch_beam_search(
+                xs[u].clone(), scorers(), weights, W, V, eos, eos, pre_beam_score_key="full",
+                maxlenratio=-POS) for u in range(4)], 4),
+        ):
+            fn()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            res = fn()
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+            out[name] = {"utterances": n_utt, "positions": POS, "s": dt,
+                         "ms_per_position": 1e3 * dt / POS / (1 if "batch" in name else n_utt),
+                         "utt_positions_per_s": n_utt * POS / dt}
+            out[name]["best0"] = [int(v) for v in (res[0][0].yseq if hasattr(res[0][0], "yseq") else res[0][0]["yseq"])][:8]
+    if bs.prof is not None:
+        out["engine_phase_s"] = bs.prof
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()
