@@ -394,9 +394,14 @@ def run_gpu(args):
         for _ in range(3):
             torch_step()
         line["torch_cuda_library_ms_per_step"] = time_region(torch_step, 10, False, dev)
-        del xr
         line["prefix_score"] = bench_prefix(dev)
         line["softmax_family"] = bench_softmax_family(x.detach(), dev)
+        del xr
+        torch.cuda.empty_cache()
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import bench_beam  # device-resident joint CTC/attention beam search
+
+        line["beam_search"] = bench_beam.run(str(dev))
     print(json.dumps(line), flush=True)
     if dist_on:
         dist.destroy_process_group()

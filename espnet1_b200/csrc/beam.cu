@@ -14,10 +14,10 @@
 //   yseq_out[j] = yseq_in[prev] ++ token, and a packed fp32 record for the host.
 //
 // The same selection core serves the pre-beam (top-P tokens of every hypothesis row,
-// :228-234).  Selection: every thread keeps its strided share of the segment in
-// registers; k rounds of block-wide arg-max (warp shuffles + one shared-memory hop),
-// the owner of a winner retires it.  Latency-bound by design: a segment is 5 000 to
-// 64 K values and lives in L2 / registers; there is one segment per CTA.
+// :228-234).  Selection: the segment's weighted scores are evaluated once into shared
+// memory (<= 56 K values); k rounds of block-wide arg-max (warp shuffles + one
+// shared-memory hop), the owner of a winner retires it.  Latency-bound by design: a
+// segment is 5 000 to 56 K values, L2-resident; there is one segment per CTA.
 #include "common.cuh"
 
 namespace b200ctc {
@@ -32,35 +32,59 @@ struct BeamScores {
   int K;
 };
 
-__device__ __forceinline__ float beam_weighted(const BeamScores& S, long long row, int v) {
-  float acc = 0.f;
-#pragma unroll 1
-  for (int k = 0; k < S.K; ++k)
-    acc = __fadd_rn(acc, __fmul_rn(S.w[k], __ldg(S.p[k] + row * S.rs[k] + (long long)v * S.cs[k])));
-  return acc;
-}
-
-// top-k of the NT*NPT values held as v[q] <-> element q*NT + tid; results in res_v/res_e
-template <int NT, int NPT>
-__device__ __forceinline__ void block_topk(float (&v)[NPT], int E, int k, float* res_v, int* res_e,
-                                           float* sm_v, int* sm_e) {
+// Phase 1: every thread evaluates its strided share of the segment (rows of V entries
+// starting at row0; element e = i*NT + tid), 8 elements x K matrices of independent loads
+// in flight, each element accumulating its terms in scorer order (the reference's fp32
+// operation order); the values go to shared memory, the thread keeps its own maximum.
+// Phase 2: k rounds of block-wide arg-max (warp shuffles + one shared-memory hop, ties ->
+// lower index); the owner of a winner retires it and rescans its share.
+template <int NT>
+__device__ __forceinline__ void segment_topk(const BeamScores& S, long long row0, int V, int E,
+                                             const float* __restrict__ run, int k, float* vals,
+                                             float* res_v, int* res_e, float* sm_v, int* sm_e) {
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  constexpr int NWARP = NT / 32;
+  constexpr int NWARP = NT / 32, UN = 8;
   float bv = kNegInf;
-  int bq = 0;
-  bool dirty = true;
-  for (int r = 0; r < k; ++r) {
-    if (dirty) {
-      bv = kNegInf;
-      bq = 0;
+  int be = 0x7fffffff;
+  for (int e0 = tid; e0 < E; e0 += NT * UN) {
+    float acc[UN];
+    long long row[UN];
+    int col[UN];
 #pragma unroll
-      for (int q = 0; q < NPT; ++q)
-        if (v[q] > bv) { bv = v[q]; bq = q; }
-      dirty = false;
+    for (int j = 0; j < UN; ++j) {
+      const int e = e0 + j * NT;
+      const int ec = e < E ? e : 0;
+      const int h = ec / V;
+      row[j] = row0 + h;
+      col[j] = ec - h * V;
+      acc[j] = 0.f;
     }
+#pragma unroll 1
+    for (int q = 0; q < S.K; ++q) {
+      const float* __restrict__ p = S.p[q];
+      const long long rs = S.rs[q], cs = S.cs[q];
+      const float wq = S.w[q];
+      float x[UN];
+#pragma unroll
+      for (int j = 0; j < UN; ++j) x[j] = __ldg(p + row[j] * rs + (long long)col[j] * cs);
+#pragma unroll
+      for (int j = 0; j < UN; ++j) acc[j] = __fadd_rn(acc[j], __fmul_rn(wq, x[j]));
+    }
+#pragma unroll
+    for (int j = 0; j < UN; ++j) {
+      const int e = e0 + j * NT;
+      if (e < E) {
+        float x = acc[j];
+        if (run) x = __fadd_rn(x, __ldg(run + row[j]));
+        if (!(x == x)) x = kNegInf;  // NaN never wins
+        vals[e] = x;
+        if (x > bv) { bv = x; be = e; }
+      }
+    }
+  }
+  for (int r = 0; r < k; ++r) {
     float cv = bv;
-    int ce = bq * NT + tid;
-    if (ce >= E) { cv = kNegInf; ce = 0; }
+    int ce = be;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
       const float ov = __shfl_xor_sync(0xffffffffu, cv, o);
@@ -78,48 +102,37 @@ __device__ __forceinline__ void block_topk(float (&v)[NPT], int E, int k, float*
         const int oe = __shfl_xor_sync(0xffffffffu, ce, o);
         if (ov > cv || (ov == cv && oe < ce)) { cv = ov; ce = oe; }
       }
-      if (lane == 0) { res_v[r] = cv; res_e[r] = ce; }
+      if (lane == 0) { res_v[r] = cv; res_e[r] = ce < E ? ce : 0; }
     }
     __syncthreads();
     const int we = res_e[r];
-    if ((we % NT) == tid && res_v[r] > kNegInf) {  // retire the winner
-      const int wq = we / NT;
-#pragma unroll
-      for (int q = 0; q < NPT; ++q)
-        if (q == wq) v[q] = kNegInf;
-      dirty = true;
+    if (res_v[r] > kNegInf && (we % NT) == tid) {  // retire the winner, rescan my share
+      vals[we] = kNegInf;
+      bv = kNegInf;
+      be = 0x7fffffff;
+      for (int e = tid; e < E; e += NT) {
+        const float x = vals[e];
+        if (x > bv) { bv = x; be = e; }
+      }
     }
   }
 }
 
-template <int NT, int NPT>
+template <int NT>
 __global__ void __launch_bounds__(NT) beam_select_kernel(
-    BeamScores S, const float* __restrict__ run, const float* __restrict__ cum_in,
+    const __grid_constant__ BeamScores S, const float* __restrict__ run, const float* __restrict__ cum_in,
     const int64_t* __restrict__ yseq_in, long long ys_in_stride, int cur_len,
     const unsigned char* __restrict__ active, const int* __restrict__ maxlen, int step_i, int W,
     int V, int k, int eos, float* __restrict__ out_val, int64_t* __restrict__ out_flat,
     float* __restrict__ out_run, float* __restrict__ cum_out, int64_t* __restrict__ yseq_out,
     long long ys_out_stride, float* __restrict__ pack) {
+  extern __shared__ float vals[];  // the segment's W*V weighted scores
   __shared__ float res_v[kBeamMaxK], sm_v[32];
   __shared__ int res_e[kBeamMaxK], sm_e[32];
   const int u = blockIdx.x, U = gridDim.x, tid = threadIdx.x;
   const int E = W * V;
   const long long n_in = (long long)U * W, n_out = (long long)U * k;
-  float v[NPT];
-#pragma unroll
-  for (int q = 0; q < NPT; ++q) {
-    const int e = q * NT + tid;
-    float x = kNegInf;
-    if (e < E) {
-      const int h = e / V, tok = e - h * V;
-      const long long row = (long long)u * W + h;
-      x = beam_weighted(S, row, tok);
-      if (run) x = __fadd_rn(x, __ldg(run + row));
-      if (!(x == x)) x = kNegInf;  // NaN never wins
-    }
-    v[q] = x;
-  }
-  block_topk<NT, NPT>(v, E, k, res_v, res_e, sm_v, sm_e);
+  segment_topk<NT>(S, (long long)u * W, V, E, run, k, vals, res_v, res_e, sm_v, sm_e);
   __syncthreads();
   const bool act = (active ? active[u] != 0 : true) && !(maxlen && maxlen[u] - 1 == step_i);
   if (tid < k) {
@@ -150,27 +163,29 @@ __global__ void __launch_bounds__(NT) beam_select_kernel(
   }
 }
 
-template <int NT, int NPT>
-__global__ void __launch_bounds__(NT) beam_prebeam_kernel(BeamScores S, int V, int k,
-                                                          int64_t* __restrict__ out_ids) {
+template <int NT>
+__global__ void __launch_bounds__(NT) beam_prebeam_kernel(const __grid_constant__ BeamScores S, int V,
+                                                          int k, int64_t* __restrict__ out_ids) {
+  extern __shared__ float vals[];
   __shared__ float res_v[kBeamMaxK], sm_v[32];
   __shared__ int res_e[kBeamMaxK], sm_e[32];
   const long long row = blockIdx.x;
-  const int tid = threadIdx.x;
-  float v[NPT];
-#pragma unroll
-  for (int q = 0; q < NPT; ++q) {
-    const int e = q * NT + tid;
-    float x = kNegInf;
-    if (e < V) {
-      x = beam_weighted(S, row, e);
-      if (!(x == x)) x = kNegInf;
-    }
-    v[q] = x;
-  }
-  block_topk<NT, NPT>(v, V, k, res_v, res_e, sm_v, sm_e);
+  segment_topk<NT>(S, row, V, V, nullptr, k, vals, res_v, res_e, sm_v, sm_e);
   __syncthreads();
-  if (tid < k) out_ids[row * k + tid] = res_e[tid];
+  if (threadIdx.x < k) out_ids[row * k + threadIdx.x] = res_e[threadIdx.x];
+}
+
+constexpr long long kBeamMaxSegment = 56 * 1024;  // fp32 values of one segment in shared memory
+
+template <typename Kern>
+static int beam_smem(Kern kern, size_t bytes) {
+  if (bytes > 48 * 1024 &&
+      cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes) != cudaSuccess) {
+    set_error("beam: cannot reserve %zu bytes of shared memory", bytes);
+    cudaGetLastError();
+    return B200CTC_ERR_DEVICE;
+  }
+  return B200CTC_OK;
 }
 
 static int fill_scores(BeamScores& S, const float* const* ptrs, const int64_t* strides,
@@ -203,18 +218,20 @@ extern "C" int b200ctc_beam_select(const float* const* score_ptrs, const int64_t
   if (int rc = fill_scores(S, score_ptrs, strides, weights, K)) return rc;
   B2_REQUIRE(U >= 1 && W >= 1 && V >= 1 && k >= 1 && k <= kBeamMaxK, "beam_select: bad sizes U=%d W=%d V=%d k=%d", U, W, V, k);
   const long long E = (long long)W * V;
-  B2_REQUIRE(E <= 1024LL * 64, "beam_select: beam x vocabulary = %lld exceeds 65536", E);
+  B2_REQUIRE(E <= kBeamMaxSegment, "beam_select: beam x vocabulary = %lld exceeds %lld", E, kBeamMaxSegment);
   B2_REQUIRE(cur_len >= 0 && cur_len < yseq_out_stride && cur_len <= yseq_in_stride, "beam_select: prefix buffers too short");
   auto st = static_cast<cudaStream_t>(stream);
-#define GO(NT, NPT)                                                                               \
-  beam_select_kernel<NT, NPT><<<U, NT, 0, st>>>(S, run_score, cum_in, yseq_in, yseq_in_stride,    \
-                                                cur_len, active, maxlen, step_i, W, V, k, eos,    \
-                                                out_val, out_flat, out_run, cum_out, yseq_out,    \
-                                                yseq_out_stride, pack)
-  if (E <= 256 * 8) GO(256, 8);
-  else if (E <= 1024 * 8) GO(1024, 8);
-  else if (E <= 1024 * 32) GO(1024, 32);
-  else GO(1024, 64);
+  const size_t smem = (size_t)E * 4;
+#define GO(NT)                                                                                     \
+  do {                                                                                             \
+    if (int rc = beam_smem(beam_select_kernel<NT>, smem)) return rc;                               \
+    beam_select_kernel<NT><<<U, NT, smem, st>>>(S, run_score, cum_in, yseq_in, yseq_in_stride,     \
+                                                cur_len, active, maxlen, step_i, W, V, k, eos,     \
+                                                out_val, out_flat, out_run, cum_out, yseq_out,     \
+                                                yseq_out_stride, pack);                            \
+  } while (0)
+  if (E <= 4096) GO(256);
+  else GO(1024);
 #undef GO
   count_launch();
   return check_launch("beam_select");
@@ -226,13 +243,16 @@ extern "C" int b200ctc_beam_prebeam(const float* const* score_ptrs, const int64_
   BeamScores S;
   if (int rc = fill_scores(S, score_ptrs, strides, weights, K)) return rc;
   B2_REQUIRE(n_rows >= 1 && V >= 1 && k >= 1 && k <= kBeamMaxK && k <= V, "beam_prebeam: bad sizes rows=%lld V=%d k=%d", (long long)n_rows, V, k);
-  B2_REQUIRE(V <= 1024 * 64, "beam_prebeam: vocabulary %d exceeds 65536", V);
+  B2_REQUIRE(V <= kBeamMaxSegment, "beam_prebeam: vocabulary %d exceeds %lld", V, kBeamMaxSegment);
   auto st = static_cast<cudaStream_t>(stream);
-#define GO(NT, NPT) beam_prebeam_kernel<NT, NPT><<<(unsigned)n_rows, NT, 0, st>>>(S, V, k, out_ids)
-  if (V <= 256 * 8) GO(256, 8);
-  else if (V <= 256 * 32) GO(256, 32);
-  else if (V <= 1024 * 32) GO(1024, 32);
-  else GO(1024, 64);
+  const size_t smem = (size_t)V * 4;
+#define GO(NT)                                                                          \
+  do {                                                                                  \
+    if (int rc = beam_smem(beam_prebeam_kernel<NT>, smem)) return rc;                   \
+    beam_prebeam_kernel<NT><<<(unsigned)n_rows, NT, smem, st>>>(S, V, k, out_ids);      \
+  } while (0)
+  if (V <= 16384) GO(256);
+  else GO(1024);
 #undef GO
   count_launch();
   return check_launch("beam_prebeam");

@@ -153,7 +153,7 @@ class BatchBeamSearch(torch.nn.Module):
         maxlen_t = torch.tensor(maxlen, device=dev).unsqueeze(1)
         active = torch.ones(U, 1, dtype=torch.bool, device=dev)          # utterance still decoding
         # fused pruning kernel (csrc/beam.cu): CUDA, fp32, segment and winner counts within its limits
-        fused = (dev.type == "cuda" and xs.dtype == torch.float32 and W * V <= 65536 and W <= 64
+        fused = (dev.type == "cuda" and xs.dtype == torch.float32 and W * V <= 57344 and V <= 57344 and W <= 64
                  and (not self.do_pre_beam or self.pre_beam_size <= 64)
                  and not os.environ.get("B200CTC_BEAM_TORCH"))
         if fused:

@@ -217,14 +217,14 @@ int b200ctc_prefix_select(const float* r, const float* log_psi,
  *   the reference's fp32 operation order; separate multiply and add)          */
 #define B200CTC_BEAM_MAX_SCORERS 8
 /* pre-beam (:228-234): out_ids (n_rows, k) int64 = top-k tokens of every row of w,
- * sorted by descending score (ties: lower token id first); k <= 64, V <= 65536. */
+ * sorted by descending score (ties: lower token id first); k <= 64, V <= 57344. */
 int b200ctc_beam_prebeam(const float* const* score_ptrs_host,
                          const int64_t* strides_host, const float* weights_host,
                          int K, int64_t n_rows, int V, int k, int64_t* out_ids,
                          b200ctc_stream_t stream);
 /* one pruning step for U utterances x W beam slots (n = U*W rows), one CTA per
  * utterance: top-k over the utterance's W*V entries of w + run_score[h]
- * (batch_beam(), :98-118; k <= 64, W*V <= 65536), then for winner j of utterance u
+ * (batch_beam(), :98-118; k <= 64, W*V <= 57344), then for winner j of utterance u
  * (prev = flat / V, tok = flat % V, row = u*W + prev, o = u*k + j):
  *   out_val[o]  = w + run                  (the new hypothesis score, :258)
  *   out_flat[o] = prev*V + tok             (what index_select_state expects)

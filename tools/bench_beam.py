@@ -26,47 +26,72 @@ from oracle.scorer_port import TableScorer  # noqa: E402
 D = 256  # encoder output size: x (T, D) -> ctc_lo -> (T, V), as espnet2/asr/ctc.py:109-117
 
 
-def main():
-    dev = "cuda:0"
-    U, W, V, T, POS = 32, 10, 5000, 500, int(os.environ.get("POS", "30"))
-    g = torch.Generator().manual_seed(5)
+def run(dev="cuda:0", POS=30, cpu_port=True):
+    """Returns the timing dict; imported by bench.py (``beam_search`` block)."""
     from espnet1_b200.espnet2.asr.ctc import CTC
+    from oracle.scorer_port import LengthBonusPort, OracleCTCPrefixScorer
 
-    xs = torch.randn(U, T, D, generator=g).to(dev)
-    ctc = CTC(V, D).to(dev)
-    with torch.no_grad():
-        ctc.ctc_lo.weight.mul_(8.0)  # peaky-ish posteriors
+    U, W, V, T = 32, 10, 5000, 500
+    g = torch.Generator().manual_seed(5)
+    xs_h = torch.randn(U, T, D, generator=g)
+    xs = xs_h.to(dev)
     lens = [T] * U
-    table = torch.log_softmax(torch.randn(V, V, generator=g) * 2, dim=1).to(dev)
+    table_h = torch.log_softmax(torch.randn(V, V, generator=g) * 2, dim=1)
+    table = table_h.to(dev)
     eos = V - 1
     weights = {"ctc": 0.3, "decoder": 0.7, "length_bonus": 0.2}
+    ctc = CTC(V, D)
+    with torch.no_grad():
+        ctc.ctc_lo.weight.copy_(torch.randn(V, D, generator=g) * 0.5)  # peaky-ish posteriors
+        ctc.ctc_lo.bias.zero_()
+    w_h, b_h = ctc.ctc_lo.weight.detach().clone(), ctc.ctc_lo.bias.detach().clone()
+    ctc = ctc.to(dev)
+
+    class CpuCTC:  # the reference's CPU arithmetic for ctc.log_softmax (espnet2/asr/ctc.py:109-117)
+        def log_softmax(self, x):
+            return torch.log_softmax(torch.nn.functional.linear(x, w_h, b_h), dim=-1)
 
     def scorers():
         return {"ctc": CTCPrefixScorer(ctc, eos), "decoder": TableScorer(table), "length_bonus": LengthBonus(V)}
 
     bs = BatchBeamSearch(scorers(), weights, W, V, eos, eos, pre_beam_score_key="full")
-    out = {}
+    out = {"config": f"beam {W}, V={V}, T={T}, D={D}, pre-beam 15 (full), ctc 0.3 + bigram-table decoder 0.7 "
+                     f"+ length bonus 0.2, {POS} positions per utterance (maxlenratio=-{POS})"}
+    cases = [
+        ("engine_batch32", lambda: bs.forward_batch(xs.clone(), lens, maxlenratio=-POS), U),
+        ("engine_single", lambda: [bs(xs[u].clone(), maxlenratio=-POS) for u in range(4)], 4),
+        ("listglue_single", lambda: [beam_harness.batch_beam_search(
+            xs[u].clone(), scorers(), weights, W, V, eos, eos, pre_beam_score_key="full",
+            maxlenratio=-POS) for u in range(4)], 4),
+    ]
+    if cpu_port:
+        torch.set_num_threads(os.cpu_count() or 1)
+        cases.append(("cpu_port_single", lambda: [beam_harness.batch_beam_search(
+            xs_h[0].clone(), {"ctc": OracleCTCPrefixScorer(CpuCTC(), eos), "decoder": TableScorer(table_h),
+                              "length_bonus": LengthBonusPort(V)},
+            weights, W, V, eos, eos, pre_beam_score_key="full", maxlenratio=-POS)], 1))
     with torch.no_grad():
-        for name, fn, n_utt in (
-            ("engine_batch32", lambda: bs.forward_batch(xs.clone(), lens, maxlenratio=-POS), U),
-            ("engine_single", lambda: [bs(xs[u].clone(), maxlenratio=-POS) for u in range(4)], 4),
-            ("listglue_single", lambda: [beam_harness.batch_beam_search(
-                xs[u].clone(), scorers(), weights, W, V, eos, eos, pre_beam_score_key="full",
-                maxlenratio=-POS) for u in range(4)], 4),
-        ):
-            fn()
+        for name, fn, n_utt in cases:
+            if not name.startswith("cpu"):
+                fn()
             torch.cuda.synchronize()
             t0 = time.perf_counter()
             res = fn()
             torch.cuda.synchronize()
             dt = time.perf_counter() - t0
+            first = res[0][0]
             out[name] = {"utterances": n_utt, "positions": POS, "s": dt,
                          "ms_per_position": 1e3 * dt / POS / (1 if "batch" in name else n_utt),
-                         "utt_positions_per_s": n_utt * POS / dt}
-            out[name]["best0"] = [int(v) for v in (res[0][0].yseq if hasattr(res[0][0], "yseq") else res[0][0]["yseq"])][:8]
+                         "utt_positions_per_s": n_utt * POS / dt,
+                         "best0": [int(v) for v in (first.yseq if hasattr(first, "yseq") else first["yseq"])][:8]}
+    out["same_best_hypothesis"] = len({tuple(v["best0"]) for k, v in out.items() if isinstance(v, dict)}) == 1
     if bs.prof is not None:
         out["engine_phase_s"] = bs.prof
-    print(json.dumps(out))
+    return out
+
+
+def main():
+    print(json.dumps(run(POS=int(os.environ.get("POS", "30")))))
 
 
 if __name__ == "__main__":
