@@ -542,7 +542,25 @@ static int loss_fwd_grad_impl(const void* logits, int dtype, const int64_t* targ
     cudaEventRecord(ev_join, sd);
   }
   const PrepArgs P = make_prep_args(w, ws, targets, tgt_offsets, in_lens, tgt_lens, blank);
-  if (!rc) {  // gather kernel with the label prep fused in
+  // Emissions: a sparse gather of the L+1 label columns moves one 64-byte DRAM atom per
+  // column and row; once that exceeds the row itself (long targets: C4 has 1201 columns
+  // = 77 KB of atoms against a 20 KB row) the full-row pass A (TMA row -> shared memory ->
+  // columns) is the cheaper way to produce the same em / cmax arrays.
+  static const int force_dense = [] { const char* e = getenv("B200CTC_DENSE_GATHER"); return e ? atoi(e) : -1; }();
+  const bool dense_gather = T > 0 && (force_dense >= 0 ? force_dense != 0
+      : (size_t)(w.Lmax + 1) * 64 > (size_t)V * (size_t)dtype_size(dtype));
+  if (!rc && dense_gather) {
+    rc = launch_prep(w, P, st);
+    if (!rc) {
+      prof_mark(1, 0, st);
+      switch (dtype) {
+        case B200CTC_F32: rc = dispatch_pass_a<float>(logits, B, T, V, w, ws, st); break;
+        case B200CTC_F16: rc = dispatch_pass_a<__half>(logits, B, T, V, w, ws, st); break;
+        default: rc = dispatch_pass_a<__nv_bfloat16>(logits, B, T, V, w, ws, st); break;
+      }
+      prof_mark(1, 1, st);
+    }
+  } else if (!rc) {  // gather kernel with the label prep fused in
     prof_mark(1, 0, st);
     switch (dtype) {
       case B200CTC_F32: rc = launch_gather<float>(logits, P, B, w, ws, st); break;
