@@ -123,6 +123,34 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
       __syncthreads();
     }
     const T* xs = reinterpret_cast<const T*>(stg);
+    // ---- wide lattices (S > NT*SM, long-form utterances): the occupancies of the positions
+    // beyond the prefetched ones are computed HERE, before the row occupies 40 registers,
+    // with kW positions' alpha / beta / offset loads in flight per thread (this loop is
+    // bound by their latency); no iterations at C2
+    float blank_part = 0.f;
+    {
+      constexpr int kW = 8;
+      for (int s0 = NT * SM; s0 < S; s0 += NT * kW) {
+        float abw[kW];
+#pragma unroll
+        for (int j = 0; j < kW; ++j) {
+          const int s = s0 + tid + j * NT;
+          abw[j] = s < S ? lattice_term(s) : kNegInf;
+        }
+#pragma unroll
+        for (int j = 0; j < kW; ++j) {
+          const int s = s0 + tid + j * NT;
+          if (s < S) {
+            const bool odd = s & 1;
+            const int k = odd ? (s + 1) >> 1 : 0;
+            const int v = odd ? lb[k] : blank;
+            const float em = fmaf(to_f32<T>(xs[v]), kLog2e, -c2);
+            const float p = ex2(abw[j] - em);
+            if (odd) pbuf[k] = p; else blank_part += p;
+          }
+        }
+      }
+    }
     // ---- phase 0: whole row -> registers; thread-local max and sum of 2^(x2 - max)
     float x[PER][N];
     float m = kNegInf;
@@ -161,13 +189,12 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
     sum = warp_sum(sum);
     if (lane == 0) wms[n & 1][wid] = make_float2(mw2, sum);
     // ---- phase 1a: occupancies gamma_t(s) (independent of the row's normaliser)
-    float blank_part = 0.f;
-    for (int s0 = 0; s0 < S; s0 += NT * SM) {
+    {
 #pragma unroll
       for (int j = 0; j < SM; ++j) {
-        const int s = s0 + tid + j * NT;
+        const int s = tid + j * NT;
         if (s < S) {
-          const float abv = s0 == 0 ? ab[j] : lattice_term(s);
+          const float abv = ab[j];
           const bool odd = s & 1;
           const int k = odd ? (s + 1) >> 1 : 0;
           const int v = odd ? lb[k] : blank;
@@ -208,14 +235,22 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
     // ---- phase 2: the <= L+1 columns that carry occupancy are overwritten by
     // their single owner thread (deterministic for repeated labels)
     const int* db = dup + (size_t)b * Lp;
-    for (int k = tid + 1; k <= L; k += NT) {
-      const int code = db[k];
-      if (code & kDupFirst) {
-        float acc = pbuf[k];
-        for (int nx = code & kDupMask; nx != 0; nx = db[nx] & kDupMask) acc += pbuf[nx];
-        const int v = lb[k];
-        const float sm = ex2(fmaf(to_f32<T>(xs[v]), kLog2e, -l2));
-        gr[v] = from_f32<T>(gb * (sm - acc));
+    for (int k0 = tid + 1; k0 <= L; k0 += NT * 4) {  // 4 positions' codes / labels in flight
+      int code[4], vv[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int k = k0 + j * NT;
+        code[j] = k <= L ? db[k] : 0;
+        vv[j] = k <= L ? lb[k] : 0;
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (code[j] & kDupFirst) {
+          float acc = pbuf[k0 + j * NT];
+          for (int nx = code[j] & kDupMask; nx != 0; nx = db[nx] & kDupMask) acc += pbuf[nx];
+          const float sm = ex2(fmaf(to_f32<T>(xs[vv[j]]), kLog2e, -l2));
+          gr[vv[j]] = from_f32<T>(gb * (sm - acc));
+        }
       }
     }
     if (tid == NT - 1) {
