@@ -122,6 +122,18 @@ __device__ __forceinline__ void stg_v4(float* p, float x, float y, float z, floa
   asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(x), "f"(y), "f"(z), "f"(w)
                : "memory");
 }
+// split lattices: boundary hand-off between CTAs through global memory (L2)
+__device__ __forceinline__ int ldg_acquire_gpu_i32(const int* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void stg_release_gpu_i32(int* p, int v) {
+  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void stg_f32(float* p, float v) {
+  asm volatile("st.global.cg.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
 // make a loop-invariant value opaque so that it is kept in a register instead
 // of being re-derived inside the serial loop
 __device__ __forceinline__ uint32_t pin(uint32_t v) {
@@ -141,6 +153,13 @@ struct LatticeArgs {
   uint32_t cons;      // shared: steps consumed   [NW] int
   uint32_t full;      // shared: full[kMaxEmRing] mbarriers, then empty[kMaxEmRing]
   int Tb, L, Lp, Sp, NWp, nw_live, zero_infinity, b, nring;
+  // split lattices (SPLIT): global index of this CTA's warp 0, staged emission row (stride
+  // Lps floats: [blank,-,-,-][label columns col0 ..]), hand-off arrays of the CTA boundary
+  // in front of this CTA (in) and behind it (out): values [Tb1] (step j at j+1), frame
+  // offsets [NB], steps published [1]
+  int W0, Lps, col0, nwc;
+  float* gv_in; int* gf_in; int* gr_in;
+  float* gv_out; int* gf_out; int* gr_out;
 };
 
 // One compute warp of the systolic lattice (see the file header).  This is the
@@ -154,13 +173,14 @@ struct LatticeArgs {
 //  * compile-time direction, full blocks of K steps as straight-line code with the
 //    block's emissions and upstream boundary values already in registers,
 //  * all hand-shaking once per block, ring slots by increment (no div / mod).
-template <int R, bool STORE, int DIR, int K>
+template <int R, bool STORE, int DIR, int K, bool SPLIT>
 __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int lane) {
   static_assert(K == 4 || K == 8 || K == 16, "block of 4, 8 or 16 steps");
   static_assert(kRenormEvery % K == 0 && kValRing >= 4 * K, "block size vs renorm period / ring");
   constexpr bool kPre = R <= 4;  // whole block's emissions preloaded into registers
-  const int Tb = A.Tb, L = A.L, S = 2 * L + 1, Lp = A.Lp;
-  const int sp0 = (w * 32 + lane) * R;  // first recursion position of this thread
+  const int Tb = A.Tb, L = A.L, S = 2 * L + 1, Lp = SPLIT ? A.Lps : A.Lp;
+  const int gw = SPLIT ? A.W0 + w : w;  // warp index within the whole lattice
+  const int sp0 = (gw * 32 + lane) * R;  // first recursion position of this thread
   // static description of this thread's positions: q even = blank, q odd = label
   uint32_t jlab[R / 2];  // byte offset of the label emission inside an em row
   bool skip[R / 2];      // may the path skip the blank in front of this label?
@@ -177,15 +197,20 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
       ok[h] = valid && (DIR ? kn <= L : kn >= 1);
       la[h] = A.lb[valid ? k : 0];
       ln[h] = A.lb[ok[h] ? kn : 0];
-      jlab[h] = pin(valid ? 4u * (uint32_t)(kEmLabel0 + k - 1) : 0u);  // dead: the blank column
+      // (split: the staged row is [blank group][columns col0 ..]); dead: the blank column
+      jlab[h] = pin(valid ? 4u * (uint32_t)(kEmLabel0 + k - 1 - (SPLIT ? A.col0 - 4 : 0)) : 0u);
     }
 #pragma unroll
     for (int h = 0; h < R / 2; ++h) skip[h] = ok[h] && la[h] != ln[h];
   }
-  const bool has_up = w > 0, has_down = w + 1 < A.nw_live;
+  const bool has_up = gw > 0, has_down = gw + 1 < A.nw_live;
   const bool lane0 = lane == 0;
-  const bool pub = has_down && lane == 31;
-  const int wu = has_up ? w - 1 : 0;
+  // neighbours in another CTA: hand-off through global memory
+  const bool up_g = SPLIT && has_up && w == 0;
+  const bool down_g = SPLIT && has_down && w == A.nwc - 1;
+  const bool pub = has_down && !down_g && lane == 31;
+  const bool pubg = down_g && lane == 31;
+  const int wu = (has_up && !up_g) ? w - 1 : 0;
   const uint32_t vals_in = pin(A.vals + (uint32_t)wu * (kValRing * 4u));
   const uint32_t vals_out = pin(A.vals + (uint32_t)w * (kValRing * 4u));
   const uint32_t fr_in = pin(A.fring + (uint32_t)wu * (kFRing * 4u));
@@ -193,7 +218,7 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
   const uint32_t ready_in = pin(A.ready + 4u * (uint32_t)wu);
   const uint32_t ready_out = pin(A.ready + 4u * (uint32_t)w);
   const uint32_t cons_mine = pin(A.cons + 4u * (uint32_t)w);
-  const uint32_t cons_down = pin(A.cons + 4u * (uint32_t)(has_down ? w + 1 : w));
+  const uint32_t cons_down = pin(A.cons + 4u * (uint32_t)((has_down && !down_g) ? w + 1 : w));
   const uint32_t row_bytes = pin(4u * (uint32_t)Lp);
   const uint32_t chunk_bytes = pin(4u * (uint32_t)(K * Lp));
   const uint32_t bar_end = pin(A.full + 8u * (uint32_t)A.nring);
@@ -204,7 +229,7 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
   int* off_p = nullptr;
   if (STORE) {
     lat_p = A.lat + (size_t)t0 * A.Sp + sp0;
-    off_p = A.off + w;  // indexed by the renorm block of the RECURSION step, both directions
+    off_p = A.off + gw;  // indexed by the renorm block of the RECURSION step, both directions
   }
   const ptrdiff_t lat_step = DIR ? -(ptrdiff_t)A.Sp : (ptrdiff_t)A.Sp;
   const bool store_ok = STORE && sp0 < A.Sp;
@@ -225,7 +250,7 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
   // sp0-1 after the previous step in MY frame (one neighbour value per thread: R is
   // even, so sp0 is a blank and needs only sp0-1, and the label at sp0+1 takes its
   // skip transition from sp0-1 as well); the new a[R-1] goes to slot `out`.
-  auto step = [&](float eb, const float (&el)[R / 2], float upv, uint32_t out) {
+  auto step = [&](float eb, const float (&el)[R / 2], float upv, uint32_t out, float* gout) {
     float p1 = __shfl_up_sync(0xffffffffu, a[R - 1], 1);
     p1 = lane0 ? upv : p1;
     float nw_[R];
@@ -244,6 +269,7 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
 #pragma unroll
     for (int q = 0; q < R; ++q) a[q] = nw_[q];
     if (pub) sts_f32_u32(out, a[R - 1]);
+    if (SPLIT && pubg) stg_f32(gout, a[R - 1]);
     // (asm stores: they stay inside their step.  Left to the scheduler they sink to the end
     //  of the block and queue up behind one another on a single address register pair.)
     if (store_ok) {
@@ -266,7 +292,21 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
     for (int u = 0; u < K; ++u) up[u] = kLogZero;
     const bool apply = (i0 & (kRenormEvery - 1)) == 0;  // first block of a renorm block
     int Fprev = 0;
-    if (has_up) {
+    if (SPLIT && up_g) {
+      // steps i0-1 .. i0+K-2 of the upstream CTA's last warp sit at gv_in[i0 .. i0+K-1]
+      const int need = (i0 + K - 1 < Tb - 1) ? i0 + K - 1 : Tb - 1;
+      while (ready_seen < need) ready_seen = ldg_acquire_gpu_i32(A.gr_in);
+#pragma unroll
+      for (int j = 0; j < K; j += 4) {
+        const float4 v = __ldcg(reinterpret_cast<const float4*>(A.gv_in + i0 + j));
+        up[j] = v.x; up[j + 1] = v.y; up[j + 2] = v.z; up[j + 3] = v.w;
+      }
+      if (i0 == 0) up[0] = kLogZero;  // "step -1": nothing arrived yet
+      if (apply) {
+        Fprev = i0 ? __ldcg(A.gf_in + ((i0 - 1) >> 4)) : 0;
+        Fup = __ldcg(A.gf_in + (i0 >> 4));
+      }
+    } else if (has_up) {
       // value of step j sits in slot (j+1) & 63: this block needs steps i0-1 .. i0+K-2.
       // The flag load and the data loads are issued back to back (shared-memory loads of
       // a warp execute in order): if the flag then says "published", the data is good and
@@ -287,7 +327,7 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
         }
       } while (ready_seen < need);
     }
-    if (has_down) {
+    if (has_down && !down_g) {
       // my slots of this block last held steps i0-64 ..: the consumer read them in the
       // block that ended at step i0 + 2K - 64
       const int needc = i0 + 2 * K - kValRing;
@@ -304,12 +344,14 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
       }
       F += D;
       if (pub) sts_i32_u32(fr_out + (((uint32_t)(i0 >> 4)) & (kFRing - 1)) * 4u, F);
+      if (SPLIT && pubg) A.gf_out[i0 >> 4] = F;
       if (STORE) {
         if (store_off) *off_p = F;
         off_p += A.NWp;
       }
     }
-    if (has_up && lane0) sts_i32_u32(cons_mine, i0 + K);  // up[] and the frame offsets are read
+    if (has_up && !up_g && lane0) sts_i32_u32(cons_mine, i0 + K);  // up[] and the frame offsets are read
+    float* const gob = SPLIT ? A.gv_out + i0 + 1 : nullptr;  // step i0+u goes to gv_out[i0+u+1]
     const uint32_t ob0 = vals_out + (((uint32_t)i0 & (kValRing - 1)) + 1u) * 4u;  // steps i0..i0+K-2
     const uint32_t ob1 = vals_out + ((uint32_t)(i0 + K) & (kValRing - 1)) * 4u;    // step i0+K-1
     mbar_wait_u32(full_addr, phase);
@@ -348,7 +390,7 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
 #pragma unroll
           for (int h = 0; h < R / 2; ++h) el[h] -= shift;
         }
-        step(eb, el, up[u] + (u == 0 ? adj0 : adj), u == K - 1 ? ob1 : ob0 + 4u * u);
+        step(eb, el, up[u] + (u == 0 ? adj0 : adj), u == K - 1 ? ob1 : ob0 + 4u * u, gob + u);
       }
       __syncwarp();
       if (lane0) mbar_arrive_u32(full_addr + 8u * kMaxEmRing);  // empty[slot]
@@ -365,14 +407,18 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
         eb -= sh;
 #pragma unroll
         for (int h = 0; h < R / 2; ++h) el[h] -= sh;
-        const float upv = has_up ? lds_f32_u32(vb + 4u * u) + (u == 0 ? adj0 : adj) : kLogZero;
-        step(eb, el, upv, ob0 + 4u * u);  // u <= K-2: no wrap
+        float upr = kLogZero;
+        if (SPLIT && up_g) upr = (i0 + u) ? __ldcg(A.gv_in + i0 + u) : kLogZero;
+        else if (has_up) upr = lds_f32_u32(vb + 4u * u);
+        const float upv = has_up ? upr + (u == 0 ? adj0 : adj) : kLogZero;
+        step(eb, el, upv, ob0 + 4u * u, gob + u);  // u <= K-2: no wrap
       }
       __syncwarp();
       if (lane0) mbar_arrive_u32(full_addr + 8u * kMaxEmRing);
     }
     // ---------------- block epilogue
     if (pub) sts_release_i32(ready_out, i0 + n);
+    if (SPLIT && pubg) stg_release_gpu_i32(A.gr_out, i0 + n);
     if ((i0 & (kRenormEvery - 1)) == kRenormEvery - K && n == K) {
       float m = kLogZero;
 #pragma unroll
@@ -395,7 +441,12 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
   // ---- epilogue: log-likelihood from the last two positions (alpha only)
   if (DIR != 0) return;
   float p1 = __shfl_up_sync(0xffffffffu, a[R - 1], 1);
-  if (has_up) {
+  if (SPLIT && up_g) {
+    while (ready_seen < Tb) ready_seen = ldg_acquire_gpu_i32(A.gr_in);
+    const float v = __ldcg(A.gv_in + Tb);
+    const int Fl = __ldcg(A.gf_in + ((Tb - 1) >> 4));
+    if (lane0) p1 = v + (float)(Fl - F);
+  } else if (has_up) {
     while (ready_seen < Tb) ready_seen = lds_acquire_i32(ready_in);
     const float v = lds_f32_u32(vals_in + ((uint32_t)Tb & (kValRing - 1)) * 4u);
     const int Fl = lds_i32_u32(fr_in + (((uint32_t)((Tb - 1) >> 4)) & (kFRing - 1)) * 4u);
@@ -425,11 +476,19 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
   }
 }
 
-template <int R, bool STORE, int K>
+struct SplitArgs {  // split lattices only (ctc_ws.cuh LossLayout::CL > 1)
+  int CL, Lps, Tb1;
+  float* bnd_val;
+  int* bnd_f;
+  int* bnd_ready;
+};
+
+template <int R, bool STORE, int K, bool SPLIT>
 __global__ void __launch_bounds__(K == 16 ? 288 : 544, 1) lattice_kernel(
     UttInfo* __restrict__ utt, const int* __restrict__ lab, int Lp, const float* __restrict__ em,
     float* __restrict__ alpha, float* __restrict__ beta, int* __restrict__ offA,
-    int* __restrict__ offB, int Tfr, int Sp, int NWp, int NB, int zero_infinity, int nring, int pdl) {
+    int* __restrict__ offB, int Tfr, int Sp, int NWp, int NB, int zero_infinity, int nring, int pdl,
+    SplitArgs sa) {
   static_assert(R % 2 == 0, "R must be even: even recursion positions are blanks");
   extern __shared__ __align__(128) float lsm[];  // em ring [nring][K*Lp] | vals | fring | ready | cons
   __shared__ __align__(8) uint64_t bars[2 * kMaxEmRing];  // full[], empty[]
@@ -437,12 +496,14 @@ __global__ void __launch_bounds__(K == 16 ? 288 : 544, 1) lattice_kernel(
   uint64_t* const empty = bars + kMaxEmRing;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int NW = (blockDim.x >> 5) - 1;  // compute warps; warp NW is the TMA producer
-  const int b = blockIdx.x, dir = blockIdx.y;
+  // split: CTA cr of CL handles warps [cr*NW, (cr+1)*NW) of utterance b's lattice
+  const int b = SPLIT ? blockIdx.x / sa.CL : blockIdx.x, dir = blockIdx.y;
+  const int cr = SPLIT ? blockIdx.x - b * sa.CL : 0;
   if (pdl == 0) griddep_launch();  // PDL: let the gradient row pass become resident behind us
   griddep_wait();                  // utt / lab / em come from the previous kernel
   const int Tb = utt[b].T, L = utt[b].L, S = 2 * L + 1;
   if (Tb == 0) {
-    if (dir == 0 && tid == 0) {
+    if (dir == 0 && tid == 0 && cr == 0) {
       const bool inf = L > 0;
       utt[b].lam = inf ? (double)kNegInf : 0.0;
       utt[b].aend = 0;
@@ -451,8 +512,24 @@ __global__ void __launch_bounds__(K == 16 ? 288 : 544, 1) lattice_kernel(
     }
     return;
   }
-  const int nw_live = (S + 32 * R - 1) / (32 * R);
-  const int chunk_elems = K * Lp;
+  const int nw_live = (S + 32 * R - 1) / (32 * R);  // over the whole lattice
+  const int W0 = cr * NW;
+  const int nw_here = SPLIT ? (nw_live - W0 < NW ? nw_live - W0 : NW) : nw_live;  // live warps of this CTA
+  if (SPLIT && nw_here <= 0) return;  // this utterance's lattice ends in an earlier CTA
+  // split: the label columns this CTA's positions [P0, P1) need, as a 16-byte aligned range
+  int col0 = 0, ncols = 0;
+  if (SPLIT) {
+    const int P0 = W0 * 32 * R;
+    const int P1 = (P0 + NW * 32 * R < S) ? P0 + NW * 32 * R : S;
+    const int s_lo = dir ? S - P1 : P0, s_hi = dir ? S - 1 - P0 : P1 - 1;  // lattice indices
+    const int k_min = (s_lo + 2) >> 1, k_max = (s_hi + 1) >> 1;           // odd s <-> label (s+1)/2
+    if (k_max >= k_min) {
+      col0 = (kEmLabel0 + k_min - 1) & ~3;
+      ncols = ((kEmLabel0 + k_max - 1 + 1 - col0) + 3) & ~3;
+    }
+  }
+  const int row_elems = SPLIT ? sa.Lps : Lp;  // staged emission row
+  const int chunk_elems = K * row_elems;
   float* ring = lsm;
   float* vals = lsm + (size_t)nring * chunk_elems;     // [NW][kValRing]
   int* fring = reinterpret_cast<int*>(vals + (size_t)NW * kValRing);  // [NW][kFRing]
@@ -461,7 +538,7 @@ __global__ void __launch_bounds__(K == 16 ? 288 : 544, 1) lattice_kernel(
   const float* emb = em + (size_t)b * Tfr * Lp;
 
   if (tid == 0) {
-    for (int i = 0; i < nring; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], nw_live); }
+    for (int i = 0; i < nring; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], nw_here); }
     fence_mbar_init();
   }
   for (int i = tid; i < NW * kValRing; i += blockDim.x) vals[i] = kLogZero;
@@ -469,6 +546,26 @@ __global__ void __launch_bounds__(K == 16 ? 288 : 544, 1) lattice_kernel(
   __syncthreads();
 
   // ------------------------------------------------------------ TMA producer warp
+  if (SPLIT && wid == NW) {
+    // partial rows: lane l copies frame l of the chunk (blank group + this CTA's columns)
+    const int nchunks = (Tb + K - 1) / K;
+    for (int c = 0; c < nchunks; ++c) {
+      const int slot = c % nring, round = c / nring;
+      if (round > 0 && lane == 0) mbar_wait(&empty[slot], (round - 1) & 1);
+      const int i0 = c * K;
+      const int n = (Tb - i0 < K) ? Tb - i0 : K;
+      const int f0 = dir ? Tb - i0 - n : i0;
+      if (lane == 0) mbar_expect_tx(&full[slot], (uint32_t)n * (16u + 4u * (uint32_t)ncols));
+      __syncwarp();
+      if (lane < n) {
+        float* dst = ring + (size_t)slot * chunk_elems + (size_t)lane * row_elems;
+        const float* src = emb + (size_t)(f0 + lane) * Lp;
+        bulk_g2s(dst, src, 16u, &full[slot]);
+        if (ncols) bulk_g2s(dst + 4, src + col0, 4u * (uint32_t)ncols, &full[slot]);
+      }
+    }
+    return;
+  }
   if (wid == NW) {
     if (lane == 0) {
       const int nchunks = (Tb + K - 1) / K;
@@ -485,7 +582,7 @@ __global__ void __launch_bounds__(K == 16 ? 288 : 544, 1) lattice_kernel(
     }
     return;
   }
-  if (wid >= nw_live) return;
+  if (wid >= nw_here) return;
 
   LatticeArgs A;
   A.utt = utt;
@@ -500,9 +597,25 @@ __global__ void __launch_bounds__(K == 16 ? 288 : 544, 1) lattice_kernel(
   A.full = smem_u32(full);
   A.Tb = Tb; A.L = L; A.Lp = Lp; A.Sp = Sp; A.NWp = NWp;
   A.nw_live = nw_live; A.zero_infinity = zero_infinity; A.b = b; A.nring = nring;
-  if (dir == 0) lattice_warp<R, STORE, 0, K>(A, wid, lane);
-  else lattice_warp<R, STORE, 1, K>(A, wid, lane);
-  if (pdl == 1 && wid == nw_live - 1) griddep_launch();  // the last warp of the pipeline is done
+  A.W0 = W0; A.Lps = row_elems; A.col0 = col0; A.nwc = NW;
+  A.gv_in = A.gv_out = nullptr; A.gf_in = A.gf_out = nullptr; A.gr_in = A.gr_out = nullptr;
+  if (SPLIT) {
+    // boundary j (between CTA j and j+1) of (b, dir): index ((b*2 + dir)*(CL-1) + j)
+    const size_t base = ((size_t)b * 2 + dir) * (size_t)(sa.CL - 1);
+    if (cr > 0) {
+      A.gv_in = sa.bnd_val + (base + cr - 1) * sa.Tb1;
+      A.gf_in = sa.bnd_f + (base + cr - 1) * NB;
+      A.gr_in = sa.bnd_ready + (base + cr - 1) * kBndReadyStride;
+    }
+    if (cr + 1 < sa.CL) {
+      A.gv_out = sa.bnd_val + (base + cr) * sa.Tb1;
+      A.gf_out = sa.bnd_f + (base + cr) * NB;
+      A.gr_out = sa.bnd_ready + (base + cr) * kBndReadyStride;
+    }
+  }
+  if (dir == 0) lattice_warp<R, STORE, 0, K, SPLIT>(A, wid, lane);
+  else lattice_warp<R, STORE, 1, K, SPLIT>(A, wid, lane);
+  if (pdl == 1 && wid == nw_here - 1) griddep_launch();  // the last warp of the pipeline is done
 }
 
 // nll[b] = -ln2 * (lam + aend + sum_t (c[t] - lse2[t]))   (ctc_ws.cuh)
@@ -572,6 +685,7 @@ static int launch_lattice_rk(const LossLayout& w, unsigned char* ws, int Tfr, in
                              int both_dirs, int nring, size_t smem, cudaStream_t st) {
   const int nt = (w.NW + 1) * 32;  // + the TMA producer warp
   dim3 grid(w.B, both_dirs ? 2 : 1);
+  const SplitArgs sa{1, 0, 0, nullptr, nullptr, nullptr};
   auto go = [&](auto k) {
     if (smem > 48 * 1024)
       cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -580,12 +694,49 @@ static int launch_lattice_rk(const LossLayout& w, unsigned char* ws, int Tfr, in
                reinterpret_cast<const float*>(ws + w.em), reinterpret_cast<float*>(ws + w.alpha),
                reinterpret_cast<float*>(ws + w.beta), reinterpret_cast<int*>(ws + w.offA),
                reinterpret_cast<int*>(ws + w.offB), Tfr, w.Sp, w.NW, w.NB, zero_infinity, nring,
-               pdl_mode());
+               pdl_mode(), sa);
   };
-  if (both_dirs) go(lattice_kernel<R, true, K>);
-  else go(lattice_kernel<R, false, K>);
+  if (both_dirs) go(lattice_kernel<R, true, K, false>);
+  else go(lattice_kernel<R, false, K, false>);
   count_launch();
   return check_launch("ctc lattice");
+}
+
+// Split lattice (LossLayout::CL > 1): R = 4, kSplitWarps compute warps + the producer per CTA,
+// 16-step blocks, CL CTAs per (utterance, direction).  blockIdx.x = b*CL + cr: an upstream CTA
+// always has the smaller index, is dispatched first and never waits on a downstream CTA (the
+// hand-off arrays hold all T steps: no back-pressure), so the wait of a downstream CTA on its
+// upstream neighbour cannot deadlock whatever the number of resident CTAs.
+static int launch_lattice_split(const LossLayout& w, unsigned char* ws, int Tfr, int zero_infinity,
+                                int both_dirs, cudaStream_t st) {
+  constexpr int R = 4, K = 16;
+  const int lps = 4 + (int)align_up((size_t)w.NWc * 16 * R + 6, 4);  // blank group + columns (+ alignment)
+  const int nring = w.NWc + 2;
+  const size_t fixed = (size_t)w.NWc * (kValRing * 4 + kFRing * 4 + 8) + 256;
+  const size_t smem = (size_t)nring * K * lps * 4 + fixed;
+  B2_REQUIRE(smem <= kLatticeSmemBudget, "ctc lattice (split): shared memory %zu", smem);
+  const size_t nb = (size_t)w.B * 2 * (size_t)(w.CL - 1);
+  if (cudaMemsetAsync(ws + w.bnd_ready, 0, 4 * nb * kBndReadyStride, st) != cudaSuccess) {
+    set_error("ctc lattice (split): memset failed");
+    return B200CTC_ERR_DEVICE;
+  }
+  const SplitArgs sa{w.CL, lps, w.Tb1, reinterpret_cast<float*>(ws + w.bnd_val),
+                     reinterpret_cast<int*>(ws + w.bnd_f), reinterpret_cast<int*>(ws + w.bnd_ready)};
+  const int nt = (w.NWc + 1) * 32;
+  dim3 grid(w.B * w.CL, both_dirs ? 2 : 1);
+  auto go = [&](auto k) {
+    cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    launch_pdl(k, grid, dim3(nt), smem, st, 0, reinterpret_cast<UttInfo*>(ws + w.utt),
+               reinterpret_cast<const int*>(ws + w.lab), w.Lp,
+               reinterpret_cast<const float*>(ws + w.em), reinterpret_cast<float*>(ws + w.alpha),
+               reinterpret_cast<float*>(ws + w.beta), reinterpret_cast<int*>(ws + w.offA),
+               reinterpret_cast<int*>(ws + w.offB), Tfr, w.Sp, w.NW, w.NB, zero_infinity, nring,
+               pdl_mode(), sa);
+  };
+  if (both_dirs) go(lattice_kernel<R, true, K, true>);
+  else go(lattice_kernel<R, false, K, true>);
+  count_launch();
+  return check_launch("ctc lattice (split)");
 }
 
 template <int R>
@@ -621,6 +772,7 @@ static int launch_lattice_r(const LossLayout& w, unsigned char* ws, int Tfr, int
 
 static inline int launch_lattice(const LossLayout& w, unsigned char* ws, int Tfr, int zero_infinity,
                                  int both_dirs, cudaStream_t st) {
+  if (w.CL > 1) return launch_lattice_split(w, ws, Tfr, zero_infinity, both_dirs, st);
   switch (w.R) {
     case 2: return launch_lattice_r<2>(w, ws, Tfr, zero_infinity, both_dirs, st);
     case 4: return launch_lattice_r<4>(w, ws, Tfr, zero_infinity, both_dirs, st);

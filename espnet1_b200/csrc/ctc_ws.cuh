@@ -51,8 +51,14 @@ constexpr int kEmLabel0 = 4;  // em row: [blank, -, -, -, label_1 .. label_L]
 
 struct LossLayout {
   int B, T, V, Lmax, Lp, Sp, R, NW, NB;
+  // wide lattices are split over CL CTAs of NWc warps each (ctc_lattice.cuh "SPLIT"); the
+  // CTAs of one (utterance, direction) hand their boundary values on through global memory
+  int CL, NWc, Tb1;  // Tb1 = padded T+1: boundary values of one CTA boundary
   size_t lse2, cmax, em, alpha, beta, offA, offB, utt, lab, dup, counter, total;
+  size_t bnd_val, bnd_f, bnd_ready;  // [B][2][CL-1] x {Tb1 floats, NB ints, 8 ints}
 };
+constexpr int kSplitWarps = 5;   // compute warps per CTA of a split lattice (R = 4)
+constexpr int kBndReadyStride = 8;  // ints per ready counter (32 B apart)
 
 // positions per thread of the lattice CTA (even); one warp covers 32*R positions.
 // Warp w+1 of the systolic lattice trails warp w by one block of K >= 4 steps, and
@@ -81,6 +87,20 @@ inline LossLayout make_loss_layout(int B, int T, int V, int Lmax) {
   w.Sp = (int)align_up((size_t)S, 8);
   w.R = lattice_R(S, w.Lp);
   w.NW = (S + 32 * w.R - 1) / (32 * w.R);
+  w.CL = 1;
+  w.NWc = w.NW;
+  // Long-form lattices (more than 16 warps of R <= 4, or an emission ring that does not fit):
+  // one SM is then MUFU-bound (~3 MUFU per position and step) and stuck with 4-step blocks.
+  // Split the positions over CL CTAs instead: R = 4, kSplitWarps warps per CTA, each CTA
+  // stages only ITS label columns of the emission rows (16-step blocks fit again).
+  static const int split = [] { const char* e = getenv("B200CTC_LAT_SPLIT"); return e ? atoi(e) : 1; }();
+  if (split && w.R > 4) {
+    w.R = 4;
+    w.NW = (S + 32 * w.R - 1) / (32 * w.R);
+    w.NWc = kSplitWarps;
+    w.CL = (w.NW + w.NWc - 1) / w.NWc;
+  }
+  w.Tb1 = (int)align_up((size_t)T + 1 + 16, 4);  // + one block: a partial block's loads overshoot
   w.NB = (T + kRenormEvery - 1) / kRenormEvery;  // renorm blocks per utterance
   size_t o = 0;
   const size_t BT = (size_t)B * T;
@@ -96,6 +116,10 @@ inline LossLayout make_loss_layout(int B, int T, int V, int Lmax) {
   w.em = take(4 * BT * w.Lp);
   w.alpha = take(4 * BT * w.Sp);
   w.beta = take(4 * BT * w.Sp);
+  const size_t nb = (size_t)B * 2 * (size_t)(w.CL - 1);
+  w.bnd_val = take(4 * nb * w.Tb1);
+  w.bnd_f = take(4 * nb * w.NB);
+  w.bnd_ready = take(4 * nb * kBndReadyStride);
   w.total = o;
   return w;
 }

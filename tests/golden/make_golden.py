@@ -313,6 +313,41 @@ def make_beam_multi():
     print("wrote beam_multi_nbest.json")
 
 
+def make_beam_opts():
+    """BatchBeamSearch options: fixed / ratio maximum lengths and a multi-token primer
+    (beam_search.py:346-365, batch_beam_search.py:131-144), single utterance each."""
+    res, arrays = {}, {}
+    cases = [
+        # name, T, V, beam, weights, pre_beam_key, seed, maxlenratio, minlenratio, primer
+        ("opt_maxlen_fixed", 30, 25, 4, {"ctc": 0.5, "decoder": 0.5, "length_bonus": 0.2}, "full", 301, -7.0, 0.0, None),
+        ("opt_maxlen_ratio", 30, 25, 3, {"ctc": 0.7, "decoder": 0.3, "length_bonus": 0.1}, "decoder", 302, 0.4, 0.0, None),
+        ("opt_primer", 26, 20, 3, {"ctc": 0.4, "decoder": 0.6, "length_bonus": 0.2}, "full", 303, 0.0, 0.0, [19, 3, 5]),
+        ("opt_beam_wide", 22, 12, 8, {"ctc": 1.0, "length_bonus": 0.4}, None, 304, 0.0, 0.0, None),
+    ]
+    for name, T, V, beam, weights, key, seed, mlr, minr, primer in cases:
+        g = torch.Generator().manual_seed(seed)
+        x = torch.randn(T, V, generator=g) * 3
+        table = torch.log_softmax(torch.randn(V, V, generator=g) * 2, dim=1)
+        arrays[f"{name}__x"] = x.numpy()
+        arrays[f"{name}__table"] = table.numpy()
+        eos = V - 1
+        scorers = {"ctc": CTCPrefixScorer(_StubCTC(), eos), "length_bonus": LengthBonus(V)}
+        if "decoder" in weights:
+            scorers["decoder"] = _Table(table)
+        bs = BatchBeamSearch(scorers=scorers, weights=weights, beam_size=beam, vocab_size=V,
+                             sos=eos, eos=eos, pre_beam_score_key=key, hyp_primer=primer)
+        with torch.no_grad():
+            nbest = bs(x=x.clone(), maxlenratio=mlr, minlenratio=minr)
+        res[name] = {"T": T, "V": V, "beam_size": beam, "weights": weights, "pre_beam_key": key,
+                     "sos": eos, "eos": eos, "maxlenratio": mlr, "minlenratio": minr, "primer": primer,
+                     "batch": [{"yseq": [int(v) for v in h.yseq], "score": float(h.score),
+                                "scores": {k: float(v) for k, v in h.scores.items()}} for h in nbest]}
+    save("beam_opts_inputs.npz", arrays)
+    with open(os.path.join(HERE, "beam_opts_nbest.json"), "w") as f:
+        json.dump(res, f, indent=1)
+    print("wrote beam_opts_nbest.json")
+
+
 def make_streaming():
     """extend_prob / extend_state (ctc_prefix_score.py:222-269) through the
     CTCPrefixScorer adapter the way batch_beam_search_online.py:306-309 does."""
@@ -354,4 +389,5 @@ if __name__ == "__main__":
     make_prefix()
     make_beam()
     make_beam_multi()
+    make_beam_opts()
     make_streaming()
