@@ -122,18 +122,38 @@ __device__ __forceinline__ void stg_v4(float* p, float x, float y, float z, floa
   asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(x), "f"(y), "f"(z), "f"(w)
                : "memory");
 }
-// split lattices: boundary hand-off between CTAs through global memory (L2)
-__device__ __forceinline__ int ldg_acquire_gpu_i32(const int* p) {
-  int v;
-  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+// Split lattices: boundary hand-off between CTAs through global memory (L2).  Every word
+// validates itself: the arrays are filled with a sentinel before the launch, the producer
+// overwrites a word exactly once (relaxed gpu-scope store), the consumer re-reads (relaxed
+// gpu-scope loads, which can be issued a block ahead) until no sentinel is left.  No flag, no
+// acquire/release fence on the serial chain.  Lattice values are never NaN by construction
+// (finite log-zero), and arithmetic NaNs are canonical (0x7fffffff), not the sentinel.
+constexpr uint32_t kBndValSentinel = 0xffffffffu;  // cudaMemset byte 0xff
+constexpr int kBndFSentinel = (int)0x80808080u;    // cudaMemset byte 0x80 (|F| stays far below)
+constexpr int kBndSpinLimit = 1 << 22;             // a lost producer gives garbage, not a hang
+__device__ __forceinline__ void stg_relaxed_f32(float* p, float v) {
+  asm volatile("st.relaxed.gpu.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+__device__ __forceinline__ void stg_relaxed_i32(int* p, int v) {
+  asm volatile("st.relaxed.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ float4 ldg_relaxed_v4(const float* p) {
+  float4 v;
+  asm volatile("ld.relaxed.gpu.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
   return v;
 }
-__device__ __forceinline__ void stg_release_gpu_i32(int* p, int v) {
-  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+__device__ __forceinline__ float ldg_relaxed_f32(const float* p) {
+  float v;
+  asm volatile("ld.relaxed.gpu.global.f32 %0, [%1];" : "=f"(v) : "l"(p));
+  return v;
 }
-__device__ __forceinline__ void stg_f32(float* p, float v) {
-  asm volatile("st.global.cg.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+__device__ __forceinline__ int ldg_relaxed_i32(const int* p) {
+  int v;
+  asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
 }
+__device__ __forceinline__ bool bnd_written(float v) { return __float_as_uint(v) != kBndValSentinel; }
 // make a loop-invariant value opaque so that it is kept in a register instead
 // of being re-derived inside the serial loop
 __device__ __forceinline__ uint32_t pin(uint32_t v) {
@@ -245,6 +265,12 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
   float adj = 0.f; // Fup - F: upstream frame -> my frame
   int ready_seen = 0, cons_seen = 0;
   uint32_t slot_addr = A.ring, full_addr = A.full, phase = 0;
+  // split, upstream in another CTA: the next block's hand-off (a flag round trip and a data
+  // round trip through L2) is fetched DURING the current block's steps
+  static_assert(!SPLIT || K == kRenormEvery, "split lattices: one renorm block per block");
+  float upn[SPLIT ? K : 1];
+  int Fupn = 0;
+  bool have_next = false;
 
   // one recursion step: emissions eb (blank) / el[] (labels), p1 = value of position
   // sp0-1 after the previous step in MY frame (one neighbour value per thread: R is
@@ -269,7 +295,7 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
 #pragma unroll
     for (int q = 0; q < R; ++q) a[q] = nw_[q];
     if (pub) sts_f32_u32(out, a[R - 1]);
-    if (SPLIT && pubg) stg_f32(gout, a[R - 1]);
+    if (SPLIT && pubg) stg_relaxed_f32(gout, a[R - 1]);
     // (asm stores: they stay inside their step.  Left to the scheduler they sink to the end
     //  of the block and queue up behind one another on a single address register pair.)
     if (store_ok) {
@@ -294,18 +320,32 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
     int Fprev = 0;
     if (SPLIT && up_g) {
       // steps i0-1 .. i0+K-2 of the upstream CTA's last warp sit at gv_in[i0 .. i0+K-1]
-      const int need = (i0 + K - 1 < Tb - 1) ? i0 + K - 1 : Tb - 1;
-      while (ready_seen < need) ready_seen = ldg_acquire_gpu_i32(A.gr_in);
+      // steps i0-1 .. i0+K-2 of the upstream CTA's last warp sit at gv_in[i0 .. i0+K-1]
+      Fprev = Fup;  // the upstream frame of the previous renorm block (0 before the first)
+      if (have_next) {  // fetched under the previous block's steps
 #pragma unroll
-      for (int j = 0; j < K; j += 4) {
-        const float4 v = __ldcg(reinterpret_cast<const float4*>(A.gv_in + i0 + j));
-        up[j] = v.x; up[j + 1] = v.y; up[j + 2] = v.z; up[j + 3] = v.w;
+        for (int j = 0; j < K; ++j) up[j] = upn[j];
+        Fup = Fupn;
       }
+      for (int spin = 0; spin < kBndSpinLimit; ++spin) {
+        bool ok = have_next || spin > 0;
+        if (ok) {
+          ok = Fup != kBndFSentinel;
+          if (n == K) {  // (a partial last block reads its values one by one below)
+#pragma unroll
+            for (int j = 0; j < K; ++j) ok = ok && (bnd_written(up[j]) || (i0 == 0 && j == 0));
+          }
+        }
+        if (__all_sync(0xffffffffu, ok)) break;
+#pragma unroll
+        for (int j = 0; j < K; j += 4) {
+          const float4 v = ldg_relaxed_v4(A.gv_in + i0 + j);
+          up[j] = v.x; up[j + 1] = v.y; up[j + 2] = v.z; up[j + 3] = v.w;
+        }
+        Fup = ldg_relaxed_i32(A.gf_in + (i0 >> 4));
+      }
+      have_next = false;
       if (i0 == 0) up[0] = kLogZero;  // "step -1": nothing arrived yet
-      if (apply) {
-        Fprev = i0 ? __ldcg(A.gf_in + ((i0 - 1) >> 4)) : 0;
-        Fup = __ldcg(A.gf_in + (i0 >> 4));
-      }
     } else if (has_up) {
       // value of step j sits in slot (j+1) & 63: this block needs steps i0-1 .. i0+K-2.
       // The flag load and the data loads are issued back to back (shared-memory loads of
@@ -344,7 +384,7 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
       }
       F += D;
       if (pub) sts_i32_u32(fr_out + (((uint32_t)(i0 >> 4)) & (kFRing - 1)) * 4u, F);
-      if (SPLIT && pubg) A.gf_out[i0 >> 4] = F;
+      if (SPLIT && pubg) stg_relaxed_i32(A.gf_out + (i0 >> 4), F);
       if (STORE) {
         if (store_off) *off_p = F;
         off_p += A.NWp;
@@ -390,6 +430,17 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
 #pragma unroll
           for (int h = 0; h < R / 2; ++h) el[h] -= shift;
         }
+        if (SPLIT && up_g && u == K / 2 && i0 + K < Tb) {
+          // the next block's hand-off: loads in flight under the remaining steps of this one
+          // (the upstream CTA is normally a block ahead; validated in the next prologue)
+#pragma unroll
+          for (int j = 0; j < K; j += 4) {
+            const float4 v = ldg_relaxed_v4(A.gv_in + i0 + K + j);
+            upn[j] = v.x; upn[j + 1] = v.y; upn[j + 2] = v.z; upn[j + 3] = v.w;
+          }
+          Fupn = ldg_relaxed_i32(A.gf_in + ((i0 + K) >> 4));
+          have_next = true;
+        }
         step(eb, el, up[u] + (u == 0 ? adj0 : adj), u == K - 1 ? ob1 : ob0 + 4u * u, gob + u);
       }
       __syncwarp();
@@ -408,8 +459,15 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
 #pragma unroll
         for (int h = 0; h < R / 2; ++h) el[h] -= sh;
         float upr = kLogZero;
-        if (SPLIT && up_g) upr = (i0 + u) ? __ldcg(A.gv_in + i0 + u) : kLogZero;
-        else if (has_up) upr = lds_f32_u32(vb + 4u * u);
+        if (SPLIT && up_g) {
+          if (i0 + u) {
+            upr = ldg_relaxed_f32(A.gv_in + i0 + u);
+            for (int spin = 0; spin < kBndSpinLimit && !bnd_written(upr); ++spin)
+              upr = ldg_relaxed_f32(A.gv_in + i0 + u);
+          }
+        } else if (has_up) {
+          upr = lds_f32_u32(vb + 4u * u);
+        }
         const float upv = has_up ? upr + (u == 0 ? adj0 : adj) : kLogZero;
         step(eb, el, upv, ob0 + 4u * u, gob + u);  // u <= K-2: no wrap
       }
@@ -418,7 +476,6 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
     }
     // ---------------- block epilogue
     if (pub) sts_release_i32(ready_out, i0 + n);
-    if (SPLIT && pubg) stg_release_gpu_i32(A.gr_out, i0 + n);
     if ((i0 & (kRenormEvery - 1)) == kRenormEvery - K && n == K) {
       float m = kLogZero;
 #pragma unroll
@@ -442,9 +499,9 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
   if (DIR != 0) return;
   float p1 = __shfl_up_sync(0xffffffffu, a[R - 1], 1);
   if (SPLIT && up_g) {
-    while (ready_seen < Tb) ready_seen = ldg_acquire_gpu_i32(A.gr_in);
-    const float v = __ldcg(A.gv_in + Tb);
-    const int Fl = __ldcg(A.gf_in + ((Tb - 1) >> 4));
+    float v = ldg_relaxed_f32(A.gv_in + Tb);
+    for (int spin = 0; spin < kBndSpinLimit && !bnd_written(v); ++spin) v = ldg_relaxed_f32(A.gv_in + Tb);
+    const int Fl = Fup;  // the upstream frame of the last renorm block, read in its prologue
     if (lane0) p1 = v + (float)(Fl - F);
   } else if (has_up) {
     while (ready_seen < Tb) ready_seen = lds_acquire_i32(ready_in);
@@ -716,7 +773,9 @@ static int launch_lattice_split(const LossLayout& w, unsigned char* ws, int Tfr,
   const size_t smem = (size_t)nring * K * lps * 4 + fixed;
   B2_REQUIRE(smem <= kLatticeSmemBudget, "ctc lattice (split): shared memory %zu", smem);
   const size_t nb = (size_t)w.B * 2 * (size_t)(w.CL - 1);
-  if (cudaMemsetAsync(ws + w.bnd_ready, 0, 4 * nb * kBndReadyStride, st) != cudaSuccess) {
+  // sentinel fill of the hand-off arrays (bnd_val and bnd_f are adjacent sections)
+  if (cudaMemsetAsync(ws + w.bnd_val, 0xff, 4 * nb * w.Tb1, st) != cudaSuccess ||
+      cudaMemsetAsync(ws + w.bnd_f, 0x80, 4 * nb * w.NB, st) != cudaSuccess) {
     set_error("ctc lattice (split): memset failed");
     return B200CTC_ERR_DEVICE;
   }
