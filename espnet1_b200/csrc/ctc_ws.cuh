@@ -94,11 +94,17 @@ inline LossLayout make_loss_layout(int B, int T, int V, int Lmax) {
   // Split the positions over CL CTAs instead: R = 4, kSplitWarps warps per CTA, each CTA
   // stages only ITS label columns of the emission rows (16-step blocks fit again).
   static const int split = [] { const char* e = getenv("B200CTC_LAT_SPLIT"); return e ? atoi(e) : 1; }();
-  if (split && w.R > 4) {
-    w.R = 4;
-    w.NW = (S + 32 * w.R - 1) / (32 * w.R);
-    w.NWc = kSplitWarps;
-    w.CL = (w.NW + w.NWc - 1) / w.NWc;
+  if (split && (w.R > 4 || (w.R == 4 && w.NW > 8))) {  // (R = 4 with > 8 warps: 4/8-step blocks)
+    const int nw4 = (S + 32 * 4 - 1) / (32 * 4);
+    const int cl = (nw4 + kSplitWarps - 1) / kSplitWarps;
+    // one CTA per SM (shared memory): only worth it while all CTAs of both directions are
+    // resident together; a second wave would start when the first has finished
+    if ((long long)B * 2 * cl <= sm_count()) {
+      w.R = 4;
+      w.NW = nw4;
+      w.NWc = kSplitWarps;
+      w.CL = cl;
+    }
   }
   w.Tb1 = (int)align_up((size_t)T + 1 + 16, 4);  // + one block: a partial block's loads overshoot
   w.NB = (T + kRenormEvery - 1) / kRenormEvery;  // renorm blocks per utterance

@@ -261,3 +261,25 @@ def test_concurrent_streams_are_bit_identical():
         torch.cuda.synchronize()
         for i in (0, 1):
             assert torch.equal(out[i][0], ref[i][0]) and torch.equal(out[i][1], ref[i][1])
+
+
+@pytest.mark.parametrize("B,T,lmin,lmax,what", [
+    (40, 700, 520, 560, "1121 positions, 160 CTAs would be needed: stays one CTA per lattice"),
+    (6, 2600, 1150, 1250, "2501 positions: 4 CTAs per lattice, ragged (some CTAs have no warps)"),
+    (5, 1100, 0, 1000, "split layout with empty and short targets in the batch"),
+])
+def test_split_lattice_layouts(B, T, lmin, lmax, what):
+    """Long lattices are split over several CTAs per (utterance, direction) with the boundary
+    values handed on through global memory (csrc/ctc_lattice.cuh SPLIT); same numbers as the
+    fp64 truth whichever layout make_loss_layout picks."""
+    logits, tg, il, tl = make_case(B, T, 48, lmin, lmax, seed=B + T, ragged=True)
+    n64, g64 = espnet_cpu.logits_loss_and_grad(logits.double(), tg, il, tl)
+    nll, g = run_cuda(logits, tg, il, tl)
+    np.testing.assert_allclose(nll.numpy(), n64.numpy(), rtol=1e-5)
+    assert (g.double() - g64).abs().max().item() < 1e-3
+    # forward-only (alpha lattice without stores) goes through the same split
+    from espnet1_b200 import functional as F
+
+    with torch.no_grad():
+        nll2 = F.ctc_loss(logits.to(DEV), tg, il, tl).cpu()
+    np.testing.assert_allclose(nll2.numpy(), n64.numpy(), rtol=1e-5)
