@@ -243,6 +243,35 @@ def bench_softmax_family(x, dev, iters=10):
     return out
 
 
+def bench_other_configs(dev, iters=10):
+    """The other loss configurations of BASELINE.json (parity-test shapes, reported for
+    completeness): C1 mini_an4 (launch-bound) and C4 long-form (split lattice), one step =
+    loss forward + gradient, device-timed; roofline fraction on SURVEY 8(d)'s bytes."""
+    from espnet1_b200 import functional as F
+
+    peak = peaks()[0]
+    out = {}
+    for name, cfg in (("C1_mini_an4", dict(B=8, T=200, V=30, lmin=25, lmax=50)),
+                      ("C4_long_form", dict(B=16, T=4000, V=5000, lmin=600, lmax=1200))):
+        logits, tg, il, tl = synth(cfg, 4321)
+        xc = logits.to(dev).requires_grad_(True)
+        tgd, ild, tld = tg.to(dev), il.to(dev), tl.to(dev)
+
+        def one():
+            xc.grad = None
+            F.ctc_loss(xc, tgd, ild, tld, max_tgt_len=cfg["lmax"], reduce_scale=1.0 / cfg["B"]).backward()
+
+        for _ in range(3):
+            one()
+        ms = time_region(one, iters, False, dev)
+        alg = algorithmic_bytes(cfg)
+        out[name] = {"config": cfg, "ms_per_step": ms, "utt_frames_per_s": cfg["B"] * cfg["T"] / (ms * 1e-3),
+                     "roofline_step_frac": alg / (ms * 1e-3) / 1e9 / peak}
+        del xc
+        torch.cuda.empty_cache()
+    return out
+
+
 def run_gpu(args):
     import ctypes
 
@@ -396,6 +425,7 @@ def run_gpu(args):
         line["torch_cuda_library_ms_per_step"] = time_region(torch_step, 10, False, dev)
         line["prefix_score"] = bench_prefix(dev)
         line["softmax_family"] = bench_softmax_family(x.detach(), dev)
+        line["other_configs"] = bench_other_configs(dev)
         del xr
         torch.cuda.empty_cache()
         sys.path.insert(0, os.path.join(ROOT, "tools"))
