@@ -71,11 +71,16 @@ __device__ __forceinline__ void prep_utterance(const PrepArgs& P, int b, int* sl
     int code = 0;
     if (k >= 1 && k <= L) {
       const int v = slab[k];
-      bool first = (v != P.blank);
-      for (int j = 1; j < k && first; ++j) first = slab[j] != v;
-      int next = 0;
-      for (int j = k + 1; j <= L; ++j)
-        if (slab[j] == v) { next = j; break; }
+      // branch-free scans: the shared-memory loads of a scan are independent and pipeline
+      // (an early exit makes every iteration wait for its load: 95 us at L = 1200)
+      bool seen = false;
+#pragma unroll 4
+      for (int j = 1; j < k; ++j) seen |= slab[j] == v;
+      const bool first = (v != P.blank) && !seen;
+      int next = 0x7fffffff;
+#pragma unroll 4
+      for (int j = k + 1; j <= L; ++j) next = min(next, slab[j] == v ? j : 0x7fffffff);
+      if (next == 0x7fffffff) next = 0;
       code = next | (first ? kDupFirst : 0);
       if (v == P.blank) atomicMin(&s_head, k);
     }
