@@ -287,7 +287,7 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
       if (q & 1) {
         const float x2r = q >= 2 ? a[q - 2] : p1;
         const float x2 = skip[q >> 1] ? x2r : kLogZero;
-        nw_[q] = R >= 8 ? lse3_lean(x0, x1, x2, el[q >> 1]) : lse3_fast(x0, x1, x2, el[q >> 1]);
+        nw_[q] = (R >= 8 || SPLIT) ? lse3_lean(x0, x1, x2, el[q >> 1]) : lse3_fast(x0, x1, x2, el[q >> 1]);
       } else {
         nw_[q] = lse2_fast(x0, x1, eb);
       }
