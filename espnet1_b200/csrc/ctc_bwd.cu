@@ -11,7 +11,11 @@
 
 namespace b200ctc {
 
-template <typename T, int NT, int PER, bool TMA>
+// WIDE (long lattices, S > 3*NT; TMA path only): the row's alpha, beta and the utterance's
+// labels are staged in shared memory by the same TMA transaction as the logits row, so the
+// occupancy loop (19 positions per thread at C4) reads shared memory instead of waiting
+// on global loads one unrolled batch at a time.
+template <typename T, int NT, int PER, bool TMA, bool WIDE>
 __global__ void __launch_bounds__(NT) grad_rows_kernel(
     const T* __restrict__ logits, T* __restrict__ grad, int B, int Tfr, int V, int blank,
     const UttInfo* __restrict__ utt, const int* __restrict__ lab, const int* __restrict__ dup,
@@ -31,6 +35,9 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int64_t nrows = (int64_t)B * Tfr;
   const uint32_t row_bytes = (uint32_t)V * sizeof(T);
+  // WIDE stage: [logits row | alpha (Sp) | beta (Sp) | labels (Lp)]
+  const uint32_t lat_off = (row_bytes + 127u) & ~127u;
+  const uint32_t lat_bytes = 4u * (uint32_t)Sp, lab_bytes = 4u * (uint32_t)Lp;
   const int nchunk = V / N;
   const int ntail = V - nchunk * N;
 
@@ -41,8 +48,14 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
     while (pc.g < nrows && (pc.t >= utt[pc.b].T || utt[pc.b].zeroed)) pc.next();
     if (pc.g < nrows) {
       const int st = np % nstage;
-      mbar_expect_tx(&bars[st], row_bytes);
-      bulk_g2s(stages + (size_t)st * stage_stride, logits + pc.g * V, row_bytes, &bars[st]);
+      unsigned char* dst = stages + (size_t)st * stage_stride;
+      mbar_expect_tx(&bars[st], WIDE ? row_bytes + 2 * lat_bytes + lab_bytes : row_bytes);
+      bulk_g2s(dst, logits + pc.g * V, row_bytes, &bars[st]);
+      if (WIDE) {
+        bulk_g2s(dst + lat_off, alpha + (size_t)pc.g * Sp, lat_bytes, &bars[st]);
+        bulk_g2s(dst + lat_off + lat_bytes, beta + (size_t)pc.g * Sp, lat_bytes, &bars[st]);
+        bulk_g2s(dst + lat_off + 2 * lat_bytes, lab + (size_t)pc.b * Lp, lab_bytes, &bars[st]);
+      }
       ++np;
       pc.next();
     }
@@ -105,10 +118,12 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
     };
     constexpr int SM = 3;  // lattice positions per thread whose loads are issued before the wait
     float ab[SM];
+    if (!WIDE) {
 #pragma unroll
-    for (int j = 0; j < SM; ++j) {
-      const int s = tid + j * NT;
-      ab[j] = s < S ? lattice_term(s) : kNegInf;
+      for (int j = 0; j < SM; ++j) {
+        const int s = tid + j * NT;
+        ab[j] = s < S ? lattice_term(s) : kNegInf;
+      }
     }
     const unsigned char* stg;
     if (TMA) {
@@ -130,12 +145,21 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
     float blank_part = 0.f;
     {
       constexpr int kW = 8;
-      for (int s0 = NT * SM; s0 < S; s0 += NT * kW) {
+      const float* als = reinterpret_cast<const float*>(stg + lat_off);  // WIDE: staged copies
+      const float* bes = als + Sp;
+      const int* lbs = reinterpret_cast<const int*>(bes + Sp);
+      for (int s0 = WIDE ? 0 : NT * SM; s0 < S; s0 += NT * kW) {
         float abw[kW];
 #pragma unroll
         for (int j = 0; j < kW; ++j) {
           const int s = s0 + tid + j * NT;
-          abw[j] = s < S ? lattice_term(s) : kNegInf;
+          if (WIDE) {
+            const int sc = s < S ? s : 0, sb = S - 1 - sc;
+            const int fo = oa[sc >> wshift] + ob[sb >> wshift] - u.aend;
+            abw[j] = s < S ? als[sc] + bes[sb] + ((float)fo + qbase) : kNegInf;
+          } else {
+            abw[j] = s < S ? lattice_term(s) : kNegInf;
+          }
         }
 #pragma unroll
         for (int j = 0; j < kW; ++j) {
@@ -143,7 +167,7 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
           if (s < S) {
             const bool odd = s & 1;
             const int k = odd ? (s + 1) >> 1 : 0;
-            const int v = odd ? lb[k] : blank;
+            const int v = odd ? (WIDE ? lbs[k] : lb[k]) : blank;
             const float em = fmaf(to_f32<T>(xs[v]), kLog2e, -c2);
             const float p = ex2(abw[j] - em);
             if (odd) pbuf[k] = p; else blank_part += p;
@@ -189,7 +213,7 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
     sum = warp_sum(sum);
     if (lane == 0) wms[n & 1][wid] = make_float2(mw2, sum);
     // ---- phase 1a: occupancies gamma_t(s) (independent of the row's normaliser)
-    {
+    if (!WIDE) {
 #pragma unroll
       for (int j = 0; j < SM; ++j) {
         const int s = tid + j * NT;
@@ -273,7 +297,20 @@ static int launch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, 
                          int gstride, float gmul, cudaStream_t st) {
   constexpr int PER = 40 / Elems<T>::N;
   const size_t extra = align_up(sizeof(float) * (size_t)w.Lp, 128);
-  const RowLaunchCfg c = row_launch_cfg(logits, (size_t)V * sizeof(T), extra, NT, "B200CTC_B");
+  RowLaunchCfg c = row_launch_cfg(logits, (size_t)V * sizeof(T), extra, NT, "B200CTC_B");
+  // long lattices: alpha / beta / labels of the row are staged next to the logits row
+  static const int wide_on = [] { const char* e = getenv("B200CTC_B_WIDE"); return e ? atoi(e) : 1; }();
+  const size_t lat_stage = align_up(4 * (2 * (size_t)w.Sp + (size_t)w.Lp), 128);
+  bool wide = wide_on && c.tma && 2 * w.Lmax + 1 > 3 * NT;
+  if (wide) {
+    const size_t row_al = align_up((size_t)V * sizeof(T), 128);
+    const RowLaunchCfg cw = row_launch_cfg(logits, row_al + lat_stage, extra, NT, "B200CTC_B");
+    if (cw.ctas_per_sm * ((size_t)cw.nstage * cw.stride + extra + 1024) <= 220 * 1024 && cw.ctas_per_sm >= 3) {
+      c.nstage = cw.nstage; c.ctas_per_sm = cw.ctas_per_sm; c.stride = cw.stride;
+    } else {
+      wide = false;
+    }
+  }
   B2_REQUIRE((size_t)c.nstage * c.stride + extra <= 226 * 1024,
              "ctc_loss grad: V=%d too large for the shared-memory row path", V);
   const size_t smem = (size_t)c.nstage * c.stride + extra;
@@ -296,8 +333,9 @@ static int launch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, 
         reinterpret_cast<const int*>(ws + w.offA), reinterpret_cast<const int*>(ws + w.offB),
         gscale, gstride, gmul, c.nstage, c.stride, pdl_mode());
   };
-  if (c.tma) go(grad_rows_kernel<T, NT, PER, true>);
-  else go(grad_rows_kernel<T, NT, PER, false>);
+  if (wide) go(grad_rows_kernel<T, NT, PER, true, true>);
+  else if (c.tma) go(grad_rows_kernel<T, NT, PER, true, false>);
+  else go(grad_rows_kernel<T, NT, PER, false, false>);
   count_launch();
   return check_launch("ctc grad_rows");
 }
