@@ -35,7 +35,7 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int64_t nrows = (int64_t)B * Tfr;
   const uint32_t row_bytes = (uint32_t)V * sizeof(T);
-  // WIDE stage: [logits row | alpha (Sp) | beta (Sp) | labels (Lp)]
+  // WIDE stage: [logits row | alpha (Sp) | beta (Sp) | labels (Lp) | duplicate codes (Lp)]
   const uint32_t lat_off = (row_bytes + 127u) & ~127u;
   const uint32_t lat_bytes = 4u * (uint32_t)Sp, lab_bytes = 4u * (uint32_t)Lp;
   const int nchunk = V / N;
@@ -49,12 +49,13 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
     if (pc.g < nrows) {
       const int st = np % nstage;
       unsigned char* dst = stages + (size_t)st * stage_stride;
-      mbar_expect_tx(&bars[st], WIDE ? row_bytes + 2 * lat_bytes + lab_bytes : row_bytes);
+      mbar_expect_tx(&bars[st], WIDE ? row_bytes + 2 * lat_bytes + 2 * lab_bytes : row_bytes);
       bulk_g2s(dst, logits + pc.g * V, row_bytes, &bars[st]);
       if (WIDE) {
         bulk_g2s(dst + lat_off, alpha + (size_t)pc.g * Sp, lat_bytes, &bars[st]);
         bulk_g2s(dst + lat_off + lat_bytes, beta + (size_t)pc.g * Sp, lat_bytes, &bars[st]);
         bulk_g2s(dst + lat_off + 2 * lat_bytes, lab + (size_t)pc.b * Lp, lab_bytes, &bars[st]);
+        bulk_g2s(dst + lat_off + 2 * lat_bytes + lab_bytes, dup + (size_t)pc.b * Lp, lab_bytes, &bars[st]);
       }
       ++np;
       pc.next();
@@ -258,14 +259,16 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
     __syncthreads();  // dense stores are ordered before the column fix-ups below
     // ---- phase 2: the <= L+1 columns that carry occupancy are overwritten by
     // their single owner thread (deterministic for repeated labels)
-    const int* db = dup + (size_t)b * Lp;
+    const int* db = WIDE ? reinterpret_cast<const int*>(stg + lat_off + 2 * lat_bytes + lab_bytes)
+                         : dup + (size_t)b * Lp;
+    const int* lb2 = WIDE ? reinterpret_cast<const int*>(stg + lat_off + 2 * lat_bytes) : lb;
     for (int k0 = tid + 1; k0 <= L; k0 += NT * 4) {  // 4 positions' codes / labels in flight
       int code[4], vv[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const int k = k0 + j * NT;
         code[j] = k <= L ? db[k] : 0;
-        vv[j] = k <= L ? lb[k] : 0;
+        vv[j] = k <= L ? lb2[k] : 0;
       }
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
@@ -300,7 +303,7 @@ static int launch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, 
   RowLaunchCfg c = row_launch_cfg(logits, (size_t)V * sizeof(T), extra, NT, "B200CTC_B");
   // long lattices: alpha / beta / labels of the row are staged next to the logits row
   static const int wide_on = [] { const char* e = getenv("B200CTC_B_WIDE"); return e ? atoi(e) : 1; }();
-  const size_t lat_stage = align_up(4 * (2 * (size_t)w.Sp + (size_t)w.Lp), 128);
+  const size_t lat_stage = align_up(4 * (2 * (size_t)w.Sp + 2 * (size_t)w.Lp), 128);
   bool wide = wide_on && c.tma && 2 * w.Lmax + 1 > 3 * NT;
   if (wide) {
     const size_t row_al = align_up((size_t)V * sizeof(T), 128);
