@@ -184,6 +184,8 @@ class BatchBeamSearch(torch.nn.Module):
                 step_sc[k], new_full[k] = d.batch_score(yseq, full_states[k], xs_rep)
                 if not fused:
                     w += self.weights[k] * step_sc[k]
+                elif step_sc[k].dtype != torch.float32:
+                    step_sc[k] = step_sc[k].float()  # the pruning kernel reads fp32 matrices
             tp = self._tick("full_scorers", tp, dev)
             part_ids = None
             if self.do_pre_beam and fused:

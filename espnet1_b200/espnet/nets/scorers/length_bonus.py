@@ -13,9 +13,16 @@ class LengthBonus(BatchScorerInterface):
 
     def __init__(self, n_vocab: int):
         self.n = n_vocab
+        self._one = {}  # (device, dtype) -> the constant, made once (the reference uploads it every call)
+
+    def _const(self, ref: torch.Tensor) -> torch.Tensor:
+        key = (ref.device, ref.dtype)
+        if key not in self._one:
+            self._one[key] = torch.tensor([1.0], device=ref.device, dtype=ref.dtype)
+        return self._one[key]
 
     def score(self, y, state, x):
-        return torch.tensor([1.0], device=x.device, dtype=x.dtype).expand(self.n), None
+        return self._const(x).expand(self.n), None
 
     def batch_score(self, ys, states, xs):
-        return torch.tensor([1.0], device=xs.device, dtype=xs.dtype).expand(ys.shape[0], self.n), None
+        return self._const(xs).expand(ys.shape[0], self.n), None
