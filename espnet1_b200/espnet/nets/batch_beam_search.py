@@ -19,7 +19,8 @@ pattern of rnn/decoders.py:752-937 with the BatchBeamSearch semantics):
   replaces n_beam ``select_state`` slices (``CTCPrefixScorer.batch_select_state``);
 * ONE device->host read per step (tokens, back-pointers, scores of the new
   slots) feeds the host-side bookkeeping that the algorithm needs anyway:
-  collecting ended hypotheses and Eq. (50) end detection.
+  collecting ended hypotheses and Eq. (50) end detection; the prefixes are read
+  only at positions where a hypothesis ends, the n-best lists go back in one upload.
 
 Scorers that only implement the reference's list-of-states interface
 (``batch_score`` / ``batch_score_partial`` / ``select_state``) are driven through
@@ -166,7 +167,6 @@ class BatchBeamSearch(torch.nn.Module):
             active_u8 = torch.ones(U, dtype=torch.uint8, device=dev)
             maxlen_i32 = torch.tensor(maxlen, dtype=torch.int32, device=dev)
             yseq = ybuf[0][:, :P0]
-        back: List[Any] = []                                             # host: (prev slot, token) per step
         ended: List[List[dict]] = [[] for _ in range(U)]
         best_all = [-np.inf] * U
         best_len: List[Dict[int, float]] = [dict() for _ in range(U)]
@@ -253,15 +253,16 @@ class BatchBeamSearch(torch.nn.Module):
                                       for j in range(W)]
 
             # ---- post-process (batch_beam_search.py:285-347) + end detection, on the host.
-            # Prefixes are kept as back-pointers; only a hypothesis that ends is written out.
-            back.append((h_prev, h_tok))
+            # The prefixes stay on the device; they are read (one copy) only at a position
+            # where some hypothesis ends.
             valid = h_val != -np.inf            # fewer than beam_size candidates: not a hypothesis
             is_last = maxlen_np - 1 == i        # eos in the final loop (:318-335)
             ends = valid & ((h_tok == self.eos) | is_last[:, None]) & ~done_np[:, None]
             running = (valid & ~ends).sum(1)
             changed = False
+            y_host = yseq.cpu().numpy() if ends.any() else None
             for u, j in zip(*np.nonzero(ends)):
-                seq = self._trace(back, int(u), int(j), primer)
+                seq = y_host[int(u) * W + int(j)].tolist()
                 if is_last[u]:
                     seq.append(self.eos)
                 states = {k: None for k in self.full_scorers}
@@ -290,24 +291,30 @@ class BatchBeamSearch(torch.nn.Module):
                     active_u8 = active.view(-1).to(torch.uint8)
         self.last_steps = i + 1
 
-        out = []
-        for u in range(U):
-            nbest = sorted(ended[u], key=lambda h: h["score"], reverse=True)
-            out.append([Hypothesis(yseq=torch.tensor(h["yseq"], dtype=torch.int64, device=dev),
-                                   score=torch.tensor(h["score"], dtype=xs.dtype),
-                                   scores={k: torch.tensor(v, dtype=xs.dtype) for k, v in h["scores"].items()},
-                                   states=h["states"])
-                        for h in nbest])
+        # n-best lists: ONE upload of all token sequences (padded) and one tensor of all scores;
+        # every Hypothesis holds views of them (yseq on the input's device like the reference's)
+        order = [sorted(ended[u], key=lambda h: h["score"], reverse=True) for u in range(U)]
+        flat = [h for nb in order for h in nb]
+        out: List[List[Hypothesis]] = [[] for _ in range(U)]
+        if flat:
+            lmax = max(len(h["yseq"]) for h in flat)
+            ypad = np.full((len(flat), lmax), self.eos, dtype=np.int64)
+            vals = np.empty((len(flat), 1 + len(names)), dtype=np.float64)
+            for r, h in enumerate(flat):
+                ypad[r, : len(h["yseq"])] = h["yseq"]
+                vals[r, 0] = h["score"]
+                for q, k in enumerate(names):
+                    vals[r, 1 + q] = h["scores"][k]
+            y_all = torch.from_numpy(ypad).to(dev)
+            v_all = torch.from_numpy(vals).to(xs.dtype)
+            r = 0
+            for u in range(U):
+                for h in order[u]:
+                    out[u].append(Hypothesis(yseq=y_all[r, : len(h["yseq"])], score=v_all[r, 0],
+                                             scores={k: v_all[r, 1 + q] for q, k in enumerate(names)},
+                                             states=h["states"]))
+                    r += 1
         return out
-
-    @staticmethod
-    def _trace(back, u: int, j: int, primer: List[int]) -> List[int]:
-        """Prefix of slot (u, j) after the last recorded step, from the back-pointers."""
-        toks = []
-        for h_prev, h_tok in reversed(back):
-            toks.append(int(h_tok[u, j]))
-            j = int(h_prev[u, j])
-        return list(primer) + toks[::-1]
 
     @staticmethod
     def _end_detect(best: float, best_by_len: Dict[int, float], i: int, M: int = 3) -> bool:
