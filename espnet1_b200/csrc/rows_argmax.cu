@@ -66,12 +66,69 @@ __device__ __forceinline__ unsigned long long row_argmax(const T* __restrict__ x
   return best;
 }
 
+// Rows of up to 256*kArgChunks*VEC elements: the thread's share goes to registers with all
+// its loads in flight, the maximum is a plain FMNMX chain (2 instructions per element instead
+// of the 64-bit key/compare/select per element above), and only the thread's winner is packed
+// for the block reduction.  NaN = maximum, first index among equals - as torch.argmax.
+constexpr int kArgChunks = 5;
+
+template <typename T, int VEC>
+__device__ __forceinline__ unsigned long long row_argmax_regs(const T* __restrict__ xr, int nchunk,
+                                                              unsigned long long* red) {
+  float v[kArgChunks][VEC];
+#pragma unroll
+  for (int j = 0; j < kArgChunks; ++j) {
+    const int i = threadIdx.x + j * 256;
+    if (i < nchunk) {
+      if (VEC == 4) {
+        const float4 t = __ldcs(reinterpret_cast<const float4*>(xr) + i);
+        v[j][0] = t.x; v[j][1] = t.y; v[j][2] = t.z; v[j][3] = t.w;
+      } else {
+        const uint4 t = __ldcs(reinterpret_cast<const uint4*>(xr) + i);
+        const T* h = reinterpret_cast<const T*>(&t);
+#pragma unroll
+        for (int e = 0; e < VEC; ++e) v[j][e] = to_f32<T>(h[e]);
+      }
+    } else {
+#pragma unroll
+      for (int e = 0; e < VEC; ++e) v[j][e] = kNegInf;
+    }
+  }
+  float m = kNegInf;
+  bool nan = false;
+#pragma unroll
+  for (int j = 0; j < kArgChunks; ++j)
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) {
+      m = fmaxf(m, v[j][e]);  // (ignores NaN)
+      nan |= v[j][e] != v[j][e];
+    }
+  uint32_t idx = 0xFFFFFFFFu;
+#pragma unroll
+  for (int j = kArgChunks - 1; j >= 0; --j)
+#pragma unroll
+    for (int e = VEC - 1; e >= 0; --e) {
+      const bool hit = nan ? (v[j][e] != v[j][e]) : (v[j][e] == m);
+      const uint32_t i = (uint32_t)((threadIdx.x + j * 256) * VEC + e);
+      idx = (hit && threadIdx.x + j * 256 < nchunk) ? i : idx;  // descending scan: first hit wins
+    }
+  unsigned long long best = idx == 0xFFFFFFFFu ? 0ull : pack(nan ? 0xFFFFFFFFu : order_key(m), idx);
+  best = warp_max_u64(best);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  if (l == 0) red[w] = best;
+  __syncthreads();
+  best = (l < 8) ? red[l] : 0ull;
+  return warp_max_u64(best);
+}
+
 template <typename T, int VEC>
 __global__ void __launch_bounds__(256) argmax_kernel(const T* __restrict__ x,
                                                      int64_t* __restrict__ out, int V) {
   __shared__ unsigned long long red[32];
   const int64_t row = blockIdx.x;
-  const unsigned long long best = row_argmax<T, VEC>(x + row * V, V, red);
+  unsigned long long best;
+  if (VEC > 1 && V / VEC <= 256 * kArgChunks) best = row_argmax_regs<T, VEC>(x + row * V, V / VEC, red);
+  else best = row_argmax<T, VEC>(x + row * V, V, red);
   if (threadIdx.x == 0) out[row] = (int64_t)(0xFFFFFFFFu - (uint32_t)(best & 0xFFFFFFFFull));
 }
 

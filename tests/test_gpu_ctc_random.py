@@ -283,3 +283,22 @@ def test_split_lattice_layouts(B, T, lmin, lmax, what):
     with torch.no_grad():
         nll2 = F.ctc_loss(logits.to(DEV), tg, il, tl).cpu()
     np.testing.assert_allclose(nll2.numpy(), n64.numpy(), rtol=1e-5)
+
+
+@pytest.mark.parametrize("V,dtype", [(5000, torch.float32), (5120, torch.float32), (8000, torch.float32),
+                                     (5000, torch.bfloat16), (1000, torch.float16), (30, torch.float32)])
+def test_argmax_integer_identical_to_torch(V, dtype):
+    """espnet2/asr/ctc.py:119-127: first maximal index; ties, -inf rows, -0/+0 and NaN rows
+    (register fast path for rows up to 256*5 16-byte chunks, loop path beyond)."""
+    from espnet1_b200 import functional as F
+
+    g = torch.Generator().manual_seed(V)
+    x = (torch.randn(64, V, generator=g) * 3).to(dtype)
+    x[1] = float("-inf")                       # all -inf: index 0
+    x[2, 7] = x[2].max() ; x[2, 4000 % V] = x[2, 7]   # a tie: the first one
+    x[3] = 0.0 ; x[3, 5] = -0.0                # -0 == +0: index 0
+    x[4, 17] = float("nan") ; x[4, 3 % V] = 1e4       # NaN counts as the maximum
+    x[5, V - 1] = 1e4                          # the last element
+    x[6] = torch.round(x[6])                   # many ties
+    got = F.argmax(x.to(DEV)).cpu()
+    assert torch.equal(got, x.float().argmax(-1)), (V, dtype)
