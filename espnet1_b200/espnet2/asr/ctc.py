@@ -107,6 +107,31 @@ class CTC(torch.nn.Module):
         )
         return loss
 
+    def forward_multi(self, hs_pads, hlens, ys_pad, ys_lens):
+        """Losses of several encoder outputs against the same labels: the intermediate-CTC
+        pattern of ``espnet2/asr/espnet_model.py:243-286`` (one ``self.ctc(...)`` call per
+        tapped layer plus the final one).  Returns ``[forward(hs, ...) for hs in hs_pads]``
+        - same values and gradients - but the heads are issued on alternating side streams,
+        so that the latency-bound lattice of one head (60 us at C2 during which nothing of
+        the same head can use the memory system) runs under the HBM-bound row pass of the
+        other."""
+        if len(hs_pads) <= 1 or not hs_pads[0].is_cuda:
+            return [self.forward(hs, hlens, ys_pad, ys_lens) for hs in hs_pads]
+        dev = hs_pads[0].device
+        cur = torch.cuda.current_stream(dev)
+        if getattr(self, "_side_streams", None) is None or self._side_streams[0].device != dev:
+            self._side_streams = [torch.cuda.Stream(dev), torch.cuda.Stream(dev)]
+        ready = cur.record_event()
+        out = []
+        for i, hs in enumerate(hs_pads):
+            side = self._side_streams[i % 2]
+            side.wait_event(ready)
+            with torch.cuda.stream(side):
+                out.append(self.forward(hs, hlens, ys_pad, ys_lens))
+        for side in self._side_streams[: len(hs_pads)]:
+            cur.wait_stream(side)
+        return out
+
     def softmax(self, hs_pad):
         """softmax of frame activations: (B, Tmax, eprojs) -> (B, Tmax, odim)."""
         return B.softmax(self.ctc_lo(hs_pad))

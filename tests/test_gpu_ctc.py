@@ -136,3 +136,34 @@ def test_c1_logits_boundary_vs_fixture_and_oracle():
     err_ref = np.abs(g["grad"] - g64).max()
     assert err_ours <= max(2 * err_ref, 2e-6), (err_ours, err_ref)
     close(nll.detach().cpu().numpy().astype(np.float64), n64, 2e-6, 0)
+
+
+def test_forward_multi_equals_sequential_calls():
+    """Intermediate-CTC heads (espnet_model.py:243-286) issued on alternating streams give
+    bit-identical losses and gradients to one ``forward`` call per head."""
+    import torch
+
+    from espnet1_b200.espnet2.asr.ctc import CTC
+
+    dev = "cuda:0"
+    g = torch.Generator().manual_seed(9)
+    B, T, D, V = 6, 70, 16, 40
+    hs = [torch.randn(B, T, D, generator=g).to(dev).requires_grad_(True) for _ in range(3)]
+    hl = torch.tensor([70, 64, 70, 33, 70, 50], device=dev)
+    yl = torch.tensor([9, 4, 0, 12, 7, 5], device=dev)
+    ys = torch.randint(1, V, (B, 12), generator=g).to(dev)
+    ctc = CTC(V, D).to(dev)
+    want = [ctc(h, hl, ys, yl) for h in hs]
+    sum(want).backward()
+    gw = [h.grad.clone() for h in hs] + [ctc.ctc_lo.weight.grad.clone()]
+    for h in hs:
+        h.grad = None
+    ctc.zero_grad(set_to_none=True)
+    got = ctc.forward_multi(hs, hl, ys, yl)
+    sum(got).backward()
+    torch.cuda.synchronize()
+    assert [float(a) for a in got] == [float(a) for a in want]
+    for a, h in zip(gw[:3], hs):
+        assert torch.equal(a, h.grad)
+    torch.testing.assert_close(ctc.ctc_lo.weight.grad, gw[3], rtol=1e-5, atol=1e-6)
+    assert len(ctc.forward_multi(hs[:1], hl, ys, yl)) == 1
