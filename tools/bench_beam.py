@@ -20,7 +20,27 @@ from espnet1_b200.espnet.nets.batch_beam_search import BatchBeamSearch  # noqa: 
 from espnet1_b200.espnet.nets.scorers.ctc import CTCPrefixScorer  # noqa: E402
 from espnet1_b200.espnet.nets.scorers.length_bonus import LengthBonus  # noqa: E402
 from oracle import beam_harness  # noqa: E402
-from oracle.scorer_port import TableScorer  # noqa: E402
+
+
+class TableScorer:
+    """Stand-in attention decoder of the benchmark (defined here: the measured engine path uses
+    nothing from oracle/): next-token log-probs depend on the last token only (a bigram table),
+    the role of the tiny random decoders in the reference's test/test_beam_search.py:90-119."""
+
+    def __init__(self, table):
+        self.table = table
+
+    def init_state(self, x):
+        return None
+
+    def batch_score(self, ys, states, xs):
+        return self.table[ys[:, -1]], None
+
+    def score(self, y, state, x):
+        return self.table[int(y[-1])], None
+
+    def final_score(self, state):
+        return 0.0
 
 
 D = 256  # encoder output size: x (T, D) -> ctc_lo -> (T, V), as espnet2/asr/ctc.py:109-117

@@ -14,7 +14,7 @@ from espnet1_b200.espnet.nets.batch_beam_search import BatchBeamSearch  # noqa: 
 from espnet1_b200.espnet.nets.scorers.ctc import CTCPrefixScorer  # noqa: E402
 from espnet1_b200.espnet.nets.scorers.length_bonus import LengthBonus  # noqa: E402
 from espnet1_b200.espnet2.asr.ctc import CTC  # noqa: E402
-from oracle.scorer_port import TableScorer  # noqa: E402
+from bench_beam import TableScorer  # noqa: E402
 
 dev = "cuda:0"
 U, W, V, T, D, POS = 32, 10, 5000, 500, 256, 30
