@@ -114,7 +114,9 @@ class CTC(torch.nn.Module):
         - same values and gradients - but the heads are issued on alternating side streams,
         so that the latency-bound lattice of one head (60 us at C2 during which nothing of
         the same head can use the memory system) runs under the HBM-bound row pass of the
-        other."""
+        other.  (PyTorch may warn once that an AccumulateGrad node runs on a
+        different stream than the head that feeds it: autograd inserts the needed
+        synchronisation itself; results are bit-identical.)"""
         if len(hs_pads) <= 1 or not hs_pads[0].is_cuda:
             return [self.forward(hs, hlens, ys_pad, ys_lens) for hs in hs_pads]
         dev = hs_pads[0].device

@@ -162,7 +162,7 @@ def test_forward_multi_equals_sequential_calls():
     got = ctc.forward_multi(hs, hl, ys, yl)
     sum(got).backward()
     torch.cuda.synchronize()
-    assert [float(a) for a in got] == [float(a) for a in want]
+    assert [float(a.detach()) for a in got] == [float(a.detach()) for a in want]
     for a, h in zip(gw[:3], hs):
         assert torch.equal(a, h.grad)
     torch.testing.assert_close(ctc.ctc_lo.weight.grad, gw[3], rtol=1e-5, atol=1e-6)
