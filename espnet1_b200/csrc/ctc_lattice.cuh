@@ -37,6 +37,10 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 // NaN guards: kLogZero absorbs every real increment (ulp(1e30) ~ 7e22), the
 // difference of two log-zeros is 0 (not NaN), and 2^(kLogZero - x) underflows to 0.
 constexpr float kLogZero = -1.0e30f;
+#ifndef B200CTC_REF_OWN
+#define B200CTC_REF_OWN 1
+#endif
+constexpr bool kRefOwn = B200CTC_REF_OWN != 0;
 constexpr float kLogZeroTest = -1.0e29f;  // "is alive" threshold
 
 // log2(2^a + 2^b) + e : 2 MUFU, chain FADD -> EX2 -> FADD -> LG2 -> FADD
@@ -284,7 +288,18 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
     for (int q = 0; q < R; ++q) {
       const float x0 = a[q];
       const float x1 = q >= 1 ? a[q - 1] : p1;
-      if (q & 1) {
+      if (kRefOwn && R == 2 && q == 1) {
+        // The label position that takes the neighbour's value p1 (fresh from the SHFL): the
+        // two own terms are summed relative to THEIR maximum before p1 is known (off the
+        // chain), p1 joins with one FADD -> EX2 -> FADD -> LG2 -> FADD instead of passing a
+        // 3-way maximum first.  d > 24: the own terms are below fp32 resolution of the result.
+        const float mo = fmaxf(x0, x1);
+        const float so = ex2(x0 - mo) + ex2(x1 - mo);
+        const float d = p1 - (skip[0] ? mo : 1.0e30f);
+        // (no clamp: for huge d, ex2 gives +inf, r = +inf - never NaN - and is not selected)
+        const float r = (mo + el[0]) + lg2(so + ex2(d));
+        nw_[q] = d > 24.f ? p1 + el[0] : r;
+      } else if (q & 1) {
         const float x2r = q >= 2 ? a[q - 2] : p1;
         const float x2 = skip[q >> 1] ? x2r : kLogZero;
         nw_[q] = (R >= 8 || SPLIT) ? lse3_lean(x0, x1, x2, el[q >> 1]) : lse3_fast(x0, x1, x2, el[q >> 1]);
