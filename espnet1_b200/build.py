@@ -25,6 +25,11 @@ NVCC_FLAGS = [
 ]
 
 
+def _extra_flags():
+    """tuning builds only: B200CTC_NVCC_EXTRA="-DB200CTC_REF_OWN=2" python -m espnet1_b200.build --force"""
+    return os.environ.get("B200CTC_NVCC_EXTRA", "").split()
+
+
 def _nvcc() -> str:
     cand = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     if not os.path.exists(cand):
@@ -55,7 +60,7 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
     procs = []
     for src in sources():
         obj = os.path.join(objdir, os.path.basename(src)[:-3] + ".o")
-        cmd = [nvcc, *NVCC_FLAGS, "-c", src, "-o", obj]
+        cmd = [nvcc, *NVCC_FLAGS, *_extra_flags(), "-c", src, "-o", obj]
         procs.append((src, obj, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))
     objs = []
     log = []

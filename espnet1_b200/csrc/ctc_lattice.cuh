@@ -288,7 +288,7 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
     for (int q = 0; q < R; ++q) {
       const float x0 = a[q];
       const float x1 = q >= 1 ? a[q - 1] : p1;
-      if (kRefOwn && R == 2 && q == 1) {
+      if (kRefOwn && (R == 2 || B200CTC_REF_OWN >= 2) && q == 1) {
         // The label position that takes the neighbour's value p1 (fresh from the SHFL): the
         // two own terms are summed relative to THEIR maximum before p1 is known (off the
         // chain), p1 joins with one FADD -> EX2 -> FADD -> LG2 -> FADD instead of passing a
