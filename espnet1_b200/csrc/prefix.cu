@@ -136,6 +136,9 @@ __global__ void __launch_bounds__(256) prefix_fill_kernel(
 }
 
 constexpr int kPF = 16;  // frames fetched ahead of the recursion
+#ifndef B200CTC_PSI_BLOCKED
+#define B200CTC_PSI_BLOCKED 0  // 1: psi reduced per group of kPF frames (tuning build, see profiles/README.md)
+#endif
 
 // TC: lp_t is the time-contiguous copy (B,V,T); else lp rows (B,T,V) are read directly
 template <bool TC>
@@ -188,16 +191,37 @@ __global__ void __launch_bounds__(128) prefix_step_kernel(
 #pragma unroll
     for (int j = 0; j < kPF; ++j) { x_k[j] = cx[j]; x_b[j] = cb[j]; phi[j] = cp[j]; }
     if (t0 + kPF < end) fetch(t0 + kPF);  // next group: in flight while this one is computed
+#if B200CTC_PSI_BLOCKED
+    // psi is a plain reduction over the frames (no recursion): one maximum and one rescale
+    // per group of kPF terms instead of a running-maximum update per frame, and none of it
+    // sits on the r^n / r^b chain below
+    {
+      float term[kPF], tm = -__builtin_huge_valf();
+#pragma unroll
+      for (int j = 0; j < kPF; ++j) {
+        term[j] = (t0 + j < end) ? phi[j] + x_k[j] : -__builtin_huge_valf();
+        tm = fmaxf(tm, term[j]);
+      }
+      const float m2 = fmaxf(pm, tm);
+      float acc = ps * __expf(pm - m2);
+#pragma unroll
+      for (int j = 0; j < kPF; ++j) acc += __expf(term[j] - m2);
+      ps = acc;
+      pm = m2;
+    }
+#endif
 #pragma unroll
     for (int j = 0; j < kPF; ++j) {
       const int t = t0 + j;
       if (t < end) {
         const float rn_new = lse2_mufu(rn, phi[j]) + x_k[j];
         const float rb_new = lse2_mufu(rn, rb) + x_b[j];
+#if !B200CTC_PSI_BLOCKED
         const float term = phi[j] + x_k[j];
         const float m2 = fmaxf(pm, term);
         ps = ps * __expf(pm - m2) + __expf(term - m2);
         pm = m2;
+#endif
         __stcs(rout + ((size_t)t * 2 + 0) * plane, rn_new);
         __stcs(rout + ((size_t)t * 2 + 1) * plane, rb_new);
         rn = rn_new;
