@@ -333,6 +333,33 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
     for (int u = 0; u < K; ++u) up[u] = kLogZero;
     const bool apply = (i0 & (kRenormEvery - 1)) == 0;  // first block of a renorm block
     int Fprev = 0;
+    // The block's emissions go to registers BEFORE the hand-shake with the upstream warp: the
+    // chunk has normally landed long ago, and a trailing warp would otherwise pay the 2*K
+    // shared-memory loads between "upstream has published" and its first step.
+    // (Only where the emission ring has slack, i.e. the short lattices that run 16-step blocks
+    //  in one CTA.  Where the ring is just deeper than the warp skew, waiting for the chunk
+    //  before acknowledging the upstream values couples the two rings: split C4 0.71 -> 0.80
+    //  ms, one-CTA S=601 / 1201 / 2401 lattices +2..5 %.)
+    float ebv[kPre ? K : 1], elv[kPre ? K : 1][R / 2];
+    auto preload = [&]() {
+      mbar_wait_u32(full_addr, phase);
+      if (kPre && n == K) {
+        uint32_t erow = slot_addr + (DIR ? (uint32_t)(K - 1) * row_bytes : 0u);
+#pragma unroll
+      for (int u = 0; u < K; ++u) {
+        ebv[u] = lds_em(erow);
+#pragma unroll
+        for (int h = 0; h < R / 2; ++h) elv[u][h] = lds_em(erow + jlab[h]);
+        if (DIR) erow -= row_bytes; else erow += row_bytes;
+      }
+      // (The slot is released only after the steps below have CONSUMED these registers:
+      //  an mbarrier arrive issued right behind the loads can overtake them - it is
+      //  served by a different unit - and the producer's next TMA write then lands
+      //  under loads that are still queued.  Seen on B200 with a busy co-resident CTA.)
+      }
+    };
+    constexpr bool kEarlyPre = !SPLIT && K == 16;  // short lattices only: their ring has slack
+    if (kEarlyPre) preload();
     if (SPLIT && up_g) {
       // steps i0-1 .. i0+K-2 of the upstream CTA's last warp sit at gv_in[i0 .. i0+K-1]
       // steps i0-1 .. i0+K-2 of the upstream CTA's last warp sit at gv_in[i0 .. i0+K-1]
@@ -409,24 +436,10 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
     float* const gob = SPLIT ? A.gv_out + i0 + 1 : nullptr;  // step i0+u goes to gv_out[i0+u+1]
     const uint32_t ob0 = vals_out + (((uint32_t)i0 & (kValRing - 1)) + 1u) * 4u;  // steps i0..i0+K-2
     const uint32_t ob1 = vals_out + ((uint32_t)(i0 + K) & (kValRing - 1)) * 4u;    // step i0+K-1
-    mbar_wait_u32(full_addr, phase);
+    if (!kEarlyPre) preload();
     if (n == K) {
       // ---------------- K straight-line steps
       uint32_t erow = slot_addr + (DIR ? (uint32_t)(K - 1) * row_bytes : 0u);
-      float ebv[kPre ? K : 1], elv[kPre ? K : 1][R / 2];
-      if (kPre) {
-#pragma unroll
-        for (int u = 0; u < K; ++u) {
-          ebv[u] = lds_em(erow);
-#pragma unroll
-          for (int h = 0; h < R / 2; ++h) elv[u][h] = lds_em(erow + jlab[h]);
-          if (DIR) erow -= row_bytes; else erow += row_bytes;
-        }
-        // (The slot is released only after the steps below have CONSUMED these registers:
-        //  an mbarrier arrive issued right behind the loads can overtake them - it is
-        //  served by a different unit - and the producer's next TMA write then lands
-        //  under loads that are still queued.  Seen on B200 with a busy co-resident CTA.)
-      }
 #pragma unroll
       for (int u = 0; u < K; ++u) {
         float eb, el[R / 2];
