@@ -20,10 +20,21 @@ int sm_count();
 // 4 prefix_step, 5 softmax family
 constexpr int kProfPhases = 8;
 void prof_mark(int phase, int end, cudaStream_t st);
+// Tuning switches exist only in a -DB200CTC_TUNING build (B200CTC_NVCC_EXTRA of build.py):
+// the shipped library reads no environment variable and has ONE code path per shape.
+#ifdef B200CTC_TUNING
+static inline const char* tuning_env(const char* name) { return getenv(name); }
+#else
+static inline const char* tuning_env(const char*) { return nullptr; }
+#endif
+static inline int tuning_int(const char* name, int dflt) {
+  const char* e = tuning_env(name);
+  return e ? atoi(e) : dflt;
+}
 // where a kernel fires griddepcontrol.launch_dependents (tuning: B200CTC_PDL_MODE):
 // 0 = at its start, 1 = at its end, 2 = never (implicit at completion)
 static inline int pdl_mode() {
-  static const int m = [] { const char* e = getenv("B200CTC_PDL_MODE"); return e ? atoi(e) : 2; }();
+  static const int m = tuning_int("B200CTC_PDL_MODE", 2);
   return m;
 }
 
@@ -45,7 +56,7 @@ static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 b
   // beside the running gather and the latency-bound recursion shares issue slots
   // (0.405 ms/step); with the trigger at the end, or never (implicit at completion, the
   // default), the kernel boundaries just get cheaper: 0.386 vs 0.393 ms without.
-  static const int pdl_mask = [] { const char* e = getenv("B200CTC_PDL"); return e ? atoi(e) : 7; }();
+  static const int pdl_mask = tuning_int("B200CTC_PDL", 7);
   cfg.numAttrs = (pdl_bit >= 0 && ((pdl_mask >> pdl_bit) & 1)) ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
@@ -152,6 +163,29 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32
           smem_u32(dst_smem)),
       "l"(src), "r"(bytes), "r"(smem_u32(bar))
       : "memory");
+}
+// ---- L2 eviction-priority policies (createpolicy; carried by the .L2::cache_hint forms) ----
+// The loss step is DRAM-bound end to end (profiles/README.md, round 2): what stays in the
+// 126 MB L2 between its kernels is worth 10 % of the traffic.  kind: 0 normal, 1 evict_first
+// (streamed once), 2 evict_last (scratch that a later kernel re-reads).
+__device__ __forceinline__ uint64_t l2_policy(int kind) {
+  uint64_t p;
+  if (kind == 1) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  else if (kind == 2) asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  else asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ void bulk_g2s_hint(void* dst_smem, const void* src, uint32_t bytes,
+                                              uint64_t* bar, uint64_t pol) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
+          smem_u32(dst_smem)),
+      "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(pol)
+      : "memory");
+}
+// drop a 128-byte line from L2 WITHOUT writing it back (scratch that was read for the last time)
+__device__ __forceinline__ void l2_discard_128(const void* p) {
+  asm volatile("discard.global.L2 [%0], 128;" ::"l"(p) : "memory");
 }
 // shared -> global bulk copy (bulk async-group completion)
 __device__ __forceinline__ void bulk_s2g(void* dst, const void* src_smem, uint32_t bytes) {

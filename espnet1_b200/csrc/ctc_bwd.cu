@@ -23,7 +23,7 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
     const float* __restrict__ alpha, const float* __restrict__ beta,
     const int* __restrict__ offA, const int* __restrict__ offB,
     const float* __restrict__ gscale, int gstride, float gmul, int nstage, int stage_stride,
-    int pdl) {
+    int pdl, const int* __restrict__ err, int l2mode) {
   constexpr int N = Elems<T>::N;
   constexpr int NWARP = NT / 32;
   extern __shared__ __align__(128) unsigned char dsm[];
@@ -41,6 +41,7 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
   const int nchunk = V / N;
   const int ntail = V - nchunk * N;
 
+  const uint64_t pol_stream = l2_policy((l2mode & 1) ? 1 : 0);
   RowCursor pc;
   pc.init(blockIdx.x, gridDim.x, Tfr);
   uint32_t np = 0;
@@ -50,10 +51,12 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
       const int st = np % nstage;
       unsigned char* dst = stages + (size_t)st * stage_stride;
       mbar_expect_tx(&bars[st], WIDE ? row_bytes + 2 * lat_bytes + 2 * lab_bytes : row_bytes);
-      bulk_g2s(dst, logits + pc.g * V, row_bytes, &bars[st]);
+      // the logits stream through once: first to be evicted, so that the lattices (written
+      // evict_last by the forward kernels) are still in L2 when their row comes up
+      bulk_g2s_hint(dst, logits + pc.g * V, row_bytes, &bars[st], pol_stream);
       if (WIDE) {
-        bulk_g2s(dst + lat_off, alpha + (size_t)pc.g * Sp, lat_bytes, &bars[st]);
-        bulk_g2s(dst + lat_off + lat_bytes, beta + (size_t)pc.g * Sp, lat_bytes, &bars[st]);
+        bulk_g2s_hint(dst + lat_off, alpha + (size_t)pc.g * Sp, lat_bytes, &bars[st], pol_stream);
+        bulk_g2s_hint(dst + lat_off + lat_bytes, beta + (size_t)pc.g * Sp, lat_bytes, &bars[st], pol_stream);
         bulk_g2s(dst + lat_off + 2 * lat_bytes, lab + (size_t)pc.b * Lp, lab_bytes, &bars[st]);
         bulk_g2s(dst + lat_off + 2 * lat_bytes + lab_bytes, dup + (size_t)pc.b * Lp, lab_bytes, &bars[st]);
       }
@@ -73,6 +76,9 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
   if (TMA && tid == 0)
     for (int i = 0; i < nstage; ++i) issue_next();
 
+  // a forward kernel of this call gave up waiting for another CTA (ctc_ws.cuh kWsErr*): the
+  // lattices are incomplete, the gradient must not look plausible
+  const bool ws_bad = __ldcg(err) != 0;
   uint32_t n = 0;
   RowCursor rc;
   rc.init(blockIdx.x, gridDim.x, Tfr);
@@ -101,7 +107,7 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
     const int L = u.L, S = 2 * L + 1;
     float gb = gmul * (gscale ? gscale[(size_t)b * gstride] : 1.f);
     float qbase = -(float)u.lam;
-    if (u.infinite) {  // inf loss kept (!zero_infinity): the reference's gradient is NaN
+    if (u.infinite || ws_bad) {  // inf loss kept (!zero_infinity): the reference's gradient is NaN
       gb = __int_as_float(0x7fc00000);
       qbase = gb;
     }
@@ -232,6 +238,14 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
     blank_part = warp_sum(blank_part);
     if (lane == 0) wp[wid] = blank_part;
     __syncthreads();  // wms, pbuf, wp visible
+    // this row's alpha / beta were read for the last time (every thread's loads completed
+    // before the barrier): drop their lines from L2 instead of writing 77 MB back to DRAM.
+    // (Sp is a multiple of 32 floats: rows do not share 128-byte lines.)
+    if (!WIDE && (l2mode & 2)) {
+      const int nl = (4 * Sp) >> 7;
+      if (tid < nl) l2_discard_128(reinterpret_cast<const char*>(al) + 128 * tid);
+      else if (tid < 2 * nl) l2_discard_128(reinterpret_cast<const char*>(be) + 128 * (tid - nl));
+    }
     // ---- row normaliser: combine the per-warp (max, sum) pairs
     float M2 = kNegInf;
 #pragma unroll
@@ -294,15 +308,198 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
   if (pdl == 1) griddep_launch();
 }
 
+// ---- DIRECT variant: one CTA per (b,t) row, the row goes global -> registers with plain
+// 128-bit loads (no shared-memory staging, no mbarrier, not persistent), like the soft-max
+// family's row kernels, which stream at the copy peak; the hardware block scheduler and ~6
+// resident CTAs per SM are the pipeline.  Same thread <-> element mapping and arithmetic as
+// grad_rows_kernel (bit-identical results); the <= L+1 label-column logits are re-read through L1.
+template <typename T, int NT, int PER>
+__global__ void __launch_bounds__(NT) grad_rows_direct_kernel(
+    const T* __restrict__ logits, T* __restrict__ grad, int Tfr, int V, int blank,
+    const UttInfo* __restrict__ utt, const int* __restrict__ lab, const int* __restrict__ dup,
+    int Lp, int Sp, int NWp, int NB, int wshift, float* __restrict__ lse2, const float* __restrict__ cmax,
+    const float* __restrict__ alpha, const float* __restrict__ beta,
+    const int* __restrict__ offA, const int* __restrict__ offB,
+    const float* __restrict__ gscale, int gstride, float gmul, const int* __restrict__ err) {
+  constexpr int N = Elems<T>::N;
+  constexpr int NWARP = NT / 32;
+  extern __shared__ __align__(16) float pbuf[];  // [Lp]
+  __shared__ float wp[32];
+  __shared__ float2 wms[32];
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int64_t g = blockIdx.x;
+  const int b = (int)(g / Tfr), t = (int)(g - (int64_t)b * Tfr);
+  const int nchunk = V / N;
+  const int ntail = V - nchunk * N;
+  const T* xr = logits + g * V;
+  T* gr = grad + g * V;
+  griddep_wait();
+  const UttInfo u = utt[b];
+  if (t >= u.T || u.zeroed) {  // padded frame or zeroed utterance: gradient is 0
+    float z[N];
+#pragma unroll
+    for (int e = 0; e < N; ++e) z[e] = 0.f;
+    for (int i = tid; i < nchunk; i += NT) store16<T>(gr + i * N, z);
+    if (tid < ntail) gr[nchunk * N + tid] = from_f32<T>(0.f);
+    return;
+  }
+  // the row: all loads in flight first
+  uint4 raw[PER];
+#pragma unroll
+  for (int j = 0; j < PER; ++j) {
+    const int i = tid + j * NT;
+    if (i < nchunk) raw[j] = __ldg(reinterpret_cast<const uint4*>(xr) + i);
+  }
+  const bool ws_bad = __ldcg(err) != 0;
+  const float c2 = cmax[g];
+  const int L = u.L, S = 2 * L + 1;
+  float gb = gmul * (gscale ? gscale[(size_t)b * gstride] : 1.f);
+  float qbase = -(float)u.lam;
+  if (u.infinite || ws_bad) {
+    gb = __int_as_float(0x7fc00000);
+    qbase = gb;
+  }
+  const float* al = alpha + (size_t)g * Sp;
+  const float* be = beta + (size_t)g * Sp;
+  const int* oa = offA + ((size_t)b * NB + (t / kRenormEvery)) * NWp;
+  const int* ob = offB + ((size_t)b * NB + ((u.T - 1 - t) / kRenormEvery)) * NWp;
+  const int* lb = lab + (size_t)b * Lp;
+  constexpr int SM = NT >= 256 ? 2 : 3;
+  float ab[SM];
+  int vcol[SM];
+#pragma unroll
+  for (int j = 0; j < SM; ++j) {
+    const int s = tid + j * NT;
+    const int sc = s < S ? s : 0, sb = S - 1 - sc;
+    const int fo = oa[sc >> wshift] + ob[sb >> wshift] - u.aend;
+    ab[j] = s < S ? al[sc] + be[sb] + ((float)fo + qbase) : kNegInf;
+    vcol[j] = (sc & 1) ? lb[(sc + 1) >> 1] : blank;
+  }
+  float blank_part = 0.f;
+  for (int s0 = NT * SM; s0 < S; s0 += NT) {  // wide lattices (not at C2)
+    const int s = s0 + tid;
+    if (s < S) {
+      const int sb = S - 1 - s;
+      const int fo = oa[s >> wshift] + ob[sb >> wshift] - u.aend;
+      const float abv = al[s] + be[sb] + ((float)fo + qbase);
+      const bool odd = s & 1;
+      const int k = odd ? (s + 1) >> 1 : 0;
+      const int v = odd ? lb[k] : blank;
+      const float em = fmaf(to_f32<T>(__ldg(xr + v)), kLog2e, -c2);
+      const float p = ex2(abv - em);
+      if (odd) pbuf[k] = p; else blank_part += p;
+    }
+  }
+  // ---- phase 0: thread-local max and sum of 2^(x2 - max)
+  float x[PER][N];
+  float m = kNegInf;
+#pragma unroll
+  for (int j = 0; j < PER; ++j) {
+    const int i = tid + j * NT;
+    if (i < nchunk) {
+      unpack16<T>(raw[j], x[j]);
+#pragma unroll
+      for (int e = 0; e < N; ++e) m = fmaxf(m, x[j][e]);
+    }
+  }
+  float xt = kNegInf;
+  if (tid < ntail) {
+    xt = to_f32<T>(__ldg(xr + nchunk * N + tid));
+    m = fmaxf(m, xt);
+  }
+  m = warp_max(m);
+  const float mw2 = ((m == kNegInf) ? 0.f : m) * kLog2e;
+  float sum = 0.f;
+#pragma unroll
+  for (int j = 0; j < PER; ++j) {
+    const int i = tid + j * NT;
+    if (i < nchunk) {
+#pragma unroll
+      for (int e = 0; e < N; ++e) {
+        x[j][e] = ex2(fmaf(x[j][e], kLog2e, -mw2));
+        sum += x[j][e];
+      }
+    }
+  }
+  if (tid < ntail) {
+    xt = ex2(fmaf(xt, kLog2e, -mw2));
+    sum += xt;
+  }
+  sum = warp_sum(sum);
+  if (lane == 0) wms[wid] = make_float2(mw2, sum);
+  // ---- phase 1a: occupancies (label-column logits: the row is in L1 by now)
+#pragma unroll
+  for (int j = 0; j < SM; ++j) {
+    const int s = tid + j * NT;
+    if (s < S) {
+      const bool odd = s & 1;
+      const float em = fmaf(to_f32<T>(__ldg(xr + vcol[j])), kLog2e, -c2);
+      const float p = ex2(ab[j] - em);
+      if (odd) pbuf[(s + 1) >> 1] = p; else blank_part += p;
+    }
+  }
+  blank_part = warp_sum(blank_part);
+  if (lane == 0) wp[wid] = blank_part;
+  __syncthreads();
+  float M2 = kNegInf;
+#pragma unroll
+  for (int w2 = 0; w2 < NWARP; ++w2) M2 = fmaxf(M2, wms[w2].x);
+  float tot = 0.f;
+#pragma unroll
+  for (int w2 = 0; w2 < NWARP; ++w2) tot += wms[w2].y * ex2(wms[w2].x - M2);
+  const float l2 = M2 + log2f(tot);
+  if (tid == 0) lse2[g] = l2;
+  const float scale = gb * ex2(mw2 - l2);
+  // ---- phase 1b: dense part
+#pragma unroll
+  for (int j = 0; j < PER; ++j) {
+    const int i = tid + j * NT;
+    if (i < nchunk) {
+#pragma unroll
+      for (int e = 0; e < N; ++e) x[j][e] *= scale;
+      store16<T>(gr + i * N, x[j]);
+    }
+  }
+  if (tid < ntail) gr[nchunk * N + tid] = from_f32<T>(xt * scale);
+  __syncthreads();  // dense stores are ordered before the column fix-ups below
+  // ---- phase 2: label columns, single owner thread per vocabulary column
+  const int* db = dup + (size_t)b * Lp;
+  for (int k0 = tid + 1; k0 <= L; k0 += NT * 4) {
+    int code[4], vv[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int k = k0 + j * NT;
+      code[j] = k <= L ? db[k] : 0;
+      vv[j] = k <= L ? lb[k] : 0;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (code[j] & kDupFirst) {
+        float acc = pbuf[k0 + j * NT];
+        for (int nx = code[j] & kDupMask; nx != 0; nx = db[nx] & kDupMask) acc += pbuf[nx];
+        const float sm = ex2(fmaf(to_f32<T>(__ldg(xr + vv[j])), kLog2e, -l2));
+        gr[vv[j]] = from_f32<T>(gb * (sm - acc));
+      }
+    }
+  }
+  if (tid == NT - 1) {
+    float acc = 0.f;
+    for (int w2 = 0; w2 < NWARP; ++w2) acc += wp[w2];
+    for (int nx = u.blank_head; nx != 0; nx = db[nx] & kDupMask) acc += pbuf[nx];
+    const float sm = ex2(fmaf(to_f32<T>(__ldg(xr + blank)), kLog2e, -l2));
+    gr[blank] = from_f32<T>(gb * (sm - acc));
+  }
+}
+
 template <typename T, int NT>
 static int launch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, int blank,
                          const LossLayout& w, unsigned char* ws, const float* gscale,
-                         int gstride, float gmul, cudaStream_t st) {
+                         int gstride, float gmul, bool last_use, cudaStream_t st) {
   constexpr int PER = 40 / Elems<T>::N;
   const size_t extra = align_up(sizeof(float) * (size_t)w.Lp, 128);
   RowLaunchCfg c = row_launch_cfg(logits, (size_t)V * sizeof(T), extra, NT, "B200CTC_B");
   // long lattices: alpha / beta / labels of the row are staged next to the logits row
-  static const int wide_on = [] { const char* e = getenv("B200CTC_B_WIDE"); return e ? atoi(e) : 1; }();
+  static const int wide_on = tuning_int("B200CTC_B_WIDE", 1);
   const size_t lat_stage = align_up(4 * (2 * (size_t)w.Sp + 2 * (size_t)w.Lp), 128);
   bool wide = wide_on && c.tma && 2 * w.Lmax + 1 > 3 * NT;
   if (wide) {
@@ -322,6 +519,27 @@ static int launch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, 
   if (grid > rows) grid = rows;
   int wshift = 0;
   while ((1 << wshift) < 32 * w.R) ++wshift;
+  // bit 0: logits evict_first; bit 1: discard the row's alpha / beta lines after use
+  static const int l2tune = tuning_int("B200CTC_ROWS_L2", 0);
+  // (deferred mode keeps the lattices for a possible second backward: no discard there)
+  const int l2mode = last_use ? l2tune : (l2tune & ~2);
+  // Short lattices, 16-byte aligned rows: the direct row kernel (one CTA per row)
+  static const int direct_on = tuning_int("B200CTC_ROWS_DIRECT", 1);
+  if (direct_on && !wide && c.tma && (reinterpret_cast<uintptr_t>(grad) & 15) == 0 && rows < (1ll << 31)) {
+    constexpr int NT2 = NT * 2 > 1024 ? 1024 : NT * 2;   // twice the threads, half the row per thread
+    constexpr int PER2 = NT2 == NT ? PER : PER / 2;
+    auto k = grad_rows_direct_kernel<T, NT2, PER2>;
+    launch_pdl(k, dim3((unsigned)rows), dim3(NT2), extra, st, 1, static_cast<const T*>(logits),
+               static_cast<T*>(grad), Tfr, V, blank, reinterpret_cast<const UttInfo*>(ws + w.utt),
+               reinterpret_cast<const int*>(ws + w.lab), reinterpret_cast<const int*>(ws + w.dup),
+               w.Lp, w.Sp, w.NW, w.NB, wshift, reinterpret_cast<float*>(ws + w.lse2),
+               reinterpret_cast<const float*>(ws + w.cmax), reinterpret_cast<const float*>(ws + w.alpha),
+               reinterpret_cast<const float*>(ws + w.beta), reinterpret_cast<const int*>(ws + w.offA),
+               reinterpret_cast<const int*>(ws + w.offB), gscale, gstride, gmul,
+               reinterpret_cast<const int*>(ws + w.err));
+    count_launch();
+    return check_launch("ctc grad_rows (direct)");
+  }
   auto go = [&](auto k) {
     cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     launch_pdl(
@@ -334,7 +552,8 @@ static int launch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, 
         reinterpret_cast<float*>(ws + w.lse2), reinterpret_cast<const float*>(ws + w.cmax),
         reinterpret_cast<const float*>(ws + w.alpha), reinterpret_cast<const float*>(ws + w.beta),
         reinterpret_cast<const int*>(ws + w.offA), reinterpret_cast<const int*>(ws + w.offB),
-        gscale, gstride, gmul, c.nstage, c.stride, pdl_mode());
+        gscale, gstride, gmul, c.nstage, c.stride, pdl_mode(),
+        reinterpret_cast<const int*>(ws + w.err), l2mode);
   };
   if (wide) go(grad_rows_kernel<T, NT, PER, true, true>);
   else if (c.tma) go(grad_rows_kernel<T, NT, PER, true, false>);
@@ -346,27 +565,27 @@ static int launch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, 
 template <typename T>
 static int dispatch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, int blank,
                            const LossLayout& w, unsigned char* ws, const float* gscale,
-                           int gstride, float gmul, cudaStream_t st) {
+                           int gstride, float gmul, bool last_use, cudaStream_t st) {
   const int need = (V + 39) / 40;
-  if (need <= 128) return launch_pass_b<T, 128>(logits, grad, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, st);
-  if (need <= 256) return launch_pass_b<T, 256>(logits, grad, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, st);
-  if (need <= 512) return launch_pass_b<T, 512>(logits, grad, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, st);
-  if (need <= 1024) return launch_pass_b<T, 1024>(logits, grad, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, st);
+  if (need <= 128) return launch_pass_b<T, 128>(logits, grad, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, last_use, st);
+  if (need <= 256) return launch_pass_b<T, 256>(logits, grad, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, last_use, st);
+  if (need <= 512) return launch_pass_b<T, 512>(logits, grad, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, last_use, st);
+  if (need <= 1024) return launch_pass_b<T, 1024>(logits, grad, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, last_use, st);
   set_error("ctc_loss grad: V=%d exceeds the supported row size", V);
   return B200CTC_ERR_ARG;
 }
 
 int launch_grad_rows(const void* logits, int dtype, void* grad, int B, int T, int V, int blank,
                      const LossLayout& w, unsigned char* ws, const float* gscale, int gstride,
-                     float gmul, cudaStream_t st) {
+                     float gmul, bool last_use, cudaStream_t st) {
   switch (dtype) {
     case B200CTC_F32:
-      return dispatch_pass_b<float>(logits, grad, B, T, V, blank, w, ws, gscale, gstride, gmul, st);
+      return dispatch_pass_b<float>(logits, grad, B, T, V, blank, w, ws, gscale, gstride, gmul, last_use, st);
     case B200CTC_F16:
-      return dispatch_pass_b<__half>(logits, grad, B, T, V, blank, w, ws, gscale, gstride, gmul, st);
+      return dispatch_pass_b<__half>(logits, grad, B, T, V, blank, w, ws, gscale, gstride, gmul, last_use, st);
     default:
       return dispatch_pass_b<__nv_bfloat16>(logits, grad, B, T, V, blank, w, ws, gscale, gstride,
-                                            gmul, st);
+                                            gmul, last_use, st);
   }
 }
 
@@ -427,7 +646,7 @@ extern "C" int b200ctc_loss_bwd(const void* logits, int dtype, const int64_t* in
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   prof_mark(3, 0, st);
   const int rc = launch_grad_rows(logits, dtype, grad, B, T, V, blank, w, ws, gscale,
-                                  gscale_stride, gscale_mul, st);
+                                  gscale_stride, gscale_mul, false, st);
   prof_mark(3, 1, st);
   return rc;
 }

@@ -2,8 +2,6 @@
 // vocabulary + gather of the lattice emissions, streamed through shared memory
 // by the TMA engine (1-D bulk copies, mbarrier ring), (3) alpha/beta lattice
 // recursion (ctc_lattice.cuh), one CTA per utterance and direction.
-#include <mutex>
-
 #include "ctc_lattice.cuh"
 #include "rows_common.cuh"
 
@@ -26,6 +24,7 @@ struct PrepArgs {
   int* lab;
   int* dup;
   int* counter;
+  int* err;  // sticky error word, cleared here; NULL: the caller's memset already did
 };
 
 __device__ __forceinline__ void prep_utterance(const PrepArgs& P, int b, int* slab, bool publish,
@@ -33,7 +32,10 @@ __device__ __forceinline__ void prep_utterance(const PrepArgs& P, int b, int* sl
   __shared__ int s_bad, s_head;
   __shared__ long long s_base;
   const int NT = blockDim.x, tid = threadIdx.x;
-  if (publish && b == 0 && tid == 0) *P.counter = 0;  // nll_kernel's "last CTA" ticket
+  if (publish && b == 0 && tid == 0) {
+    *P.counter = 0;  // nll_kernel's "last CTA" ticket
+    if (P.err) *P.err = 0;
+  }
   const long long L64 = P.tgt_lens[b], T64 = P.in_lens[b];
   const int L = (int)(L64 < 0 ? 0 : (L64 > P.Lmax ? P.Lmax : L64));
   const int Tb = (int)(T64 < 0 ? 0 : (T64 > P.T ? P.T : T64));
@@ -111,6 +113,43 @@ __global__ void __launch_bounds__(1024) prep_kernel(PrepArgs P) {
 // em[t][k] = logit[t][label_k]*log2(e) - c[t] with c[t] = max_k (ctc_ws.cuh).
 // The label preparation is fused in: every CTA stages its utterance's labels
 // itself, and the first CTA of each utterance publishes lab/dup/utt.
+// one 4-byte (2-byte) read per 128-byte line: ask L2 for 64 bytes around it, not the line
+#ifndef B200CTC_GATHER_LTC
+#define B200CTC_GATHER_LTC 64
+#endif
+#ifndef B200CTC_GATHER_POL
+#define B200CTC_GATHER_POL 0
+#endif
+template <typename T>
+__device__ __forceinline__ float ldg_gather(const T* p) {
+#if B200CTC_GATHER_LTC == 64 && B200CTC_GATHER_POL != 0
+  // + L2 evict_first: the gather's lines are dead on arrival; do not let them push out the
+  // previous kernel's dirty lines (their write-back then happens under the lattice, HBM idle)
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  if (sizeof(T) == 4) {
+    float v;
+    asm volatile("ld.global.nc.L2::cache_hint.L2::64B.f32 %0, [%1], %2;" : "=f"(v) : "l"(p), "l"(pol));
+    return v;
+  } else {
+    unsigned short h;
+    asm volatile("ld.global.nc.L2::cache_hint.L2::64B.u16 %0, [%1], %2;" : "=h"(h) : "l"(p), "l"(pol));
+    return to_f32<T>(*reinterpret_cast<const T*>(&h));
+  }
+#elif B200CTC_GATHER_LTC == 64
+  if (sizeof(T) == 4) {
+    float v;
+    asm volatile("ld.global.nc.L2::64B.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+  } else {
+    unsigned short h;
+    asm volatile("ld.global.nc.L2::64B.u16 %0, [%1];" : "=h"(h) : "l"(p));
+    return to_f32<T>(*reinterpret_cast<const T*>(&h));
+  }
+#else
+  return to_f32<T>(__ldg(p));
+#endif
+}
 constexpr int kGatherWarps = 8;
 constexpr int kGatherRows = 4;   // rows per warp in flight
 constexpr int kGatherRegs = 8;   // values kept in registers per lane and row (L+1 <= 256)
@@ -148,7 +187,7 @@ __global__ void __launch_bounds__(kGatherWarps * 32) gather_kernel(
 #pragma unroll
       for (int r = 0; r < kGatherRows; ++r) {  // clamped row: always a valid address
         const T* row = logits + (g0 + (r < nr ? r : nr - 1)) * V;
-        v[r][j] = (j == 0 || k <= L) ? to_f32<T>(__ldg(row + col)) * kLog2e : kNegInf;
+        v[r][j] = (j == 0 || k <= L) ? ldg_gather<T>(row + col) * kLog2e : kNegInf;
       }
     }
 #pragma unroll
@@ -201,6 +240,10 @@ static int launch_gather(const void* logits, const PrepArgs& P, int B, const Los
   count_launch();
   return check_launch("ctc gather");
 }
+
+}  // namespace b200ctc
+#include "ctc_fused.cuh"
+namespace b200ctc {
 
 // --------------------------------------------------------- pass A (rows)
 // Persistent CTAs; each loops over (b,t) rows.  TMA=true: rows arrive in an
@@ -413,6 +456,7 @@ static PrepArgs make_prep_args(const LossLayout& w, unsigned char* ws, const int
   P.lab = reinterpret_cast<int*>(ws + w.lab);
   P.dup = reinterpret_cast<int*>(ws + w.dup);
   P.counter = reinterpret_cast<int*>(ws + w.counter);
+  P.err = reinterpret_cast<int*>(ws + w.err);
   return P;
 }
 
@@ -427,42 +471,10 @@ static int launch_prep(const LossLayout& w, const PrepArgs& P, cudaStream_t st) 
   return check_launch("ctc prep");
 }
 
-// defined in ctc_bwd.cu / ctc_dense.cu
+// defined in ctc_bwd.cu
 int launch_grad_rows(const void* logits, int dtype, void* grad, int B, int T, int V, int blank,
                      const LossLayout& w, unsigned char* ws, const float* gscale, int gstride,
-                     float gmul, cudaStream_t st);
-int launch_dense_rows(const void* logits, int dtype, void* grad, int B, int T, int V,
-                      const int64_t* in_lens, const LossLayout& w, unsigned char* ws, float gmul,
-                      cudaStream_t st);
-int launch_fixup(void* grad, int dtype, int B, int T, int V, int blank, const LossLayout& w,
-                 const unsigned char* ws, float gmul, cudaStream_t st);
-
-// internal low-priority stream (one per device) on which the dense row pass of
-// the eager mode overlaps the caller-stream gather + lattice chain
-static std::mutex g_side_mu;
-static cudaStream_t g_side[64] = {};
-
-static cudaStream_t side_stream() {
-  int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
-  std::lock_guard<std::mutex> lk(g_side_mu);
-  if (!g_side[dev]) {
-    int lo = 0, hi = 0;
-    cudaDeviceGetStreamPriorityRange(&lo, &hi);  // lo = numerically largest = lowest priority
-    if (cudaStreamCreateWithPriority(&g_side[dev], cudaStreamNonBlocking, lo) != cudaSuccess)
-      g_side[dev] = nullptr;
-  }
-  return g_side[dev];
-}
-
-// Split mode (dense rows on the side stream + sparse fix-up) is opt-in: measured on
-// B200 at C2 it loses to the fused row pass (profiles/README.md) because the
-// fix-up's partial-sector writes and the contention on the gather cost more than
-// the lattice latency they hide.
-static bool eager_split_enabled() {
-  const char* e = getenv("B200CTC_EAGER_SPLIT");
-  return e && e[0] == '1';
-}
+                     float gmul, bool last_use, cudaStream_t st);
 
 }  // namespace b200ctc
 
@@ -525,76 +537,61 @@ static int loss_fwd_grad_impl(const void* logits, int dtype, const int64_t* targ
   B2_REQUIRE(grad_hint != 0.f && grad_hint == grad_hint, "loss_fwd_grad: grad_hint must be non-zero");
   unsigned char* ws = static_cast<unsigned char*>(ws_);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  // fork: the dense row pass needs nothing from the chain below
-  const bool split = T > 0 && eager_split_enabled();
-  cudaStream_t sd = split ? side_stream() : nullptr;
-  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
-  if (sd) {
-    if (cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming) != cudaSuccess ||
-        cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming) != cudaSuccess) {
-      if (ev_fork) cudaEventDestroy(ev_fork);
-      ev_fork = ev_join = nullptr;
-      sd = nullptr;
-      cudaGetLastError();
-    }
-  }
-  if (sd) {
-    cudaEventRecord(ev_fork, st);
-    cudaStreamWaitEvent(sd, ev_fork, 0);
-    prof_mark(3, 0, sd);
-    rc = launch_dense_rows(logits, dtype, grad, B, T, V, in_lens, w, ws, grad_hint, sd);
-    prof_mark(3, 1, sd);
-    cudaEventRecord(ev_join, sd);
-  }
-  const PrepArgs P = make_prep_args(w, ws, targets, tgt_offsets, in_lens, tgt_lens, blank);
+  PrepArgs P = make_prep_args(w, ws, targets, tgt_offsets, in_lens, tgt_lens, blank);
   // Emissions: a sparse gather of the L+1 label columns moves one 64-byte DRAM atom per
   // column and row; once that exceeds the row itself (long targets: C4 has 1201 columns
   // = 77 KB of atoms against a 20 KB row) the full-row pass A (TMA row -> shared memory ->
   // columns) is the cheaper way to produce the same em / cmax arrays.
-  static const int force_dense = [] { const char* e = getenv("B200CTC_DENSE_GATHER"); return e ? atoi(e) : -1; }();
+  static const int force_dense = tuning_int("B200CTC_DENSE_GATHER", -1);
   const bool dense_gather = T > 0 && (force_dense >= 0 ? force_dense != 0
       : (size_t)(w.Lmax + 1) * 64 > (size_t)V * (size_t)dtype_size(dtype));
-  if (!rc && dense_gather) {
-    rc = launch_prep(w, P, st);
-    if (!rc) {
+  // Short lattices (R = 2, both directions of an utterance in one CTA): prep + gather + lattice
+  // as ONE launch with the SMs partitioned by role (ctc_fused.cuh)
+  static const int fused_on = tuning_int("B200CTC_FUSED", 1);
+  int fnring = 0;
+  size_t fsmem = 0;
+  const bool fused = T > 0 && !dense_gather && fused_on && fused_fwd_fits(w, &fnring, &fsmem);
+  if (fused) {
+    P.err = nullptr;  // cleared by the launcher's memset (CTAs may set it before utterance 0's prep)
+    prof_mark(2, 0, st);
+    switch (dtype) {
+      case B200CTC_F32: rc = launch_fused_fwd<float>(logits, P, w, ws, zero_infinity, fnring, fsmem, st); break;
+      case B200CTC_F16: rc = launch_fused_fwd<__half>(logits, P, w, ws, zero_infinity, fnring, fsmem, st); break;
+      default: rc = launch_fused_fwd<__nv_bfloat16>(logits, P, w, ws, zero_infinity, fnring, fsmem, st); break;
+    }
+    prof_mark(2, 1, st);
+  } else {
+    if (dense_gather) {
+      rc = launch_prep(w, P, st);
+      if (!rc) {
+        prof_mark(1, 0, st);
+        switch (dtype) {
+          case B200CTC_F32: rc = dispatch_pass_a<float>(logits, B, T, V, w, ws, st); break;
+          case B200CTC_F16: rc = dispatch_pass_a<__half>(logits, B, T, V, w, ws, st); break;
+          default: rc = dispatch_pass_a<__nv_bfloat16>(logits, B, T, V, w, ws, st); break;
+        }
+        prof_mark(1, 1, st);
+      }
+    } else {  // gather kernel with the label prep fused in
       prof_mark(1, 0, st);
       switch (dtype) {
-        case B200CTC_F32: rc = dispatch_pass_a<float>(logits, B, T, V, w, ws, st); break;
-        case B200CTC_F16: rc = dispatch_pass_a<__half>(logits, B, T, V, w, ws, st); break;
-        default: rc = dispatch_pass_a<__nv_bfloat16>(logits, B, T, V, w, ws, st); break;
+        case B200CTC_F32: rc = launch_gather<float>(logits, P, B, w, ws, st); break;
+        case B200CTC_F16: rc = launch_gather<__half>(logits, P, B, w, ws, st); break;
+        default: rc = launch_gather<__nv_bfloat16>(logits, P, B, w, ws, st); break;
       }
       prof_mark(1, 1, st);
     }
-  } else if (!rc) {  // gather kernel with the label prep fused in
-    prof_mark(1, 0, st);
-    switch (dtype) {
-      case B200CTC_F32: rc = launch_gather<float>(logits, P, B, w, ws, st); break;
-      case B200CTC_F16: rc = launch_gather<__half>(logits, P, B, w, ws, st); break;
-      default: rc = launch_gather<__nv_bfloat16>(logits, P, B, w, ws, st); break;
+    if (!rc) {
+      prof_mark(2, 0, st);
+      rc = launch_lattice(w, ws, T, zero_infinity, 1, st);
+      prof_mark(2, 1, st);
     }
-    prof_mark(1, 1, st);
-  }
-  if (!rc) {
-    prof_mark(2, 0, st);
-    rc = launch_lattice(w, ws, T, zero_infinity, 1, st);
-    prof_mark(2, 1, st);
-  }
-  if (sd) {  // join (always, also on error: the caller's stream must cover the side work)
-    cudaStreamWaitEvent(st, ev_join, 0);
-    cudaEventDestroy(ev_fork);
-    cudaEventDestroy(ev_join);
   }
   if (rc) return rc;
   if (T > 0) {
-    if (sd) {
-      prof_mark(7, 0, st);
-      rc = launch_fixup(grad, dtype, B, T, V, blank, w, ws, grad_hint, st);
-      prof_mark(7, 1, st);
-    } else {
-      prof_mark(3, 0, st);
-      rc = launch_grad_rows(logits, dtype, grad, B, T, V, blank, w, ws, nullptr, 0, grad_hint, st);
-      prof_mark(3, 1, st);
-    }
+    prof_mark(3, 0, st);
+    rc = launch_grad_rows(logits, dtype, grad, B, T, V, blank, w, ws, nullptr, 0, grad_hint, true, st);
+    prof_mark(3, 1, st);
     if (rc) return rc;
   }
   return launch_nll(w, ws, T, zero_infinity, nll, loss_out, loss_scale, st, pd, global_out);

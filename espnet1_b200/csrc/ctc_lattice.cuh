@@ -119,11 +119,14 @@ __device__ __forceinline__ void mbar_wait_u32(uint32_t bar, uint32_t parity) {
 __device__ __forceinline__ void mbar_arrive_u32(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
-__device__ __forceinline__ void stg_v2(float* p, float x, float y) {
-  asm volatile("st.global.v2.f32 [%0], {%1,%2};" ::"l"(p), "f"(x), "f"(y) : "memory");
+// alpha / beta rows: scratch that the gradient row pass re-reads -> L2 policy operand
+__device__ __forceinline__ void stg_v2(float* p, float x, float y, uint64_t pol) {
+  asm volatile("st.global.L2::cache_hint.v2.f32 [%0], {%1,%2}, %3;" ::"l"(p), "f"(x), "f"(y), "l"(pol)
+               : "memory");
 }
-__device__ __forceinline__ void stg_v4(float* p, float x, float y, float z, float w) {
-  asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(x), "f"(y), "f"(z), "f"(w)
+__device__ __forceinline__ void stg_v4(float* p, float x, float y, float z, float w, uint64_t pol) {
+  asm volatile("st.global.L2::cache_hint.v4.f32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "f"(x), "f"(y),
+               "f"(z), "f"(w), "l"(pol)
                : "memory");
 }
 // Split lattices: boundary hand-off between CTAs through global memory (L2).  Every word
@@ -134,7 +137,7 @@ __device__ __forceinline__ void stg_v4(float* p, float x, float y, float z, floa
 // (finite log-zero), and arithmetic NaNs are canonical (0x7fffffff), not the sentinel.
 constexpr uint32_t kBndValSentinel = 0xffffffffu;  // cudaMemset byte 0xff
 constexpr int kBndFSentinel = (int)0x80808080u;    // cudaMemset byte 0x80 (|F| stays far below)
-constexpr int kBndSpinLimit = 1 << 22;             // a lost producer gives garbage, not a hang
+constexpr int kBndSpinLimit = 1 << 22;             // a lost producer: sticky error + NaN loss, not a hang
 __device__ __forceinline__ void stg_relaxed_f32(float* p, float v) {
   asm volatile("st.relaxed.gpu.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
 }
@@ -165,6 +168,12 @@ __device__ __forceinline__ uint32_t pin(uint32_t v) {
   return v;
 }
 
+// alpha / beta are written by the lattice and read once by the gradient row pass, with the
+// whole (B,T,V) logits + gradient streaming through L2 in between: evict_last keeps them there
+static inline int lat_policy_host() {
+  static const int v = tuning_int("B200CTC_LAT_POL", 2);
+  return v;
+}
 struct LatticeArgs {
   UttInfo* utt;
   const int* lb;      // labels of this utterance (k = 0 blank)
@@ -184,6 +193,8 @@ struct LatticeArgs {
   int W0, Lps, col0, nwc;
   float* gv_in; int* gf_in; int* gr_in;
   float* gv_out; int* gf_out; int* gr_out;
+  int* err;  // sticky error word of the workspace (ctc_ws.cuh)
+  int lat_policy;  // L2 policy of the alpha / beta stores (common.cuh l2_policy)
 };
 
 // One compute warp of the systolic lattice (see the file header).  This is the
@@ -257,6 +268,7 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
   }
   const ptrdiff_t lat_step = DIR ? -(ptrdiff_t)A.Sp : (ptrdiff_t)A.Sp;
   const bool store_ok = STORE && sp0 < A.Sp;
+  const uint64_t lat_pol = l2_policy(A.lat_policy);
   const bool store_off = STORE && lane0;
 
   float a[R];
@@ -315,10 +327,10 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
     //  of the block and queue up behind one another on a single address register pair.)
     if (store_ok) {
       if (R == 2) {
-        stg_v2(lat_p, a[0], a[1]);
+        stg_v2(lat_p, a[0], a[1], lat_pol);
       } else {
 #pragma unroll
-        for (int q = 0; q < R; q += 4) stg_v4(lat_p + q, a[q], a[q + 1], a[q + 2], a[q + 3]);
+        for (int q = 0; q < R; q += 4) stg_v4(lat_p + q, a[q], a[q + 1], a[q + 2], a[q + 3], lat_pol);
       }
     }
     lat_p += lat_step;
@@ -385,6 +397,7 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
           up[j] = v.x; up[j + 1] = v.y; up[j + 2] = v.z; up[j + 3] = v.w;
         }
         Fup = ldg_relaxed_i32(A.gf_in + (i0 >> 4));
+        if (spin == kBndSpinLimit - 1 && lane0) atomicExch(A.err, kWsErrHandoff);
       }
       have_next = false;
       if (i0 == 0) up[0] = kLogZero;  // "step -1": nothing arrived yet
@@ -490,8 +503,10 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
         if (SPLIT && up_g) {
           if (i0 + u) {
             upr = ldg_relaxed_f32(A.gv_in + i0 + u);
-            for (int spin = 0; spin < kBndSpinLimit && !bnd_written(upr); ++spin)
+            for (int spin = 0; spin < kBndSpinLimit && !bnd_written(upr); ++spin) {
               upr = ldg_relaxed_f32(A.gv_in + i0 + u);
+              if (spin == kBndSpinLimit - 1 && lane0) atomicExch(A.err, kWsErrHandoff);
+            }
           }
         } else if (has_up) {
           upr = lds_f32_u32(vb + 4u * u);
@@ -528,7 +543,10 @@ __device__ __forceinline__ void lattice_warp(const LatticeArgs& A, int w, int la
   float p1 = __shfl_up_sync(0xffffffffu, a[R - 1], 1);
   if (SPLIT && up_g) {
     float v = ldg_relaxed_f32(A.gv_in + Tb);
-    for (int spin = 0; spin < kBndSpinLimit && !bnd_written(v); ++spin) v = ldg_relaxed_f32(A.gv_in + Tb);
+    for (int spin = 0; spin < kBndSpinLimit && !bnd_written(v); ++spin) {
+      v = ldg_relaxed_f32(A.gv_in + Tb);
+      if (spin == kBndSpinLimit - 1 && lane0) atomicExch(A.err, kWsErrHandoff);
+    }
     const int Fl = Fup;  // the upstream frame of the last renorm block, read in its prologue
     if (lane0) p1 = v + (float)(Fl - F);
   } else if (has_up) {
@@ -573,7 +591,7 @@ __global__ void __launch_bounds__(K == 16 ? 288 : 544, 1) lattice_kernel(
     UttInfo* __restrict__ utt, const int* __restrict__ lab, int Lp, const float* __restrict__ em,
     float* __restrict__ alpha, float* __restrict__ beta, int* __restrict__ offA,
     int* __restrict__ offB, int Tfr, int Sp, int NWp, int NB, int zero_infinity, int nring, int pdl,
-    SplitArgs sa) {
+    SplitArgs sa, int* __restrict__ err, int lat_pol) {
   static_assert(R % 2 == 0, "R must be even: even recursion positions are blanks");
   extern __shared__ __align__(128) float lsm[];  // em ring [nring][K*Lp] | vals | fring | ready | cons
   __shared__ __align__(8) uint64_t bars[2 * kMaxEmRing];  // full[], empty[]
@@ -684,6 +702,8 @@ __global__ void __launch_bounds__(K == 16 ? 288 : 544, 1) lattice_kernel(
   A.nw_live = nw_live; A.zero_infinity = zero_infinity; A.b = b; A.nring = nring;
   A.W0 = W0; A.Lps = row_elems; A.col0 = col0; A.nwc = NW;
   A.gv_in = A.gv_out = nullptr; A.gf_in = A.gf_out = nullptr; A.gr_in = A.gr_out = nullptr;
+  A.err = err;
+  A.lat_policy = lat_pol;
   if (SPLIT) {
     // boundary j (between CTA j and j+1) of (b, dir): index ((b*2 + dir)*(CL-1) + j)
     const size_t base = ((size_t)b * 2 + dir) * (size_t)(sa.CL - 1);
@@ -712,7 +732,8 @@ __global__ void __launch_bounds__(256) nll_kernel(const UttInfo* __restrict__ ut
                                                   const float* __restrict__ lse2, int Tfr,
                                                   int zero_infinity, float* __restrict__ nll,
                                                   float* __restrict__ loss_out, float loss_scale,
-                                                  int* __restrict__ counter, PeerDev peer,
+                                                  int* __restrict__ counter,
+                                                  const int* __restrict__ err, PeerDev peer,
                                                   float* __restrict__ global_out) {
   __shared__ double dred[8];
   __shared__ int s_last;
@@ -734,6 +755,9 @@ __global__ void __launch_bounds__(256) nll_kernel(const UttInfo* __restrict__ ut
     float v;
     if (u.infinite) v = zero_infinity ? 0.f : -kNegInf;
     else v = (float)(-(u.lam + (double)u.aend + tot) * 0.6931471805599453);
+    // a kernel of this call gave up waiting for another CTA (ctc_ws.cuh kWsErr*): the
+    // lattices are incomplete - fail loudly
+    if (__ldcg(err) != 0) v = __int_as_float(0x7fc00000);
     nll[b] = v;
     s_last = 0;
     if (loss_out || peer.bufs) {
@@ -779,7 +803,7 @@ static int launch_lattice_rk(const LossLayout& w, unsigned char* ws, int Tfr, in
                reinterpret_cast<const float*>(ws + w.em), reinterpret_cast<float*>(ws + w.alpha),
                reinterpret_cast<float*>(ws + w.beta), reinterpret_cast<int*>(ws + w.offA),
                reinterpret_cast<int*>(ws + w.offB), Tfr, w.Sp, w.NW, w.NB, zero_infinity, nring,
-               pdl_mode(), sa);
+               pdl_mode(), sa, reinterpret_cast<int*>(ws + w.err), lat_policy_host());
   };
   if (both_dirs) go(lattice_kernel<R, true, K, false>);
   else go(lattice_kernel<R, false, K, false>);
@@ -818,7 +842,7 @@ static int launch_lattice_split(const LossLayout& w, unsigned char* ws, int Tfr,
                reinterpret_cast<const float*>(ws + w.em), reinterpret_cast<float*>(ws + w.alpha),
                reinterpret_cast<float*>(ws + w.beta), reinterpret_cast<int*>(ws + w.offA),
                reinterpret_cast<int*>(ws + w.offB), Tfr, w.Sp, w.NW, w.NB, zero_infinity, nring,
-               pdl_mode(), sa);
+               pdl_mode(), sa, reinterpret_cast<int*>(ws + w.err), lat_policy_host());
   };
   if (both_dirs) go(lattice_kernel<R, true, K, true>);
   else go(lattice_kernel<R, false, K, true>);
@@ -840,13 +864,13 @@ static int launch_lattice_r(const LossLayout& w, unsigned char* ws, int Tfr, int
   if ((size_t)(w.NW + 1) * 8 * frame > budget) K = 4;
   // short lattices: 16-step blocks halve the per-block hand-shaking (needs the registers
   // of a <= 8-warp CTA; the pipeline skew between the warps grows to 16 steps)
-  static const int k16 = [] { const char* e = getenv("B200CTC_LAT_K16"); return e ? atoi(e) : 1; }();
+  static const int k16 = tuning_int("B200CTC_LAT_K16", 1);
   if (k16 && R <= 4 && w.NW <= 8 && (size_t)(w.NW + 3) * 16 * frame <= budget) K = 16;
   B2_REQUIRE(2 * (size_t)K * frame <= budget, "ctc lattice: target too long for shared memory");
   int nring = (int)(budget / (K * frame));
   if (nring > kMaxEmRing) nring = kMaxEmRing;
   // keep small cases small: ~32 KB of emissions in flight is plenty
-  static const int slack = [] { const char* e = getenv("B200CTC_LAT_SLACK"); return e ? atoi(e) : 2; }();
+  static const int slack = tuning_int("B200CTC_LAT_SLACK", 2);
   while (nring > w.NW + slack && nring > 3 && (size_t)nring * K * frame > 32 * 1024) --nring;
   const size_t smem = (size_t)nring * K * frame + fixed;
   if (K == 16) {
@@ -876,7 +900,8 @@ static inline int launch_nll(const LossLayout& w, unsigned char* ws, int Tfr, in
              reinterpret_cast<const UttInfo*>(ws + w.utt),
              reinterpret_cast<const float*>(ws + w.cmax),
              reinterpret_cast<const float*>(ws + w.lse2), Tfr, zero_infinity, nll, loss_out,
-             loss_scale, reinterpret_cast<int*>(ws + w.counter), peer, global_out);
+             loss_scale, reinterpret_cast<int*>(ws + w.counter),
+             reinterpret_cast<const int*>(ws + w.err), peer, global_out);
   count_launch();
   return check_launch("ctc nll");
 }

@@ -51,12 +51,21 @@ constexpr int kEmLabel0 = 4;  // em row: [blank, -, -, -, label_1 .. label_L]
 
 struct LossLayout {
   int B, T, V, Lmax, Lp, Sp, R, NW, NB;
+  int NG;  // frame groups of kRenormEvery frames per utterance (fused forward: gather -> lattice flags)
   // wide lattices are split over CL CTAs of NWc warps each (ctc_lattice.cuh "SPLIT"); the
   // CTAs of one (utterance, direction) hand their boundary values on through global memory
   int CL, NWc, Tb1;  // Tb1 = padded T+1: boundary values of one CTA boundary
   size_t lse2, cmax, em, alpha, beta, offA, offB, utt, lab, dup, counter, total;
+  // sync words: {role ticket, sticky error} then the per-(utterance, group) gather flags -
+  // adjacent, so that one memset clears them (ctc_fused.cuh)
+  size_t ticket, err, flags;
   size_t bnd_val, bnd_f, bnd_ready;  // [B][2][CL-1] x {Tb1 floats, NB ints, 8 ints}
 };
+// sticky error word of a loss workspace (LossLayout::err; 0 = none).  A kernel that gives up
+// waiting for another CTA sets it; nll_kernel then returns NaN losses (never silent garbage)
+// and b200ctc_loss_status() reports it.
+constexpr int kWsErrHandoff = 1;  // split lattice: an upstream CTA's boundary values never arrived
+constexpr int kWsErrGather = 2;   // fused forward: a frame group's emissions never arrived
 constexpr int kSplitWarps = 5;   // compute warps per CTA of a split lattice (R = 4)
 constexpr int kBndReadyStride = 8;  // ints per ready counter (32 B apart)
 
@@ -66,7 +75,7 @@ constexpr int kBndReadyStride = 8;  // ints per ready counter (32 B apart)
 // ring must span NW+1 blocks.  R is the smallest value (<= 16 warps) that fits.
 constexpr size_t kLatticeSmemBudget = 222 * 1024;  // of the 227 KB an SM can hand to one CTA
 inline int lattice_R(int Smax, int Lp) {
-  if (const char* e = getenv("B200CTC_LAT_R")) {  // tuning sweeps only
+  if (const char* e = tuning_env("B200CTC_LAT_R")) {  // tuning builds only
     const int r = atoi(e);
     if ((r == 2 || r == 4 || r == 8 || r == 16 || r == 32) && Smax <= 16 * 32 * r) return r;
   }
@@ -84,7 +93,7 @@ inline LossLayout make_loss_layout(int B, int T, int V, int Lmax) {
   w.B = B; w.T = T; w.V = V; w.Lmax = Lmax;
   const int S = 2 * Lmax + 1;
   w.Lp = kEmLabel0 + (int)align_up((size_t)(Lmax > 0 ? Lmax : 1), 4);
-  w.Sp = (int)align_up((size_t)S, 8);
+  w.Sp = (int)align_up((size_t)S, 32);  // rows of alpha / beta own their 128-byte lines (L2 discard)
   w.R = lattice_R(S, w.Lp);
   w.NW = (S + 32 * w.R - 1) / (32 * w.R);
   w.CL = 1;
@@ -93,7 +102,7 @@ inline LossLayout make_loss_layout(int B, int T, int V, int Lmax) {
   // one SM is then MUFU-bound (~3 MUFU per position and step) and stuck with 4-step blocks.
   // Split the positions over CL CTAs instead: R = 4, kSplitWarps warps per CTA, each CTA
   // stages only ITS label columns of the emission rows (16-step blocks fit again).
-  static const int split = [] { const char* e = getenv("B200CTC_LAT_SPLIT"); return e ? atoi(e) : 1; }();
+  static const int split = tuning_int("B200CTC_LAT_SPLIT", 1);
   if (split && (w.R > 4 || (w.R == 4 && w.NW > 8))) {  // (R = 4 with > 8 warps: 4/8-step blocks)
     const int nw4 = (S + 32 * 4 - 1) / (32 * 4);
     const int cl = (nw4 + kSplitWarps - 1) / kSplitWarps;
@@ -112,6 +121,11 @@ inline LossLayout make_loss_layout(int B, int T, int V, int Lmax) {
   const size_t BT = (size_t)B * T;
   auto take = [&](size_t bytes) { size_t r = o; o = align_up(o + bytes, 256); return r; };
   w.counter = take(sizeof(int));  // "last CTA reduces" ticket of nll_kernel (zeroed by prep)
+  w.NG = (T + kRenormEvery - 1) / kRenormEvery;
+  if (w.NG < 1) w.NG = 1;
+  w.ticket = take(256);
+  w.err = w.ticket + 4;
+  w.flags = take(4 * (size_t)B * w.NG);
   w.utt = take(sizeof(UttInfo) * (size_t)B);
   w.lab = take(4 * (size_t)B * w.Lp);
   w.dup = take(4 * (size_t)B * w.Lp);

@@ -68,9 +68,9 @@ static inline RowLaunchCfg row_launch_cfg(const void* base, size_t row_bytes, si
   int want_stages = nt <= 128 ? 1 : 2;
   char name[64];
   snprintf(name, sizeof(name), "%s_CTAS", env_prefix);
-  if (const char* e = getenv(name)) want_ctas = atoi(e);
+  if (const char* e = tuning_env(name)) want_ctas = atoi(e);
   snprintf(name, sizeof(name), "%s_STAGES", env_prefix);
-  if (const char* e = getenv(name)) want_stages = atoi(e);
+  if (const char* e = tuning_env(name)) want_stages = atoi(e);
   if (want_ctas < 1) want_ctas = 1;
   if (want_stages < 1) want_stages = 1;
   if (want_stages > kMaxRowStages) want_stages = kMaxRowStages;
