@@ -308,6 +308,7 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
   if (pdl == 1) griddep_launch();
 }
 
+#ifdef B200CTC_TUNING  // measured loser (profiles/README.md round 2): tuning builds only
 // ---- DIRECT variant: one CTA per (b,t) row, the row goes global -> registers with plain
 // 128-bit loads (no shared-memory staging, no mbarrier, not persistent), like the soft-max
 // family's row kernels, which stream at the copy peak; the hardware block scheduler and ~6
@@ -491,6 +492,8 @@ __global__ void __launch_bounds__(NT) grad_rows_direct_kernel(
   }
 }
 
+#endif  // B200CTC_TUNING
+
 template <typename T, int NT>
 static int launch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, int blank,
                          const LossLayout& w, unsigned char* ws, const float* gscale,
@@ -523,8 +526,9 @@ static int launch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, 
   static const int l2tune = tuning_int("B200CTC_ROWS_L2", 0);
   // (deferred mode keeps the lattices for a possible second backward: no discard there)
   const int l2mode = last_use ? l2tune : (l2tune & ~2);
-  // Short lattices, 16-byte aligned rows: the direct row kernel (one CTA per row)
-  static const int direct_on = tuning_int("B200CTC_ROWS_DIRECT", 1);
+#ifdef B200CTC_TUNING
+  // experiment: the direct row kernel (one CTA per row)
+  static const int direct_on = tuning_int("B200CTC_ROWS_DIRECT", 0);
   if (direct_on && !wide && c.tma && (reinterpret_cast<uintptr_t>(grad) & 15) == 0 && rows < (1ll << 31)) {
     constexpr int NT2 = NT * 2 > 1024 ? 1024 : NT * 2;   // twice the threads, half the row per thread
     constexpr int PER2 = NT2 == NT ? PER : PER / 2;
@@ -540,6 +544,7 @@ static int launch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, 
     count_launch();
     return check_launch("ctc grad_rows (direct)");
   }
+#endif
   auto go = [&](auto k) {
     cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     launch_pdl(

@@ -242,7 +242,9 @@ static int launch_gather(const void* logits, const PrepArgs& P, int B, const Los
 }
 
 }  // namespace b200ctc
+#ifdef B200CTC_TUNING  // measured loser at C2 (profiles/README.md round 2): tuning builds only
 #include "ctc_fused.cuh"
+#endif
 namespace b200ctc {
 
 // --------------------------------------------------------- pass A (rows)
@@ -545,12 +547,13 @@ static int loss_fwd_grad_impl(const void* logits, int dtype, const int64_t* targ
   static const int force_dense = tuning_int("B200CTC_DENSE_GATHER", -1);
   const bool dense_gather = T > 0 && (force_dense >= 0 ? force_dense != 0
       : (size_t)(w.Lmax + 1) * 64 > (size_t)V * (size_t)dtype_size(dtype));
-  // Short lattices (R = 2, both directions of an utterance in one CTA): prep + gather + lattice
-  // as ONE launch with the SMs partitioned by role (ctc_fused.cuh)
-  static const int fused_on = tuning_int("B200CTC_FUSED", 1);
+  bool fused = false;
+#ifdef B200CTC_TUNING
+  // experiment (ctc_fused.cuh): prep + gather + lattice as ONE launch, SMs partitioned by role
+  static const int fused_on = tuning_int("B200CTC_FUSED", 0);
   int fnring = 0;
   size_t fsmem = 0;
-  const bool fused = T > 0 && !dense_gather && fused_on && fused_fwd_fits(w, &fnring, &fsmem);
+  fused = T > 0 && !dense_gather && fused_on && fused_fwd_fits(w, &fnring, &fsmem);
   if (fused) {
     P.err = nullptr;  // cleared by the launcher's memset (CTAs may set it before utterance 0's prep)
     prof_mark(2, 0, st);
@@ -560,7 +563,9 @@ static int loss_fwd_grad_impl(const void* logits, int dtype, const int64_t* targ
       default: rc = launch_fused_fwd<__nv_bfloat16>(logits, P, w, ws, zero_infinity, fnring, fsmem, st); break;
     }
     prof_mark(2, 1, st);
-  } else {
+  }
+#endif
+  if (!fused) {
     if (dense_gather) {
       rc = launch_prep(w, P, st);
       if (!rc) {
