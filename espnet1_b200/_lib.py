@@ -51,6 +51,7 @@ SIGNATURES = {
                                      _P]),
     "b200ctc_align_workspace_bytes": (c_size_t, [c_int, c_int]),
     "b200ctc_forced_align": (c_int, [_P, _P, c_int, c_int, c_int, c_int, _P, _P, c_size_t, _P]),
+    "b200ctc_forced_align_static": (c_int, [_P, _P, c_int, c_int, c_int, c_int, _P, _P]),
     "b200ctc_prefix_pad": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_float, _P]),
     "b200ctc_prefix_init_state": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, c_float, _P, _P]),
     "b200ctc_prefix_window": (c_int, [_P, c_int, c_int, _P, _P]),

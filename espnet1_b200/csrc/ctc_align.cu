@@ -3,6 +3,8 @@
 // The reference keeps the lattice in fp64 (numpy default) with a finite
 // log-zero of -1e11 and lets index -1 wrap to the last state for s = 0; both
 // are reproduced so that the integer alignment is identical.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace b200ctc {
@@ -77,4 +79,79 @@ extern "C" int b200ctc_forced_align(const float* lp, const int64_t* target, int 
                                                                   out_ids, static_cast<int*>(ws));
   count_launch();
   return check_launch("forced_align");
+}
+
+// ---- allocation-free variant ------------------------------------------------------------
+// b200ctc_forced_align_static: the same kernel with its back-pointer scratch in a file-scope
+// device array instead of a caller-provided workspace, for callers that cannot allocate (code
+// under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No
+// counterpart in the reference.
+//  * the array costs B200CTC_ALIGN_STATIC_MAX_BYTES on every GPU that loads the library,
+//    until the process exits;
+//  * in HOST code `g_align_scratch` is only a stand-in for the symbol, not a device address:
+//    the address is resolved once per device (with that device current) by
+//    cudaGetSymbolAddress below and that pointer is what the kernel receives;
+//  * all calls on a device share the array and it keeps the previous call's contents.  Nothing
+//    has to start at zero: the kernel writes back[t][s] for every t in [1,T), s in [0,S) before
+//    thread 0 back-tracks through exactly those words, so stale contents are never read;
+//  * calls that overlap on one GPU (two streams, two host threads) RACE on the array: the
+//    caller must serialise them (one stream, or events).
+static __device__ __align__(256) unsigned char g_align_scratch[B200CTC_ALIGN_STATIC_MAX_BYTES];
+
+namespace b200ctc {
+constexpr int kAlignMaxDevices = 64;
+static std::mutex g_align_mu;
+static void* g_align_ptr[kAlignMaxDevices] = {};
+
+// device address of g_align_scratch on the CURRENT device (resolved once per device)
+static int align_scratch_ptr(int** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kAlignMaxDevices) {
+    set_error("forced_align_static: no usable CUDA device (%s)",
+              e != cudaSuccess ? cudaGetErrorString(e) : "device index out of range");
+    return B200CTC_ERR_DEVICE;
+  }
+  std::lock_guard<std::mutex> lk(g_align_mu);
+  if (!g_align_ptr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_align_scratch);
+    if (e != cudaSuccess || !p) {
+      set_error("forced_align_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+      return B200CTC_ERR_DEVICE;
+    }
+    g_align_ptr[dev] = p;
+  }
+  *out = static_cast<int*>(g_align_ptr[dev]);
+  return B200CTC_OK;
+}
+}  // namespace b200ctc
+
+extern "C" int b200ctc_forced_align_static(const float* lp, const int64_t* target, int T, int V,
+                                           int tgt_len, int blank, int64_t* out_ids,
+                                           b200ctc_stream_t stream) {
+  B2_REQUIRE(lp && target && out_ids, "forced_align_static: null pointer");
+  B2_REQUIRE(T > 0 && V > 0 && tgt_len >= 1 && blank >= 0 && blank < V,
+             "forced_align_static: bad shape");
+  const int S = 2 * tgt_len + 1;
+  const size_t need = (size_t)T * (size_t)S * sizeof(int);
+  if (need > (size_t)B200CTC_ALIGN_STATIC_MAX_BYTES) {
+    set_error("forced_align_static: T=%d x (2*tgt_len+1)=%d back-pointers need %zu bytes, the static "
+              "scratch holds %zu (B200CTC_ALIGN_STATIC_MAX_BYTES); use b200ctc_forced_align with a "
+              "caller workspace", T, S, need, (size_t)B200CTC_ALIGN_STATIC_MAX_BYTES);
+    return B200CTC_ERR_WORKSPACE;
+  }
+  const size_t smem = 2 * (size_t)S * sizeof(double);
+  B2_REQUIRE(smem <= 200 * 1024, "forced_align_static: target too long (%d)", tgt_len);
+  int* back = nullptr;
+  const int rc = align_scratch_ptr(&back);
+  if (rc) return rc;
+  int nt = (S + 31) / 32 * 32;
+  if (nt > 1024) nt = 1024;
+  if (smem > 48 * 1024)
+    cudaFuncSetAttribute(align_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  align_kernel<<<1, nt, smem, static_cast<cudaStream_t>(stream)>>>(lp, target, T, V, tgt_len, blank,
+                                                                  out_ids, back);
+  count_launch();
+  return check_launch("forced_align_static");
 }

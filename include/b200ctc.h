@@ -166,6 +166,22 @@ size_t b200ctc_align_workspace_bytes(int T, int tgt_len);
 int b200ctc_forced_align(const float* lp, const int64_t* target, int T, int V,
                          int tgt_len, int blank, int64_t* out_ids, void* ws,
                          size_t ws_bytes, b200ctc_stream_t stream);
+/* Allocation-free variant of b200ctc_forced_align.  NO counterpart in the
+ * reference: added for callers that
+ * cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same inputs, outputs and result; the back-pointer scratch
+ * lives in a file-scope `static __device__` array of
+ * B200CTC_ALIGN_STATIC_MAX_BYTES that every GPU loading the library holds until
+ * exit.  Neither this call nor anything it calls allocates or frees memory.
+ * T * (2*tgt_len+1) * 4 bytes beyond the maximum -> B200CTC_ERR_WORKSPACE with
+ * a message naming the limit.  All calls on a device share the array (it keeps
+ * the previous call's contents; every word that is read is written first by
+ * the same call, so nothing needs clearing): calls that OVERLAP on one GPU
+ * race - serialise them on one stream or with events.                        */
+#define B200CTC_ALIGN_STATIC_MAX_BYTES (4u << 20) /* e.g. T=2000, tgt_len<=261 */
+int b200ctc_forced_align_static(const float* lp, const int64_t* target, int T,
+                                int V, int tgt_len, int blank, int64_t* out_ids,
+                                b200ctc_stream_t stream);
 
 /* ---- (a4-a7) batched CTC prefix scoring -----------------------------------
  * replaces CTCPrefixScoreTH (espnet/nets/ctc_prefix_score.py:11-269).        */
