@@ -128,13 +128,20 @@ class ClockSampler(threading.Thread):
 
 
 def cpu_reference_step(case, threads):
+    """One CPU step of the reference path.  The leaf is prepared and its gradient dropped OUTSIDE
+    the clock (no 640 MB clone inside the timed call: the reference's forward makes none)."""
     from oracle import espnet_cpu
 
     torch.set_num_threads(threads)
     logits, tg, il, tl = case
+    if not logits.requires_grad:
+        logits.requires_grad_(True)
+    logits.grad = None
     t0 = time.perf_counter()
-    espnet_cpu.logits_loss_and_grad(logits, tg, il, tl)
-    return time.perf_counter() - t0
+    espnet_cpu.loss_and_backward(logits, tg, il, tl)
+    dt = time.perf_counter() - t0
+    logits.grad = None
+    return dt
 
 
 def run_reference(args):
@@ -158,7 +165,8 @@ def run_reference(args):
         "config": {"workload": "C2 LibriSpeech-100 BPE-5000 CTC: B=64,T=500,V=5000,L in [75,150], fp32 fwd+bwd"},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
                          "sample": "full C2 batch per step: torch-CPU log_softmax+ctc_loss(reduction=none,"
-                                   "zero_infinity)+backward via oracle/espnet_cpu.py"},
+                                   "zero_infinity)+backward via oracle/espnet_cpu.loss_and_backward "
+                                   "(leaf prepared outside the clock, no input copy)"},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -213,7 +221,7 @@ def bench_prefix(dev, steps=20):
     out = {}
     for name, snum, margin, n, n_cpu in (("snum15_margin0", 15, 0, steps, 3),
                                          ("snum15_margin20", 15, 20, steps, 3),
-                                         ("fullvocab_margin20", None, 20, 3, 0)):
+                                         ("fullvocab_margin20", None, 20, 3, 1)):
         sc = CTCPrefixScoreTH(lpz.clone().to(dev), xl, 0, V - 1, margin=margin)
         pre = [inputs(i, snum, margin, dev) for i in range(n + 1)]
         # prefixes as a device tensor, as BatchBeamSearch passes them (batch_beam_search.py:
@@ -234,6 +242,18 @@ def bench_prefix(dev, steps=20):
             torch.cuda.synchronize(dev)
         ms = [e0.elapsed_time(e1) / n] * n
         entry = {"gpu_ms_per_step": sum(ms) / len(ms), "gpu_steps_per_s": 1e3 * len(ms) / sum(ms)}
+        if n_cpu and snum is None:
+            # full vocabulary on CPU: the state alone is T*2*n_bh*V*4 = 6.4 GB per step plus several
+            # temporaries of that size (decoders.py:752-757 is the reference's CUDA-only default)
+            try:
+                import psutil
+
+                avail_gb = psutil.virtual_memory().available / 2 ** 30
+            except Exception:  # noqa: BLE001
+                avail_gb = 0.0
+            if avail_gb < 64:
+                n_cpu = 0
+                entry["cpu"] = f"skipped: memory ({avail_gb:.0f} GB available, ~40 GB needed)"
         if n_cpu:
             ora = PrefixOracle(lpz.clone(), xl, 0, V - 1, margin)
             state, ts = None, []
@@ -246,12 +266,18 @@ def bench_prefix(dev, steps=20):
                 if i > 0:
                     ts.append(time.perf_counter() - t0)
             entry["cpu_steps_per_s"] = len(ts) / sum(ts)
+            entry["cpu_steps_timed"] = len(ts)
             entry["gpu_over_cpu"] = entry["gpu_steps_per_s"] / entry["cpu_steps_per_s"]
+            del ora, state, st5
         else:
             entry["cpu_steps_per_s"] = None
         out[name] = entry
-        del sc, state
+        del sc
         torch.cuda.empty_cache()
+    out["cpu_comparator"] = ("oracle.prefix_torch.PrefixOracle: CTCPrefixScoreTH restated with index tensors "
+                             "(bit-identical to the reference class on CPU, and FASTER than it - the reference "
+                             "loops over hypotheses in Python), torch CPU threads = all host cores; the "
+                             "gpu_over_cpu ratios are therefore conservative")
     return out
 
 
@@ -299,6 +325,159 @@ def bench_other_configs(dev, iters=10):
                      "roofline_step_frac": alg / (ms * 1e-3) / 1e9 / peak}
         del xc
         torch.cuda.empty_cache()
+    return out
+
+
+def bench_amp(dev, iters=20):
+    """SURVEY 8(d) "dtype variants bf16/fp16 logits for C2 (AMP path,
+    espnet2/train/trainer.py:562-565), reported separately": the same step with 16-bit logits
+    and a 16-bit gradient; arithmetic stays fp32.  Algorithmic bytes B*T*(2*2V + 2*4S)."""
+    from espnet1_b200 import functional as F
+
+    peak = peaks()[0]
+    cfg = C2
+    logits, tg, il, tl = synth(cfg, 1234)
+    tgd, ild, tld = tg.to(dev), il.to(dev), tl.to(dev)
+    out = {}
+    for name, dt in (("bf16", torch.bfloat16), ("fp16", torch.float16)):
+        xc = logits.to(dev, dt).requires_grad_(True)
+
+        def one():
+            xc.grad = None
+            F.ctc_loss(xc, tgd, ild, tld, max_tgt_len=cfg["lmax"], reduce_scale=1.0 / cfg["B"]).backward()
+
+        for _ in range(3):
+            one()
+        ms = time_region(one, iters, False, dev)
+        alg = algorithmic_bytes(cfg, esize=2)
+        out[name] = {"ms_per_step": ms, "utt_frames_per_s": cfg["B"] * cfg["T"] / (ms * 1e-3),
+                     "algorithmic_bytes": alg, "roofline_step_frac": alg / (ms * 1e-3) / 1e9 / peak}
+        del xc
+        torch.cuda.empty_cache()
+    return out
+
+
+C5 = dict(B=1024, T=500, V=5000, lmin=75, lmax=150)
+
+
+def bench_c5(dev, world, rank, dist_on, exchange, iters=10):
+    """BASELINE.json configs[4] as named: batch-sharded CTC training loss, B=1024, T=500, V=5000,
+    at N GPUs - STRONG scaling: rank r owns utterances shard_range(1024, r, N) (1024 / 512 / 256 /
+    128 per rank), no data-path collective, the [sum nll, count] all-reduce fused into the loss
+    kernel.  Labels and lengths come from one global seed (the same 1024 utterances at every N);
+    logits are generated on the device per rank."""
+    from espnet1_b200.espnet2.asr.ctc import CTC
+    from espnet1_b200.sharded import reduce_sharded_mean, shard_range
+
+    cfg = C5
+    T, V = cfg["T"], cfg["V"]
+    g = torch.Generator().manual_seed(1234)
+    tl_all = torch.randint(cfg["lmin"], cfg["lmax"] + 1, (cfg["B"],), generator=g)
+    tg_all = torch.randint(1, V, (int(tl_all.sum()),), generator=g)
+    lo, hi = shard_range(cfg["B"], rank, world)
+    Bl = hi - lo
+    o0, o1 = int(tl_all[:lo].sum()), int(tl_all[:hi].sum())
+    tg, tl = tg_all[o0:o1].to(dev), tl_all[lo:hi].to(dev)
+    il = torch.full((Bl,), T, dtype=torch.long, device=dev)
+    gd = torch.Generator(device=dev).manual_seed(4321 + rank)
+    x = torch.empty(Bl, T, V, device=dev).normal_(generator=gd).mul_(2.0).requires_grad_(True)
+    module = CTC(V, 8).to(dev)
+    module.loss_exchange = exchange
+
+    def step():
+        x.grad = None
+        loss = module.loss_fn(x.transpose(0, 1), tg, il, tl, max_tgt_len=cfg["lmax"])
+        if dist_on and exchange is None:
+            reduce_sharded_mean(loss, Bl)
+        loss.backward()
+        return loss
+
+    for _ in range(3):
+        step()
+    ms = time_region(step, iters, dist_on, dev)
+    ok, rel = (None, None)
+    if dist_on and exchange is not None:
+        ok, rel = exchange_check(exchange, step().detach(), Bl, dev, world)
+    peak = peaks()[0]
+    alg = algorithmic_bytes(dict(cfg, B=Bl))
+    res = {"workload": "C5 batch-sharded CTC training loss: B=1024,T=500,V=5000,L in [75,150], fp32 fwd+bwd",
+           "scaling": "strong", "utterances_per_rank": Bl, "ms_per_step": ms,
+           "utt_frames_per_s": cfg["B"] * T / (ms * 1e-3),
+           "roofline_step_frac_per_gpu": alg / (ms * 1e-3) / 1e9 / peak,
+           "exchange_ok": ok, "exchange_rel_err_vs_nccl": rel}
+    del x, module
+    torch.cuda.empty_cache()
+    return res
+
+
+def exchange_check(exchange, loss_local_mean, n_local, dev, world):
+    """N > 1: the fused peer-memory all-reduce (csrc/peer.cuh) against NCCL on the same step:
+    global mean within 2e-6 relative, total count equal, result BIT-identical on every rank and no
+    time-out flag.  Collective: every rank calls it; returns (ok on all ranks, max relative error)."""
+    import torch.distributed as dist
+
+    from espnet1_b200.sharded import reduce_sharded_mean
+
+    torch.cuda.synchronize(dev)
+    got = exchange.out.detach().clone()
+    ref_loss, ref_w = reduce_sharded_mean(loss_local_mean, n_local)  # NCCL all-reduce of 2 floats
+    rel = float((got[0] - ref_loss).abs() / ref_loss.abs().clamp_min(1e-30))
+    bits = got.view(torch.int32)
+    every = [torch.empty_like(bits) for _ in range(world)]
+    dist.all_gather(every, bits)
+    same = all(torch.equal(every[0], e) for e in every)
+    ok = rel <= 2e-6 and float(got[1]) == float(ref_w) and same and not exchange.timed_out()
+    t = torch.tensor([1.0 if ok else 0.0, -rel], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    return bool(t[0].item() == 1.0), float(-t[1].item())
+
+
+def bench_e2e_variants(L, host_logits, tg_h, il_h, tl_h, B, T, V, dev, n=5):
+    """Two more end-to-end legs through b200ctc_loss_fwd_bwd_host (wall clock, host buffers):
+    (a) the 640 MB gradient - the path's main output - copied BACK to pinned host memory as well;
+    (b) bf16 logits in (half the H2D bytes; the kernels take bf16 directly), loss out."""
+    import ctypes
+
+    from espnet1_b200 import _lib
+
+    nll_h = torch.empty(B, dtype=torch.float32).pin_memory()
+    out = {}
+
+    def timed(call):
+        for _ in range(2):
+            call()
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        for _ in range(n):
+            call()
+        torch.cuda.synchronize(dev)
+        return (time.perf_counter() - t0) / n
+
+    grad_h = torch.empty(B, T, V, dtype=torch.float32).pin_memory()
+
+    def with_grad():
+        _lib.check(L.b200ctc_loss_fwd_bwd_host(host_logits.data_ptr(), 0, tg_h.data_ptr(), il_h.data_ptr(),
+                                               tl_h.data_ptr(), B, T, V, 0, 1, 1.0 / B, nll_h.data_ptr(),
+                                               grad_h.data_ptr(), None, 8), "loss_fwd_bwd_host(grad_host)")
+
+    dt = timed(with_grad)
+    out["fp32_grad_to_host"] = {"ms_per_step": dt * 1e3, "utt_frames_per_s": B * T / dt,
+                                "h2d_bytes_per_step": host_logits.numel() * 4,
+                                "d2h_bytes_per_step": grad_h.numel() * 4 + 4 * B,
+                                "grad_abs_sum": float(grad_h.abs().sum())}
+    del grad_h
+    hb = host_logits.to(torch.bfloat16).pin_memory()
+    gd = ctypes.c_void_p()
+
+    def bf16_in():
+        _lib.check(L.b200ctc_loss_fwd_bwd_host(hb.data_ptr(), 2, tg_h.data_ptr(), il_h.data_ptr(),
+                                               tl_h.data_ptr(), B, T, V, 0, 1, 1.0 / B, nll_h.data_ptr(),
+                                               None, ctypes.byref(gd), 8), "loss_fwd_bwd_host(bf16)")
+
+    dt = timed(bf16_in)
+    out["bf16_logits_loss_to_host"] = {"ms_per_step": dt * 1e3, "utt_frames_per_s": B * T / dt,
+                                       "h2d_bytes_per_step": hb.numel() * 2, "d2h_bytes_per_step": 4 * B}
+    L.b200ctc_host_pipeline_release()
     return out
 
 
@@ -397,6 +576,15 @@ def run_gpu(args):
     L.b200ctc_host_pipeline_release()
     e2e_ok = abs(float(nll_h.sum()) / B - float(step().detach())) <= 1e-4 * abs(float(nll_h.sum()) / B)
 
+    exch_ok, exch_rel = (None, None)
+    if dist_on and module.loss_exchange is not None:
+        exch_ok, exch_rel = exchange_check(module.loss_exchange, step().detach(), B, dev, world)
+        if not exch_ok:
+            raise SystemExit(f"bench.py: the fused loss exchange disagrees with NCCL (rel err {exch_rel}): "
+                             "the multi-GPU number would be invalid")
+    c5 = bench_c5(dev, world, rank, dist_on, module.loss_exchange if dist_on else None)
+    if c5["exchange_ok"] is False:
+        raise SystemExit("bench.py: C5 fused loss exchange disagrees with NCCL")
     if rank != 0:
         if dist_on:
             dist.destroy_process_group()
@@ -412,17 +600,24 @@ def run_gpu(args):
         "config": {"workload": "C2 LibriSpeech-100 BPE-5000 CTC: B=64,T=500,V=5000,L in [75,150], fp32 fwd+bwd"
                                + (f" per rank (utterance-sharded; loss exchange: {exchange})" if dist_on else ""),
                    "l2": "inputs (640 MB logits) exceed the 126 MB L2; no flush needed",
-                   "api": "espnet1_b200.espnet2.asr.ctc.CTC.loss_fn + backward"},
-        "roofline": {"bound": "hbm", "kernel": "grad_rows_kernel (pass B: softmax - occupancy, written once)",
-                     "achieved": alg / (gr_ms * 1e-3) / 1e9 if gr_ms else None, "peak": peak,
-                     "unit": "GB/s", "frac": (alg / (gr_ms * 1e-3) / 1e9 / peak) if gr_ms else None,
-                     "traffic": ncu_traffic(), "peak_source": peak_src,
-                     "algorithmic_bytes_per_launch": alg,
-                     "note": "grad_rows_kernel's own algorithmic bytes = read logits + write grad + "
-                             "read alpha,beta = 4*B*T*(2V+2S), the SURVEY 8(d) figure; 'roofline_step' "
-                             "divides the same bytes by the whole step"},
-        "roofline_step": {"achieved": alg / (ms * 1e-3) / 1e9, "frac": alg / (ms * 1e-3) / 1e9 / peak,
-                          "frac_of_8TBps_nominal": alg / (ms * 1e-3) / 8e12},
+                   "api": "espnet1_b200.espnet2.asr.ctc.CTC.loss_fn + backward; max_tgt_len= is passed (an "
+                          "extension of the reference signature espnet2/asr/ctc.py:52 that CTC.forward fills "
+                          "from ys_pad.size(1)); without it loss_fn reads max(ys_lens) back from the device"},
+        # headline fraction = the WHOLE STEP (north_star: "CTC fwd+bwd ... reaching >= 60% of HBM
+        # roofline"): SURVEY 8(d)'s algorithmic bytes / the step's device time / measured copy peak.
+        # kernel_* = the dominant kernel alone (its own CUDA-event duration, same bytes).
+        "roofline": {"bound": "hbm", "achieved": alg / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                     "frac": alg / (ms * 1e-3) / 1e9 / peak, "traffic": ncu_traffic(),
+                     "scope": "whole step (gather + lattice + grad_rows + nll + rescale)",
+                     "kernel": "grad_rows_kernel (pass B: softmax - occupancy, gradient written once)",
+                     "kernel_ms": gr_ms,
+                     "kernel_achieved": alg / (gr_ms * 1e-3) / 1e9 if gr_ms else None,
+                     "kernel_frac": (alg / (gr_ms * 1e-3) / 1e9 / peak) if gr_ms else None,
+                     "peak_source": peak_src, "algorithmic_bytes_per_launch": alg,
+                     "frac_of_8TBps_nominal": alg / (ms * 1e-3) / 8e12,
+                     "note": "algorithmic bytes = read logits + write grad + write/read alpha,beta = "
+                             "4*B*T*(2V+2S), the SURVEY 8(d) figure; `traffic` = dram bytes of the dominant "
+                             "kernel per launch from the committed ncu capture (profiles/grad_rows_traffic.json)"},
         "kernel_ms": phases,
         "e2e": {"value": world * B * T / float(e2e_s), "unit": UNIT,
                 "h2d_bytes_per_step": host_logits.numel() * 4 + 8 * (tg_h.numel() + 3 * B + 1),
@@ -431,9 +626,11 @@ def run_gpu(args):
                 "matches_device_path": bool(e2e_ok)},
         "gpu_launches": int(launches * 1),
         "clocks": sampler.summary(),
+        "exchange_ok": exch_ok, "exchange_rel_err_vs_nccl": exch_rel,
+        "c5_sharded": c5,
     }
     if world == 1 and not args.quick:
-        case = (host_logits, tg_h, il_h, tl_h)
+        case = (host_logits.detach(), tg_h, il_h, tl_h)  # a view: no copy, the leaf flag stays off host_logits
         threads = os.cpu_count() or 1
         t1 = cpu_reference_step(case, threads)
         reps = max(2, min(20, int(12.0 / max(t1, 1e-3))))
@@ -455,6 +652,8 @@ def run_gpu(args):
         line["torch_cuda_library_ms_per_step"] = time_region(torch_step, 10, False, dev)
         line["prefix_score"] = bench_prefix(dev)
         line["softmax_family"] = bench_softmax_family(x.detach(), dev)
+        line["amp_variants"] = bench_amp(dev)
+        line["e2e_variants"] = bench_e2e_variants(L, host_logits, tg_h, il_h, tl_h, B, T, V, dev)
         line["other_configs"] = bench_other_configs(dev)
         del xr
         torch.cuda.empty_cache()

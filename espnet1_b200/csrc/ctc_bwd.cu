@@ -15,6 +15,8 @@ namespace b200ctc {
 // labels are staged in shared memory by the same TMA transaction as the logits row, so the
 // occupancy loop (19 positions per thread at C4) reads shared memory instead of waiting
 // on global loads one unrolled batch at a time.
+// (plain __launch_bounds__(NT): an explicit minBlocks = 1 lets ptxas take 154 registers here and
+//  the persistent grid then runs a second wave - measured: 414 us instead of 225 us)
 template <typename T, int NT, int PER, bool TMA, bool WIDE>
 __global__ void __launch_bounds__(NT) grad_rows_kernel(
     const T* __restrict__ logits, T* __restrict__ grad, int B, int Tfr, int V, int blank,
@@ -91,7 +93,9 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
     if (g + rc.stride < nrows) c_nx = cmax[g + rc.stride];
     const UttInfo u = utt[b];
     T* gr = grad + g * V;
-    const bool al16 = (reinterpret_cast<uintptr_t>(gr) & 15) == 0;
+    // TMA instantiations are only launched with a 16-byte aligned gradient base (rows are then
+    // aligned too: row_bytes % 16 == 0): the scalar store path does not exist in them
+    const bool al16 = TMA ? true : (reinterpret_cast<uintptr_t>(gr) & 15) == 0;
     if (t >= u.T || u.zeroed) {  // padded frame or zeroed utterance: gradient is 0
       float z[N];
 #pragma unroll
@@ -309,11 +313,12 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
 }
 
 #ifdef B200CTC_TUNING  // measured loser (profiles/README.md round 2): tuning builds only
-// ---- DIRECT variant: one CTA per (b,t) row, the row goes global -> registers with plain
-// 128-bit loads (no shared-memory staging, no mbarrier, not persistent), like the soft-max
-// family's row kernels, which stream at the copy peak; the hardware block scheduler and ~6
-// resident CTAs per SM are the pipeline.  Same thread <-> element mapping and arithmetic as
-// grad_rows_kernel (bit-identical results); the <= L+1 label-column logits are re-read through L1.
+// ---- DIRECT variant: one CTA per (b,t) row, not persistent, no TMA / mbarrier: the row goes
+// global -> registers with plain 128-bit loads (all in flight at once) and is ALSO parked in
+// shared memory, so that the ~450 label-column reads of the occupancy and fix-up phases are LDS
+// (as scattered global loads they cost 32 L1 tag look-ups per warp instruction: +78 us, measured).
+// The hardware block scheduler and the other resident CTAs of the SM are the pipeline.
+// mode bit 0 (timing probe): dense part only.
 template <typename T, int NT, int PER>
 __global__ void __launch_bounds__(NT) grad_rows_direct_kernel(
     const T* __restrict__ logits, T* __restrict__ grad, int Tfr, int V, int blank,
@@ -321,19 +326,21 @@ __global__ void __launch_bounds__(NT) grad_rows_direct_kernel(
     int Lp, int Sp, int NWp, int NB, int wshift, float* __restrict__ lse2, const float* __restrict__ cmax,
     const float* __restrict__ alpha, const float* __restrict__ beta,
     const int* __restrict__ offA, const int* __restrict__ offB,
-    const float* __restrict__ gscale, int gstride, float gmul, const int* __restrict__ err) {
+    const float* __restrict__ gscale, int gstride, float gmul, const int* __restrict__ err, int mode) {
   constexpr int N = Elems<T>::N;
   constexpr int NWARP = NT / 32;
-  extern __shared__ __align__(16) float pbuf[];  // [Lp]
+  extern __shared__ __align__(16) unsigned char dsm[];  // [row | pbuf (Lp floats)]
   __shared__ float wp[32];
   __shared__ float2 wms[32];
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int64_t g = blockIdx.x;
   const int b = (int)(g / Tfr), t = (int)(g - (int64_t)b * Tfr);
-  const int nchunk = V / N;
-  const int ntail = V - nchunk * N;
+  const int nchunk = V / N;  // the launcher guarantees V % N == 0 and 16-byte aligned rows
   const T* xr = logits + g * V;
   T* gr = grad + g * V;
+  uint4* srow = reinterpret_cast<uint4*>(dsm);
+  const T* xs = reinterpret_cast<const T*>(dsm);
+  float* pbuf = reinterpret_cast<float*>(dsm + (((size_t)V * sizeof(T) + 127) & ~(size_t)127));
   griddep_wait();
   const UttInfo u = utt[b];
   if (t >= u.T || u.zeroed) {  // padded frame or zeroed utterance: gradient is 0
@@ -341,7 +348,6 @@ __global__ void __launch_bounds__(NT) grad_rows_direct_kernel(
 #pragma unroll
     for (int e = 0; e < N; ++e) z[e] = 0.f;
     for (int i = tid; i < nchunk; i += NT) store16<T>(gr + i * N, z);
-    if (tid < ntail) gr[nchunk * N + tid] = from_f32<T>(0.f);
     return;
   }
   // the row: all loads in flight first
@@ -353,7 +359,7 @@ __global__ void __launch_bounds__(NT) grad_rows_direct_kernel(
   }
   const bool ws_bad = __ldcg(err) != 0;
   const float c2 = cmax[g];
-  const int L = u.L, S = 2 * L + 1;
+  const int L = (mode & 1) ? 0 : u.L, S = (mode & 1) ? 0 : 2 * L + 1;
   float gb = gmul * (gscale ? gscale[(size_t)b * gstride] : 1.f);
   float qbase = -(float)u.lam;
   if (u.infinite || ws_bad) {
@@ -365,7 +371,7 @@ __global__ void __launch_bounds__(NT) grad_rows_direct_kernel(
   const int* oa = offA + ((size_t)b * NB + (t / kRenormEvery)) * NWp;
   const int* ob = offB + ((size_t)b * NB + ((u.T - 1 - t) / kRenormEvery)) * NWp;
   const int* lb = lab + (size_t)b * Lp;
-  constexpr int SM = NT >= 256 ? 2 : 3;
+  constexpr int SM = NT >= 256 ? 2 : 3;  // lattice positions per thread with loads in flight early
   float ab[SM];
   int vcol[SM];
 #pragma unroll
@@ -376,37 +382,18 @@ __global__ void __launch_bounds__(NT) grad_rows_direct_kernel(
     ab[j] = s < S ? al[sc] + be[sb] + ((float)fo + qbase) : kNegInf;
     vcol[j] = (sc & 1) ? lb[(sc + 1) >> 1] : blank;
   }
-  float blank_part = 0.f;
-  for (int s0 = NT * SM; s0 < S; s0 += NT) {  // wide lattices (not at C2)
-    const int s = s0 + tid;
-    if (s < S) {
-      const int sb = S - 1 - s;
-      const int fo = oa[s >> wshift] + ob[sb >> wshift] - u.aend;
-      const float abv = al[s] + be[sb] + ((float)fo + qbase);
-      const bool odd = s & 1;
-      const int k = odd ? (s + 1) >> 1 : 0;
-      const int v = odd ? lb[k] : blank;
-      const float em = fmaf(to_f32<T>(__ldg(xr + v)), kLog2e, -c2);
-      const float p = ex2(abv - em);
-      if (odd) pbuf[k] = p; else blank_part += p;
-    }
-  }
-  // ---- phase 0: thread-local max and sum of 2^(x2 - max)
+  // ---- phase 0: park the row in shared memory; thread-local max and sum of 2^(x2 - max)
   float x[PER][N];
   float m = kNegInf;
 #pragma unroll
   for (int j = 0; j < PER; ++j) {
     const int i = tid + j * NT;
     if (i < nchunk) {
+      srow[i] = raw[j];
       unpack16<T>(raw[j], x[j]);
 #pragma unroll
       for (int e = 0; e < N; ++e) m = fmaxf(m, x[j][e]);
     }
-  }
-  float xt = kNegInf;
-  if (tid < ntail) {
-    xt = to_f32<T>(__ldg(xr + nchunk * N + tid));
-    m = fmaxf(m, xt);
   }
   m = warp_max(m);
   const float mw2 = ((m == kNegInf) ? 0.f : m) * kLog2e;
@@ -422,26 +409,37 @@ __global__ void __launch_bounds__(NT) grad_rows_direct_kernel(
       }
     }
   }
-  if (tid < ntail) {
-    xt = ex2(fmaf(xt, kLog2e, -mw2));
-    sum += xt;
-  }
   sum = warp_sum(sum);
   if (lane == 0) wms[wid] = make_float2(mw2, sum);
-  // ---- phase 1a: occupancies (label-column logits: the row is in L1 by now)
+  __syncthreads();  // srow and wms visible
+  // ---- phase 1a: occupancies gamma_t(s)
+  float blank_part = 0.f;
 #pragma unroll
   for (int j = 0; j < SM; ++j) {
     const int s = tid + j * NT;
     if (s < S) {
-      const bool odd = s & 1;
-      const float em = fmaf(to_f32<T>(__ldg(xr + vcol[j])), kLog2e, -c2);
+      const float em = fmaf(to_f32<T>(xs[vcol[j]]), kLog2e, -c2);
       const float p = ex2(ab[j] - em);
-      if (odd) pbuf[(s + 1) >> 1] = p; else blank_part += p;
+      if (s & 1) pbuf[(s + 1) >> 1] = p; else blank_part += p;
+    }
+  }
+  for (int s0 = NT * SM; s0 < S; s0 += NT) {  // wider lattices
+    const int s = s0 + tid;
+    if (s < S) {
+      const int sb = S - 1 - s;
+      const int fo = oa[s >> wshift] + ob[sb >> wshift] - u.aend;
+      const float abv = al[s] + be[sb] + ((float)fo + qbase);
+      const bool odd = s & 1;
+      const int k = odd ? (s + 1) >> 1 : 0;
+      const int v = odd ? lb[k] : blank;
+      const float em = fmaf(to_f32<T>(xs[v]), kLog2e, -c2);
+      const float p = ex2(abv - em);
+      if (odd) pbuf[k] = p; else blank_part += p;
     }
   }
   blank_part = warp_sum(blank_part);
   if (lane == 0) wp[wid] = blank_part;
-  __syncthreads();
+  // ---- row normaliser and the dense part, straight from registers
   float M2 = kNegInf;
 #pragma unroll
   for (int w2 = 0; w2 < NWARP; ++w2) M2 = fmaxf(M2, wms[w2].x);
@@ -451,7 +449,6 @@ __global__ void __launch_bounds__(NT) grad_rows_direct_kernel(
   const float l2 = M2 + log2f(tot);
   if (tid == 0) lse2[g] = l2;
   const float scale = gb * ex2(mw2 - l2);
-  // ---- phase 1b: dense part
 #pragma unroll
   for (int j = 0; j < PER; ++j) {
     const int i = tid + j * NT;
@@ -461,24 +458,24 @@ __global__ void __launch_bounds__(NT) grad_rows_direct_kernel(
       store16<T>(gr + i * N, x[j]);
     }
   }
-  if (tid < ntail) gr[nchunk * N + tid] = from_f32<T>(xt * scale);
-  __syncthreads();  // dense stores are ordered before the column fix-ups below
+  __syncthreads();  // pbuf / wp visible; dense stores ordered before the column fix-ups
+  if (mode & 1) return;
   // ---- phase 2: label columns, single owner thread per vocabulary column
   const int* db = dup + (size_t)b * Lp;
-  for (int k0 = tid + 1; k0 <= L; k0 += NT * 4) {
-    int code[4], vv[4];
+  for (int k0 = tid + 1; k0 <= L; k0 += NT * 2) {
+    int code[2], vv[2];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
+    for (int j = 0; j < 2; ++j) {
       const int k = k0 + j * NT;
       code[j] = k <= L ? db[k] : 0;
       vv[j] = k <= L ? lb[k] : 0;
     }
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
+    for (int j = 0; j < 2; ++j) {
       if (code[j] & kDupFirst) {
         float acc = pbuf[k0 + j * NT];
         for (int nx = code[j] & kDupMask; nx != 0; nx = db[nx] & kDupMask) acc += pbuf[nx];
-        const float sm = ex2(fmaf(to_f32<T>(__ldg(xr + vv[j])), kLog2e, -l2));
+        const float sm = ex2(fmaf(to_f32<T>(xs[vv[j]]), kLog2e, -l2));
         gr[vv[j]] = from_f32<T>(gb * (sm - acc));
       }
     }
@@ -487,7 +484,7 @@ __global__ void __launch_bounds__(NT) grad_rows_direct_kernel(
     float acc = 0.f;
     for (int w2 = 0; w2 < NWARP; ++w2) acc += wp[w2];
     for (int nx = u.blank_head; nx != 0; nx = db[nx] & kDupMask) acc += pbuf[nx];
-    const float sm = ex2(fmaf(to_f32<T>(__ldg(xr + blank)), kLog2e, -l2));
+    const float sm = ex2(fmaf(to_f32<T>(xs[blank]), kLog2e, -l2));
     gr[blank] = from_f32<T>(gb * (sm - acc));
   }
 }
@@ -501,14 +498,42 @@ static int launch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, 
   constexpr int PER = 40 / Elems<T>::N;
   const size_t extra = align_up(sizeof(float) * (size_t)w.Lp, 128);
   RowLaunchCfg c = row_launch_cfg(logits, (size_t)V * sizeof(T), extra, NT, "B200CTC_B");
-  // long lattices: alpha / beta / labels of the row are staged next to the logits row
+  if ((reinterpret_cast<uintptr_t>(grad) & 15) != 0) {  // unaligned gradient: the generic kernel
+    c.tma = false;
+    c.nstage = 1;
+  }
+  // WIDE staging: alpha / beta / labels / duplicate codes of the row travel with the logits row
+  // in one TMA transaction, the row loop then has no dependent global loads.
+  //  * long lattices (S > 3 NT): needed - the occupancy loop was latency-bound without it (C4);
+  //  * short lattices at 128 threads per row (C2): the instantiation needs 72 registers instead
+  //    of 80, so SEVEN CTAs per SM fit (24 KB stages): row pass 238 -> 225 us at C2, measured.
+  //    Taken only if 7 CTAs are really resident (occupancy query), else the 6-CTA kernel.
   static const int wide_on = tuning_int("B200CTC_B_WIDE", 1);
   const size_t lat_stage = align_up(4 * (2 * (size_t)w.Sp + 2 * (size_t)w.Lp), 128);
-  bool wide = wide_on && c.tma && 2 * w.Lmax + 1 > 3 * NT;
+  const bool wide_needed = 2 * w.Lmax + 1 > 3 * NT;
+  bool wide = wide_on && c.tma && (wide_needed || NT == 128);
   if (wide) {
     const size_t row_al = align_up((size_t)V * sizeof(T), 128);
-    const RowLaunchCfg cw = row_launch_cfg(logits, row_al + lat_stage, extra, NT, "B200CTC_B");
-    if (cw.ctas_per_sm * ((size_t)cw.nstage * cw.stride + extra + 1024) <= 220 * 1024 && cw.ctas_per_sm >= 3) {
+    const int want = wide_needed ? 0 : 7;
+    const RowLaunchCfg cw = row_launch_cfg(logits, row_al + lat_stage, extra, NT, "B200CTC_B", want);
+    bool ok = cw.ctas_per_sm * ((size_t)cw.nstage * cw.stride + extra + 1024) <= 220 * 1024 &&
+              cw.ctas_per_sm >= (wide_needed ? 3 : 7);
+    if (ok && !wide_needed) {  // all 7 must be resident at once: a persistent grid must not run a second wave
+      static thread_local int occ_cached = -1;
+      static thread_local size_t occ_smem = 0;
+      const size_t smem_w = (size_t)cw.nstage * cw.stride + extra;
+      if (occ_cached < 0 || occ_smem != smem_w) {
+        auto kw = grad_rows_kernel<T, NT, PER, true, true>;
+        cudaFuncSetAttribute(kw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_w);
+        int occ = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kw, NT, smem_w) != cudaSuccess) occ = 0;
+        cudaGetLastError();
+        occ_cached = occ;
+        occ_smem = smem_w;
+      }
+      ok = occ_cached >= cw.ctas_per_sm;
+    }
+    if (ok) {
       c.nstage = cw.nstage; c.ctas_per_sm = cw.ctas_per_sm; c.stride = cw.stride;
     } else {
       wide = false;
@@ -533,14 +558,16 @@ static int launch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, 
     constexpr int NT2 = NT * 2 > 1024 ? 1024 : NT * 2;   // twice the threads, half the row per thread
     constexpr int PER2 = NT2 == NT ? PER : PER / 2;
     auto k = grad_rows_direct_kernel<T, NT2, PER2>;
-    launch_pdl(k, dim3((unsigned)rows), dim3(NT2), extra, st, 1, static_cast<const T*>(logits),
+    const size_t dsmem = align_up((size_t)V * sizeof(T), 128) + extra;
+    cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dsmem);
+    launch_pdl(k, dim3((unsigned)rows), dim3(NT2), dsmem, st, 1, static_cast<const T*>(logits),
                static_cast<T*>(grad), Tfr, V, blank, reinterpret_cast<const UttInfo*>(ws + w.utt),
                reinterpret_cast<const int*>(ws + w.lab), reinterpret_cast<const int*>(ws + w.dup),
                w.Lp, w.Sp, w.NW, w.NB, wshift, reinterpret_cast<float*>(ws + w.lse2),
                reinterpret_cast<const float*>(ws + w.cmax), reinterpret_cast<const float*>(ws + w.alpha),
                reinterpret_cast<const float*>(ws + w.beta), reinterpret_cast<const int*>(ws + w.offA),
                reinterpret_cast<const int*>(ws + w.offB), gscale, gstride, gmul,
-               reinterpret_cast<const int*>(ws + w.err));
+               reinterpret_cast<const int*>(ws + w.err), tuning_int("B200CTC_DIRECT_MODE", 0));
     count_launch();
     return check_launch("ctc grad_rows (direct)");
   }

@@ -57,7 +57,7 @@ struct RowLaunchCfg { int nstage, ctas_per_sm, stride; bool tma; };
 
 // shared-memory budgeting for the row passes; env overrides are for tuning sweeps only
 static inline RowLaunchCfg row_launch_cfg(const void* base, size_t row_bytes, size_t extra_smem,
-                                          int nt, const char* env_prefix) {
+                                          int nt, const char* env_prefix, int want_ctas_hint = 0) {
   RowLaunchCfg c;
   c.tma = (row_bytes % 16 == 0) && ((reinterpret_cast<uintptr_t>(base) & 15) == 0);
   c.stride = (int)align_up(row_bytes, 128);
@@ -66,6 +66,7 @@ static inline RowLaunchCfg row_launch_cfg(const void* base, size_t row_bytes, si
   // double-buffered ones - the other CTAs of the SM are the pipeline
   int want_ctas = nt <= 128 ? 6 : (nt <= 256 ? 3 : 1);
   int want_stages = nt <= 128 ? 1 : 2;
+  if (want_ctas_hint > 0) want_ctas = want_ctas_hint;
   char name[64];
   snprintf(name, sizeof(name), "%s_CTAS", env_prefix);
   if (const char* e = tuning_env(name)) want_ctas = atoi(e);

@@ -56,6 +56,19 @@ def legacy_ctc_forward(hs_pad, hlens, ys_pad, weight, bias, reduce=True, ignore_
     return loss.sum() if reduce else loss
 
 
+def loss_and_backward(x_leaf, targets_1d, in_lens, tgt_lens, zero_infinity=True):
+    """The timed part of the CPU baseline: ``x_leaf`` is a (B,T,V) leaf that already requires a
+    gradient and whose ``.grad`` is None (the caller prepares both OUTSIDE the clock): log_softmax
+    + ctc_loss + ``sum()/B`` + backward, espnet2/asr/ctc.py:54-60.  No input copy is made - the
+    reference's forward makes none; the gradient buffer is allocated by autograd, as it is for
+    the reference's (non-leaf) logits.  Returns nll (B,); the gradient is in ``x_leaf.grad``."""
+    lp = x_leaf.transpose(0, 1).log_softmax(2)
+    nll = F.ctc_loss(lp, targets_1d, in_lens, tgt_lens, reduction="none",
+                     zero_infinity=zero_infinity)
+    (nll.sum() / x_leaf.size(0)).backward()
+    return nll.detach()
+
+
 def logits_loss_and_grad(logits_btv, targets_1d, in_lens, tgt_lens, zero_infinity=True):
     """Timed CPU baseline at the logits boundary: log_softmax + ctc_loss
     (reduction none) + ``sum()/B`` + backward, exactly the arithmetic of
