@@ -47,6 +47,8 @@ SIGNATURES = {
     "b200ctc_peer_destroy": (c_int, [_P]),
     "b200ctc_peer_error": (c_int, [_P]),
     "b200ctc_peer_exchange": (c_int, [_P, _P, _P, _P]),
+    "b200ctc_peer_configure": (c_int, [_P, c_int, c_int]),
+    "b200ctc_peer_wait": (c_int, [_P, _P, _P]),
     "b200ctc_grad_rescale": (c_int, [_P, c_int, _P, c_int, c_float, c_float, c_int, c_int, c_int,
                                      _P]),
     "b200ctc_align_workspace_bytes": (c_size_t, [c_int, c_int]),

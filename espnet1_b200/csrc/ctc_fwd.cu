@@ -524,12 +524,12 @@ static int loss_fwd_grad_impl(const void* logits, int dtype, const int64_t* targ
                               float* loss_out, float loss_scale, void* grad, void* ws_,
                               size_t ws_bytes, b200ctc_stream_t stream, b200ctc_peer* peer,
                               float* global_out) {
-  PeerDev pd{nullptr, 0, 0};
+  PeerDev pd{nullptr, 0, 0, 0, 0};
   if (peer) {
     B2_REQUIRE(peer->connected, "loss_fwd_grad_sharded: peer handle is not connected");
     B2_REQUIRE(global_out, "loss_fwd_grad_sharded: null global_out");
     B2_REQUIRE(B > 0, "loss_fwd_grad_sharded: a rank without utterances must call b200ctc_peer_exchange");
-    pd = PeerDev{peer->d_bufs, peer->world, peer->rank};
+    pd = PeerDev{peer->d_bufs, peer->world, peer->rank, peer->deferred, peer->timeout_ns};
   }
   LossLayout w;
   int rc = check_loss_args("loss_fwd_grad", logits, dtype, targets, tgt_offsets, in_lens, tgt_lens,

@@ -895,7 +895,7 @@ static inline int launch_lattice(const LossLayout& w, unsigned char* ws, int Tfr
 
 static inline int launch_nll(const LossLayout& w, unsigned char* ws, int Tfr, int zero_infinity,
                              float* nll, float* loss_out, float loss_scale, cudaStream_t st,
-                             PeerDev peer = PeerDev{nullptr, 0, 0}, float* global_out = nullptr) {
+                             PeerDev peer = PeerDev{nullptr, 0, 0, 0, 0}, float* global_out = nullptr) {
   launch_pdl(nll_kernel, dim3(w.B), dim3(256), 0, st, 2,
              reinterpret_cast<const UttInfo*>(ws + w.utt),
              reinterpret_cast<const float*>(ws + w.cmax),

@@ -11,9 +11,30 @@ __global__ void __launch_bounds__(32) peer_exchange_kernel(PeerDev P, const floa
   peer_exchange_warp(P, pair[0], pair[1], out);
 }
 
+__global__ void __launch_bounds__(32) peer_wait_kernel(PeerDev P, float* __restrict__ out) {
+  peer_wait_warp(P, out);
+}
+
 }  // namespace b200ctc
 
 using namespace b200ctc;
+
+extern "C" int b200ctc_peer_configure(b200ctc_peer* p, int deferred, int timeout_ms) {
+  B2_REQUIRE(p, "peer_configure: null handle");
+  B2_REQUIRE(timeout_ms >= 0, "peer_configure: timeout_ms must be >= 0 (0 = default)");
+  p->deferred = deferred ? 1 : 0;
+  p->timeout_ns = (unsigned long long)timeout_ms * 1000000ull;
+  return B200CTC_OK;
+}
+
+extern "C" int b200ctc_peer_wait(b200ctc_peer* p, float* global_out, b200ctc_stream_t stream) {
+  B2_REQUIRE(p && p->connected, "peer_wait: handle is not connected");
+  B2_REQUIRE(global_out, "peer_wait: null pointer");
+  PeerDev P{p->d_bufs, p->world, p->rank, p->deferred, p->timeout_ns};
+  peer_wait_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(P, global_out);
+  count_launch();
+  return check_launch("peer wait");
+}
 
 extern "C" int b200ctc_peer_create(int world, int rank, b200ctc_peer** out,
                                    unsigned char* handle_out) {
@@ -95,7 +116,8 @@ extern "C" int b200ctc_peer_exchange(b200ctc_peer* p, const float* local_pair, f
                                      b200ctc_stream_t stream) {
   B2_REQUIRE(p && p->connected, "peer_exchange: handle is not connected");
   B2_REQUIRE(local_pair && global_out, "peer_exchange: null pointer");
-  PeerDev P{p->d_bufs, p->world, p->rank};
+  // (stand-alone: always consumes its own step - the caller wants the result now)
+  PeerDev P{p->d_bufs, p->world, p->rank, 0, p->timeout_ns};
   peer_exchange_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(P, local_pair, global_out);
   count_launch();
   return check_launch("peer exchange");

@@ -11,10 +11,17 @@
 // No NCCL launch, no host work per step, one-shot latency of a single NVLink hop.
 //
 // Buffer of a rank (cudaMalloc + cudaIpc, mapped by every peer):
-//   header {u32 step, u32 error}, then slots[2 parities][world] x {f32 sum, f32 weight,
-//   u32 seq, u32 pad}.  Parity double-buffering is enough: a rank can only reach step
-//   s+2 after it has seen every peer's push of step s+1, which a peer issues after it
-//   has consumed step s (stream order).
+//   header {u32 pushed step, u32 error, u32 consumed step}, then slots[2 parities][world] x
+//   {f32 sum, f32 weight, u32 seq, u32 pad}.
+//
+// DEFERRED mode (the default of sharded.PeerLossExchange): the kernel that finishes the loss
+// only PUSHES; the wait for the peers' words - a barrier on the slowest rank that nothing on
+// the device needs inside the step - moves to the consumer: the next step's exchange consumes
+// the previous step first (its words arrived a whole step ago: no wait in steady state), and
+// b200ctc_peer_wait consumes the latest step when the result is read.  A rank therefore still
+// cannot push step s+1 before it has consumed step s, i.e. before every peer pushed s, and a
+// peer pushes s only after consuming s-1: ranks stay within one step of each other and parity
+// double-buffering remains sufficient.
 #pragma once
 #include "common.cuh"
 
@@ -24,11 +31,13 @@ constexpr int kMaxPeers = 64;
 constexpr int kPeerSlotBytes = 16;
 constexpr int kPeerHeaderBytes = 64;
 constexpr size_t kPeerBufBytes = kPeerHeaderBytes + 2 * kMaxPeers * kPeerSlotBytes;
-constexpr unsigned long long kPeerTimeoutNs = 5ull * 1000 * 1000 * 1000;  // then NaN + error flag
+constexpr unsigned long long kPeerDefaultTimeoutNs = 30ull * 1000 * 1000 * 1000;  // then NaN + error flag
 
 struct PeerDev {  // passed by value to kernels
   unsigned char* const* bufs;  // device array [world]: every rank's buffer (bufs[rank] = mine)
   int world, rank;
+  int deferred;                   // 1: push only, consume later (see above)
+  unsigned long long timeout_ns;  // 0 = kPeerDefaultTimeoutNs
 };
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
@@ -45,27 +54,31 @@ __device__ __forceinline__ unsigned ld_acquire_sys_u32(const unsigned* p) {
   return v;
 }
 
-// Called by ONE full warp (all 32 lanes converged).  out[0] = sum_r sum / sum_r weight,
-// out[1] = sum_r weight on every rank.
-__device__ __forceinline__ void peer_exchange_warp(const PeerDev& P, float my_sum, float my_weight,
-                                                   float* __restrict__ out) {
+// ---- all three helpers are called by ONE full warp (all 32 lanes converged) of ONE CTA per
+// kernel; kernels of a rank are stream-ordered, so the header needs no atomics.
+
+// push my pair of `step` into slot[rank] of every rank's buffer
+__device__ __forceinline__ void peer_push_warp(const PeerDev& P, unsigned step, float my_sum,
+                                               float my_weight) {
   const int lane = threadIdx.x & 31;
-  unsigned char* mine = P.bufs[P.rank];
-  unsigned* hdr = reinterpret_cast<unsigned*>(mine);
-  unsigned step = 0;
-  if (lane == 0) {
-    step = hdr[0] + 1u;  // only this kernel touches it; calls are stream-ordered
-    hdr[0] = step;
-  }
-  step = __shfl_sync(0xffffffffu, step, 0);
   const unsigned par = step & 1u;
   const size_t my_slot = kPeerHeaderBytes + ((size_t)par * kMaxPeers + P.rank) * kPeerSlotBytes;
-  for (int r = lane; r < P.world; r += 32) {  // push: my pair into slot[rank] of rank r
+  for (int r = lane; r < P.world; r += 32) {
     unsigned char* s = P.bufs[r] + my_slot;
     asm volatile("st.global.v2.f32 [%0], {%1,%2};" ::"l"(s), "f"(my_sum), "f"(my_weight) : "memory");
     st_release_sys_u32(reinterpret_cast<unsigned*>(s + 8), step);
   }
-  // pull: wait for every rank's word of this step in MY buffer, then sum in rank order
+}
+
+// wait for every rank's word of `step` in MY buffer, sum in rank order (the same order on every
+// rank: bit-identical results), write out[0] = sum_r sum / sum_r weight, out[1] = sum_r weight
+__device__ __forceinline__ void peer_consume_warp(const PeerDev& P, unsigned step,
+                                                  float* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  unsigned char* mine = P.bufs[P.rank];
+  unsigned* hdr = reinterpret_cast<unsigned*>(mine);
+  const unsigned par = step & 1u;
+  const unsigned long long limit = P.timeout_ns ? P.timeout_ns : kPeerDefaultTimeoutNs;
   double tot_s = 0.0, tot_w = 0.0;
   bool ok = true;
   const unsigned long long t0 = globaltimer_ns();
@@ -75,7 +88,7 @@ __device__ __forceinline__ void peer_exchange_warp(const PeerDev& P, float my_su
     if (r < P.world) {
       const unsigned char* s = mine + kPeerHeaderBytes + ((size_t)par * kMaxPeers + r) * kPeerSlotBytes;
       while (ld_acquire_sys_u32(reinterpret_cast<const unsigned*>(s + 8)) != step) {
-        if (globaltimer_ns() - t0 > kPeerTimeoutNs) { ok = false; break; }
+        if (globaltimer_ns() - t0 > limit) { ok = false; break; }
         __nanosleep(100);
       }
       asm volatile("ld.volatile.global.v2.f32 {%0,%1}, [%2];" : "=f"(v.x), "=f"(v.y) : "l"(s) : "memory");
@@ -95,7 +108,35 @@ __device__ __forceinline__ void peer_exchange_warp(const PeerDev& P, float my_su
       out[0] = tot_w > 0.0 ? (float)(tot_s / tot_w) : 0.f;
       out[1] = (float)tot_w;
     }
+    hdr[2] = step;
   }
+  __syncwarp();
+}
+
+// one exchange call: consume the previous step if that is still owed, push this step, and -
+// unless deferred - consume it right away (out then holds THIS step's result on return)
+__device__ __forceinline__ void peer_exchange_warp(const PeerDev& P, float my_sum, float my_weight,
+                                                   float* __restrict__ out) {
+  unsigned* hdr = reinterpret_cast<unsigned*>(P.bufs[P.rank]);
+  unsigned step = 0, consumed = 0;
+  if ((threadIdx.x & 31) == 0) { step = hdr[0] + 1u; consumed = hdr[2]; }
+  step = __shfl_sync(0xffffffffu, step, 0);
+  consumed = __shfl_sync(0xffffffffu, consumed, 0);
+  if (consumed + 1u < step) peer_consume_warp(P, step - 1u, out);
+  peer_push_warp(P, step, my_sum, my_weight);
+  if ((threadIdx.x & 31) == 0) hdr[0] = step;
+  __syncwarp();
+  if (!P.deferred) peer_consume_warp(P, step, out);
+}
+
+// consume the latest pushed step if that has not happened yet (b200ctc_peer_wait)
+__device__ __forceinline__ void peer_wait_warp(const PeerDev& P, float* __restrict__ out) {
+  unsigned* hdr = reinterpret_cast<unsigned*>(P.bufs[P.rank]);
+  unsigned step = 0, consumed = 0;
+  if ((threadIdx.x & 31) == 0) { step = hdr[0]; consumed = hdr[2]; }
+  step = __shfl_sync(0xffffffffu, step, 0);
+  consumed = __shfl_sync(0xffffffffu, consumed, 0);
+  if (consumed < step) peer_consume_warp(P, step, out);
 }
 
 }  // namespace b200ctc
@@ -104,6 +145,8 @@ __device__ __forceinline__ void peer_exchange_warp(const PeerDev& P, float my_su
 struct b200ctc_peer {
   int world = 0, rank = 0, dev = 0;
   bool connected = false;
+  int deferred = 0;                   // b200ctc_peer_configure
+  unsigned long long timeout_ns = 0;  // 0 = default (30 s)
   unsigned char* local = nullptr;
   unsigned char* mapped[b200ctc::kMaxPeers] = {};
   unsigned char** d_bufs = nullptr;

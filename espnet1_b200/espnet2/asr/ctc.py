@@ -63,14 +63,31 @@ class CTC(torch.nn.Module):
         # leaves the global batch-weighted loss of all ranks in `loss_exchange.out`
         # (the all-reduce of trainer.py:604-613, fused into the loss kernel)
         self.loss_exchange = None
+        # The gradient w.r.t. the logits is produced during the forward call, pre-scaled by the
+        # upstream gradient this loss is EXPECTED to receive: 1/B times `upstream_scale`.  Set it to
+        # the factor the caller multiplies the CTC loss with before backward() - `ctc_weight` in
+        # espnet2/asr/espnet_model.py (`loss = ctc_weight * loss_ctc + ...`), an AMP loss scale -
+        # and backward stays a no-op check; any other upstream gradient is still exact, it only
+        # costs one rescaling pass over the (B,T,V) gradient.
+        self.upstream_scale = 1.0
+
+    def _grad_hint(self, per_utt_scale: float):
+        if self.upstream_scale == 1.0:
+            return None  # functional default: per_utt_scale itself
+        import numpy as np
+
+        # fp32 product, exactly what autograd hands to backward (fl32(weight) * fl32(1/B))
+        return float(np.float32(self.upstream_scale) * np.float32(per_utt_scale))
 
     # same call convention as torch.nn.CTCLoss(reduction="none") but fed with
     # batch-major LOGITS: log-softmax is fused into the loss kernels.
     def _builtin_ctc_loss(self, logits_btv, th_target, th_ilen, th_olen, max_tgt_len=None,
                           reduce_scale=None):
+        per_utt = reduce_scale if reduce_scale is not None else B._f32_recip(logits_btv.shape[0])
         return B.ctc_loss(logits_btv, th_target, th_ilen, th_olen, blank=0,
                           zero_infinity=self.zero_infinity, max_tgt_len=max_tgt_len,
-                          reduce_scale=reduce_scale, peer=self.loss_exchange)
+                          reduce_scale=reduce_scale, grad_hint=self._grad_hint(per_utt),
+                          peer=self.loss_exchange)
 
     def loss_fn(self, th_pred, th_target, th_ilen, th_olen, max_tgt_len=None) -> torch.Tensor:
         """th_pred is (T, B, V) like the reference (:52); a transposed view of a

@@ -112,7 +112,7 @@ class _CTCLossFn(torch.autograd.Function):
         scale = float(reduce_scale) if reduced else 0.0
         ctx.eager = bool(need_grad and eager and B > 0)
         ctx.gmul = float(reduce_scale) if reduced else 1.0
-        if peer is not None and not (ctx.eager):
+        if peer is not None and not (ctx.eager):  # ctc_loss() routes such calls to peer.exchange
             raise RuntimeError("the fused sharded-loss exchange needs the eager gradient mode, logits "
                                "that require a gradient and at least one utterance on every rank")
         if ctx.eager:
@@ -122,7 +122,7 @@ class _CTCLossFn(torch.autograd.Function):
                     ptr(x), dtype_code(x), ptr(targets), ptr(tgt_offsets), ptr(in_lens),
                     ptr(tgt_lens), B, T, V, max_tgt_len, blank, int(zero_infinity), grad_hint,
                     ptr(nll), ptr(loss), scale, ptr(grad), ptr(ws), nbytes, peer.handle,
-                    ptr(peer.out), stream_ptr(dev)), "loss_fwd_grad_sharded")
+                    ptr(peer.out_buffer), stream_ptr(dev)), "loss_fwd_grad_sharded")
             else:
                 check(lib().b200ctc_loss_fwd_grad(ptr(x), dtype_code(x), ptr(targets),
                                                   ptr(tgt_offsets), ptr(in_lens), ptr(tgt_lens), B, T,
@@ -202,10 +202,23 @@ def ctc_loss(logits, targets, in_lens, tgt_lens, blank: int = 0, zero_infinity: 
         max_tgt_len = int(torch.as_tensor(src).max()) if tl_dev.numel() else 0
     if grad_hint is None:
         grad_hint = float(reduce_scale) if reduce_scale is not None else _f32_recip(logits.shape[0])
-    return _CTCLossFn.apply(logits, tg_dev, tgt_offsets, il_dev, tl_dev, int(max_tgt_len),
-                            int(blank), bool(zero_infinity), float(grad_hint),
-                            grad_mode == "eager",
-                            None if reduce_scale is None else float(reduce_scale), peer)
+    # the exchange is fused into the loss kernel only in the eager gradient mode; any other call
+    # with a `peer` (validation under no_grad, deferred mode, an empty shard) computes the local
+    # loss and makes the SAME collective with the stand-alone exchange kernel
+    fused = (peer is not None and grad_mode == "eager" and torch.is_grad_enabled()
+             and logits.requires_grad and logits.shape[0] > 0)
+    out = _CTCLossFn.apply(logits, tg_dev, tgt_offsets, il_dev, tl_dev, int(max_tgt_len),
+                           int(blank), bool(zero_infinity), float(grad_hint),
+                           grad_mode == "eager",
+                           None if reduce_scale is None else float(reduce_scale),
+                           peer if fused else None)
+    if peer is not None and not fused:
+        from .sharded import pack_sum
+
+        total = out.detach() if reduce_scale is not None else out.detach().sum()
+        inv = 1.0 / float(reduce_scale) if reduce_scale else 1.0
+        peer.exchange(pack_sum(total, inv, logits.shape[0]))
+    return out
 
 
 def forced_align(lp: torch.Tensor, target: torch.Tensor, blank: int = 0) -> torch.Tensor:

@@ -45,6 +45,17 @@ def pack_local(nll_local: torch.Tensor) -> torch.Tensor:
     return torch.addcmul(offs, scale, nll_local.float().sum() / max(n, 1))
 
 
+def pack_sum(total: torch.Tensor, mul: float, n_local: int) -> torch.Tensor:
+    """[total * mul, n_local] from a device scalar, one launch, no host round trip."""
+    key = ("sum", float(mul), int(n_local), str(total.device))
+    c = _CONST.get(key)
+    if c is None:
+        c = (torch.tensor([float(mul), 0.0], device=total.device),
+             torch.tensor([0.0, float(n_local)], device=total.device))
+        _CONST[key] = c
+    return torch.addcmul(c[1], c[0], total.float().reshape(()))
+
+
 def pack_local_mean(loss_mean: torch.Tensor, n_local: int) -> torch.Tensor:
     """Same pair from the rank-local batch mean that ``CTC.forward`` returns
     (espnet2/asr/ctc.py:56-60): [mean * n, n] in one launch, no host round trip."""
@@ -84,7 +95,12 @@ class PeerLossExchange:
     ``reduce_sharded_loss`` without a collective launch or any host work.
     """
 
-    def __init__(self, group=None, device=None):
+    def __init__(self, group=None, device=None, deferred: bool = True, timeout_s: float = 0.0):
+        """``deferred`` (default): the loss kernel only pushes this rank's pair; the wait for the
+        peers - a per-step barrier on the slowest rank that nothing on the device needs - happens
+        when ``out`` is read (and, for the previous step, at the start of the next exchange).
+        ``timeout_s``: how long a wait may last before it gives NaN + a sticky error flag
+        (0 = the library default, 30 s)."""
         import ctypes
 
         from ._lib import check, lib
@@ -106,21 +122,46 @@ class PeerLossExchange:
                 blob = mine
             buf = (ctypes.c_ubyte * len(blob)).from_buffer_copy(blob)
             check(lib().b200ctc_peer_connect(self.handle, buf), "peer_connect")
-        self.out = torch.zeros(2, dtype=torch.float32, device=self.device)
+            check(lib().b200ctc_peer_configure(self.handle, int(bool(deferred)),
+                                               int(round(timeout_s * 1000))), "peer_configure")
+        self.deferred = bool(deferred)
+        # written by the loss / exchange kernels; read it through ``out``
+        self.out_buffer = torch.zeros(2, dtype=torch.float32, device=self.device)
         if self.world > 1:
             dist.barrier(group=group)  # every rank has mapped every buffer before the first push
 
+    @property
+    def out(self) -> torch.Tensor:
+        """[global batch-weighted mean loss, total utterance count] of the LATEST exchange, valid on
+        the current stream.  In deferred mode reading it issues the (tiny) wait kernel there."""
+        if self.deferred:
+            from ._lib import check, lib, ptr, stream_ptr
+            with torch.cuda.device(self.device):
+                check(lib().b200ctc_peer_wait(self.handle, ptr(self.out_buffer),
+                                              stream_ptr(self.device)), "peer_wait")
+        return self.out_buffer
+
     def exchange(self, pair: torch.Tensor) -> torch.Tensor:
-        """Stand-alone collective on a device pair [sum, weight] (ranks without utterances)."""
+        """Stand-alone collective on a device pair [sum, weight]: ranks without utterances, and
+        calls that cannot use the fused form (no gradient wanted, deferred gradient mode)."""
         from ._lib import check, lib, ptr, stream_ptr
         pair = pair.to(device=self.device, dtype=torch.float32).contiguous()
-        check(lib().b200ctc_peer_exchange(self.handle, ptr(pair), ptr(self.out),
-                                          stream_ptr(self.device)), "peer_exchange")
-        return self.out
+        with torch.cuda.device(self.device):
+            check(lib().b200ctc_peer_exchange(self.handle, ptr(pair), ptr(self.out_buffer),
+                                              stream_ptr(self.device)), "peer_exchange")
+        return self.out_buffer
 
     def timed_out(self) -> bool:
+        """True if a wait ever ran into the time-out (synchronises the device)."""
         from ._lib import lib
         return lib().b200ctc_peer_error(self.handle) != 0
+
+    def raise_if_timed_out(self) -> None:
+        """Call at a natural synchronisation point (end of epoch, logging): a peer that never
+        showed up turned ``out`` into NaN; this makes it an exception."""
+        if self.timed_out():
+            raise RuntimeError("sharded CTC loss exchange: a rank did not push its loss within the "
+                               "time-out; `out` is NaN (see PeerLossExchange(timeout_s=...))")
 
     def close(self):
         from ._lib import lib

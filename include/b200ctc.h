@@ -136,7 +136,14 @@ int b200ctc_loss_fwd_grad(const void* logits, int dtype, const int64_t* targets,
  * (bit-identical on all ranks: summed in rank order).  Collective semantics:
  * every rank must make the same sequence of exchange calls; a rank with no
  * utterances calls b200ctc_peer_exchange({0,0}).  A peer that does not show up
- * within 5 s yields NaN and sets the sticky flag read by b200ctc_peer_error.  */
+ * within the time-out (default 30 s) yields NaN and sets the sticky flag read by
+ * b200ctc_peer_error.
+ * b200ctc_peer_configure(deferred = 1): loss_fwd_grad_sharded only PUSHES; the
+ * wait for the peers' words - a barrier on the slowest rank that nothing on the
+ * device needs inside the step - is done by the NEXT exchange call (for the
+ * previous step: its words arrived a step ago) and by b200ctc_peer_wait, which
+ * the caller issues on the stream where it reads global_out.  Ranks still stay
+ * within one step of each other.  timeout_ms = 0 keeps the default.           */
 typedef struct b200ctc_peer b200ctc_peer_t;
 int b200ctc_peer_create(int world, int rank, b200ctc_peer_t** out,
                         unsigned char* handle_out /* 64 bytes */);
@@ -144,6 +151,9 @@ int b200ctc_peer_connect(b200ctc_peer_t* peer,
                          const unsigned char* all_handles /* world*64 bytes, rank order */);
 int b200ctc_peer_destroy(b200ctc_peer_t* peer);
 int b200ctc_peer_error(b200ctc_peer_t* peer); /* synchronises; 1 = a peer timed out */
+int b200ctc_peer_configure(b200ctc_peer_t* peer, int deferred, int timeout_ms);
+/* consume the latest pushed step if still owed: global_out = its result        */
+int b200ctc_peer_wait(b200ctc_peer_t* peer, float* global_out, b200ctc_stream_t stream);
 /* stand-alone exchange of a device pair {sum, weight} (same collective)       */
 int b200ctc_peer_exchange(b200ctc_peer_t* peer, const float* local_pair,
                           float* global_out, b200ctc_stream_t stream);

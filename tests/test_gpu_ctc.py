@@ -167,3 +167,31 @@ def test_forward_multi_equals_sequential_calls():
         assert torch.equal(a, h.grad)
     torch.testing.assert_close(ctc.ctc_lo.weight.grad, gw[3], rtol=1e-5, atol=1e-6)
     assert len(ctc.forward_multi(hs[:1], hl, ys, yl)) == 1
+
+
+def test_upstream_scale_hint_matches_weighted_loss():
+    """`loss = ctc_weight * ctc(...)` (espnet2/asr/espnet_model.py): with `upstream_scale` set to the
+    weight the pre-scaled gradient needs no rescaling pass, without it the rescale makes it exact -
+    both must give the reference's gradient."""
+    from oracle import espnet_cpu
+
+    d = _dev()
+    g = torch.Generator().manual_seed(3)
+    Bn, T, D, V, w = 5, 60, 12, 40, 0.3
+    hs = torch.randn(Bn, T, D, generator=g)
+    hl = torch.tensor([60, 50, 60, 41, 33])
+    yl = torch.tensor([7, 3, 9, 1, 5])
+    ys = torch.randint(1, V, (Bn, 9), generator=g)
+    from espnet1_b200.espnet2.asr.ctc import CTC
+
+    m = CTC(V, D).to(d)
+    xr = hs.clone().requires_grad_(True)
+    ref = w * espnet_cpu.ctc_forward(xr, hl, ys, yl, m.ctc_lo.weight.detach().cpu(), m.ctc_lo.bias.detach().cpu())
+    ref.backward()
+    for scale in (1.0, w):
+        m.upstream_scale = scale
+        x = hs.to(d).requires_grad_(True)
+        loss = w * m(x, hl.to(d), ys.to(d), yl.to(d))
+        loss.backward()
+        close(loss, ref.detach().numpy(), LOSS_RTOL, 1e-6)
+        close(x.grad, xr.grad.numpy(), 0, GRAD_ATOL)

@@ -11,11 +11,12 @@ DEV = "cuda:0"
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def test_single_rank_exchange_is_the_local_mean():
+@pytest.mark.parametrize("deferred", [True, False])
+def test_single_rank_exchange_is_the_local_mean(deferred):
     from espnet1_b200 import functional as F
     from espnet1_b200.sharded import PeerLossExchange
 
-    ex = PeerLossExchange()
+    ex = PeerLossExchange(deferred=deferred)
     g = torch.Generator().manual_seed(3)
     x = (torch.randn(5, 30, 40, generator=g) * 2).to(DEV).requires_grad_(True)
     tl = torch.tensor([3, 5, 2, 7, 4]); il = torch.full((5,), 30)
@@ -23,12 +24,46 @@ def test_single_rank_exchange_is_the_local_mean():
     for _ in range(3):  # the step counter / parity slots are reused call after call
         loss = F.ctc_loss(x, tg, il, tl, reduce_scale=F._f32_recip(5), peer=ex)
         assert float(ex.out[1]) == 5.0
-        assert abs(float(ex.out[0]) - float(loss)) <= 1e-6 * abs(float(loss))
+        assert abs(float(ex.out[0]) - float(loss.detach())) <= 1e-6 * abs(float(loss.detach()))
     out = ex.exchange(torch.tensor([6.0, 3.0]))
     assert out.tolist() == [2.0, 3.0]
+    assert ex.out.tolist() == [2.0, 3.0]
+    # a call that cannot use the fused form (no gradient wanted: validation) makes the same
+    # collective through the stand-alone kernel instead of raising
+    with torch.no_grad():
+        nll = F.ctc_loss(x.detach(), tg, il, tl, peer=ex)
+    assert float(ex.out[1]) == 5.0
+    assert abs(float(ex.out[0]) - float(nll.mean())) <= 2e-6 * abs(float(nll.mean()))
+    lossd = F.ctc_loss(x, tg, il, tl, reduce_scale=F._f32_recip(5), peer=ex, grad_mode="deferred")
+    assert abs(float(ex.out[0]) - float(lossd.detach())) <= 2e-6 * abs(float(lossd.detach()))
     assert not ex.timed_out()
-    with pytest.raises(RuntimeError):  # needs the eager gradient path
-        F.ctc_loss(x.detach(), tg, il, tl, peer=ex)
+    ex.raise_if_timed_out()
+    ex.close()
+
+
+def test_deferred_exchange_reads_the_latest_step():
+    """Steps issued back to back WITHOUT reading `out` in between (the training loop): each
+    exchange consumes its predecessor first; reading `out` afterwards gives the LAST step."""
+    from espnet1_b200 import functional as F
+    from espnet1_b200.sharded import PeerLossExchange
+
+    ex = PeerLossExchange()  # deferred by default
+    assert ex.deferred
+    g = torch.Generator().manual_seed(4)
+    losses = []
+    for it in range(5):
+        Bn = 3 + it
+        x = (torch.randn(Bn, 25, 30, generator=g) * 2).to(DEV).requires_grad_(True)
+        tl = torch.randint(1, 6, (Bn,), generator=g)
+        il = torch.full((Bn,), 25)
+        tg = torch.randint(1, 30, (int(tl.sum()),), generator=g)
+        loss = F.ctc_loss(x, tg, il, tl, reduce_scale=F._f32_recip(Bn), peer=ex)
+        loss.backward()
+        losses.append((float(loss.detach()), Bn))
+    want, n = losses[-1]
+    got = ex.out.tolist()
+    assert got[1] == float(n) and abs(got[0] - want) <= 1e-6 * abs(want)
+    assert ex.out.tolist() == got  # idempotent: nothing left to consume
     ex.close()
 
 
