@@ -96,6 +96,39 @@ def check(rc: int, what: str = "") -> None:
         raise RuntimeError(f"libb200ctc {what} failed (status {rc}): {msg}")
 
 
+def _find_cuda_device(args):
+    for a in args:
+        if isinstance(a, torch.Tensor):
+            if a.is_cuda:
+                return a.device
+        elif isinstance(a, (list, tuple)) and a and isinstance(a[0], torch.Tensor) and a[0].is_cuda:
+            return a[0].device
+        else:
+            d = getattr(a, "device", None)  # a scorer object (self) that remembers its device
+            if isinstance(d, torch.device) and d.type == "cuda":
+                return d
+    return None
+
+
+def on_tensor_device(fn):
+    """Run ``fn`` with the CUDA device of its first CUDA tensor argument (or of ``self.device``)
+    current.  The library launches on the process's CURRENT device and takes the current stream
+    of the tensor's device: with tensors on cuda:1 and cuda:0 current (a model moved with
+    ``.to('cuda:1')`` and no ``set_device``) that would be device-1 pointers in a device-0
+    launch.  The previous device is restored on return."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapper(*args, **kwargs):
+        dev = _find_cuda_device(args)
+        if dev is not None and dev.index is not None and dev.index != torch.cuda.current_device():
+            with torch.cuda.device(dev):
+                return fn(*args, **kwargs)
+        return fn(*args, **kwargs)
+
+    return wrapper
+
+
 def stream_ptr(device) -> int:
     return torch.cuda.current_stream(device).cuda_stream
 

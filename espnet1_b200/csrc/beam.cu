@@ -76,9 +76,9 @@ __device__ __forceinline__ void segment_topk(const BeamScores& S, long long row0
       if (e < E) {
         float x = acc[j];
         if (run) x = __fadd_rn(x, __ldg(run + row[j]));
-        if (!(x == x)) x = kNegInf;  // NaN never wins
+        if (!(x == x)) x = kNegInf;  // NaN never wins (and NaN is free to mark retired winners)
         vals[e] = x;
-        if (x > bv) { bv = x; be = e; }
+        if (x > bv || (x == bv && e < be)) { bv = x; be = e; }  // -inf entries are candidates too
       }
     }
   }
@@ -105,14 +105,17 @@ __device__ __forceinline__ void segment_topk(const BeamScores& S, long long row0
       if (lane == 0) { res_v[r] = cv; res_e[r] = ce < E ? ce : 0; }
     }
     __syncthreads();
+    // retire the winner (NaN: compares false with everything, so it can never win again -
+    // also when the finite candidates are exhausted and -inf entries are being handed out:
+    // the k winners stay DISTINCT, lowest index first, like torch.topk) and rescan my share
     const int we = res_e[r];
-    if (res_v[r] > kNegInf && (we % NT) == tid) {  // retire the winner, rescan my share
-      vals[we] = kNegInf;
+    if ((we % NT) == tid) {
+      vals[we] = __int_as_float(0x7fc00000);
       bv = kNegInf;
       be = 0x7fffffff;
       for (int e = tid; e < E; e += NT) {
         const float x = vals[e];
-        if (x > bv) { bv = x; be = e; }
+        if (x > bv || (x == bv && e < be)) { bv = x; be = e; }
       }
     }
   }

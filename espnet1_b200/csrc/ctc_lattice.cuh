@@ -591,7 +591,7 @@ __global__ void __launch_bounds__(K == 16 ? 288 : 544, 1) lattice_kernel(
     UttInfo* __restrict__ utt, const int* __restrict__ lab, int Lp, const float* __restrict__ em,
     float* __restrict__ alpha, float* __restrict__ beta, int* __restrict__ offA,
     int* __restrict__ offB, int Tfr, int Sp, int NWp, int NB, int zero_infinity, int nring, int pdl,
-    SplitArgs sa, int* __restrict__ err, int lat_pol) {
+    SplitArgs sa, int* __restrict__ err, int lat_pol, int* __restrict__ tickets) {
   static_assert(R % 2 == 0, "R must be even: even recursion positions are blanks");
   extern __shared__ __align__(128) float lsm[];  // em ring [nring][K*Lp] | vals | fring | ready | cons
   __shared__ __align__(8) uint64_t bars[2 * kMaxEmRing];  // full[], empty[]
@@ -599,9 +599,21 @@ __global__ void __launch_bounds__(K == 16 ? 288 : 544, 1) lattice_kernel(
   uint64_t* const empty = bars + kMaxEmRing;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int NW = (blockDim.x >> 5) - 1;  // compute warps; warp NW is the TMA producer
-  // split: CTA cr of CL handles warps [cr*NW, (cr+1)*NW) of utterance b's lattice
-  const int b = SPLIT ? blockIdx.x / sa.CL : blockIdx.x, dir = blockIdx.y;
-  const int cr = SPLIT ? blockIdx.x - b * sa.CL : 0;
+  // split: CTA cr of CL handles warps [cr*NW, (cr+1)*NW) of utterance b's lattice.  A downstream
+  // CTA spin-waits on its upstream neighbour, so the logical position comes from a TICKET taken
+  // in dispatch order (one counter per direction, zeroed before the launch), not from
+  // blockIdx: whatever order the hardware starts CTAs in, a CTA only ever waits for CTAs that
+  // took an earlier ticket, i.e. that are already running or done (decoupled look-back's rule).
+  const int dir = blockIdx.y;
+  int bx = blockIdx.x;
+  if (SPLIT) {
+    __shared__ int s_ticket;
+    if (tid == 0) s_ticket = atomicAdd(tickets + dir, 1);
+    __syncthreads();
+    bx = s_ticket;
+  }
+  const int b = SPLIT ? bx / sa.CL : bx;
+  const int cr = SPLIT ? bx - b * sa.CL : 0;
   if (pdl == 0) griddep_launch();  // PDL: let the gradient row pass become resident behind us
   griddep_wait();                  // utt / lab / em come from the previous kernel
   const int Tb = utt[b].T, L = utt[b].L, S = 2 * L + 1;
@@ -803,7 +815,8 @@ static int launch_lattice_rk(const LossLayout& w, unsigned char* ws, int Tfr, in
                reinterpret_cast<const float*>(ws + w.em), reinterpret_cast<float*>(ws + w.alpha),
                reinterpret_cast<float*>(ws + w.beta), reinterpret_cast<int*>(ws + w.offA),
                reinterpret_cast<int*>(ws + w.offB), Tfr, w.Sp, w.NW, w.NB, zero_infinity, nring,
-               pdl_mode(), sa, reinterpret_cast<int*>(ws + w.err), lat_policy_host());
+               pdl_mode(), sa, reinterpret_cast<int*>(ws + w.err), lat_policy_host(),
+               static_cast<int*>(nullptr));
   };
   if (both_dirs) go(lattice_kernel<R, true, K, false>);
   else go(lattice_kernel<R, false, K, false>);
@@ -827,7 +840,8 @@ static int launch_lattice_split(const LossLayout& w, unsigned char* ws, int Tfr,
   const size_t nb = (size_t)w.B * 2 * (size_t)(w.CL - 1);
   // sentinel fill of the hand-off arrays (bnd_val and bnd_f are adjacent sections)
   if (cudaMemsetAsync(ws + w.bnd_val, 0xff, 4 * nb * w.Tb1, st) != cudaSuccess ||
-      cudaMemsetAsync(ws + w.bnd_f, 0x80, 4 * nb * w.NB, st) != cudaSuccess) {
+      cudaMemsetAsync(ws + w.bnd_f, 0x80, 4 * nb * w.NB, st) != cudaSuccess ||
+      cudaMemsetAsync(ws + w.split_tickets, 0, 2 * sizeof(int), st) != cudaSuccess) {
     set_error("ctc lattice (split): memset failed");
     return B200CTC_ERR_DEVICE;
   }
@@ -842,7 +856,8 @@ static int launch_lattice_split(const LossLayout& w, unsigned char* ws, int Tfr,
                reinterpret_cast<const float*>(ws + w.em), reinterpret_cast<float*>(ws + w.alpha),
                reinterpret_cast<float*>(ws + w.beta), reinterpret_cast<int*>(ws + w.offA),
                reinterpret_cast<int*>(ws + w.offB), Tfr, w.Sp, w.NW, w.NB, zero_infinity, nring,
-               pdl_mode(), sa, reinterpret_cast<int*>(ws + w.err), lat_policy_host());
+               pdl_mode(), sa, reinterpret_cast<int*>(ws + w.err), lat_policy_host(),
+               reinterpret_cast<int*>(ws + w.split_tickets));
   };
   if (both_dirs) go(lattice_kernel<R, true, K, true>);
   else go(lattice_kernel<R, false, K, true>);

@@ -59,6 +59,7 @@ struct LossLayout {
   // sync words: {role ticket, sticky error} then the per-(utterance, group) gather flags -
   // adjacent, so that one memset clears them (ctc_fused.cuh)
   size_t ticket, err, flags;
+  size_t split_tickets;  // two ints: dispatch-order tickets of the split lattice, per direction
   size_t bnd_val, bnd_f, bnd_ready;  // [B][2][CL-1] x {Tb1 floats, NB ints, 8 ints}
 };
 // sticky error word of a loss workspace (LossLayout::err; 0 = none).  A kernel that gives up
@@ -125,6 +126,7 @@ inline LossLayout make_loss_layout(int B, int T, int V, int Lmax) {
   if (w.NG < 1) w.NG = 1;
   w.ticket = take(256);
   w.err = w.ticket + 4;
+  w.split_tickets = w.ticket + 8;
   w.flags = take(4 * (size_t)B * w.NG);
   w.utt = take(sizeof(UttInfo) * (size_t)B);
   w.lab = take(4 * (size_t)B * w.Lp);

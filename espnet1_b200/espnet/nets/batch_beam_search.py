@@ -110,11 +110,40 @@ class BatchBeamSearch(torch.nn.Module):
     def forward_batch(self, xs: torch.Tensor, xlens, maxlenratio: float = 0.0) -> List[List[Hypothesis]]:
         """N-best lists of several utterances ``xs (U, Tmax, D)`` decoded together; each list
         equals ``forward(xs[u, :xlens[u]])``.  Partial scorers must offer the batched-state
-        API of :class:`..scorers.ctc.CTCPrefixScorer`; full scorers see padded ``xs`` rows."""
+        API of :class:`..scorers.ctc.CTCPrefixScorer`.  Full scorers never see padding frames
+        unless they ask for them (see :meth:`_score_full`)."""
         lens = [int(v) for v in (xlens.tolist() if isinstance(xlens, torch.Tensor) else xlens)]
         return self._decode(xs, lens, maxlenratio)
 
     # ------------------------------------------------------------- internals
+    @staticmethod
+    def _score_full(d, yseq, states, xs, xs_rep, lens, W):
+        """``d.batch_score`` of a full scorer for all slots.  With several utterances of
+        DIFFERENT lengths the rows of ``xs`` are padded: a scorer that looks at the encoder output
+        (an attention decoder) must not see the padding frames, or its scores differ from
+        decoding the utterance alone.  So, unless the scorer declares that it ignores ``xs``
+        (``ignores_x = True``, e.g. a length bonus or an LM) or masks the padding itself
+        (``batch_score_padded(ys, states, xs, xlens)``), every utterance is scored on its own
+        unpadded frames - exactly what ``forward(xs[u, :xlens[u]])`` does."""
+        U = len(lens)
+        if U == 1 or min(lens) == xs.shape[1] or getattr(d, "ignores_x", False):
+            return d.batch_score(yseq, states, xs_rep)
+        if hasattr(d, "batch_score_padded"):
+            xl = torch.tensor(lens, device=xs.device).repeat_interleave(W)
+            return d.batch_score_padded(yseq, states, xs_rep, xl)
+        outs, new_states = [], []
+        for u in range(U):
+            sl = slice(u * W, (u + 1) * W)
+            xu = xs[u, : lens[u]].unsqueeze(0).expand(W, *xs[u, : lens[u]].shape)
+            sc_u, st_u = d.batch_score(yseq[sl], states[sl], xu)
+            outs.append(sc_u)
+            new_states.append(st_u)
+        if all(st is None for st in new_states):
+            merged = None
+        else:
+            merged = [st for st_u in new_states for st in (st_u if st_u is not None else [None] * W)]
+        return torch.cat(outs, dim=0), merged
+
     def _maxlen(self, T: int, maxlenratio: float) -> int:
         if maxlenratio == 0:
             return T
@@ -181,7 +210,7 @@ class BatchBeamSearch(torch.nn.Module):
             step_sc: Dict[str, torch.Tensor] = {}
             new_full: Dict[str, Any] = {}
             for k, d in self.full_scorers.items():
-                step_sc[k], new_full[k] = d.batch_score(yseq, full_states[k], xs_rep)
+                step_sc[k], new_full[k] = self._score_full(d, yseq, full_states[k], xs, xs_rep, lens, W)
                 if not fused:
                     w += self.weights[k] * step_sc[k]
                 elif step_sc[k].dtype != torch.float32:

@@ -11,13 +11,14 @@ from __future__ import annotations
 
 import torch
 
-from ..._lib import check, lib, ptr, require_cuda, stream_ptr
+from ..._lib import check, lib, on_tensor_device, ptr, require_cuda, stream_ptr
 
 
 class CTCPrefixScoreTH(object):
     """Batch processing of CTCPrefixScore (Watanabe et al. 2017, Algorithm 2;
     Seki et al. 2019) on the GPU."""
 
+    @on_tensor_device
     def __init__(self, x, xlens, blank, eos, margin=0):
         """Construct CTC prefix scorer
 
@@ -50,6 +51,7 @@ class CTCPrefixScoreTH(object):
         self.scoring_num = 0
 
     # -- log-prob storage -------------------------------------------------
+    @on_tensor_device
     def _set_lp(self, x, pad):
         B, T, V = x.shape
         inplace = x.dtype == torch.float32 and x.is_contiguous()
@@ -62,6 +64,7 @@ class CTCPrefixScoreTH(object):
         self._lp = lp
         self._lp_t = None  # (B, V, T) time-contiguous copy, made on the first pre-beam step
 
+    @on_tensor_device
     def _time_contiguous(self):
         if self._lp_t is None:
             B, T, V = self._lp.shape
@@ -79,6 +82,7 @@ class CTCPrefixScoreTH(object):
         return torch.stack([xn, xb]).to(self.dtype)
 
     # -- scoring ----------------------------------------------------------
+    @on_tensor_device
     def __call__(self, y, state, scoring_ids=None, att_w=None):
         """Compute CTC prefix scores for next labels
 
@@ -150,6 +154,7 @@ class CTCPrefixScoreTH(object):
             scores, r, log_psi = scores.to(self.dtype), r.to(self.dtype), log_psi.to(self.dtype)
         return scores, (r, log_psi, f_min, f_max, idmap)
 
+    @on_tensor_device
     def index_select_state(self, state, best_ids):
         """Select CTC states according to best ids
 
@@ -175,6 +180,7 @@ class CTCPrefixScoreTH(object):
         return r_new, s_new, f_min, f_max
 
     # -- streaming (:222-269), batch == 1 ---------------------------------
+    @on_tensor_device
     def extend_prob(self, x):
         """Extend CTC prob.
 
@@ -195,6 +201,7 @@ class CTCPrefixScoreTH(object):
                 self.frame_ids = torch.arange(self.input_length, dtype=self.dtype,
                                               device=self.device)
 
+    @on_tensor_device
     def extend_state(self, state):
         """Compute CTC prefix state for the extended input (blank running sum).
 

@@ -11,7 +11,7 @@ from __future__ import annotations
 
 import torch
 
-from ...._lib import check, lib, ptr, stream_ptr
+from ...._lib import check, lib, on_tensor_device, ptr, stream_ptr
 from ..ctc_prefix_score import CTCPrefixScoreTH
 from ..scorer_interface import BatchPartialScorerInterface
 
@@ -37,6 +37,7 @@ class CTCPrefixScorer(BatchPartialScorerInterface):
         self.impl = CTCPrefixScoreTH(logp, xlen, 0, self.eos)
 
     # ---- per-hypothesis API (BeamSearch) --------------------------------
+    @on_tensor_device
     def init_state(self, x: torch.Tensor):
         """Initial state for non-batched decoding: (prev_score, r (T,2))."""
         self._make_impl(x)

@@ -11,6 +11,8 @@ from ..scorer_interface import BatchScorerInterface
 class LengthBonus(BatchScorerInterface):
     """Length bonus in beam search."""
 
+    ignores_x = True  # BatchBeamSearch.forward_batch: no need to hide padding frames from it
+
     def __init__(self, n_vocab: int):
         self.n = n_vocab
         self._one = {}  # (device, dtype) -> the constant, made once (the reference uploads it every call)

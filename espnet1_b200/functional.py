@@ -9,7 +9,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import check, dtype_code, lib, ptr, require_cuda, stream_ptr
+from ._lib import check, dtype_code, lib, on_tensor_device, ptr, require_cuda, stream_ptr
 
 
 def _rows(x: torch.Tensor):
@@ -19,6 +19,7 @@ def _rows(x: torch.Tensor):
 
 class _SoftmaxFn(torch.autograd.Function):
     @staticmethod
+    @on_tensor_device
     def forward(ctx, x, mode):
         require_cuda(x, "softmax input")
         xc = x.contiguous()
@@ -31,6 +32,7 @@ class _SoftmaxFn(torch.autograd.Function):
         return y
 
     @staticmethod
+    @on_tensor_device
     def backward(ctx, dy):
         (y,) = ctx.saved_tensors
         dyc = dy.contiguous()
@@ -51,6 +53,7 @@ def softmax(x: torch.Tensor) -> torch.Tensor:
     return _SoftmaxFn.apply(x, 1)
 
 
+@on_tensor_device
 def argmax(x: torch.Tensor) -> torch.Tensor:
     """argmax over the last dim, int64, first-max tie rule (espnet2/asr/ctc.py:127)."""
     require_cuda(x, "argmax input")
@@ -62,6 +65,7 @@ def argmax(x: torch.Tensor) -> torch.Tensor:
     return out
 
 
+@on_tensor_device
 def greedy_decode(logits: torch.Tensor, in_lens=None, blank: int = 0):
     """Best-path decode: (ids (B,T) padded with -1, lens (B,))."""
     require_cuda(logits, "greedy_decode input")
@@ -96,6 +100,7 @@ class _CTCLossFn(torch.autograd.Function):
     gradient row pass with the real upstream gradient."""
 
     @staticmethod
+    @on_tensor_device
     def forward(ctx, logits, targets, tgt_offsets, in_lens, tgt_lens, max_tgt_len, blank,
                 zero_infinity, grad_hint, eager, reduce_scale, peer=None):
         require_cuda(logits, "CTC logits")
@@ -142,6 +147,7 @@ class _CTCLossFn(torch.autograd.Function):
         return loss if reduced else nll
 
     @staticmethod
+    @on_tensor_device
     def backward(ctx, g):
         none10 = (None,) * 11
         gs, stride = _upstream(g)
@@ -221,6 +227,7 @@ def ctc_loss(logits, targets, in_lens, tgt_lens, blank: int = 0, zero_infinity: 
     return out
 
 
+@on_tensor_device
 def forced_align(lp: torch.Tensor, target: torch.Tensor, blank: int = 0) -> torch.Tensor:
     """Viterbi alignment of one utterance; lp (T,V) fp32 log-probs, target (L,)."""
     require_cuda(lp, "forced_align input")
@@ -256,6 +263,7 @@ def _score_args(mats, weights):
     return ptrs, strides, ws, K
 
 
+@on_tensor_device
 def beam_prebeam(mats, weights, k: int) -> torch.Tensor:
     """Top-k token ids (n, k) of every row of ``sum_q weights[q] * mats[q]`` (pre-beam)."""
     ptrs, strides, ws, K = _score_args(mats, weights)
@@ -266,6 +274,7 @@ def beam_prebeam(mats, weights, k: int) -> torch.Tensor:
     return out
 
 
+@on_tensor_device
 def beam_select(mats, weights, run_score, cum_in, yseq_in, cur_len, active, maxlen, step_i,
                 U: int, W: int, k: int, eos: int, yseq_out):
     """One fused pruning step (include/b200ctc.h ``b200ctc_beam_select``).

@@ -75,3 +75,42 @@ def test_two_ranks_match_the_nccl_allreduce():
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=240, cwd=ROOT)
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
     assert out.stdout.count("ok") == 2
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_tensors_on_a_non_current_device():
+    """tensors on cuda:1 while cuda:0 is the current device (a model moved with
+    .to('cuda:1'), no set_device).  Every wrapper must launch on the TENSOR's device."""
+    import numpy as np
+
+    from espnet1_b200 import functional as F
+    from espnet1_b200.espnet.nets.ctc_prefix_score import CTCPrefixScoreTH
+    from oracle import espnet_cpu
+    from oracle.prefix_torch import PrefixOracle
+
+    torch.cuda.set_device(0)
+    d1 = torch.device("cuda", 1)
+    g = torch.Generator().manual_seed(12)
+    logits = torch.randn(4, 50, 64, generator=g) * 2
+    tl = torch.tensor([5, 9, 3, 7]); il = torch.tensor([50, 44, 50, 39])
+    tg = torch.randint(1, 64, (int(tl.sum()),), generator=g)
+    x = logits.to(d1).requires_grad_(True)
+    nll = F.ctc_loss(x, tg, il, tl)
+    (nll.sum() / 4).backward()
+    rn, rg = espnet_cpu.logits_loss_and_grad(logits, tg, il, tl)
+    np.testing.assert_allclose(nll.detach().cpu().numpy(), rn.numpy(), rtol=1e-5)
+    np.testing.assert_allclose(x.grad.cpu().numpy(), rg.numpy(), rtol=0, atol=1e-4)
+    assert x.grad.device == d1 and torch.cuda.current_device() == 0
+    y = F.log_softmax(logits.to(d1))
+    np.testing.assert_allclose(y.cpu().numpy(), torch.log_softmax(logits, -1).numpy(), rtol=1e-5, atol=1e-6)
+    assert torch.equal(F.argmax(logits.to(d1)).cpu(), logits.argmax(-1))
+    lpz = torch.log_softmax(logits, -1)
+    xl = torch.tensor([50, 44, 50, 39])
+    sc = CTCPrefixScoreTH(lpz.clone().to(d1), xl, 0, 63)
+    ora = PrefixOracle(lpz.clone(), xl, 0, 63)
+    yy = [[63] for _ in range(8)]
+    ids = torch.randint(1, 63, (8, 6), generator=g)
+    got, _ = sc(yy, None, ids.to(d1))
+    want, _ = ora.score(yy, None, ids)
+    np.testing.assert_allclose(got.cpu().numpy(), want.numpy(), rtol=2e-6, atol=2e-5)
+    assert torch.cuda.current_device() == 0
