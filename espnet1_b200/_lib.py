@@ -42,6 +42,9 @@ SIGNATURES = {
     "b200ctc_loss_fwd_grad_sharded": (c_int, [_P, c_int, _P, _P, _P, _P, c_int, c_int, c_int, c_int,
                                               c_int, c_int, c_float, _P, _P, c_float, _P, _P,
                                               c_size_t, _P, _P, _P]),
+    "b200ctc_loss_fwd_grad_hints": (c_int, [_P, c_int, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int,
+                                            c_int, _P, _P, _P, _P, c_size_t, _P]),
+    "b200ctc_grad_rescale_hints": (c_int, [_P, c_int, _P, c_int, c_float, _P, c_int, c_int, c_int, _P]),
     "b200ctc_peer_create": (c_int, [c_int, c_int, _P, _P]),
     "b200ctc_peer_connect": (c_int, [_P, _P]),
     "b200ctc_peer_destroy": (c_int, [_P]),
@@ -57,10 +60,10 @@ SIGNATURES = {
     "b200ctc_prefix_pad": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_float, _P]),
     "b200ctc_prefix_init_state": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, c_float, _P, _P]),
     "b200ctc_prefix_window": (c_int, [_P, c_int, c_int, _P, _P]),
-    "b200ctc_prefix_transpose": (c_int, [_P, _P, c_int, c_int, c_int, _P]),
+    "b200ctc_prefix_transpose": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_int, _P]),
     "b200ctc_prefix_step": (c_int, [_P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int,
                                     c_int, c_int, c_int, c_int, c_int, c_float, _P, _P, _P, _P,
-                                    _P, _P]),
+                                    _P, c_int, _P]),
     "b200ctc_prefix_select": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int,
                                       _P, _P, _P]),
     "b200ctc_beam_prebeam": (c_int, [_P, _P, _P, c_int, c_int64, c_int, c_int, _P, _P]),

@@ -628,10 +628,12 @@ int launch_grad_rows(const void* logits, int dtype, void* grad, int B, int T, in
 template <typename T>
 __global__ void __launch_bounds__(256) rescale_kernel(T* __restrict__ grad, int64_t per_utt,
                                                       const float* __restrict__ gscale,
-                                                      int gstride, float gmul, float hint) {
+                                                      int gstride, float gmul, float hint0,
+                                                      const float* __restrict__ hints) {
   constexpr int N = Elems<T>::N;
   const int b = blockIdx.y;
   const float gv = gscale[(size_t)b * gstride] * gmul;
+  const float hint = hints ? hints[b] : hint0;
   if (gv == hint) return;
   const float ratio = gv / hint;
   T* base = grad + (size_t)b * per_utt;
@@ -683,37 +685,54 @@ extern "C" int b200ctc_loss_bwd(const void* logits, int dtype, const int64_t* in
   return rc;
 }
 
-extern "C" int b200ctc_grad_rescale(void* grad, int dtype, const float* gscale, int gscale_stride,
-                                    float gscale_mul, float grad_hint, int B, int T, int V,
-                                    b200ctc_stream_t stream) {
+static int grad_rescale_impl(void* grad, int dtype, const float* gscale, int gscale_stride,
+                             float gscale_mul, float grad_hint, const float* utt_hints, int B, int T,
+                             int V, b200ctc_stream_t stream) {
   B2_REQUIRE(B >= 0 && T >= 0 && V > 0, "grad_rescale: bad shape");
   if (B == 0 || T == 0) return B200CTC_OK;
   B2_REQUIRE(grad && gscale, "grad_rescale: null pointer");
   B2_REQUIRE(dtype >= 0 && dtype <= 2, "grad_rescale: unknown dtype %d", dtype);
   B2_REQUIRE(gscale_stride == 0 || gscale_stride == 1, "grad_rescale: gscale_stride must be 0 or 1");
-  B2_REQUIRE(grad_hint != 0.f && grad_hint == grad_hint, "grad_rescale: grad_hint must be non-zero");
+  B2_REQUIRE(utt_hints || (grad_hint != 0.f && grad_hint == grad_hint),
+             "grad_rescale: grad_hint must be non-zero");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int64_t per_utt = (int64_t)T * V;
   int gx = (2 * sm_count() + B - 1) / B;
   if (gx < 1) gx = 1;
   dim3 grid(gx, B);
-  const float inv = grad_hint;
   prof_mark(6, 0, st);
   switch (dtype) {
     case B200CTC_F32:
       rescale_kernel<float><<<grid, 256, 0, st>>>(static_cast<float*>(grad), per_utt, gscale,
-                                                  gscale_stride, gscale_mul, inv);
+                                                  gscale_stride, gscale_mul, grad_hint, utt_hints);
       break;
     case B200CTC_F16:
       rescale_kernel<__half><<<grid, 256, 0, st>>>(static_cast<__half*>(grad), per_utt, gscale,
-                                                   gscale_stride, gscale_mul, inv);
+                                                   gscale_stride, gscale_mul, grad_hint, utt_hints);
       break;
     default:
-      rescale_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(static_cast<__nv_bfloat16*>(grad),
-                                                          per_utt, gscale, gscale_stride, gscale_mul, inv);
+      rescale_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(static_cast<__nv_bfloat16*>(grad), per_utt,
+                                                          gscale, gscale_stride, gscale_mul, grad_hint,
+                                                          utt_hints);
       break;
   }
   prof_mark(6, 1, st);
   count_launch();
   return check_launch("ctc grad_rescale");
+}
+
+extern "C" int b200ctc_grad_rescale(void* grad, int dtype, const float* gscale, int gscale_stride,
+                                    float gscale_mul, float grad_hint, int B, int T, int V,
+                                    b200ctc_stream_t stream) {
+  return grad_rescale_impl(grad, dtype, gscale, gscale_stride, gscale_mul, grad_hint, nullptr, B, T, V,
+                           stream);
+}
+
+extern "C" int b200ctc_grad_rescale_hints(void* grad, int dtype, const float* gscale,
+                                          int gscale_stride, float gscale_mul,
+                                          const float* utt_hints, int B, int T, int V,
+                                          b200ctc_stream_t stream) {
+  B2_REQUIRE(utt_hints || B == 0, "grad_rescale_hints: null utt_hints");
+  return grad_rescale_impl(grad, dtype, gscale, gscale_stride, gscale_mul, 0.f, utt_hints, B, T, V,
+                           stream);
 }

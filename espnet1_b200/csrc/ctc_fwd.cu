@@ -523,7 +523,7 @@ static int loss_fwd_grad_impl(const void* logits, int dtype, const int64_t* targ
                               int blank, int zero_infinity, float grad_hint, float* nll,
                               float* loss_out, float loss_scale, void* grad, void* ws_,
                               size_t ws_bytes, b200ctc_stream_t stream, b200ctc_peer* peer,
-                              float* global_out) {
+                              float* global_out, const float* utt_hints = nullptr) {
   PeerDev pd{nullptr, 0, 0, 0, 0};
   if (peer) {
     B2_REQUIRE(peer->connected, "loss_fwd_grad_sharded: peer handle is not connected");
@@ -536,7 +536,8 @@ static int loss_fwd_grad_impl(const void* logits, int dtype, const int64_t* targ
                            B, T, V, max_tgt_len, blank, nll, ws_, ws_bytes, &w);
   if (rc || B == 0) return rc;
   B2_REQUIRE(grad || T == 0, "loss_fwd_grad: null grad");
-  B2_REQUIRE(grad_hint != 0.f && grad_hint == grad_hint, "loss_fwd_grad: grad_hint must be non-zero");
+  B2_REQUIRE(utt_hints || (grad_hint != 0.f && grad_hint == grad_hint),
+             "loss_fwd_grad: grad_hint must be non-zero");
   unsigned char* ws = static_cast<unsigned char*>(ws_);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   PrepArgs P = make_prep_args(w, ws, targets, tgt_offsets, in_lens, tgt_lens, blank);
@@ -595,7 +596,9 @@ static int loss_fwd_grad_impl(const void* logits, int dtype, const int64_t* targ
   if (rc) return rc;
   if (T > 0) {
     prof_mark(3, 0, st);
-    rc = launch_grad_rows(logits, dtype, grad, B, T, V, blank, w, ws, nullptr, 0, grad_hint, true, st);
+    // the expected upstream gradient is baked into the gradient: one scalar, or one per utterance
+    rc = utt_hints ? launch_grad_rows(logits, dtype, grad, B, T, V, blank, w, ws, utt_hints, 1, 1.f, true, st)
+                   : launch_grad_rows(logits, dtype, grad, B, T, V, blank, w, ws, nullptr, 0, grad_hint, true, st);
     prof_mark(3, 1, st);
     if (rc) return rc;
   }
@@ -626,4 +629,17 @@ extern "C" int b200ctc_loss_fwd_grad_sharded(const void* logits, int dtype, cons
   return loss_fwd_grad_impl(logits, dtype, targets, tgt_offsets, in_lens, tgt_lens, B, T, V,
                             max_tgt_len, blank, zero_infinity, grad_hint, nll, loss_out, loss_scale,
                             grad, ws, ws_bytes, stream, peer, global_out);
+}
+
+// per-utterance hints (several CTC heads with different loss weights in ONE batched call)
+extern "C" int b200ctc_loss_fwd_grad_hints(const void* logits, int dtype, const int64_t* targets,
+                                           const int64_t* tgt_offsets, const int64_t* in_lens,
+                                           const int64_t* tgt_lens, int B, int T, int V,
+                                           int max_tgt_len, int blank, int zero_infinity,
+                                           const float* utt_hints, float* nll, void* grad, void* ws,
+                                           size_t ws_bytes, b200ctc_stream_t stream) {
+  B2_REQUIRE(utt_hints || B == 0, "loss_fwd_grad_hints: null utt_hints");
+  return loss_fwd_grad_impl(logits, dtype, targets, tgt_offsets, in_lens, tgt_lens, B, T, V,
+                            max_tgt_len, blank, zero_infinity, 0.f, nll, nullptr, 0.f, grad, ws,
+                            ws_bytes, stream, nullptr, nullptr, utt_hints);
 }

@@ -25,19 +25,20 @@ __device__ __forceinline__ float lse2_mufu(float a, float b) {
 }
 
 // (B,T,V) -> (B,V,T) tiled transpose (32x32 tiles through shared memory)
+// frames [tfirst, T) only; `ld` = time stride of the copy (>= T: room for streaming appends)
 __global__ void __launch_bounds__(256) prefix_transpose_kernel(const float* __restrict__ in,
                                                                float* __restrict__ out, int T,
-                                                               int V) {
+                                                               int V, int tfirst, int ld) {
   __shared__ float tile[32][33];
-  const int b = blockIdx.z, v0 = blockIdx.x * 32, t0 = blockIdx.y * 32;
+  const int b = blockIdx.z, v0 = blockIdx.x * 32, t0 = tfirst + blockIdx.y * 32;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 8 rows per pass
   const float* src = in + (size_t)b * T * V;
-  float* dst = out + (size_t)b * V * T;
+  float* dst = out + (size_t)b * V * ld;
   for (int r = ty; r < 32; r += 8)
     if (t0 + r < T && v0 + tx < V) tile[r][tx] = src[(size_t)(t0 + r) * V + v0 + tx];
   __syncthreads();
   for (int r = ty; r < 32; r += 8)
-    if (v0 + r < V && t0 + tx < T) dst[(size_t)(v0 + r) * T + t0 + tx] = tile[tx][r];
+    if (v0 + r < V && t0 + tx < T) dst[(size_t)(v0 + r) * ld + t0 + tx] = tile[tx][r];
 }
 
 // frames t >= xlens[b]: every label logzero, blank 0   (:47-50)
@@ -148,7 +149,7 @@ __global__ void __launch_bounds__(128) prefix_step_kernel(
     const int64_t* __restrict__ last_ids, const int64_t* __restrict__ scoring_ids,
     const int64_t* __restrict__ end_frames, int n_bh, int n_hyps, int T, int V, int snum,
     int out_len, int start, int end, int blank, int eos, float logzero, float* __restrict__ r,
-    float* __restrict__ log_psi, float* __restrict__ scores, int64_t* __restrict__ idmap) {
+    float* __restrict__ log_psi, float* __restrict__ scores, int64_t* __restrict__ idmap, int ldt) {
   const size_t idx = (size_t)blockIdx.x * 128 + threadIdx.x;
   if (idx >= (size_t)n_bh * snum) return;
   const int h = (int)(idx / snum);
@@ -157,8 +158,8 @@ __global__ void __launch_bounds__(128) prefix_step_kernel(
   const bool same = (k == (int)last_ids[h]);
   // per-frame input streams: x_t[k], x_t[blank], phi_{t-1} (= r^b_prev if k repeats the
   // last label, else logsumexp(r^n_prev, r^b_prev), :132-141) with their strides over t
-  const float* xk = TC ? lp_t + ((size_t)b * V + k) * T : lp + (size_t)b * T * V + k;
-  const float* xb = TC ? lp_t + ((size_t)b * V + blank) * T : lp + (size_t)b * T * V + blank;
+  const float* xk = TC ? lp_t + ((size_t)b * V + k) * ldt : lp + (size_t)b * T * V + k;
+  const float* xb = TC ? lp_t + ((size_t)b * V + blank) * ldt : lp + (size_t)b * T * V + blank;
   const size_t xs = TC ? 1 : (size_t)V;
   const float* ph = same ? r_prev + n_bh + h : rsum + h;
   const size_t phs = same ? 2 * (size_t)n_bh : (size_t)n_bh;
@@ -315,14 +316,17 @@ extern "C" int b200ctc_prefix_window(const float* att_w, int n_bh, int T, float*
   return check_launch("prefix_window");
 }
 
-extern "C" int b200ctc_prefix_transpose(const float* lp, float* lp_t, int B, int T, int V,
-                                        b200ctc_stream_t stream) {
+extern "C" int b200ctc_prefix_transpose(const float* lp, float* lp_t, int B, int T, int V, int t0,
+                                        int lp_t_ld, b200ctc_stream_t stream) {
   B2_REQUIRE(lp && lp_t, "prefix_transpose: null pointer");
   B2_REQUIRE(B >= 0 && T >= 0 && V > 0, "prefix_transpose: bad shape");
-  if (B == 0 || T == 0) return B200CTC_OK;
-  B2_REQUIRE(B <= 65535 && (T + 31) / 32 <= 65535, "prefix_transpose: shape too large");
-  prefix_transpose_kernel<<<dim3((V + 31) / 32, (T + 31) / 32, B), 256, 0,
-                            static_cast<cudaStream_t>(stream)>>>(lp, lp_t, T, V);
+  B2_REQUIRE(t0 >= 0 && t0 <= T && lp_t_ld >= T, "prefix_transpose: bad range t0=%d T=%d ld=%d", t0, T,
+             lp_t_ld);
+  if (B == 0 || T == t0) return B200CTC_OK;
+  const int nt = T - t0;
+  B2_REQUIRE(B <= 65535 && (nt + 31) / 32 <= 65535, "prefix_transpose: shape too large");
+  prefix_transpose_kernel<<<dim3((V + 31) / 32, (nt + 31) / 32, B), 256, 0,
+                            static_cast<cudaStream_t>(stream)>>>(lp, lp_t, T, V, t0, lp_t_ld);
   count_launch();
   return check_launch("prefix_transpose");
 }
@@ -333,9 +337,11 @@ extern "C" int b200ctc_prefix_step(const float* lp, const float* lp_t, const flo
                                    const int64_t* end_frames, int B, int n_hyps, int T, int V,
                                    int snum, int out_len, int start, int end, int blank, int eos,
                                    float logzero, float* r, float* log_psi, float* scores,
-                                   int64_t* idmap, float* rsum_ws, b200ctc_stream_t stream) {
+                                   int64_t* idmap, float* rsum_ws, int lp_t_ld,
+                                   b200ctc_stream_t stream) {
   B2_REQUIRE(lp && r_prev && last_ids && end_frames && r && log_psi && scores && rsum_ws,
              "prefix_step: null pointer");
+  B2_REQUIRE(!lp_t || lp_t_ld >= T, "prefix_step: lp_t_ld=%d < T=%d", lp_t_ld, T);
   B2_REQUIRE(B > 0 && n_hyps > 0 && T > 0 && V > 0 && snum > 0, "prefix_step: bad shape");
   B2_REQUIRE(scoring_ids ? idmap != nullptr : snum == V,
              "prefix_step: scoring_ids/idmap/snum mismatch (snum=%d V=%d)", snum, V);
@@ -355,11 +361,11 @@ extern "C" int b200ctc_prefix_step(const float* lp, const float* lp_t, const flo
   if (lp_t && scoring_ids)
     prefix_step_kernel<true><<<blocks((size_t)n_bh * snum, 128), 128, 0, st>>>(
         lp, lp_t, r_prev, rsum_ws, s_prev, last_ids, scoring_ids, end_frames, n_bh, n_hyps, T, V,
-        snum, out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap);
+        snum, out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap, lp_t_ld);
   else
     prefix_step_kernel<false><<<blocks((size_t)n_bh * snum, 128), 128, 0, st>>>(
         lp, lp_t, r_prev, rsum_ws, s_prev, last_ids, scoring_ids, end_frames, n_bh, n_hyps, T, V,
-        snum, out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap);
+        snum, out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap, lp_t_ld);
   count_launch();
   prof_mark(4, 1, st);
   return check_launch("prefix_step");

@@ -62,15 +62,29 @@ class CTCPrefixScoreTH(object):
             if not inplace:  # keep the reference's side effect on the caller's tensor (:47-50)
                 x.copy_(lp.to(x.dtype))
         self._lp = lp
-        self._lp_t = None  # (B, V, T) time-contiguous copy, made on the first pre-beam step
+        self._lp_store = None  # streaming (extend_prob): (1, Tcap, V) buffer that _lp is a view of
+        # (B, V, ld) time-contiguous copy, made on the first pre-beam step; frames [0, _lp_t_T)
+        # of it are valid.  ld > T once extend_prob has given it headroom.
+        self._lp_t = None
+        self._lp_t_T = 0
 
     @on_tensor_device
     def _time_contiguous(self):
-        if self._lp_t is None:
-            B, T, V = self._lp.shape
-            self._lp_t = torch.empty(B, V, T, dtype=torch.float32, device=self.device)
+        B, T, V = self._lp.shape
+        if self._lp_t is None or self._lp_t.shape[2] < T:
+            old, t_old = self._lp_t, self._lp_t_T
+            # streaming grows by chunks: geometric headroom makes the appends O(new frames)
+            ld = T if self._lp_store is None else max(T, int(1.5 * T) + 32)
+            self._lp_t = torch.empty(B, V, ld, dtype=torch.float32, device=self.device)
+            if old is not None and t_old > 0:
+                self._lp_t[:, :, :t_old] = old[:, :, :t_old]
+            else:
+                self._lp_t_T = 0
+        if self._lp_t_T < T:  # transpose only the frames that are new
             check(lib().b200ctc_prefix_transpose(ptr(self._lp), ptr(self._lp_t), B, T, V,
+                                                 self._lp_t_T, self._lp_t.shape[2],
                                                  stream_ptr(self.device)), "prefix_transpose")
+            self._lp_t_T = T
         return self._lp_t
 
     @property
@@ -145,11 +159,12 @@ class CTCPrefixScoreTH(object):
         scores = torch.empty(n_bh, V, dtype=torch.float32, device=dev)
         rsum = torch.empty(T, n_bh, dtype=torch.float32, device=dev)
         lp_t = self._time_contiguous() if ids is not None else None
+        lp_t_ld = lp_t.shape[2] if lp_t is not None else T
         check(lib().b200ctc_prefix_step(ptr(self._lp), ptr(lp_t), ptr(r_prev), ptr(s_prev), ptr(last_ids),
                                         ptr(ids), ptr(self._end_frames_dev), self.batch, n_hyps,
                                         T, V, snum, output_length, start, end, self.blank,
                                         self.eos, self.logzero, ptr(r), ptr(log_psi), ptr(scores),
-                                        ptr(idmap), ptr(rsum), st), "prefix_step")
+                                        ptr(idmap), ptr(rsum), lp_t_ld, st), "prefix_step")
         if self.dtype != torch.float32:
             scores, r, log_psi = scores.to(self.dtype), r.to(self.dtype), log_psi.to(self.dtype)
         return scores, (r, log_psi, f_min, f_max, idmap)
@@ -188,10 +203,23 @@ class CTCPrefixScoreTH(object):
         """
         if self.input_length < x.shape[1]:
             old = self._lp
-            new = x.to(torch.float32).contiguous().clone()
-            new[:, : old.shape[1]] = old  # keep the already-scored prefix (:238)
-            self._lp = new
-            self._lp_t = None
+            T_old, T_new = old.shape[1], x.shape[1]
+            if self.batch == 1:
+                # streaming (the reference uses extend_prob with batch 1, scorers/ctc.py:128-146):
+                # both copies live in buffers with headroom and only the NEW frames are written -
+                # the already-scored prefix (:238) stays where it is, (B,T,V) and (B,V,T) alike
+                if self._lp_store is None or self._lp_store.shape[1] < T_new:
+                    cap = max(T_new, int(1.5 * T_new) + 32)
+                    store = torch.empty(1, cap, self.odim, dtype=torch.float32, device=self.device)
+                    store[:, :T_old] = old
+                    self._lp_store = store
+                self._lp_store[:, T_old:T_new] = x[:, T_old:T_new].to(torch.float32)
+                self._lp = self._lp_store[:, :T_new]  # contiguous for batch 1
+            else:
+                new = x.to(torch.float32).contiguous().clone()
+                new[:, :T_old] = old
+                self._lp = new
+                self._lp_t, self._lp_t_T = None, 0
             self.input_length = x.size(1)
             self.end_frames = torch.as_tensor([x.size(1)]) - 1
             self._xlens_dev = torch.full((self.batch,), x.size(1), dtype=torch.int64,

@@ -124,16 +124,50 @@ class CTC(torch.nn.Module):
         )
         return loss
 
-    def forward_multi(self, hs_pads, hlens, ys_pad, ys_lens):
-        """Losses of several encoder outputs against the same labels: the intermediate-CTC
+    def forward_multi(self, hs_pads, hlens, ys_pad, ys_lens, upstream_scales=None):
+        """Losses of several encoder outputs against the SAME labels: the intermediate-CTC
         pattern of ``espnet2/asr/espnet_model.py:243-286`` (one ``self.ctc(...)`` call per
         tapped layer plus the final one).  Returns ``[forward(hs, ...) for hs in hs_pads]``
-        - same values and gradients - but the heads are issued on alternating side streams,
-        so that the latency-bound lattice of one head (60 us at C2 during which nothing of
-        the same head can use the memory system) runs under the HBM-bound row pass of the
-        other.  (PyTorch may warn once that an AccumulateGrad node runs on a
-        different stream than the head that feeds it: autograd inserts the needed
-        synchronisation itself; results are bit-identical.)"""
+        (same values and gradients) from ONE batched pass over heads x utterances:
+        the hidden states are stacked (32 MB per head at C2, the logits would be 640 MB), ``ctc_lo``
+        runs as one GEMM, and the loss kernels see a (H*B, T, V) batch - one label prep, one
+        emission gather, one lattice launch with the heads' lattices co-resident on the SMs, one
+        gradient row pass.  ``upstream_scales[h]``: the factor the caller multiplies head h's loss
+        with before backward (ESPnet weights the final and the intermediate heads differently);
+        with it backward is a no-op check per utterance, without it (or with other factors)
+        gradients are still exact, the mismatching heads pay one rescaling pass."""
+        H = len(hs_pads)
+        if H <= 1 or not hs_pads[0].is_cuda or self.ctc_type != "builtin":
+            return [self.forward(hs, hlens, ys_pad, ys_lens) for hs in hs_pads]
+        import numpy as np
+
+        Bn = hs_pads[0].size(0)
+        dev = hs_pads[0].device
+        hs = torch.cat(list(hs_pads), dim=0)  # (H*B, T, D)
+        ys_hat = self.ctc_lo(F.dropout(hs, p=self.dropout_rate))  # one GEMM, independent masks per head
+        Lmax = ys_pad.size(1)
+        lens_dev = torch.as_tensor(ys_lens).to(device=ys_pad.device)
+        keep = torch.arange(Lmax, device=ys_pad.device).unsqueeze(0) < lens_dev.unsqueeze(1)
+        ys_true = ys_pad[keep].repeat(H)
+        il = torch.as_tensor(hlens).to(device=dev, dtype=torch.int64).repeat(H)
+        tl = lens_dev.to(device=dev, dtype=torch.int64).repeat(H)
+        inv = B._f32_recip(Bn)
+        scales = [self.upstream_scale] * H if upstream_scales is None else list(upstream_scales)
+        hints = torch.tensor([float(np.float32(sc) * np.float32(inv)) for sc in scales],
+                             dtype=torch.float32).repeat_interleave(Bn).to(dev, non_blocking=True)
+        nll = B.ctc_loss(ys_hat, ys_true, il, tl, blank=0, zero_infinity=self.zero_infinity,
+                         max_tgt_len=Lmax, grad_hint=hints)
+        per_head = nll.view(H, Bn)
+        if self.reduce:
+            losses = [per_head[h].sum() * inv for h in range(H)]
+        else:
+            losses = [per_head[h] / Bn for h in range(H)]
+        return [l.to(device=dev, dtype=hs_pads[0].dtype) for l in losses]
+
+    def forward_multi_streams(self, hs_pads, hlens, ys_pad, ys_lens):
+        """Round-1 form of :meth:`forward_multi`, kept for A/B measurement (tools/bench_multihead.py):
+        one ``forward`` per head, issued on alternating side streams so that the latency-bound
+        lattice of one head runs under the HBM-bound row pass of another."""
         if len(hs_pads) <= 1 or not hs_pads[0].is_cuda:
             return [self.forward(hs, hlens, ys_pad, ys_lens) for hs in hs_pads]
         dev = hs_pads[0].device

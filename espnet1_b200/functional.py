@@ -102,7 +102,7 @@ class _CTCLossFn(torch.autograd.Function):
     @staticmethod
     @on_tensor_device
     def forward(ctx, logits, targets, tgt_offsets, in_lens, tgt_lens, max_tgt_len, blank,
-                zero_infinity, grad_hint, eager, reduce_scale, peer=None):
+                zero_infinity, grad_hint, eager, reduce_scale, peer=None, hint_vec=None):
         require_cuda(logits, "CTC logits")
         x = logits.contiguous()
         B, T, V = x.shape
@@ -120,7 +120,22 @@ class _CTCLossFn(torch.autograd.Function):
         if peer is not None and not (ctx.eager):  # ctc_loss() routes such calls to peer.exchange
             raise RuntimeError("the fused sharded-loss exchange needs the eager gradient mode, logits "
                                "that require a gradient and at least one utterance on every rank")
+        if ctx.eager and hint_vec is not None:
+            # one expected upstream gradient PER UTTERANCE (several heads in one batched call)
+            if reduced or peer is not None:
+                raise RuntimeError("per-utterance gradient hints: no batch reduction / exchange")
+            grad = torch.empty_like(x)
+            check(lib().b200ctc_loss_fwd_grad_hints(ptr(x), dtype_code(x), ptr(targets), ptr(tgt_offsets),
+                                                    ptr(in_lens), ptr(tgt_lens), B, T, V, max_tgt_len,
+                                                    blank, int(zero_infinity), ptr(hint_vec), ptr(nll),
+                                                    ptr(grad), ptr(ws), nbytes, stream_ptr(dev)),
+                  "loss_fwd_grad_hints")
+            ctx.grad_buf = grad
+            ctx.hint_vec = hint_vec
+            ctx.cfg = (B, T, V, None)
+            return nll
         if ctx.eager:
+            ctx.hint_vec = None
             grad = torch.empty_like(x)
             if peer is not None:  # sharded: the loss kernel also all-reduces {sum, B} over the ranks
                 check(lib().b200ctc_loss_fwd_grad_sharded(
@@ -149,7 +164,7 @@ class _CTCLossFn(torch.autograd.Function):
     @staticmethod
     @on_tensor_device
     def backward(ctx, g):
-        none10 = (None,) * 11
+        none10 = (None,) * 12
         gs, stride = _upstream(g)
         if ctx.eager:
             grad = ctx.grad_buf
@@ -159,6 +174,11 @@ class _CTCLossFn(torch.autograd.Function):
                     "use ctc_loss(..., grad_mode='deferred') to backpropagate twice")
             ctx.grad_buf = None
             B, T, V, hint = ctx.cfg
+            if ctx.hint_vec is not None:
+                check(lib().b200ctc_grad_rescale_hints(ptr(grad), dtype_code(grad), ptr(gs), stride,
+                                                       ctx.gmul, ptr(ctx.hint_vec), B, T, V,
+                                                       stream_ptr(grad.device)), "grad_rescale_hints")
+                return (grad,) + none10
             check(lib().b200ctc_grad_rescale(ptr(grad), dtype_code(grad), ptr(gs), stride, ctx.gmul,
                                              hint, B, T, V, stream_ptr(grad.device)),
                   "grad_rescale")
@@ -206,6 +226,12 @@ def ctc_loss(logits, targets, in_lens, tgt_lens, blank: int = 0, zero_infinity: 
     if max_tgt_len is None:
         src = tgt_lens if not (isinstance(tgt_lens, torch.Tensor) and tgt_lens.is_cuda) else tl_dev
         max_tgt_len = int(torch.as_tensor(src).max()) if tl_dev.numel() else 0
+    hint_vec = None
+    if isinstance(grad_hint, torch.Tensor):  # one expected upstream gradient per utterance
+        hint_vec = grad_hint.to(device=dev, dtype=torch.float32).contiguous()
+        if hint_vec.numel() != logits.shape[0]:
+            raise ValueError("grad_hint tensor must have one entry per utterance")
+        grad_hint = 1.0
     if grad_hint is None:
         grad_hint = float(reduce_scale) if reduce_scale is not None else _f32_recip(logits.shape[0])
     # the exchange is fused into the loss kernel only in the eager gradient mode; any other call
@@ -217,7 +243,7 @@ def ctc_loss(logits, targets, in_lens, tgt_lens, blank: int = 0, zero_infinity: 
                            int(blank), bool(zero_infinity), float(grad_hint),
                            grad_mode == "eager",
                            None if reduce_scale is None else float(reduce_scale),
-                           peer if fused else None)
+                           peer if fused else None, hint_vec)
     if peer is not None and not fused:
         from .sharded import pack_sum
 

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define B200CTC_ABI_VERSION 4
+#define B200CTC_ABI_VERSION 5
 
 #define B200CTC_OK 0
 #define B200CTC_ERR_ARG (-1)     /* bad argument (null pointer, size, dtype) */
@@ -169,6 +169,22 @@ int b200ctc_loss_fwd_grad_sharded(const void* logits, int dtype, const int64_t* 
 int b200ctc_grad_rescale(void* grad, int dtype, const float* gscale,
                          int gscale_stride, float gscale_mul, float grad_hint,
                          int B, int T, int V, b200ctc_stream_t stream);
+/* loss_fwd_grad / grad_rescale with ONE EXPECTED UPSTREAM GRADIENT PER UTTERANCE
+ * (device vector utt_hints (B,), all non-zero) instead of a scalar: several CTC
+ * heads that share labels but carry different loss weights - intermediate CTC,
+ * espnet2/asr/espnet_model.py:243-286 - run as one batched call over
+ * heads x utterances and backward stays a no-op check per utterance.  nll (B,)
+ * only (no batch reduction: the caller sums per head).                         */
+int b200ctc_loss_fwd_grad_hints(const void* logits, int dtype, const int64_t* targets,
+                                const int64_t* tgt_offsets, const int64_t* in_lens,
+                                const int64_t* tgt_lens, int B, int T, int V,
+                                int max_tgt_len, int blank, int zero_infinity,
+                                const float* utt_hints, float* nll, void* grad,
+                                void* ws, size_t ws_bytes, b200ctc_stream_t stream);
+int b200ctc_grad_rescale_hints(void* grad, int dtype, const float* gscale,
+                               int gscale_stride, float gscale_mul,
+                               const float* utt_hints, int B, int T, int V,
+                               b200ctc_stream_t stream);
 /* forced alignment (espnet/nets/pytorch_backend/ctc.py:163-226): max-semiring
  * lattice with back-pointers for ONE utterance; lp (T,V) fp32 log-probs,
  * out_ids (T,) int64 = label emitted at each frame (tgt_len >= 1).            */
@@ -208,11 +224,14 @@ int b200ctc_prefix_init_state(const float* lp, int B, int T, int V, int n_hyps,
  * minmax[0]=min_h f_arg, minmax[1]=max_h f_arg (fp32).                        */
 int b200ctc_prefix_window(const float* att_w, int n_bh, int T, float* minmax,
                           b200ctc_stream_t stream);
-/* time-contiguous copy of the padded posteriors: lp (B,T,V) -> lp_t (B,V,T).
- * Made once per utterance batch (after prefix_pad); lets a pre-beam scoring
- * step read one cache line per 32 frames of a candidate instead of one each. */
+/* time-contiguous copy of the padded posteriors: lp (B,T,V) -> lp_t (B,V,lp_t_ld),
+ * frames [t0,T) only.  Made once per utterance batch (after prefix_pad, t0 = 0);
+ * lets a pre-beam scoring step read one cache line per 32 frames of a candidate
+ * instead of one each.  lp_t_ld >= T is the time stride of the copy: a streaming
+ * caller (extend_prob, :222-242) allocates it with headroom and appends only
+ * the new frames [T_old, T_new).                            (ABI 5: t0, lp_t_ld) */
 int b200ctc_prefix_transpose(const float* lp, float* lp_t, int B, int T, int V,
-                             b200ctc_stream_t stream);
+                             int t0, int lp_t_ld, b200ctc_stream_t stream);
 /* one scoring step (__call__, :68-187) over frames [start,end).
  *  lp (B,T,V) ; lp_t (B,V,T) from prefix_transpose or NULL ;
  *  r_prev (T,2,n_bh) ; s_prev (n_bh,V) or NULL (=0) ; last_ids (n_bh) ;
@@ -226,6 +245,7 @@ int b200ctc_prefix_step(const float* lp, const float* lp_t, const float* r_prev,
                         int snum, int out_len, int start, int end, int blank,
                         int eos, float logzero, float* r, float* log_psi,
                         float* scores, int64_t* idmap, float* rsum_ws /*(T,n_bh) scratch*/,
+                        int lp_t_ld /* time stride of lp_t (>= T; ABI 5) */,
                         b200ctc_stream_t stream);
 /* index_select_state (:189-220): best_ids (B,W) flat (hyp*V + label) ids.     */
 int b200ctc_prefix_select(const float* r, const float* log_psi,

@@ -139,8 +139,9 @@ def test_c1_logits_boundary_vs_fixture_and_oracle():
 
 
 def test_forward_multi_equals_sequential_calls():
-    """Intermediate-CTC heads (espnet_model.py:243-286) issued on alternating streams give
-    bit-identical losses and gradients to one ``forward`` call per head."""
+    """Intermediate-CTC heads (espnet_model.py:243-286) as ONE batched pass over heads x utterances
+    give the losses and gradients of one ``forward`` call per head - with equal and with different
+    loss weights per head (with and without the matching ``upstream_scales``)."""
     import torch
 
     from espnet1_b200.espnet2.asr.ctc import CTC
@@ -153,20 +154,37 @@ def test_forward_multi_equals_sequential_calls():
     yl = torch.tensor([9, 4, 0, 12, 7, 5], device=dev)
     ys = torch.randint(1, V, (B, 12), generator=g).to(dev)
     ctc = CTC(V, D).to(dev)
-    want = [ctc(h, hl, ys, yl) for h in hs]
-    sum(want).backward()
-    gw = [h.grad.clone() for h in hs] + [ctc.ctc_lo.weight.grad.clone()]
-    for h in hs:
-        h.grad = None
-    ctc.zero_grad(set_to_none=True)
-    got = ctc.forward_multi(hs, hl, ys, yl)
-    sum(got).backward()
-    torch.cuda.synchronize()
-    assert [float(a.detach()) for a in got] == [float(a.detach()) for a in want]
-    for a, h in zip(gw[:3], hs):
-        assert torch.equal(a, h.grad)
-    torch.testing.assert_close(ctc.ctc_lo.weight.grad, gw[3], rtol=1e-5, atol=1e-6)
+    for wts, scales in (([1.0, 1.0, 1.0], None), ([0.35, 0.15, 0.5], [0.35, 0.15, 0.5]),
+                        ([0.35, 0.15, 0.5], None)):
+        for h in hs:
+            h.grad = None
+        ctc.zero_grad(set_to_none=True)
+        want = [ctc(h, hl, ys, yl) for h in hs]
+        sum(w * l for w, l in zip(wts, want)).backward()
+        gw = [h.grad.clone() for h in hs] + [ctc.ctc_lo.weight.grad.clone(), ctc.ctc_lo.bias.grad.clone()]
+        for h in hs:
+            h.grad = None
+        ctc.zero_grad(set_to_none=True)
+        got = ctc.forward_multi(hs, hl, ys, yl, upstream_scales=scales)
+        sum(w * l for w, l in zip(wts, got)).backward()
+        torch.cuda.synchronize()
+        for a, b_ in zip(got, want):
+            assert abs(float(a.detach()) - float(b_.detach())) <= 2e-6 * abs(float(b_.detach()))
+        for a, h in zip(gw[:3], hs):
+            torch.testing.assert_close(h.grad, a, rtol=1e-5, atol=1e-6)
+        torch.testing.assert_close(ctc.ctc_lo.weight.grad, gw[3], rtol=1e-5, atol=2e-6)
+        torch.testing.assert_close(ctc.ctc_lo.bias.grad, gw[4], rtol=1e-5, atol=2e-6)
     assert len(ctc.forward_multi(hs[:1], hl, ys, yl)) == 1
+    ctc.reduce = False
+    a = ctc.forward_multi(hs, hl, ys, yl)
+    b_ = [ctc(h, hl, ys, yl) for h in hs]
+    for x, y in zip(a, b_):
+        torch.testing.assert_close(x, y, rtol=2e-6, atol=1e-6)
+    # the round-1 stream-alternation form stays bit-identical to sequential calls
+    ctc.reduce = True
+    c = ctc.forward_multi_streams(hs, hl, ys, yl)
+    torch.cuda.synchronize()
+    assert [float(v.detach()) for v in c] == [float(v.detach()) for v in want]
 
 
 def test_upstream_scale_hint_matches_weighted_loss():

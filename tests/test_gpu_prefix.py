@@ -138,6 +138,51 @@ def test_streaming_extend_vs_reference_fixture():
     close(st[0], g["r1"], RTOL, ATOL)
 
 
+def test_streaming_extend_in_several_chunks_vs_oracle():
+    """Online decoding (batch_beam_search_online.py:306-309) extends the posteriors chunk by chunk.
+    `extend_prob` keeps both layouts in buffers with headroom and writes only the NEW frames
+    ((B,T,V) rows and the time-contiguous (B,V,T) columns): four growing lengths - the second
+    fits the first buffer, the later ones regrow it - against the oracle scorer at every stage."""
+    from espnet1_b200.espnet.nets.scorers.ctc import CTCPrefixScorer
+    from oracle.scorer_port import OracleCTCPrefixScorer
+
+    class _CpuCTC:
+        def log_softmax(self, x):
+            return torch.log_softmax(x, dim=-1)
+
+    g = torch.Generator().manual_seed(21)
+    V, W, snum, eos = 60, 4, 7, 59
+    lens = [40, 55, 130, 400]
+    x_full = torch.randn(lens[-1], V, generator=g) * 2
+    cu = CTCPrefixScorer(_StubCTC(), eos)
+    ora = OracleCTCPrefixScorer(_CpuCTC(), eos)
+    cu.batch_init_state(x_full[: lens[0]].to(DEV))
+    ora.batch_init_state(x_full[: lens[0]].clone())
+    y = torch.full((W, 1), eos, dtype=torch.long)
+    st_c, st_o = [None] * W, [None] * W
+    for stage, T in enumerate(lens):
+        if stage > 0:
+            cu.extend_prob(x_full[:T].to(DEV))
+            ora.extend_prob(x_full[:T].clone())
+            st_c, st_o = cu.extend_state(st_c), ora.extend_state(st_o)
+            for a, b in zip(st_c, st_o):
+                close(a[0], b[0].numpy(), RTOL, ATOL, f"extended r, stage {stage}")
+            assert cu.impl.input_length == T and tuple(cu.impl._lp.shape) == (1, T, V)
+        ids = torch.stack([torch.randperm(V - 2, generator=g)[:snum] + 1 for _ in range(W)])
+        sc_c, s5c = cu.batch_score_partial(y.to(DEV), ids.to(DEV), st_c, x_full[:T].to(DEV))
+        sc_o, s5o = ora.batch_score_partial(y, ids, st_o, x_full[:T])
+        close(sc_c, sc_o.numpy(), RTOL, ATOL, f"scores, stage {stage}")
+        tok = ids[:, stage % snum]
+        st_c = [cu.select_state(s5c, i, int(tok[i])) for i in range(W)]
+        st_o = [ora.select_state(s5o, i, int(tok[i])) for i in range(W)]
+        y = torch.cat((y, tok.view(-1, 1)), 1)
+    # the time-contiguous copy was appended to, not rebuilt: it has headroom and holds all frames
+    lp_t = cu.impl._lp_t
+    assert lp_t is not None and lp_t.shape[2] >= lens[-1] and cu.impl._lp_t_T == lens[-1]
+    np.testing.assert_array_equal(lp_t[0, :, : lens[-1]].cpu().numpy(),
+                                  cu.impl._lp[0].transpose(0, 1).cpu().numpy())
+
+
 def test_public_attributes_and_x_view():
     lpz = torch.log_softmax(torch.randn(2, 6, 5), dim=2).to(DEV)
     s = _th()(lpz, torch.tensor([6, 4]), 0, 4, margin=3)
