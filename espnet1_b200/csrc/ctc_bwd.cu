@@ -491,11 +491,12 @@ __global__ void __launch_bounds__(NT) grad_rows_direct_kernel(
 
 #endif  // B200CTC_TUNING
 
-template <typename T, int NT>
+// PERX: 16-byte chunks per thread (0: the default 40 elements per thread)
+template <typename T, int NT, int PERX = 0>
 static int launch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, int blank,
                          const LossLayout& w, unsigned char* ws, const float* gscale,
                          int gstride, float gmul, bool last_use, cudaStream_t st) {
-  constexpr int PER = 40 / Elems<T>::N;
+  constexpr int PER = PERX ? PERX : 40 / Elems<T>::N;
   const size_t extra = align_up(sizeof(float) * (size_t)w.Lp, 128);
   RowLaunchCfg c = row_launch_cfg(logits, (size_t)V * sizeof(T), extra, NT, "B200CTC_B");
   if ((reinterpret_cast<uintptr_t>(grad) & 15) != 0) {  // unaligned gradient: the generic kernel
@@ -511,13 +512,16 @@ static int launch_pass_b(const void* logits, void* grad, int B, int Tfr, int V, 
   static const int wide_on = tuning_int("B200CTC_B_WIDE", 1);
   const size_t lat_stage = align_up(4 * (2 * (size_t)w.Sp + 2 * (size_t)w.Lp), 128);
   const bool wide_needed = 2 * w.Lmax + 1 > 3 * NT;
-  bool wide = wide_on && c.tma && (wide_needed || NT == 128);
+  bool wide = wide_on && c.tma && (wide_needed || NT == 128 || (NT == 256 && PERX));
   if (wide) {
     const size_t row_al = align_up((size_t)V * sizeof(T), 128);
-    const int want = wide_needed ? 0 : 7;
-    const RowLaunchCfg cw = row_launch_cfg(logits, row_al + lat_stage, extra, NT, "B200CTC_B", want);
+    // (256 threads per row - long lattices, see dispatch_pass_b: 61 registers, 4 single-stage
+    //  CTAs = 32 warps per SM; measured at C4: 831 us vs 989 us at 128 threads, 947 us with 3 CTAs)
+    const int want = wide_needed ? (NT == 256 ? 4 : 0) : 7;
+    const RowLaunchCfg cw = row_launch_cfg(logits, row_al + lat_stage, extra, NT, "B200CTC_B", want,
+                                           (wide_needed && NT == 256) ? 1 : 0);
     bool ok = cw.ctas_per_sm * ((size_t)cw.nstage * cw.stride + extra + 1024) <= 220 * 1024 &&
-              cw.ctas_per_sm >= (wide_needed ? 3 : 7);
+              cw.ctas_per_sm >= (wide_needed ? 3 : (NT == 128 ? 7 : 4));
     if (ok && !wide_needed) {  // all 7 must be resident at once: a persistent grid must not run a second wave
       static thread_local int occ_cached = -1;
       static thread_local size_t occ_smem = 0;
@@ -599,6 +603,11 @@ static int dispatch_pass_b(const void* logits, void* grad, int B, int Tfr, int V
                            const LossLayout& w, unsigned char* ws, const float* gscale,
                            int gstride, float gmul, bool last_use, cudaStream_t st) {
   const int need = (V + 39) / 40;
+  // long lattices (C4: 19 lattice positions and ~10 label columns per thread at 128 threads):
+  // 256 threads per row with 20 elements each halve the serial work per thread
+  static const int wide256 = tuning_int("B200CTC_B_WIDE256", 1);  // (2: also short lattices, tuning builds)
+  if (wide256 && need <= 128 && (2 * w.Lmax + 1 > 3 * 128 || wide256 >= 2))
+    return launch_pass_b<T, 256, 20 / Elems<T>::N>(logits, grad, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, last_use, st);
   if (need <= 128) return launch_pass_b<T, 128>(logits, grad, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, last_use, st);
   if (need <= 256) return launch_pass_b<T, 256>(logits, grad, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, last_use, st);
   if (need <= 512) return launch_pass_b<T, 512>(logits, grad, B, Tfr, V, blank, w, ws, gscale, gstride, gmul, last_use, st);

@@ -57,7 +57,8 @@ struct RowLaunchCfg { int nstage, ctas_per_sm, stride; bool tma; };
 
 // shared-memory budgeting for the row passes; env overrides are for tuning sweeps only
 static inline RowLaunchCfg row_launch_cfg(const void* base, size_t row_bytes, size_t extra_smem,
-                                          int nt, const char* env_prefix, int want_ctas_hint = 0) {
+                                          int nt, const char* env_prefix, int want_ctas_hint = 0,
+                                          int want_stages_hint = 0) {
   RowLaunchCfg c;
   c.tma = (row_bytes % 16 == 0) && ((reinterpret_cast<uintptr_t>(base) & 15) == 0);
   c.stride = (int)align_up(row_bytes, 128);
@@ -67,6 +68,7 @@ static inline RowLaunchCfg row_launch_cfg(const void* base, size_t row_bytes, si
   int want_ctas = nt <= 128 ? 6 : (nt <= 256 ? 3 : 1);
   int want_stages = nt <= 128 ? 1 : 2;
   if (want_ctas_hint > 0) want_ctas = want_ctas_hint;
+  if (want_stages_hint > 0) want_stages = want_stages_hint;
   char name[64];
   snprintf(name, sizeof(name), "%s_CTAS", env_prefix);
   if (const char* e = tuning_env(name)) want_ctas = atoi(e);
