@@ -63,7 +63,8 @@ SIGNATURES = {
     "b200ctc_prefix_transpose": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_int, _P]),
     "b200ctc_prefix_step": (c_int, [_P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int,
                                     c_int, c_int, c_int, c_int, c_int, c_float, _P, _P, _P, _P,
-                                    _P, c_int, _P]),
+                                    _P, c_int, _P, _P]),
+    "b200ctc_prefix_window_utt": (c_int, [_P, c_int, c_int, c_int, c_int, c_int, _P, _P, _P, _P]),
     "b200ctc_prefix_select": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int,
                                       _P, _P, _P]),
     "b200ctc_beam_prebeam": (c_int, [_P, _P, _P, c_int, c_int64, c_int, c_int, _P, _P]),

@@ -111,6 +111,44 @@ __global__ void __launch_bounds__(kWinWarps * 32) prefix_window_kernel(
   }
 }
 
+// Per-utterance windows (opt-in extension; the reference takes ONE window over the
+// whole batch, :144-153): the same formula applied to the hypotheses of each utterance alone -
+// i.e. what the reference computes when the utterance is decoded by itself.  Everything stays
+// on the device (no read-back): fprev / fnew (B,2) int32 = {f_min, f_max}, win (B,2) = {start, end}.
+__global__ void __launch_bounds__(kWinWarps * 32) prefix_window_utt_kernel(
+    const float* __restrict__ att_w, int n_hyps, int T, int margin, int out_len,
+    const int* __restrict__ fprev, int* __restrict__ fnew, int* __restrict__ win) {
+  __shared__ float smin[kWinWarps], smax[kWinWarps];
+  const int b = blockIdx.x, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  float lo = -kNegInf, hi = kNegInf;
+  for (int h = wid; h < n_hyps; h += kWinWarps) {
+    const float* row = att_w + ((size_t)b * n_hyps + h) * T;
+    float acc = 0.f;
+    for (int t0 = lane; t0 < T; t0 += 32 * 16) {  // same accumulation order as the global kernel
+      float v[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) v[j] = (t0 + 32 * j < T) ? __ldg(row + t0 + 32 * j) : 0.f;
+#pragma unroll
+      for (int j = 0; j < 16; ++j)
+        if (t0 + 32 * j < T) acc = fmaf(v[j], (float)(t0 + 32 * j), acc);
+    }
+    acc = warp_sum(acc);
+    lo = fminf(lo, acc);
+    hi = fmaxf(hi, acc);
+  }
+  if (lane == 0) { smin[wid] = lo; smax[wid] = hi; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int i = 1; i < kWinWarps; ++i) { lo = fminf(lo, smin[i]); hi = fmaxf(hi, smax[i]); }
+    const int pmin = fprev ? fprev[2 * b] : 0, pmax = fprev ? fprev[2 * b + 1] : 1;  // (:95)
+    const int f_min = max((int)lo, pmin), f_max = max((int)hi, pmax);  // int(): toward zero
+    fnew[2 * b] = f_min;
+    fnew[2 * b + 1] = f_max;
+    win[2 * b] = min(pmax, max(max(f_min - margin, out_len), 1));
+    win[2 * b + 1] = min(f_max + margin, T);
+  }
+}
+
 // r_sum[t,h] = logsumexp(r_prev[t,0,h], r_prev[t,1,h])   (:131)
 __global__ void __launch_bounds__(256) prefix_rsum_kernel(const float* __restrict__ r_prev, int T,
                                                           int n_bh, float* __restrict__ rsum) {
@@ -149,11 +187,16 @@ __global__ void __launch_bounds__(128) prefix_step_kernel(
     const int64_t* __restrict__ last_ids, const int64_t* __restrict__ scoring_ids,
     const int64_t* __restrict__ end_frames, int n_bh, int n_hyps, int T, int V, int snum,
     int out_len, int start, int end, int blank, int eos, float logzero, float* __restrict__ r,
-    float* __restrict__ log_psi, float* __restrict__ scores, int64_t* __restrict__ idmap, int ldt) {
+    float* __restrict__ log_psi, float* __restrict__ scores, int64_t* __restrict__ idmap, int ldt,
+    const int* __restrict__ win_utt) {
   const size_t idx = (size_t)blockIdx.x * 128 + threadIdx.x;
   if (idx >= (size_t)n_bh * snum) return;
   const int h = (int)(idx / snum);
   const int b = h / n_hyps;
+  if (win_utt) {  // per-utterance window instead of the batch-wide one
+    start = win_utt[2 * b];
+    end = win_utt[2 * b + 1];
+  }
   const int k = scoring_ids ? (int)scoring_ids[idx] : (int)(idx - (size_t)h * snum);
   const bool same = (k == (int)last_ids[h]);
   // per-frame input streams: x_t[k], x_t[blank], phi_{t-1} (= r^b_prev if k repeats the
@@ -316,6 +359,17 @@ extern "C" int b200ctc_prefix_window(const float* att_w, int n_bh, int T, float*
   return check_launch("prefix_window");
 }
 
+extern "C" int b200ctc_prefix_window_utt(const float* att_w, int B, int n_hyps, int T, int margin,
+                                         int out_len, const int* fprev, int* fnew, int* win,
+                                         b200ctc_stream_t stream) {
+  B2_REQUIRE(att_w && fnew && win && B > 0 && n_hyps > 0 && T > 0 && margin >= 0 && out_len >= 0,
+             "prefix_window_utt: bad argument");
+  prefix_window_utt_kernel<<<B, kWinWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+      att_w, n_hyps, T, margin, out_len, fprev, fnew, win);
+  count_launch();
+  return check_launch("prefix_window_utt");
+}
+
 extern "C" int b200ctc_prefix_transpose(const float* lp, float* lp_t, int B, int T, int V, int t0,
                                         int lp_t_ld, b200ctc_stream_t stream) {
   B2_REQUIRE(lp && lp_t, "prefix_transpose: null pointer");
@@ -337,7 +391,7 @@ extern "C" int b200ctc_prefix_step(const float* lp, const float* lp_t, const flo
                                    const int64_t* end_frames, int B, int n_hyps, int T, int V,
                                    int snum, int out_len, int start, int end, int blank, int eos,
                                    float logzero, float* r, float* log_psi, float* scores,
-                                   int64_t* idmap, float* rsum_ws, int lp_t_ld,
+                                   int64_t* idmap, float* rsum_ws, int lp_t_ld, const int* win_utt,
                                    b200ctc_stream_t stream) {
   B2_REQUIRE(lp && r_prev && last_ids && end_frames && r && log_psi && scores && rsum_ws,
              "prefix_step: null pointer");
@@ -345,8 +399,9 @@ extern "C" int b200ctc_prefix_step(const float* lp, const float* lp_t, const flo
   B2_REQUIRE(B > 0 && n_hyps > 0 && T > 0 && V > 0 && snum > 0, "prefix_step: bad shape");
   B2_REQUIRE(scoring_ids ? idmap != nullptr : snum == V,
              "prefix_step: scoring_ids/idmap/snum mismatch (snum=%d V=%d)", snum, V);
-  B2_REQUIRE(start >= 1 && start <= T && end <= T && blank >= 0 && blank < V && eos >= 0 && eos < V,
-             "prefix_step: bad window [%d,%d) or ids", start, end);
+  B2_REQUIRE(win_utt || (start >= 1 && start <= T && end <= T), "prefix_step: bad window [%d,%d)", start,
+             end);
+  B2_REQUIRE(blank >= 0 && blank < V && eos >= 0 && eos < V, "prefix_step: bad blank / eos id");
   const int n_bh = B * n_hyps;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   prof_mark(4, 0, st);
@@ -361,11 +416,11 @@ extern "C" int b200ctc_prefix_step(const float* lp, const float* lp_t, const flo
   if (lp_t && scoring_ids)
     prefix_step_kernel<true><<<blocks((size_t)n_bh * snum, 128), 128, 0, st>>>(
         lp, lp_t, r_prev, rsum_ws, s_prev, last_ids, scoring_ids, end_frames, n_bh, n_hyps, T, V,
-        snum, out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap, lp_t_ld);
+        snum, out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap, lp_t_ld, win_utt);
   else
     prefix_step_kernel<false><<<blocks((size_t)n_bh * snum, 128), 128, 0, st>>>(
         lp, lp_t, r_prev, rsum_ws, s_prev, last_ids, scoring_ids, end_frames, n_bh, n_hyps, T, V,
-        snum, out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap, lp_t_ld);
+        snum, out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap, lp_t_ld, win_utt);
   count_launch();
   prof_mark(4, 1, st);
   return check_launch("prefix_step");

@@ -19,7 +19,7 @@ class CTCPrefixScoreTH(object):
     Seki et al. 2019) on the GPU."""
 
     @on_tensor_device
-    def __init__(self, x, xlens, blank, eos, margin=0):
+    def __init__(self, x, xlens, blank, eos, margin=0, per_utt_window=False):
         """Construct CTC prefix scorer
 
         :param torch.Tensor x: input label posterior sequences (B, T, O)
@@ -27,6 +27,12 @@ class CTCPrefixScoreTH(object):
         :param int blank: blank label id
         :param int eos: end-of-sequence id
         :param int margin: margin parameter for windowing (0 means no windowing)
+        :param bool per_utt_window: EXTENSION (not in the reference): with
+            ``margin > 0`` take the attention window per utterance instead of one window over
+            the whole batch (ctc_prefix_score.py:144-153) - each utterance is then scored
+            exactly as if it were decoded alone.  The window never leaves the device (no
+            read-back); the state's ``f_min`` slot then holds a (B, 2) int32 device tensor
+            ``{f_min, f_max}`` and the ``f_max`` slot a view of its second column.
         """
         require_cuda(x, "CTCPrefixScoreTH x")
         self.logzero = -10000000000.0
@@ -43,6 +49,7 @@ class CTCPrefixScoreTH(object):
         self._end_frames_dev = self._xlens_dev - 1
         self._set_lp(x, pad=True)
         self.margin = margin
+        self.per_utt_window = bool(per_utt_window)
         if margin > 0:
             self.frame_ids = torch.arange(self.input_length, dtype=self.dtype, device=self.device)
         self.idx_bh = None
@@ -139,8 +146,26 @@ class CTCPrefixScoreTH(object):
         else:
             snum, ids, idmap = V, None, None
 
+        win = None
+        if att_w is not None and self.margin > 0 and self.per_utt_window:
+            # per-utterance windows, computed and consumed on the device
+            aw = att_w.to(torch.float32).contiguous()
+            if isinstance(f_min_prev, torch.Tensor):
+                fprev = f_min_prev.to(device=dev, dtype=torch.int32).contiguous()
+            elif state is None:
+                fprev = None
+            else:
+                fprev = torch.tensor([[int(f_min_prev), int(f_max_prev)]] * self.batch,
+                                     dtype=torch.int32, device=dev)
+            fnew = torch.empty(self.batch, 2, dtype=torch.int32, device=dev)
+            win = torch.empty(self.batch, 2, dtype=torch.int32, device=dev)
+            check(lib().b200ctc_prefix_window_utt(ptr(aw), self.batch, n_hyps, T, self.margin,
+                                                  output_length, ptr(fprev), ptr(fnew), ptr(win), st),
+                  "prefix_window_utt")
+            f_min, f_max = fnew, fnew[:, 1]
+            start, end = 1, T  # ignored: the kernel reads `win`
         # window (:144-153); one global window for the whole batch like the reference
-        if att_w is not None and self.margin > 0:
+        elif att_w is not None and self.margin > 0:
             mm = torch.empty(2, dtype=torch.float32, device=dev)
             aw = att_w.to(torch.float32).contiguous()
             check(lib().b200ctc_prefix_window(ptr(aw), n_bh, T, ptr(mm), st), "prefix_window")
@@ -164,7 +189,7 @@ class CTCPrefixScoreTH(object):
                                         ptr(ids), ptr(self._end_frames_dev), self.batch, n_hyps,
                                         T, V, snum, output_length, start, end, self.blank,
                                         self.eos, self.logzero, ptr(r), ptr(log_psi), ptr(scores),
-                                        ptr(idmap), ptr(rsum), lp_t_ld, st), "prefix_step")
+                                        ptr(idmap), ptr(rsum), lp_t_ld, ptr(win), st), "prefix_step")
         if self.dtype != torch.float32:
             scores, r, log_psi = scores.to(self.dtype), r.to(self.dtype), log_psi.to(self.dtype)
         return scores, (r, log_psi, f_min, f_max, idmap)

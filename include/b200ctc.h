@@ -246,7 +246,18 @@ int b200ctc_prefix_step(const float* lp, const float* lp_t, const float* r_prev,
                         int eos, float logzero, float* r, float* log_psi,
                         float* scores, int64_t* idmap, float* rsum_ws /*(T,n_bh) scratch*/,
                         int lp_t_ld /* time stride of lp_t (>= T; ABI 5) */,
+                        const int* win_utt /* (B,2) {start,end} per utterance from
+                                              prefix_window_utt, or NULL: [start,end) for all */,
                         b200ctc_stream_t stream);
+/* Per-utterance attention windows - an opt-in EXTENSION: the reference
+ * takes one window over the whole batch (:144-153); here the same formula runs over
+ * the n_hyps hypotheses of each utterance alone, i.e. what the reference computes
+ * when that utterance is decoded by itself.  Device-only (no read-back):
+ * fprev (B,2) int32 {f_min,f_max} of the previous step or NULL ({0,1}, :95);
+ * writes fnew (B,2) and win (B,2) {start,end} for b200ctc_prefix_step.          */
+int b200ctc_prefix_window_utt(const float* att_w, int B, int n_hyps, int T, int margin,
+                              int out_len, const int* fprev, int* fnew, int* win,
+                              b200ctc_stream_t stream);
 /* index_select_state (:189-220): best_ids (B,W) flat (hyp*V + label) ids.     */
 int b200ctc_prefix_select(const float* r, const float* log_psi,
                           const int64_t* idmap, const int64_t* best_ids, int B,

@@ -378,6 +378,68 @@ def make_streaming():
     save("prefix_stream.npz", o)
 
 
+def make_align_greedy():
+    """(1) forced alignment (espnet/nets/pytorch_backend/ctc.py:163-226) on several shapes - short
+    and long targets, repeated labels, a target nearly as long as the input; (2) the greedy CTC
+    collapse of ``ErrorCalculator.calculate_cer_ctc`` (espnet/nets/e2e_asr_common.py:159-191):
+    the reference joins the surviving characters and hands them to ``editdistance.eval``.  That
+    package is not installed here, so a stand-in module records the strings the REFERENCE's own
+    collapse code produced (one unique character per id: the strings map back to ids exactly)."""
+    import types
+
+    from espnet.nets.e2e_asr_common import ErrorCalculator
+
+    out = {}
+    torch.manual_seed(31)
+    V, D = 14, 6
+    m1 = RefCTC1(V, D, 0.0)
+    cases = [(40, [3, 3, 5, 1, 1]), (80, list(np.random.RandomState(1).randint(1, V, 20))),
+             (25, list(np.random.RandomState(2).randint(1, V, 11))), (60, [7]),
+             (33, [2, 2, 2, 2, 9, 9, 4])]
+    for i, (T, y) in enumerate(cases):
+        h = torch.randn(1, T, D) * 3
+        with torch.no_grad():
+            lpz = m1.log_softmax(h).squeeze(0)
+            ali = m1.forced_align(h, [int(v) for v in y])
+        out[f"align{i}__lp"] = lpz.numpy()
+        out[f"align{i}__y"] = np.asarray(y, dtype=np.int64)
+        out[f"align{i}__ali"] = np.asarray(ali, dtype=np.int64)
+    out["align_n"] = len(cases)
+
+    captured = []
+    fake = types.ModuleType("editdistance")
+    fake.eval = lambda hyp, ref: captured.append(hyp) or 0
+    sys.modules["editdistance"] = fake
+    try:
+        Vg, B, T = 40, 6, 70
+        chars = [chr(0x4E00 + i) for i in range(Vg)]  # one unique character per id
+        chars[0] = "<blank>"
+        chars[Vg - 1] = "<space>"
+        ec = ErrorCalculator(chars, "<space>", "<blank>", report_cer=False, report_wer=False)
+        g = torch.Generator().manual_seed(17)
+        logits = torch.randn(B, T, Vg, generator=g) * 2
+        logits[:, :, 0] += 2.5      # plenty of blanks
+        logits[:, :, Vg - 1] = -50  # the space symbol is never the arg-max (the collapse drops it)
+        hold = torch.rand(B, T, generator=g) < 0.45  # repeat the previous frame: runs to collapse
+        for t in range(1, T):
+            logits[:, t][hold[:, t]] = logits[:, t - 1][hold[:, t]]
+        ys_hat = logits.argmax(-1)
+        ys_pad = torch.randint(1, Vg - 1, (B, 5))
+        ec.calculate_cer_ctc(ys_hat, ys_pad)
+    finally:
+        del sys.modules["editdistance"]
+    assert len(captured) == B
+    ids = [[chars.index(c) for c in hyp] for hyp in captured]
+    lmax = max(len(v) for v in ids)
+    pad = np.full((B, lmax), -1, dtype=np.int64)
+    for b, v in enumerate(ids):
+        pad[b, : len(v)] = v
+    out["greedy__logits"] = logits.numpy()
+    out["greedy__ids"] = pad
+    out["greedy__lens"] = np.asarray([len(v) for v in ids], dtype=np.int64)
+    save("align_greedy.npz", out)
+
+
 if __name__ == "__main__":
     torch.set_num_threads(1)
     if len(sys.argv) > 1:  # regenerate selected fixtures only: make_golden.py make_beam_multi ...
@@ -391,3 +453,4 @@ if __name__ == "__main__":
     make_beam_multi()
     make_beam_opts()
     make_streaming()
+    make_align_greedy()

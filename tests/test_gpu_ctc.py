@@ -213,3 +213,32 @@ def test_upstream_scale_hint_matches_weighted_loss():
         loss.backward()
         close(loss, ref.detach().numpy(), LOSS_RTOL, 1e-6)
         close(x.grad, xr.grad.numpy(), 0, GRAD_ATOL)
+
+
+def test_forced_align_and_greedy_decode_vs_reference_fixture():
+    """The CUDA forced alignment (workspace and static-scratch entry points) and greedy decode
+    against outputs of the REAL reference (tests/golden/align_greedy.npz): five alignment shapes
+    incl. repeated labels and a target nearly as long as the input; the collapse of
+    ``ErrorCalculator.calculate_cer_ctc``.  Integer-identical."""
+    from espnet1_b200 import _lib
+    from espnet1_b200 import functional as F
+
+    d = _dev()
+    g = load_npz("align_greedy.npz")
+    for i in range(int(g["align_n"])):
+        lp = torch.tensor(g[f"align{i}__lp"], device=d)
+        y = torch.tensor(g[f"align{i}__y"], device=d)
+        ali = F.forced_align(lp, y)
+        np.testing.assert_array_equal(ali.cpu().numpy(), g[f"align{i}__ali"], err_msg=f"case {i}")
+        out = torch.empty(lp.shape[0], dtype=torch.int64, device=d)
+        lpc = lp.contiguous()
+        _lib.check(_lib.lib().b200ctc_forced_align_static(lpc.data_ptr(), y.data_ptr(), lp.shape[0], lp.shape[1],
+                                                          y.numel(), 0, out.data_ptr(), _lib.stream_ptr(lp.device)),
+                   "forced_align_static")
+        np.testing.assert_array_equal(out.cpu().numpy(), g[f"align{i}__ali"], err_msg=f"static, case {i}")
+    ids, lens = F.greedy_decode(torch.tensor(g["greedy__logits"], device=d))
+    np.testing.assert_array_equal(lens.cpu().numpy(), g["greedy__lens"])
+    ids = ids.cpu().numpy()
+    for b, n in enumerate(g["greedy__lens"]):
+        np.testing.assert_array_equal(ids[b, :n], g["greedy__ids"][b, :n])
+        assert (ids[b, n:] == -1).all()

@@ -183,6 +183,47 @@ def test_streaming_extend_in_several_chunks_vs_oracle():
                                   cu.impl._lp[0].transpose(0, 1).cpu().numpy())
 
 
+def test_per_utterance_windows_equal_decoding_each_utterance_alone():
+    """`per_utt_window=True` (extension): the batched scorer must give every utterance
+    the scores, states and f_min / f_max that the REFERENCE-semantics scorer gives when that
+    utterance is scored alone (a batch-wide window over a batch of one IS the per-utterance
+    window) - here the oracle with batch 1; 5 carried steps, ragged lengths, attention centres
+    that differ a lot between utterances (so the batch-wide window is much wider)."""
+    B, W, V, T, snum, margin, steps = 4, 3, 80, 120, 6, 7, 5
+    g = torch.Generator().manual_seed(77)
+    lpz = torch.log_softmax(torch.randn(B, T, V, generator=g) * 2, dim=2)
+    xlens = torch.tensor([120, 90, 120, 64])
+    eos = V - 1
+    cu = _th()(lpz.clone().to(DEV), xlens, 0, eos, margin, per_utt_window=True)
+    alone = [PrefixOracle(lpz[b:b + 1].clone(), xlens[b:b + 1], 0, eos, margin) for b in range(B)]
+    t = torch.arange(T, dtype=torch.float32)
+    yseq = [[eos] for _ in range(B * W)]
+    st_c, st_o = None, [None] * B
+    speed = torch.tensor([3.0, 9.0, 15.0, 6.0])
+    for i in range(steps):
+        c = (speed.repeat_interleave(W) * (i + 1) + torch.rand(B * W, generator=g) * 4 - 2).clamp(1, T - 2)
+        att = torch.softmax(-((t[None] - c[:, None]) ** 2) / 8.0, dim=1)
+        part = torch.stack([torch.randperm(V - 2, generator=g)[:snum] + 1 for _ in range(B * W)])
+        sc, st5 = cu(yseq, st_c, part.to(DEV), att.to(DEV))
+        fwin = st5[2].cpu()
+        best = []
+        for b in range(B):
+            sl = slice(b * W, (b + 1) * W)
+            so, s5o = alone[b].score(yseq[sl], st_o[b], part[sl], att[sl])
+            close(sc[sl], so.numpy(), RTOL, ATOL, f"scores utt {b} step {i}")
+            close(st5[1][sl], s5o[1].numpy(), RTOL, ATOL, f"log_psi utt {b} step {i}")
+            assert fwin[b].tolist() == [int(s5o[2]), int(s5o[3])], (b, i)
+            bi = torch.topk(so.view(1, -1), W, 1)[1]
+            best.append(bi)
+            st_o[b] = alone[b].select(s5o, bi)
+        best = torch.cat(best, 0)
+        st_c = cu.index_select_state(st5, best.to(DEV))
+        tok = torch.fmod(best, V).view(-1).tolist()
+        src = (best // V + (torch.arange(B) * W).view(-1, 1)).view(-1).tolist()
+        yseq = [yseq[s_][:] + [k] for s_, k in zip(src, tok)]
+    assert len({tuple(v) for v in fwin.tolist()}) > 1  # the windows really differ per utterance
+
+
 def test_public_attributes_and_x_view():
     lpz = torch.log_softmax(torch.randn(2, 6, 5), dim=2).to(DEV)
     s = _th()(lpz, torch.tensor([6, 4]), 0, 4, margin=3)

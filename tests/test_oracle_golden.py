@@ -77,6 +77,19 @@ def test_forced_align(gm):
     np.testing.assert_array_equal(np.asarray(ali), gm["forced_align_utt0"])
 
 
+def test_forced_align_and_greedy_collapse_vs_reference_fixture():
+    """tests/golden/align_greedy.npz: five alignments of the reference's ``forced_align`` and the
+    greedy collapse its own ``calculate_cer_ctc`` produced (make_golden.py ``make_align_greedy``)."""
+    g = load_npz("align_greedy.npz")
+    for i in range(int(g["align_n"])):
+        ali = ctc_numpy.viterbi_align(g[f"align{i}__lp"], g[f"align{i}__y"])
+        np.testing.assert_array_equal(np.asarray(ali), g[f"align{i}__ali"], err_msg=f"case {i}")
+    am = ctc_numpy.argmax(g["greedy__logits"])
+    for b in range(am.shape[0]):
+        want = g["greedy__ids"][b, : int(g["greedy__lens"][b])].tolist()
+        assert ctc_numpy.greedy_collapse(am[b]) == want, b
+
+
 def test_numpy_ctc_c1():
     g = load_npz("ctc_c1.npz")
     off = np.concatenate(([0], np.cumsum(g["tgt_lens"])))
