@@ -27,6 +27,8 @@ import torch  # noqa: E402
 
 C2 = dict(B=64, T=500, V=5000, lmin=75, lmax=150)
 METRIC = "ctc_fwd_bwd_utt_frames_per_s"
+# the same string in both arms' `config` (the driver compares the dicts); it describes the GPU arm
+L2_NOTE = "inputs (640 MB logits per step) exceed the 126 MB L2; no flush needed"
 UNIT = "utt-frames/s"
 
 
@@ -162,7 +164,8 @@ def run_reference(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": "C2 LibriSpeech-100 BPE-5000 CTC: B=64,T=500,V=5000,L in [75,150], fp32 fwd+bwd"},
+        "config": {"workload": "C2 LibriSpeech-100 BPE-5000 CTC: B=64,T=500,V=5000,L in [75,150], fp32 fwd+bwd",
+                   "l2": L2_NOTE},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
                          "sample": "full C2 batch per step: torch-CPU log_softmax+ctc_loss(reduction=none,"
                                    "zero_infinity)+backward via oracle/espnet_cpu.loss_and_backward "
@@ -597,12 +600,13 @@ def run_gpu(args):
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
+        # `config` is exactly the reference arm's at N=1 (the driver compares the two dicts)
         "config": {"workload": "C2 LibriSpeech-100 BPE-5000 CTC: B=64,T=500,V=5000,L in [75,150], fp32 fwd+bwd"
                                + (f" per rank (utterance-sharded; loss exchange: {exchange})" if dist_on else ""),
-                   "l2": "inputs (640 MB logits) exceed the 126 MB L2; no flush needed",
-                   "api": "espnet1_b200.espnet2.asr.ctc.CTC.loss_fn + backward; max_tgt_len= is passed (an "
-                          "extension of the reference signature espnet2/asr/ctc.py:52 that CTC.forward fills "
-                          "from ys_pad.size(1)); without it loss_fn reads max(ys_lens) back from the device"},
+                   "l2": L2_NOTE},
+        "notes": {"api": "espnet1_b200.espnet2.asr.ctc.CTC.loss_fn + backward; max_tgt_len= is passed (an "
+                         "extension of the reference signature espnet2/asr/ctc.py:52 that CTC.forward fills "
+                         "from ys_pad.size(1)); without it loss_fn reads max(ys_lens) back from the device"},
         # headline fraction = the WHOLE STEP (north_star: "CTC fwd+bwd ... reaching >= 60% of HBM
         # roofline"): SURVEY 8(d)'s algorithmic bytes / the step's device time / measured copy peak.
         # kernel_* = the dominant kernel alone (its own CUDA-event duration, same bytes).
