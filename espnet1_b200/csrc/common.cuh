@@ -56,7 +56,8 @@ static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 b
   // beside the running gather and the latency-bound recursion shares issue slots
   // (0.405 ms/step); with the trigger at the end, or never (implicit at completion, the
   // default), the kernel boundaries just get cheaper: 0.386 vs 0.393 ms without.
-  static const int pdl_mask = tuning_int("B200CTC_PDL", 7);
+  // bits: 0 lattice, 1 gradient row pass, 2 nll, 3 emission gather, 4 rescale check
+  static const int pdl_mask = tuning_int("B200CTC_PDL", 31);
   cfg.numAttrs = (pdl_bit >= 0 && ((pdl_mask >> pdl_bit) & 1)) ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }

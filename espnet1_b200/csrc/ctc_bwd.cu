@@ -641,6 +641,7 @@ __global__ void __launch_bounds__(256) rescale_kernel(T* __restrict__ grad, int6
                                                       const float* __restrict__ hints) {
   constexpr int N = Elems<T>::N;
   const int b = blockIdx.y;
+  griddep_wait();  // (programmatic launch: gscale / grad come from the previous kernels)
   const float gv = gscale[(size_t)b * gstride] * gmul;
   const float hint = hints ? hints[b] : hint0;
   if (gv == hint) return;
@@ -712,17 +713,17 @@ static int grad_rescale_impl(void* grad, int dtype, const float* gscale, int gsc
   prof_mark(6, 0, st);
   switch (dtype) {
     case B200CTC_F32:
-      rescale_kernel<float><<<grid, 256, 0, st>>>(static_cast<float*>(grad), per_utt, gscale,
-                                                  gscale_stride, gscale_mul, grad_hint, utt_hints);
+      launch_pdl(rescale_kernel<float>, grid, dim3(256), 0, st, 4, static_cast<float*>(grad), per_utt,
+                 gscale, gscale_stride, gscale_mul, grad_hint, utt_hints);
       break;
     case B200CTC_F16:
-      rescale_kernel<__half><<<grid, 256, 0, st>>>(static_cast<__half*>(grad), per_utt, gscale,
-                                                   gscale_stride, gscale_mul, grad_hint, utt_hints);
+      launch_pdl(rescale_kernel<__half>, grid, dim3(256), 0, st, 4, static_cast<__half*>(grad), per_utt,
+                 gscale, gscale_stride, gscale_mul, grad_hint, utt_hints);
       break;
     default:
-      rescale_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(static_cast<__nv_bfloat16*>(grad), per_utt,
-                                                          gscale, gscale_stride, gscale_mul, grad_hint,
-                                                          utt_hints);
+      launch_pdl(rescale_kernel<__nv_bfloat16>, grid, dim3(256), 0, st, 4,
+                 static_cast<__nv_bfloat16*>(grad), per_utt, gscale, gscale_stride, gscale_mul, grad_hint,
+                 utt_hints);
       break;
   }
   prof_mark(6, 1, st);

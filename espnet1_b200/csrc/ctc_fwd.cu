@@ -150,8 +150,14 @@ __device__ __forceinline__ float ldg_gather(const T* p) {
   return to_f32<T>(__ldg(p));
 #endif
 }
-constexpr int kGatherWarps = 8;
-constexpr int kGatherRows = 4;   // rows per warp in flight
+#ifndef B200CTC_GATHER_WARPS
+#define B200CTC_GATHER_WARPS 8
+#endif
+#ifndef B200CTC_GATHER_ROWS
+#define B200CTC_GATHER_ROWS 1
+#endif
+constexpr int kGatherWarps = B200CTC_GATHER_WARPS;
+constexpr int kGatherRows = B200CTC_GATHER_ROWS;   // rows per warp in flight
 constexpr int kGatherRegs = 8;   // values kept in registers per lane and row (L+1 <= 256)
 
 template <typename T>
@@ -159,6 +165,9 @@ __global__ void __launch_bounds__(kGatherWarps * 32) gather_kernel(
     const T* __restrict__ logits, PrepArgs P, float* __restrict__ em, float* __restrict__ cmax,
     int pdl) {
   extern __shared__ int slab[];  // [Lp] label columns of this utterance
+  // launched with programmatic stream serialisation (its launch latency overlaps the tail of the
+  // previous kernel); everything it reads may come from that kernel: wait first
+  griddep_wait();
   if (pdl == 0) griddep_launch();  // the lattice CTAs may become resident and set up meanwhile
   struct AtExit {  // every return path below fires the end-of-kernel trigger
     int pdl;
@@ -234,9 +243,8 @@ static int launch_gather(const void* logits, const PrepArgs& P, int B, const Los
   const size_t smem = sizeof(int) * (size_t)w.Lp;
   auto k = gather_kernel<T>;
   if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  k<<<grid, kGatherWarps * 32, smem, st>>>(static_cast<const T*>(logits), P,
-                                           reinterpret_cast<float*>(ws + w.em),
-                                           reinterpret_cast<float*>(ws + w.cmax), pdl_mode());
+  launch_pdl(k, grid, dim3(kGatherWarps * 32), smem, st, 3, static_cast<const T*>(logits), P,
+             reinterpret_cast<float*>(ws + w.em), reinterpret_cast<float*>(ws + w.cmax), pdl_mode());
   count_launch();
   return check_launch("ctc gather");
 }
