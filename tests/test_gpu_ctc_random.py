@@ -302,3 +302,70 @@ def test_argmax_integer_identical_to_torch(V, dtype):
     x[6] = torch.round(x[6])                   # many ties
     got = F.argmax(x.to(DEV)).cpu()
     assert torch.equal(got, x.float().argmax(-1)), (V, dtype)
+
+
+def _sweep_cases():
+    """Seeded shapes chosen to straddle every dispatch threshold of the loss path: V*4 % 16 != 0
+    (non-TMA rows), V <= 5120 / > 5120 (128 vs 256 threads per row), 2L+1 around 3*128 (short vs
+    long row staging), L+1 around V*4/64 (sparse vs dense emission gather), S > 1024 with few
+    utterances (split lattice), T % 16 != 0, T < 16, B = 1."""
+    g = torch.Generator().manual_seed(2024)
+    cases = []
+    for i in range(28):
+        V = int([7, 30, 33, 64, 127, 512, 1000, 2049, 5000, 5124][int(torch.randint(0, 10, (1,), generator=g))])
+        T = int([3, 15, 16, 17, 61, 128, 200, 333][int(torch.randint(0, 8, (1,), generator=g))])
+        B = int([1, 2, 3, 5, 9][int(torch.randint(0, 5, (1,), generator=g))])
+        lmax = int([0, 1, 4, 20, 60, 150, 191, 192, 200][int(torch.randint(0, 9, (1,), generator=g))])
+        lmax = max(0, min(lmax, T))  # some utterances still end up infeasible through repeats
+        cases.append((B, T, V, lmax, 500 + i))
+    cases += [(2, 1400, 96, 560, 901), (3, 1100, 5000, 540, 902), (1, 2200, 40, 1000, 903)]  # wide lattices
+    return cases
+
+
+def compare_vs_fp64(logits, tg, il, tl):
+    """The yardstick for small batches: with B = 1..9 the gradient is not scaled down by 1/64 as at
+    C2, and torch's own fp32 log-space lattice is off by up to a few 1e-3 RELATIVE at T ~ 300
+     - so the truth is the same torch CPU path in fp64.  At unit upstream
+    scale (gradient times B) we must be within 2e-4 absolute of it AND at least as close to it as
+    torch-fp32 is (plus rounding slack)."""
+    B = logits.shape[0]
+    n64, g64 = espnet_cpu.logits_loss_and_grad(logits.double(), tg, il, tl)
+    n32, g32 = espnet_cpu.logits_loss_and_grad(logits, tg, il, tl)
+    nll, g = run_cuda(logits, tg, il, tl)
+    np.testing.assert_allclose(nll.numpy(), n64.float().numpy(), rtol=1e-5, atol=1e-6)
+    err_ours = float((g.double() - g64).abs().max()) * B
+    err_ref = float((g32.double() - g64).abs().max()) * B
+    # measured over the sweep on B200: ours <= 2.2e-4, torch-fp32 up to 2.2e-3 (both at unit scale)
+    assert err_ours <= 5e-4, (err_ours, err_ref)
+    assert err_ours <= err_ref + 2e-5, (err_ours, err_ref)
+    return nll, g
+
+
+@pytest.mark.parametrize("B,T,V,lmax,seed", _sweep_cases())
+def test_randomised_shape_sweep_fp32(B, T, V, lmax, seed):
+    logits, tg, il, tl = make_case(B, T, V, 0, lmax, seed=seed, ragged=True, repeat_p=0.3 if seed % 2 else 0.0)
+    if seed % 5 == 0 and B > 1:
+        tl[-1] = 0  # an empty target
+        tg = tg[: int(tl.sum())]
+    nll, g = compare_vs_fp64(logits, tg, il, tl)
+    # frames beyond an utterance's length carry no gradient; an infeasible utterance none at all
+    for b in range(B):
+        assert torch.all(g[b, il[b]:] == 0)
+        if nll[b] == 0 and tl[b] > 0:
+            assert torch.all(g[b] == 0)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("B,T,V,lmax,seed", [(3, 61, 512, 20, 31), (2, 200, 5000, 150, 32), (2, 333, 1000, 192, 33),
+                                            (1, 1400, 96, 560, 34), (4, 17, 33, 4, 35)])
+def test_randomised_shape_sweep_16bit(B, T, V, lmax, seed, dtype):
+    """16-bit logits in, 16-bit gradient out, fp32 arithmetic.  Checker: the torch CPU path in fp64
+    on the SAME rounded inputs; the gradient tolerance is the output rounding (bf16 keeps 8 bits:
+    2^-8 relative) plus the fp32 slack of the sweep above, at the batch's own 1/B scale."""
+    logits, tg, il, tl = make_case(B, T, V, 1, lmax, seed=seed, ragged=True, repeat_p=0.2)
+    src = logits.to(dtype).double()
+    n64, g64 = espnet_cpu.logits_loss_and_grad(src, tg, il, tl)
+    nll, g = run_cuda(logits, tg, il, tl, dtype)
+    np.testing.assert_allclose(nll.numpy(), n64.float().numpy(), rtol=2e-5, atol=1e-6)
+    rel = 2.0 ** -8 if dtype == torch.bfloat16 else 2.0 ** -11
+    np.testing.assert_allclose(g.double().numpy(), g64.numpy(), rtol=rel, atol=5e-4 / B)
