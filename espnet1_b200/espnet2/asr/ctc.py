@@ -137,7 +137,9 @@ class CTC(torch.nn.Module):
         with it backward is a no-op check per utterance, without it (or with other factors)
         gradients are still exact, the mismatching heads pay one rescaling pass."""
         H = len(hs_pads)
-        if H <= 1 or not hs_pads[0].is_cuda or self.ctc_type != "builtin":
+        # (with a sharded-loss exchange attached every head must make its own exchange call, in
+        #  the same order on every rank: one `forward` per head, as the reference issues them)
+        if H <= 1 or not hs_pads[0].is_cuda or self.ctc_type != "builtin" or self.loss_exchange is not None:
             return [self.forward(hs, hlens, ys_pad, ys_lens) for hs in hs_pads]
         import numpy as np
 

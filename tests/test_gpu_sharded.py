@@ -67,6 +67,29 @@ def test_deferred_exchange_reads_the_latest_step():
     ex.close()
 
 
+def test_forward_multi_with_an_exchange_attached_exchanges_once_per_head():
+    """Sharded training + intermediate CTC: `forward_multi` must not bypass `loss_exchange` - every
+    head makes its own exchange (the batched single call has no batch reduction to exchange)."""
+    from espnet1_b200.espnet2.asr.ctc import CTC
+    from espnet1_b200.sharded import PeerLossExchange
+
+    g = torch.Generator().manual_seed(6)
+    Bn, T, D, V = 4, 40, 8, 30
+    hs = [torch.randn(Bn, T, D, generator=g).to(DEV).requires_grad_(True) for _ in range(3)]
+    hl = torch.tensor([40, 31, 40, 22], device=DEV)
+    yl = torch.tensor([5, 2, 7, 3], device=DEV)
+    ys = torch.randint(1, V, (Bn, 7), generator=g).to(DEV)
+    m = CTC(V, D).to(DEV)
+    want = [float(m(h, hl, ys, yl).detach()) for h in hs]
+    m.loss_exchange = PeerLossExchange()
+    got = m.forward_multi(hs, hl, ys, yl)
+    sum(got).backward()
+    assert [float(v.detach()) for v in got] == want
+    out = m.loss_exchange.out.tolist()  # the LAST head's exchange
+    assert out[1] == float(Bn) and abs(out[0] - want[-1]) <= 1e-6 * abs(want[-1])
+    m.loss_exchange.close()
+
+
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
 def test_two_ranks_match_the_nccl_allreduce():
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
