@@ -224,8 +224,12 @@ def bench_prefix(dev, steps=20):
     out = {}
     for name, snum, margin, n, n_cpu in (("snum15_margin0", 15, 0, steps, 3),
                                          ("snum15_margin20", 15, 20, steps, 3),
-                                         ("fullvocab_margin20", None, 20, 3, 1)):
-        sc = CTCPrefixScoreTH(lpz.clone().to(dev), xl, 0, V - 1, margin=margin)
+                                         ("fullvocab_margin20", None, 20, 3, 1),
+                                         # extension: per-utterance windows, computed and consumed on
+                                         # the device (no read-back); no reference counterpart to time
+                                         ("snum15_margin20_per_utt_window", 15, 20, steps, 0)):
+        sc = CTCPrefixScoreTH(lpz.clone().to(dev), xl, 0, V - 1, margin=margin,
+                              per_utt_window=name.endswith("per_utt_window"))
         pre = [inputs(i, snum, margin, dev) for i in range(n + 1)]
         # prefixes as a device tensor, as BatchBeamSearch passes them (batch_beam_search.py:
         # hyp.yseq); steps are issued back to back and timed as one region (CUDA events),
