@@ -71,10 +71,30 @@ SIGNATURES = {
     "b200ctc_beam_select": (c_int, [_P, _P, _P, c_int, _P, _P, _P, c_int64, c_int, _P, _P, c_int,
                                     c_int, c_int, c_int, c_int, c_int, _P, _P, _P, _P, _P, c_int64,
                                     _P, _P]),
+    "b200ctc_beam_plan_bytes": (c_size_t, []),
+    "b200ctc_beam_position": (c_int, [_P, _P, _P, c_int, c_int, _P]),
     "b200ctc_loss_fwd_bwd_host": (c_int, [_P, c_int, _P, _P, _P, c_int, c_int, c_int, c_int,
                                           c_int, c_float, _P, _P, POINTER(c_void_p), c_int]),
     "b200ctc_host_pipeline_release": (None, []),
 }
+
+
+class BeamPlan(ctypes.Structure):
+    """``b200ctc_beam_plan`` (include/b200ctc.h): the per-decode buffers of
+    ``b200ctc_beam_position``.  ``lib()`` checks the size against the library's own."""
+
+    _fields_ = [
+        ("U", ctypes.c_int32), ("W", ctypes.c_int32), ("V", ctypes.c_int32), ("T", ctypes.c_int32),
+        ("snum", ctypes.c_int32), ("K_full", ctypes.c_int32), ("prebeam_key", ctypes.c_int32),
+        ("blank", ctypes.c_int32), ("eos", ctypes.c_int32), ("logzero", c_float),
+        ("weights", c_float * 8),
+        ("lp", _P), ("lp_t", _P), ("lp_t_ld", c_int64), ("end_frames", _P),
+        ("r_state", _P * 2), ("s_state", _P * 2), ("r", _P), ("log_psi", _P), ("ctc_scores", _P),
+        ("idmap", _P), ("rsum", _P), ("last_ids", _P), ("part_ids", _P),
+        ("run_score", _P * 2), ("cum", _P * 2), ("yseq", _P * 2), ("yseq_stride", c_int64),
+        ("active", _P), ("maxlen", _P), ("out_val", _P), ("out_flat", _P),
+        ("pack", _P), ("pack_host", _P),
+    ]
 
 
 def lib():
@@ -90,6 +110,9 @@ def lib():
             fn = getattr(h, name)
             fn.restype = res
             fn.argtypes = args
+        if h.b200ctc_beam_plan_bytes() != ctypes.sizeof(BeamPlan):
+            raise RuntimeError("b200ctc_beam_plan: the ctypes mirror and the library disagree on the layout "
+                               f"({ctypes.sizeof(BeamPlan)} vs {h.b200ctc_beam_plan_bytes()} bytes)")
         _lib = h
     return _lib
 

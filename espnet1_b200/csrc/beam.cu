@@ -25,6 +25,26 @@ namespace b200ctc {
 constexpr int kBeamMaxScorers = B200CTC_BEAM_MAX_SCORERS;
 constexpr int kBeamMaxK = 64;  // winners per segment
 
+__device__ __forceinline__ unsigned cluster_ctarank() {
+  unsigned r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// read one word of CTA `rank`'s shared memory (same offset as `p` in mine)
+__device__ __forceinline__ unsigned ld_dsmem_u32(const void* p, int rank) {
+  unsigned a = (unsigned)__cvta_generic_to_shared(p), ra, v;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(a), "r"(rank));
+  asm volatile("ld.shared::cluster.u32 %0, [%1];" : "=r"(v) : "r"(ra) : "memory");
+  return v;
+}
+__device__ __forceinline__ float ld_dsmem_f32(const float* p, int rank) {
+  return __uint_as_float(ld_dsmem_u32(p, rank));
+}
+__device__ __forceinline__ int ld_dsmem_i32(const int* p, int rank) { return (int)ld_dsmem_u32(p, rank); }
+
 struct BeamScores {
   const float* p[kBeamMaxScorers];
   long long rs[kBeamMaxScorers], cs[kBeamMaxScorers];  // row / column strides in elements
@@ -32,20 +52,56 @@ struct BeamScores {
   int K;
 };
 
+// The k best of n <= 2048 DISTINCT candidates (value, index; index 0x7fffffff = empty slot) by
+// rank counting: every thread takes candidates, counts how many beat each (the candidate list
+// is read by all threads in step: shared-memory broadcasts) and files it under its rank.  No
+// serial rounds: one warp selecting k times over the list kept the other warps at a barrier
+// for a third of the kernel.  Ends with a barrier; res_* hold the winners in order.
+template <int NT>
+__device__ __forceinline__ void rank_select(const float* cv, const int* ce, int n, int k, float* res_v,
+                                            int* res_e) {
+  const int tid = threadIdx.x;
+  if (tid < k) { res_v[tid] = kNegInf; res_e[tid] = 0; }  // fewer than k candidates: like the first version
+  __syncthreads();
+  for (int i = tid; i < n; i += NT) {
+    const float x = cv[i];
+    const int e = ce[i];
+    if (e == 0x7fffffff) continue;
+    int rank = 0;
+    for (int j = 0; j < n; ++j) {
+      const float y = cv[j];
+      const int f = ce[j];
+      rank += (f != 0x7fffffff && (y > x || (y == x && f < e))) ? 1 : 0;
+    }
+    if (rank < k) { res_v[rank] = x; res_e[rank] = e; }
+  }
+  __syncthreads();
+}
+
 // Phase 1: every thread evaluates its strided share of the segment (rows of V entries
 // starting at row0; element e = i*NT + tid), 8 elements x K matrices of independent loads
 // in flight, each element accumulating its terms in scorer order (the reference's fp32
 // operation order); the values go to shared memory, the thread keeps its own maximum.
-// Phase 2: k rounds of block-wide arg-max (warp shuffles + one shared-memory hop, ties ->
-// lower index); the owner of a winner retires it and rescans its share.
+// Phase 2: the k best, ties -> lower index (two levels, see below).
+// `off`: the CTA owns elements [off, off + E) of a larger segment (a cluster shares one
+// utterance, below); vals[] is indexed locally, the reported winners res_e[] carry LOCAL
+// indices too (the caller adds `off`; ties inside a slice are by index either way).
 template <int NT>
 __device__ __forceinline__ void segment_topk(const BeamScores& S, long long row0, int V, int E,
                                              const float* __restrict__ run, int k, float* vals,
-                                             float* res_v, int* res_e, float* sm_v, int* sm_e) {
+                                             float* res_v, int* res_e, int off = 0) {
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   constexpr int NWARP = NT / 32, UN = 8;
-  float bv = kNegInf;
-  int be = 0x7fffffff;
+  // the thread's best AND second best: a retired winner is replaced without a rescan of the
+  // share (a dependent chain of E/NT shared-memory reads - it, not the barriers, was most of a
+  // round); only a thread that wins twice rescans
+  float bv = kNegInf, sv = kNegInf;
+  int be = 0x7fffffff, se = 0x7fffffff;
+  bool stale = false;  // the second best is unknown (it was promoted)
+  auto offer = [&](float x, int e) {
+    if (x > bv || (x == bv && e < be)) { sv = bv; se = be; bv = x; be = e; }
+    else if (x > sv || (x == sv && e < se)) { sv = x; se = e; }
+  };
   for (int e0 = tid; e0 < E; e0 += NT * UN) {
     float acc[UN];
     long long row[UN];
@@ -53,7 +109,7 @@ __device__ __forceinline__ void segment_topk(const BeamScores& S, long long row0
 #pragma unroll
     for (int j = 0; j < UN; ++j) {
       const int e = e0 + j * NT;
-      const int ec = e < E ? e : 0;
+      const int ec = (e < E ? e : 0) + off;
       const int h = ec / V;
       row[j] = row0 + h;
       col[j] = ec - h * V;
@@ -78,10 +134,20 @@ __device__ __forceinline__ void segment_topk(const BeamScores& S, long long row0
         if (run) x = __fadd_rn(x, __ldg(run + row[j]));
         if (!(x == x)) x = kNegInf;  // NaN never wins (and NaN is free to mark retired winners)
         vals[e] = x;
-        if (x > bv || (x == bv && e < be)) { bv = x; be = e; }  // -inf entries are candidates too
+        offer(x, e);  // -inf entries are candidates too
       }
     }
   }
+  // Phase 2, two levels.  (a) every WARP selects the k best of its own lanes' shares: k rounds
+  // of shuffle-only arg-max, the owner of a winner retires it (NaN: compares false with
+  // everything, so it can never win again - also when the finite candidates are exhausted and
+  // -inf entries are being handed out: the winners stay DISTINCT, lowest index first, like
+  // torch.topk) and rescans its share.  No block barrier inside the rounds: the first version
+  // (k block-wide rounds, two __syncthreads each) spent 1.5 us per round - 23 us of a pre-beam
+  // launch, 40 us of a pruning launch.  (b) the global k best are among the NWARP*k warp winners
+  // (one total order - value descending, index ascending - at both levels): one warp merges them.
+  float* wl_v = vals + ((E + 31) & ~31);  // NWARP * k warp winners, behind the segment
+  int* wl_e = reinterpret_cast<int*>(wl_v + NWARP * k);
   for (int r = 0; r < k; ++r) {
     float cv = bv;
     int ce = be;
@@ -91,34 +157,21 @@ __device__ __forceinline__ void segment_topk(const BeamScores& S, long long row0
       const int oe = __shfl_xor_sync(0xffffffffu, ce, o);
       if (ov > cv || (ov == cv && oe < ce)) { cv = ov; ce = oe; }
     }
-    if (lane == 0) { sm_v[wid] = cv; sm_e[wid] = ce; }
-    __syncthreads();
-    if (wid == 0) {
-      cv = lane < NWARP ? sm_v[lane] : kNegInf;
-      ce = lane < NWARP ? sm_e[lane] : 0x7fffffff;
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        const float ov = __shfl_xor_sync(0xffffffffu, cv, o);
-        const int oe = __shfl_xor_sync(0xffffffffu, ce, o);
-        if (ov > cv || (ov == cv && oe < ce)) { cv = ov; ce = oe; }
-      }
-      if (lane == 0) { res_v[r] = cv; res_e[r] = ce < E ? ce : 0; }
-    }
-    __syncthreads();
-    // retire the winner (NaN: compares false with everything, so it can never win again -
-    // also when the finite candidates are exhausted and -inf entries are being handed out:
-    // the k winners stay DISTINCT, lowest index first, like torch.topk) and rescan my share
-    const int we = res_e[r];
-    if ((we % NT) == tid) {
-      vals[we] = __int_as_float(0x7fc00000);
-      bv = kNegInf;
-      be = 0x7fffffff;
-      for (int e = tid; e < E; e += NT) {
-        const float x = vals[e];
-        if (x > bv || (x == bv && e < be)) { bv = x; be = e; }
+    if (lane == 0) { wl_v[wid * k + r] = cv; wl_e[wid * k + r] = ce; }
+    if (ce == be && ce != 0x7fffffff) {  // mine: retire it
+      vals[ce] = __int_as_float(0x7fc00000);
+      if (!stale) {
+        bv = sv; be = se; stale = true;
+      } else {
+        bv = sv = kNegInf;
+        be = se = 0x7fffffff;
+        for (int e = tid; e < E; e += NT) offer(vals[e], e);  // NaN (retired) never enters
+        stale = false;
       }
     }
   }
+  __syncthreads();
+  rank_select<NT>(wl_v, wl_e, NWARP * k, k, res_v, res_e);
 }
 
 template <int NT>
@@ -130,12 +183,12 @@ __global__ void __launch_bounds__(NT) beam_select_kernel(
     float* __restrict__ out_run, float* __restrict__ cum_out, int64_t* __restrict__ yseq_out,
     long long ys_out_stride, float* __restrict__ pack) {
   extern __shared__ float vals[];  // the segment's W*V weighted scores
-  __shared__ float res_v[kBeamMaxK], sm_v[32];
-  __shared__ int res_e[kBeamMaxK], sm_e[32];
+  __shared__ float res_v[kBeamMaxK];
+  __shared__ int res_e[kBeamMaxK];
   const int u = blockIdx.x, U = gridDim.x, tid = threadIdx.x;
   const int E = W * V;
   const long long n_in = (long long)U * W, n_out = (long long)U * k;
-  segment_topk<NT>(S, (long long)u * W, V, E, run, k, vals, res_v, res_e, sm_v, sm_e);
+  segment_topk<NT>(S, (long long)u * W, V, E, run, k, vals, res_v, res_e);
   __syncthreads();
   const bool act = (active ? active[u] != 0 : true) && !(maxlen && maxlen[u] - 1 == step_i);
   if (tid < k) {
@@ -158,11 +211,81 @@ __global__ void __launch_bounds__(NT) beam_select_kernel(
     }
     yseq_out[o * ys_out_stride + cur_len] = tok;
   }
-  for (int j = 0; j < k; ++j) {  // prefix rows: yseq_out[j] = yseq_in[prev_j] ++ tok_j
+  // prefix rows: yseq_out[j] = yseq_in[prev_j] ++ tok_j - one flat pass (k dependent
+  // load -> store round trips in a row cost more than the selection)
+  for (int i = tid; i < k * cur_len; i += NT) {
+    const int j = i / cur_len, cpos = i - j * cur_len;
     const int prev = res_e[j] / V;
-    const int64_t* src = yseq_in + ((long long)u * W + prev) * ys_in_stride;
-    int64_t* dst = yseq_out + ((long long)u * k + j) * ys_out_stride;
-    for (int c = tid; c < cur_len; c += NT) dst[c] = src[c];
+    yseq_out[((long long)u * k + j) * ys_out_stride + cpos] =
+        yseq_in[((long long)u * W + prev) * ys_in_stride + cpos];
+  }
+}
+
+// The same step with one utterance's segment shared by a thread-block CLUSTER of C CTAs: with
+// one CTA per utterance 32 utterances occupy 32 of 148 SMs and a CTA walks 50 K values alone
+// (62 us per position, as long as the prefix scoring itself).  Every CTA of the cluster takes a
+// contiguous slice of the W*V entries, finds its own k best (the global k best are among them:
+// one total order - value descending, index ascending - everywhere), and CTA 0 merges the C
+// sorted lists out of its neighbours' shared memory (DSMEM) and writes the step's outputs.
+template <int NT>
+__global__ void __launch_bounds__(NT) beam_select_cluster_kernel(
+    const __grid_constant__ BeamScores S, const float* __restrict__ run, const float* __restrict__ cum_in,
+    const int64_t* __restrict__ yseq_in, long long ys_in_stride, int cur_len,
+    const unsigned char* __restrict__ active, const int* __restrict__ maxlen, int step_i, int W,
+    int V, int k, int eos, float* __restrict__ out_val, int64_t* __restrict__ out_flat,
+    float* __restrict__ out_run, float* __restrict__ cum_out, int64_t* __restrict__ yseq_out,
+    long long ys_out_stride, float* __restrict__ pack, int C, int slice) {
+  extern __shared__ float vals[];  // this CTA's slice of the weighted scores
+  __shared__ float res_v[kBeamMaxK];
+  __shared__ int res_e[kBeamMaxK];
+  __shared__ float mg_v[8 * kBeamMaxK];  // CTA 0: the C candidate lists
+  __shared__ int mg_e[8 * kBeamMaxK];
+  const int c = (int)cluster_ctarank(), u = blockIdx.x / C, U = gridDim.x / C, tid = threadIdx.x;
+  const int E = W * V;
+  const int off = c * slice, mine = min(slice, E - off);  // the launcher keeps mine >= k
+  const long long n_in = (long long)U * W, n_out = (long long)U * k;
+  segment_topk<NT>(S, (long long)u * W, V, mine, run, k, vals, res_v, res_e, off);
+  __syncthreads();
+  cluster_sync_all();  // every CTA's res_v / res_e are complete and visible cluster-wide
+  if (c == 0) {
+    for (int i = tid; i < C * k; i += NT) {
+      const int src = i / k, j = i - src * k;
+      mg_v[i] = ld_dsmem_f32(&res_v[j], src);
+      mg_e[i] = ld_dsmem_i32(&res_e[j], src) + src * slice;
+    }
+  }
+  cluster_sync_all();  // the neighbours may exit: their lists have been copied
+  if (c != 0) return;
+  __syncthreads();
+  rank_select<NT>(mg_v, mg_e, C * k, k, res_v, res_e);
+  const bool act = (active ? active[u] != 0 : true) && !(maxlen && maxlen[u] - 1 == step_i);
+  if (tid < k) {
+    const int j = tid, e = res_e[j];
+    const float val = res_v[j];
+    const int prev = e / V, tok = e - prev * V;
+    const long long row = (long long)u * W + prev, o = (long long)u * k + j;
+    out_val[o] = val;
+    out_flat[o] = e;
+    const bool alive = act && tok != eos && val > kNegInf;
+    out_run[o] = alive ? val : kNegInf;
+    pack[o] = val;
+    pack[n_out + o] = (float)prev;
+    pack[2 * n_out + o] = (float)tok;
+    for (int q = 0; q < S.K; ++q) {
+      const float cq = __fadd_rn(cum_in[(long long)q * n_in + row],
+                                 S.p[q][row * S.rs[q] + (long long)tok * S.cs[q]]);
+      cum_out[(long long)q * n_out + o] = cq;
+      pack[(3 + q) * n_out + o] = cq;
+    }
+    yseq_out[o * ys_out_stride + cur_len] = tok;
+  }
+  // prefix rows: yseq_out[j] = yseq_in[prev_j] ++ tok_j - one flat pass (k dependent
+  // load -> store round trips in a row cost more than the selection)
+  for (int i = tid; i < k * cur_len; i += NT) {
+    const int j = i / cur_len, cpos = i - j * cur_len;
+    const int prev = res_e[j] / V;
+    yseq_out[((long long)u * k + j) * ys_out_stride + cpos] =
+        yseq_in[((long long)u * W + prev) * ys_in_stride + cpos];
   }
 }
 
@@ -170,15 +293,20 @@ template <int NT>
 __global__ void __launch_bounds__(NT) beam_prebeam_kernel(const __grid_constant__ BeamScores S, int V,
                                                           int k, int64_t* __restrict__ out_ids) {
   extern __shared__ float vals[];
-  __shared__ float res_v[kBeamMaxK], sm_v[32];
-  __shared__ int res_e[kBeamMaxK], sm_e[32];
+  __shared__ float res_v[kBeamMaxK];
+  __shared__ int res_e[kBeamMaxK];
   const long long row = blockIdx.x;
-  segment_topk<NT>(S, row, V, V, nullptr, k, vals, res_v, res_e, sm_v, sm_e);
+  segment_topk<NT>(S, row, V, V, nullptr, k, vals, res_v, res_e);
   __syncthreads();
   if (threadIdx.x < k) out_ids[row * k + threadIdx.x] = res_e[threadIdx.x];
 }
 
-constexpr long long kBeamMaxSegment = 56 * 1024;  // fp32 values of one segment in shared memory
+constexpr long long kBeamMaxSegment = 54 * 1024;  // fp32 values of one segment in shared memory
+constexpr size_t kBeamSmemBudget = 227 * 1024 - 6 * 1024;  // dynamic; the rest: static arrays
+// dynamic shared memory of a selection CTA: its segment + the warps' winner lists
+static size_t topk_smem(long long E, int nt, int k) {
+  return (size_t)((E + 31) & ~31LL) * 4 + (size_t)(nt / 32) * k * 8;
+}
 
 template <typename Kern>
 static int beam_smem(Kern kern, size_t bytes) {
@@ -224,7 +352,44 @@ extern "C" int b200ctc_beam_select(const float* const* score_ptrs, const int64_t
   B2_REQUIRE(E <= kBeamMaxSegment, "beam_select: beam x vocabulary = %lld exceeds %lld", E, kBeamMaxSegment);
   B2_REQUIRE(cur_len >= 0 && cur_len < yseq_out_stride && cur_len <= yseq_in_stride, "beam_select: prefix buffers too short");
   auto st = static_cast<cudaStream_t>(stream);
-  const size_t smem = (size_t)E * 4;
+  // few utterances x a large segment: a cluster of C CTAs per utterance (see the kernel)
+  static const int cluster_on = tuning_int("B200CTC_BEAM_CLUSTER", 1);
+  // (one CTA of 512 threads per SM at 90 registers: all clusters in ONE wave of 148 SMs)
+  const int C = (!cluster_on || E < 16384) ? 1 : U <= 18 ? 8 : U <= 37 ? 4 : U <= 74 ? 2 : 1;
+  if (C > 1) {
+    constexpr int NT = 512;
+    const int slice = (int)((E + C - 1) / C);
+    const size_t smem_c = topk_smem(slice, NT, k);
+    if (int rc = beam_smem(beam_select_cluster_kernel<NT>, smem_c)) return rc;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(U * C));
+    cfg.blockDim = dim3(NT);
+    cfg.dynamicSmemBytes = smem_c;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = (unsigned)C;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, beam_select_cluster_kernel<NT>, S, run_score, cum_in, yseq_in,
+                                       (long long)yseq_in_stride, cur_len, active, maxlen, step_i, W, V, k, eos,
+                                       out_val, out_flat, out_run, cum_out, yseq_out,
+                                       (long long)yseq_out_stride, pack, C, slice);
+    if (e != cudaSuccess) {
+      set_error("beam_select: cluster launch: %s", cudaGetErrorString(e));
+      cudaGetLastError();
+      return B200CTC_ERR_DEVICE;
+    }
+    count_launch();
+    return check_launch("beam_select");
+  }
+  // most threads whose winner lists still fit beside the segment
+  const int nt = E <= 4096 ? 256 : topk_smem(E, 1024, k) <= kBeamSmemBudget ? 1024
+               : topk_smem(E, 512, k) <= kBeamSmemBudget ? 512 : 256;
+  const size_t smem = topk_smem(E, nt, k);
+  B2_REQUIRE(smem <= kBeamSmemBudget, "beam_select: beam x vocabulary = %lld with k = %d does not fit shared memory", E, k);
 #define GO(NT)                                                                                     \
   do {                                                                                             \
     if (int rc = beam_smem(beam_select_kernel<NT>, smem)) return rc;                               \
@@ -233,7 +398,8 @@ extern "C" int b200ctc_beam_select(const float* const* score_ptrs, const int64_t
                                                 out_val, out_flat, out_run, cum_out, yseq_out,     \
                                                 yseq_out_stride, pack);                            \
   } while (0)
-  if (E <= 4096) GO(256);
+  if (nt == 256) GO(256);
+  else if (nt == 512) GO(512);
   else GO(1024);
 #undef GO
   count_launch();
@@ -248,13 +414,17 @@ extern "C" int b200ctc_beam_prebeam(const float* const* score_ptrs, const int64_
   B2_REQUIRE(n_rows >= 1 && V >= 1 && k >= 1 && k <= kBeamMaxK && k <= V, "beam_prebeam: bad sizes rows=%lld V=%d k=%d", (long long)n_rows, V, k);
   B2_REQUIRE(V <= kBeamMaxSegment, "beam_prebeam: vocabulary %d exceeds %lld", V, kBeamMaxSegment);
   auto st = static_cast<cudaStream_t>(stream);
-  const size_t smem = (size_t)V * 4;
+  const int nt = V <= 16384 ? 256 : topk_smem(V, 1024, k) <= kBeamSmemBudget ? 1024
+               : topk_smem(V, 512, k) <= kBeamSmemBudget ? 512 : 256;
+  const size_t smem = topk_smem(V, nt, k);
+  B2_REQUIRE(smem <= kBeamSmemBudget, "beam_prebeam: vocabulary %d with k = %d does not fit shared memory", V, k);
 #define GO(NT)                                                                          \
   do {                                                                                  \
     if (int rc = beam_smem(beam_prebeam_kernel<NT>, smem)) return rc;                   \
     beam_prebeam_kernel<NT><<<(unsigned)n_rows, NT, smem, st>>>(S, V, k, out_ids);      \
   } while (0)
-  if (V <= 16384) GO(256);
+  if (nt == 256) GO(256);
+  else if (nt == 512) GO(512);
   else GO(1024);
 #undef GO
   count_launch();

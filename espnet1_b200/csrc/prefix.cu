@@ -175,12 +175,16 @@ __global__ void __launch_bounds__(256) prefix_fill_kernel(
 }
 
 constexpr int kPF = 16;  // frames fetched ahead of the recursion
-#ifndef B200CTC_PSI_BLOCKED
-#define B200CTC_PSI_BLOCKED 0  // 1: psi reduced per group of kPF frames (tuning build, see profiles/README.md)
-#endif
 
-// TC: lp_t is the time-contiguous copy (B,V,T); else lp rows (B,T,V) are read directly
-template <bool TC>
+// TC: lp_t is the time-contiguous copy (B,V,T); else lp rows (B,T,V) are read directly.
+// AH: groups of kPF frames in flight ahead of the recursion.  With a pre-beam the launch is
+// small (n_bh * snum = 4 800 threads at C3) and its rows are cold in DRAM: the launcher then
+// uses 32-thread CTAs (one warp per SM - the per-frame loads of a warp touch 32 different
+// rows, so four warps on one SM queue behind one load/store unit), AH = 2, and - when the
+// copy's time stride allows 16-byte loads - frame groups ALIGNED to kPF so that a thread's
+// 16 frames of x_t[k] are four LDG.128 instead of sixteen LDG.32 (frames outside [start, end)
+// of the first and last group are fetched and ignored).  The arithmetic per frame is unchanged.
+template <bool TC, int AH>
 __global__ void __launch_bounds__(128) prefix_step_kernel(
     const float* __restrict__ lp, const float* __restrict__ lp_t, const float* __restrict__ r_prev,
     const float* __restrict__ rsum, const float* __restrict__ s_prev,
@@ -188,8 +192,8 @@ __global__ void __launch_bounds__(128) prefix_step_kernel(
     const int64_t* __restrict__ end_frames, int n_bh, int n_hyps, int T, int V, int snum,
     int out_len, int start, int end, int blank, int eos, float logzero, float* __restrict__ r,
     float* __restrict__ log_psi, float* __restrict__ scores, int64_t* __restrict__ idmap, int ldt,
-    const int* __restrict__ win_utt) {
-  const size_t idx = (size_t)blockIdx.x * 128 + threadIdx.x;
+    const int* __restrict__ win_utt, int vec) {
+  const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (size_t)n_bh * snum) return;
   const int h = (int)(idx / snum);
   const int b = h / n_hyps;
@@ -219,57 +223,61 @@ __global__ void __launch_bounds__(128) prefix_step_kernel(
   // psi = logsumexp({phi_{t-1} + x_t[k]}_{t in window} U {r^n_{start-1}})  (:164-179),
   // accumulated on line as (running max pm, sum ps of e^(term - pm))
   float pm = rn, ps = 1.f;
-  float cx[kPF], cb[kPF], cp[kPF];
-  auto fetch = [&](int t0) {  // clamped: always a valid address, values beyond `end` unused
+  float cx[AH][kPF], cb[AH][kPF], cp[AH][kPF];
+  const bool aligned = TC && vec != 0;
+  auto fetch = [&](int a, int g) {  // clamped: always a valid address, frames outside the window unused
+    if (aligned && g + kPF <= ldt) {
+      const float4* pk = reinterpret_cast<const float4*>(xk + g);
+      const float4* pb = reinterpret_cast<const float4*>(xb + g);
 #pragma unroll
-    for (int j = 0; j < kPF; ++j) {
-      const int t = (t0 + j < end) ? t0 + j : end - 1;
-      cx[j] = __ldg(xk + (size_t)t * xs);
-      cb[j] = __ldg(xb + (size_t)t * xs);
-      cp[j] = __ldg(ph + (size_t)(t - 1) * phs);
-    }
-  };
-  if (start < end) fetch(start);
-  for (int t0 = start; t0 < end; t0 += kPF) {
-    float x_k[kPF], x_b[kPF], phi[kPF];
-#pragma unroll
-    for (int j = 0; j < kPF; ++j) { x_k[j] = cx[j]; x_b[j] = cb[j]; phi[j] = cp[j]; }
-    if (t0 + kPF < end) fetch(t0 + kPF);  // next group: in flight while this one is computed
-#if B200CTC_PSI_BLOCKED
-    // psi is a plain reduction over the frames (no recursion): one maximum and one rescale
-    // per group of kPF terms instead of a running-maximum update per frame, and none of it
-    // sits on the r^n / r^b chain below
-    {
-      float term[kPF], tm = -__builtin_huge_valf();
+      for (int j = 0; j < kPF / 4; ++j) {
+        const float4 vk = __ldg(pk + j), vb = __ldg(pb + j);
+        cx[a][4 * j] = vk.x; cx[a][4 * j + 1] = vk.y; cx[a][4 * j + 2] = vk.z; cx[a][4 * j + 3] = vk.w;
+        cb[a][4 * j] = vb.x; cb[a][4 * j + 1] = vb.y; cb[a][4 * j + 2] = vb.z; cb[a][4 * j + 3] = vb.w;
+      }
+    } else {
 #pragma unroll
       for (int j = 0; j < kPF; ++j) {
-        term[j] = (t0 + j < end) ? phi[j] + x_k[j] : -__builtin_huge_valf();
-        tm = fmaxf(tm, term[j]);
+        const int t = min(max(g + j, start), end - 1);
+        cx[a][j] = __ldg(xk + (size_t)t * xs);
+        cb[a][j] = __ldg(xb + (size_t)t * xs);
       }
-      const float m2 = fmaxf(pm, tm);
-      float acc = ps * __expf(pm - m2);
-#pragma unroll
-      for (int j = 0; j < kPF; ++j) acc += __expf(term[j] - m2);
-      ps = acc;
-      pm = m2;
     }
-#endif
 #pragma unroll
     for (int j = 0; j < kPF; ++j) {
-      const int t = t0 + j;
-      if (t < end) {
-        const float rn_new = lse2_mufu(rn, phi[j]) + x_k[j];
-        const float rb_new = lse2_mufu(rn, rb) + x_b[j];
-#if !B200CTC_PSI_BLOCKED
-        const float term = phi[j] + x_k[j];
-        const float m2 = fmaxf(pm, term);
-        ps = ps * __expf(pm - m2) + __expf(term - m2);
-        pm = m2;
-#endif
-        __stcs(rout + ((size_t)t * 2 + 0) * plane, rn_new);
-        __stcs(rout + ((size_t)t * 2 + 1) * plane, rb_new);
-        rn = rn_new;
-        rb = rb_new;
+      const int t = min(max(g + j, start), end - 1);  // start >= 1: t - 1 >= 0
+      cp[a][j] = __ldg(ph + (size_t)(t - 1) * phs);
+    }
+  };
+  const int g0 = aligned ? (start & ~(kPF - 1)) : start;
+#pragma unroll
+  for (int a = 0; a < AH; ++a)
+    if (g0 + a * kPF < end) fetch(a, g0 + a * kPF);
+  for (int gq = g0; gq < end; gq += AH * kPF) {
+#pragma unroll
+    for (int a = 0; a < AH; ++a) {
+      const int t0 = gq + a * kPF;
+      if (t0 < end) {
+        float x_k[kPF], x_b[kPF], phi[kPF];
+#pragma unroll
+        for (int j = 0; j < kPF; ++j) { x_k[j] = cx[a][j]; x_b[j] = cb[a][j]; phi[j] = cp[a][j]; }
+        if (t0 + AH * kPF < end) fetch(a, t0 + AH * kPF);  // in flight while this group is computed
+#pragma unroll
+        for (int j = 0; j < kPF; ++j) {
+          const int t = t0 + j;
+          if (t >= start && t < end) {
+            const float rn_new = lse2_mufu(rn, phi[j]) + x_k[j];
+            const float rb_new = lse2_mufu(rn, rb) + x_b[j];
+            const float term = phi[j] + x_k[j];
+            const float m2 = fmaxf(pm, term);
+            ps = ps * __expf(pm - m2) + __expf(term - m2);
+            pm = m2;
+            __stcs(rout + ((size_t)t * 2 + 0) * plane, rn_new);
+            __stcs(rout + ((size_t)t * 2 + 1) * plane, rb_new);
+            rn = rn_new;
+            rb = rb_new;
+          }
+        }
       }
     }
   }
@@ -288,6 +296,192 @@ __global__ void __launch_bounds__(128) prefix_step_kernel(
   }
   log_psi[o] = psi;
   scores[o] = psi - (s_prev ? s_prev[o] : 0.f);
+}
+
+// ---------------------------------------------------------------------------------------
+// The same step with the frame loop PARALLEL IN TIME, for the pre-beam case (few candidates).
+//
+// With a pre-beam the step is tiny and serial: n_bh * snum = 4 800 threads at C3 each walking
+// 500 dependent frames (~250 cycles per frame with one warp per scheduler and nothing to hide
+// its latencies behind): 66 us per position, a third of a decoding position, on 1 % of the
+// machine's threads.  But the recursion is linear in the probability domain,
+//     R^n_t = (R^n_{t-1} + Phi_{t-1}) X_t[k]        R^b_t = (R^n_{t-1} + R^b_{t-1}) X_t[blank]
+// (:156-161; Phi does not depend on the state), i.e. an affine map of (R^n, R^b) with a
+// lower-triangular matrix.  Such maps compose into maps of the same shape,
+//     (a, b, d, c_n, c_b):  R^n' = a R^n + c_n,   R^b' = b R^n + d R^b + c_b,
+// so a WARP takes one (hypothesis, candidate) pair, every lane a chunk of ceil(len/32) frames:
+//   1. the lane composes the maps of its frames (in the log domain, all terms non-negative in
+//      the probability domain: sums only, no cancellation) and its share of psi;
+//   2. a warp scan of the 32 chunk maps gives every lane the state at the start of its chunk;
+//   3. from there the lane runs the reference recursion itself over its frames, so every
+//      r_t comes out of the same formula as in the serial kernel (only the chunk-start states
+//      see a different summation order; differences are at rounding level, tests as before).
+// One CTA = one hypothesis and up to 16 of its candidates: phi_{t-1} (both variants) and
+// x_t[blank] are staged once per CTA, x_t[k] per warp, all coalesced; results are staged in
+// shared memory (r^n over x_t[k]) and written as rows of r.  Chunks are stored with an odd
+// stride so that the lanes' chunk walks are bank-conflict free.
+constexpr float kScanZero = -1e30f;  // log of 0 for the map coefficients (finite: no inf - inf)
+constexpr int kScanCand = 16;        // candidates (warps) per CTA
+
+struct ScanMap { float a, b, d, cn, cb; };
+
+// `m` applied AFTER `e`
+__device__ __forceinline__ ScanMap scan_compose(const ScanMap& e, const ScanMap& m) {
+  ScanMap o;
+  o.a = m.a + e.a;
+  o.d = m.d + e.d;
+  o.b = lse2_mufu(m.b + e.a, m.d + e.b);
+  o.cn = lse2_mufu(m.a + e.cn, m.cn);
+  o.cb = lse2_mufu(lse2_mufu(m.b + e.cn, m.d + e.cb), m.cb);
+  return o;
+}
+
+__global__ void __launch_bounds__(32 * kScanCand, 2) prefix_step_scan_kernel(
+    const float* __restrict__ lp_t, const float* __restrict__ r_prev, const float* __restrict__ rsum,
+    const float* __restrict__ s_prev, const int64_t* __restrict__ last_ids,
+    const int64_t* __restrict__ scoring_ids, int n_bh, int n_hyps, int T, int V, int snum, int out_len,
+    int start, int end, int blank, int eos, float logzero, float* __restrict__ r,
+    float* __restrict__ log_psi, float* __restrict__ scores, int64_t* __restrict__ idmap, int ldt,
+    const int* __restrict__ win_utt, int cap /* frames a staged array can hold */) {
+  extern __shared__ float sm[];
+  const int h = blockIdx.y, c0 = blockIdx.x * kScanCand;
+  const int ncand = min(kScanCand, snum - c0);
+  const int b = h / n_hyps, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, NT = blockDim.x;
+  if (win_utt) {
+    start = win_utt[2 * b];
+    end = win_utt[2 * b + 1];
+  }
+  const int len = max(end - start, 0);
+  const int c = (len + 31) / 32, cs = c | 1;  // frames per lane; odd chunk stride in shared memory
+  const int S = cap + 1;                      // per-array stride (odd multiple pattern across arrays)
+  float* phiA = sm;                 // logsumexp(r^n_prev, r^b_prev)[t-1]
+  float* phiB = sm + S;             // r^b_prev[t-1]
+  float* xbl = sm + 2 * S;          // x_t[blank]
+  float* xk_all = sm + 3 * S;       // per warp: x_t[k], later r^n_t
+  float* rb_all = xk_all + (NT >> 5) * S;  // per warp: r^b_t
+  __shared__ float v0s[kScanCand];
+  // i / c and e / ncand by multiply-high: exact for operands below 2^16 (frames, candidates)
+  const unsigned c_magic = c > 1 ? (unsigned)(0x100000000ull / (unsigned)c) + 1u : 0u;
+  auto slot = [&](int i) {
+    const int L = c > 1 ? (int)__umulhi((unsigned)i, c_magic) : i;
+    return i + L * (cs - c);
+  };
+
+  // ---- stage the CTA's inputs: frame i of the window is absolute frame start + i
+  const float* xb_row = lp_t + ((size_t)b * V + blank) * ldt + start;
+  for (int i = tid; i < len; i += NT) {
+    const int sl = slot(i);
+    const size_t tp = (size_t)(start + i - 1);  // start >= 1
+    phiA[sl] = __ldg(rsum + tp * n_bh + h);
+    phiB[sl] = __ldg(r_prev + (tp * 2 + 1) * n_bh + h);
+    xbl[sl] = __ldg(xb_row + i);
+  }
+  const bool have = wid < ncand;
+  const size_t idx = (size_t)h * snum + c0 + wid;
+  int k = 0;
+  bool same = false;
+  float* xk = xk_all + wid * S;
+  float* rbo = rb_all + wid * S;
+  if (have) {
+    k = (int)scoring_ids[idx];
+    same = (k == (int)last_ids[h]);
+    const float* xk_row = lp_t + ((size_t)b * V + k) * ldt;
+    for (int i = lane; i < len; i += 32) xk[slot(i)] = __ldg(xk_row + start + i);
+    if (lane == 0) v0s[wid] = (out_len == 0) ? __ldg(xk_row) : logzero;  // r^n_0 of the empty prefix (:129-130)
+  }
+  __syncthreads();
+
+  if (have) {
+    const float* phi = same ? phiB : phiA;
+    const int base = lane * cs, i0 = lane * c;
+    const int nmine = max(0, min(c, len - i0));
+    // r^n / r^b at frame start-1: logzero, except r^n_0 = x_0[k] when the window starts at frame 1
+    const float rn0 = (start == 1) ? ((out_len == 0) ? __ldg(lp_t + ((size_t)b * V + k) * ldt) : logzero) : logzero;
+    const float rb0 = logzero;
+    // ---- 1. this lane's chunk as one affine map, and its share of psi
+    ScanMap m = {0.f, kScanZero, 0.f, kScanZero, kScanZero};
+    float pm = (lane == 0) ? rn0 : kScanZero, ps = (lane == 0) ? 1.f : 0.f;
+    for (int j = 0; j < nmine; ++j) {
+      const float x_k = xk[base + j], x_b = xbl[base + j], ph = phi[base + j];
+      const float nb = x_b + lse2_mufu(m.a, m.b);
+      const float ncb = x_b + lse2_mufu(m.cn, m.cb);
+      m.cn = x_k + lse2_mufu(m.cn, ph);
+      m.a += x_k;
+      m.d += x_b;
+      m.b = nb;
+      m.cb = ncb;
+      const float term = ph + x_k;
+      const float m2 = fmaxf(pm, term);
+      ps = ps * __expf(pm - m2) + __expf(term - m2);
+      pm = m2;
+    }
+    // ---- 2. inclusive scan of the maps over the lanes, then shift by one lane
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      ScanMap e;
+      e.a = __shfl_up_sync(0xffffffffu, m.a, o);
+      e.b = __shfl_up_sync(0xffffffffu, m.b, o);
+      e.d = __shfl_up_sync(0xffffffffu, m.d, o);
+      e.cn = __shfl_up_sync(0xffffffffu, m.cn, o);
+      e.cb = __shfl_up_sync(0xffffffffu, m.cb, o);
+      if (lane >= o) m = scan_compose(e, m);
+    }
+    ScanMap pre;
+    pre.a = __shfl_up_sync(0xffffffffu, m.a, 1);
+    pre.b = __shfl_up_sync(0xffffffffu, m.b, 1);
+    pre.d = __shfl_up_sync(0xffffffffu, m.d, 1);
+    pre.cn = __shfl_up_sync(0xffffffffu, m.cn, 1);
+    pre.cb = __shfl_up_sync(0xffffffffu, m.cb, 1);
+    float rn = rn0, rb = rb0;
+    if (lane > 0) {
+      rn = lse2_mufu(pre.a + rn0, pre.cn);
+      rb = lse2_mufu(lse2_mufu(pre.b + rn0, pre.d + rb0), pre.cb);
+    }
+    // ---- 3. the reference recursion over my frames from that state; r^n replaces x_t[k]
+    for (int j = 0; j < nmine; ++j) {
+      const float x_k = xk[base + j], x_b = xbl[base + j], ph = phi[base + j];
+      const float rn_new = lse2_mufu(rn, ph) + x_k;
+      const float rb_new = lse2_mufu(rn, rb) + x_b;
+      xk[base + j] = rn_new;
+      rbo[base + j] = rb_new;
+      rn = rn_new;
+      rb = rb_new;
+    }
+    // ---- psi = logsumexp over the window's terms and r^n_{start-1} (:164-179)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float om = __shfl_xor_sync(0xffffffffu, pm, o), os = __shfl_xor_sync(0xffffffffu, ps, o);
+      const float m2 = fmaxf(pm, om);
+      ps = ps * __expf(pm - m2) + os * __expf(om - m2);
+      pm = m2;
+    }
+    if (lane == 0) {
+      const size_t o = (size_t)h * V + k;
+      idmap[o] = (int64_t)(c0 + wid);
+      if (k != eos && k != blank) {  // those two are set by prefix_fill_kernel (:181-185)
+        const float psi = pm + __logf(ps);
+        log_psi[o] = psi;
+        scores[o] = psi - (s_prev ? s_prev[o] : 0.f);
+      }
+    }
+  }
+  __syncthreads();
+
+  // ---- rows of r: (t, n|b) -> ncand contiguous values
+  const size_t plane = (size_t)n_bh * snum;
+  const int total = T * 2 * ncand;
+  const unsigned n_magic = ncand > 1 ? (unsigned)(0x100000000ull / (unsigned)ncand) + 1u : 0u;
+  for (int e = tid; e < total; e += NT) {
+    const int tx = ncand > 1 ? (int)__umulhi((unsigned)e, n_magic) : e;
+    const int cc = e - tx * ncand, x = tx & 1, t = tx >> 1;
+    float v = logzero;
+    if (t >= start && t < end) {
+      v = (x ? rb_all : xk_all)[cc * S + slot(t - start)];
+    } else if (t == 0 && x == 0 && t < start) {
+      v = v0s[cc];
+    }
+    __stcs(r + ((size_t)t * 2 + x) * plane + (size_t)h * snum + c0 + cc, v);
+  }
 }
 
 // index_select_state (:189-220)
@@ -413,14 +607,45 @@ extern "C" int b200ctc_prefix_step(const float* lp, const float* lp_t, const flo
     count_launch();
   }
   // the time-contiguous copy pays off when few of the V columns are touched per hypothesis
-  if (lp_t && scoring_ids)
-    prefix_step_kernel<true><<<blocks((size_t)n_bh * snum, 128), 128, 0, st>>>(
+  const size_t pairs = (size_t)n_bh * snum;
+  static const int scan_on = tuning_int("B200CTC_PREFIX_SCAN", 1);
+  const int scan_warps = snum < kScanCand ? snum : kScanCand;
+  const int scan_cap = 32 * (((T + 31) / 32) | 1);
+  const size_t scan_smem = (size_t)(3 + 2 * scan_warps) * (scan_cap + 1) * sizeof(float);
+  if (lp_t && scoring_ids && scan_on && pairs <= 32768 && T >= 64 && T < 2048 && n_bh <= 65535 &&
+      scan_smem <= 100 * 1024) {
+    // few candidates: the frame loop parallel in time, one warp per (hypothesis, candidate)
+    if (scan_smem > 48 * 1024 &&  // per device: set on every call (the process may use several)
+        cudaFuncSetAttribute(prefix_step_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)scan_smem) != cudaSuccess) {
+      set_error("prefix_step: cannot reserve %zu bytes of shared memory for the scan kernel", scan_smem);
+      cudaGetLastError();
+      return B200CTC_ERR_DEVICE;
+    }
+    prefix_step_scan_kernel<<<dim3((snum + kScanCand - 1) / kScanCand, n_bh), 32 * scan_warps, scan_smem, st>>>(
+        lp_t, r_prev, rsum_ws, s_prev, last_ids, scoring_ids, n_bh, n_hyps, T, V, snum, out_len, start, end,
+        blank, eos, logzero, r, log_psi, scores, idmap, lp_t_ld, win_utt, scan_cap);
+  } else if (lp_t && scoring_ids) {
+    // small launch: spread the warps over the SMs (see the kernel); 16-byte loads need a
+    // 16-byte aligned copy whose time stride is a multiple of 4 frames
+    static const int small_nt = tuning_int("B200CTC_PREFIX_SMALL_NT", 32);
+    static const int ahead = tuning_int("B200CTC_PREFIX_AHEAD", 2);
+    static const int vec_on = tuning_int("B200CTC_PREFIX_VEC", 1);
+    const int nt = pairs <= (size_t)2 * 148 * small_nt ? small_nt : pairs <= (size_t)2 * 148 * 64 ? 64 : 128;
+    const int vec = vec_on && lp_t_ld % 4 == 0 && (reinterpret_cast<uintptr_t>(lp_t) & 15) == 0;
+    if (ahead >= 2 && nt < 128)
+      prefix_step_kernel<true, 2><<<blocks(pairs, nt), nt, 0, st>>>(
+          lp, lp_t, r_prev, rsum_ws, s_prev, last_ids, scoring_ids, end_frames, n_bh, n_hyps, T, V,
+          snum, out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap, lp_t_ld, win_utt, vec);
+    else
+      prefix_step_kernel<true, 1><<<blocks(pairs, nt), nt, 0, st>>>(
+          lp, lp_t, r_prev, rsum_ws, s_prev, last_ids, scoring_ids, end_frames, n_bh, n_hyps, T, V,
+          snum, out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap, lp_t_ld, win_utt, vec);
+  } else {
+    prefix_step_kernel<false, 1><<<blocks(pairs, 128), 128, 0, st>>>(
         lp, lp_t, r_prev, rsum_ws, s_prev, last_ids, scoring_ids, end_frames, n_bh, n_hyps, T, V,
-        snum, out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap, lp_t_ld, win_utt);
-  else
-    prefix_step_kernel<false><<<blocks((size_t)n_bh * snum, 128), 128, 0, st>>>(
-        lp, lp_t, r_prev, rsum_ws, s_prev, last_ids, scoring_ids, end_frames, n_bh, n_hyps, T, V,
-        snum, out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap, lp_t_ld, win_utt);
+        snum, out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap, lp_t_ld, win_utt, 0);
+  }
   count_launch();
   prof_mark(4, 1, st);
   return check_launch("prefix_step");

@@ -81,7 +81,10 @@ class CTCPrefixScoreTH(object):
         if self._lp_t is None or self._lp_t.shape[2] < T:
             old, t_old = self._lp_t, self._lp_t_T
             # streaming grows by chunks: geometric headroom makes the appends O(new frames)
+            # (a time stride that is a multiple of 16 frames lets the scoring kernel fetch whole
+            # groups of frames with 16-byte loads up to the end of a row)
             ld = T if self._lp_store is None else max(T, int(1.5 * T) + 32)
+            ld = -(-ld // 16) * 16
             self._lp_t = torch.empty(B, V, ld, dtype=torch.float32, device=self.device)
             if old is not None and t_old > 0:
                 self._lp_t[:, :, :t_old] = old[:, :, :t_old]

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define B200CTC_ABI_VERSION 5
+#define B200CTC_ABI_VERSION 6
 
 #define B200CTC_OK 0
 #define B200CTC_ERR_ARG (-1)     /* bad argument (null pointer, size, dtype) */
@@ -274,14 +274,14 @@ int b200ctc_prefix_select(const float* r, const float* log_psi,
  *   the reference's fp32 operation order; separate multiply and add)          */
 #define B200CTC_BEAM_MAX_SCORERS 8
 /* pre-beam (:228-234): out_ids (n_rows, k) int64 = top-k tokens of every row of w,
- * sorted by descending score (ties: lower token id first); k <= 64, V <= 57344. */
+ * sorted by descending score (ties: lower token id first); k <= 64, V <= 55296. */
 int b200ctc_beam_prebeam(const float* const* score_ptrs_host,
                          const int64_t* strides_host, const float* weights_host,
                          int K, int64_t n_rows, int V, int k, int64_t* out_ids,
                          b200ctc_stream_t stream);
 /* one pruning step for U utterances x W beam slots (n = U*W rows), one CTA per
  * utterance: top-k over the utterance's W*V entries of w + run_score[h]
- * (batch_beam(), :98-118; k <= 64, W*V <= 57344), then for winner j of utterance u
+ * (batch_beam(), :98-118; k <= 64, W*V <= 55296), then for winner j of utterance u
  * (prev = flat / V, tok = flat % V, row = u*W + prev, o = u*k + j):
  *   out_val[o]  = w + run                  (the new hypothesis score, :258)
  *   out_flat[o] = prev*V + tok             (what index_select_state expects)
@@ -302,6 +302,64 @@ int b200ctc_beam_select(const float* const* score_ptrs_host,
                         int64_t* out_flat, float* out_run, float* cum_out,
                         int64_t* yseq_out, int64_t yseq_out_stride, float* pack,
                         b200ctc_stream_t stream);
+
+/* One whole decoding position of the joint CTC/attention search (ABI 6) - everything of
+ * BatchBeamSearch.search (espnet/nets/batch_beam_search.py:206-283) that follows the full
+ * scorers, for U utterances x W beam slots (n = U*W rows), issued by ONE call on buffers the
+ * caller allocated once per decode:
+ *   beam_prebeam (if snum > 0)  ->  prefix_init_state (step_i == 0 only)  ->  prefix_step
+ *   ->  beam_select (k = W)  ->  prefix_select  ->  pack copied to pinned host memory.
+ * Same kernels, arguments and arithmetic as those entry points called one after the other (the
+ * host-side mirror's generic path does exactly that; tests/test_beam_engine.py compares the
+ * two), without the per-call argument marshalling and allocations of the host language: the
+ * position is otherwise bound by the host, not by its kernels.  The CTC scorer is the LAST of
+ * the K = K_full + 1 score matrices (the reference's accumulation order: full scorers, then
+ * partial ones, :217-241).  The caller synchronises the stream before it reads pack_host. */
+typedef struct b200ctc_beam_plan {
+  int32_t U, W, V, T;
+  int32_t snum;        /* pre-beam width (:228-234); 0 = the CTC scorer sees the full vocabulary */
+  int32_t K_full;      /* number of full-scorer matrices handed in per position (<= 7) */
+  int32_t prebeam_key; /* -1: pre-beam on the weighted sum of all full scorers ("full"),
+                          else the index of the one full scorer it is taken from (weight 1) */
+  int32_t blank, eos;
+  float logzero;
+  float weights[B200CTC_BEAM_MAX_SCORERS]; /* K_full full-scorer weights, then the CTC weight */
+  /* CTC prefix scorer, device memory (shapes as in prefix_step / prefix_select) */
+  const float* lp;           /* (U,T,V) padded log-probs */
+  const float* lp_t;         /* (U,V,lp_t_ld) from prefix_transpose; required iff snum > 0 */
+  int64_t lp_t_ld;
+  const int64_t* end_frames; /* (U) */
+  float* r_state[2];         /* (T,2,n)  state carried between positions, like the beam state */
+  float* s_state[2];         /* (n,V)    below: [step_i & 1] read by prefix_step (position 0:
+                                written by init_state first), [(step_i + 1) & 1] written by
+                                prefix_select - so that position i + 1 can be in flight while
+                                the host still copies position i's state */
+  float* r;                  /* (T,2,n,snum or V) */
+  float* log_psi;            /* (n,V) */
+  float* ctc_scores;         /* (n,V) */
+  int64_t* idmap;            /* (n,V); unused when snum == 0 */
+  float* rsum;               /* (T,n) scratch */
+  int64_t* last_ids;         /* (n) scratch: last token of every prefix */
+  int64_t* part_ids;         /* (n,snum) scratch: pre-beam candidates */
+  /* beam state, device memory; [step_i & 1] is read, [(step_i + 1) & 1] is written */
+  float* run_score[2];       /* (n) */
+  float* cum[2];             /* (K,n) */
+  int64_t* yseq[2];          /* (n, yseq_stride) prefixes */
+  int64_t yseq_stride;
+  const unsigned char* active; /* (U) */
+  const int* maxlen;           /* (U) */
+  float* out_val;            /* (n) */
+  int64_t* out_flat;         /* (n) */
+  float* pack;               /* (3+K,U,W) device */
+  float* pack_host;          /* (3+K,U,W) PINNED host memory */
+} b200ctc_beam_plan;
+size_t b200ctc_beam_plan_bytes(void); /* sizeof(b200ctc_beam_plan): layout check for FFI mirrors */
+/* full_ptrs_host[K_full] device pointers, full_strides_host[2*K_full] (row, column stride in
+ * elements; 0 = broadcast) of this position's full-scorer matrices; cur_len = current prefix
+ * length (primer included), i.e. prefix_step's out_len + 1.                                  */
+int b200ctc_beam_position(const b200ctc_beam_plan* plan, const float* const* full_ptrs_host,
+                          const int64_t* full_strides_host, int step_i, int cur_len,
+                          b200ctc_stream_t stream);
 
 /* ---- host-buffer pipeline (bench.py `e2e`) --------------------------------
  * Same arithmetic as loss_fwd + loss_bwd, but logits/targets/lengths are HOST

@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(h, n), f"{n} declared in b200ctc.h but not exported"
     assert sorted(_lib.SIGNATURES) == names  # ctypes table mirrors the header 1:1
-    assert h.b200ctc_abi_version() == 5
+    assert h.b200ctc_abi_version() == 6
     assert h.b200ctc_loss_workspace_bytes(64, 500, 5000, 150) > 64 * 500 * 301 * 8
 
 

@@ -90,11 +90,16 @@ def run(dev="cuda:0", POS=30, cpu_port=True):
             xs_h[0].clone(), {"ctc": OracleCTCPrefixScorer(CpuCTC(), eos), "decoder": TableScorer(table_h),
                               "length_bonus": LengthBonusPort(V)},
             weights, W, V, eos, eos, pre_beam_score_key="full", maxlenratio=-POS)], 1))
+    only = os.environ.get("CASES")  # e.g. CASES=engine_batch32 under ncu
+    if only:
+        cases = [c for c in cases if c[0] in only.split(",")]
     with torch.no_grad():
         for name, fn, n_utt in cases:
             if not name.startswith("cpu"):
                 fn()
             torch.cuda.synchronize()
+            if bs.prof is not None:
+                bs.prof.clear()
             t0 = time.perf_counter()
             res = fn()
             torch.cuda.synchronize()
@@ -104,9 +109,10 @@ def run(dev="cuda:0", POS=30, cpu_port=True):
                          "ms_per_position": 1e3 * dt / POS / (1 if "batch" in name else n_utt),
                          "utt_positions_per_s": n_utt * POS / dt,
                          "best0": [int(v) for v in (first.yseq if hasattr(first, "yseq") else first["yseq"])][:8]}
+            if bs.prof is not None and name.startswith("engine"):
+                out[name]["phase_ms_per_position"] = {
+                    k: round(1e3 * v / POS / (1 if "batch" in name else n_utt), 4) for k, v in bs.prof.items()}
     out["same_best_hypothesis"] = len({tuple(v["best0"]) for k, v in out.items() if isinstance(v, dict)}) == 1
-    if bs.prof is not None:
-        out["engine_phase_s"] = bs.prof
     return out
 
 
