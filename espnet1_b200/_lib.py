@@ -90,7 +90,7 @@ class BeamPlan(ctypes.Structure):
         ("weights", c_float * 8),
         ("lp", _P), ("lp_t", _P), ("lp_t_ld", c_int64), ("end_frames", _P),
         ("r_state", _P * 2), ("s_state", _P * 2), ("r", _P), ("log_psi", _P), ("ctc_scores", _P),
-        ("idmap", _P), ("rsum", _P), ("last_ids", _P), ("part_ids", _P),
+        ("idmap", _P), ("rsum", _P), ("part_ids", _P),
         ("run_score", _P * 2), ("cum", _P * 2), ("yseq", _P * 2), ("yseq_stride", c_int64),
         ("active", _P), ("maxlen", _P), ("out_val", _P), ("out_flat", _P),
         ("pack", _P), ("pack_host", _P),

@@ -10,17 +10,6 @@
 // which is what bounded a position: ~0.2 ms of kernels inside 0.56 ms.
 #include "common.cuh"
 
-namespace b200ctc {
-
-// last token of every prefix: prefix_step wants it contiguous (ctc_prefix_score.py:78)
-__global__ void last_token_kernel(const int64_t* __restrict__ yseq, int64_t stride, int pos, int n,
-                                  int64_t* __restrict__ out) {
-  const int h = blockIdx.x * blockDim.x + threadIdx.x;
-  if (h < n) out[h] = yseq[(int64_t)h * stride + pos];
-}
-
-}  // namespace b200ctc
-
 using namespace b200ctc;
 
 extern "C" size_t b200ctc_beam_plan_bytes(void) { return sizeof(b200ctc_beam_plan); }
@@ -41,7 +30,7 @@ extern "C" int b200ctc_beam_position(const b200ctc_beam_plan* p, const float* co
              "beam_position: cur_len=%d does not fit the prefix buffers (stride %lld)", cur_len,
              (long long)p->yseq_stride);
   B2_REQUIRE(p->lp && p->end_frames && p->r_state[0] && p->r_state[1] && p->s_state[0] && p->s_state[1] && p->r && p->log_psi && p->ctc_scores &&
-                 p->rsum && p->last_ids && p->run_score[0] && p->run_score[1] && p->cum[0] && p->cum[1] &&
+                 p->rsum && p->run_score[0] && p->run_score[1] && p->cum[0] && p->cum[1] &&
                  p->yseq[0] && p->yseq[1] && p->out_val && p->out_flat && p->pack && p->pack_host,
              "beam_position: null buffer in the plan");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -63,15 +52,14 @@ extern "C" int b200ctc_beam_position(const b200ctc_beam_plan* p, const float* co
   }
 
   // ---- CTC prefix scores of the candidates (ctc_prefix_score.py:68-187; no attention window)
-  last_token_kernel<<<(n + 127) / 128, 128, 0, st>>>(p->yseq[in], p->yseq_stride, cur_len - 1, n, p->last_ids);
-  count_launch();
   if (step_i == 0) {
     rc = b200ctc_prefix_init_state(p->lp, U, T, V, W, p->blank, p->logzero, p->r_state[0], stream);
     if (rc != B200CTC_OK) return rc;
   }
   const int out_len = cur_len - 1;
-  rc = b200ctc_prefix_step(p->lp, pre ? p->lp_t : nullptr, p->r_state[in], step_i == 0 ? nullptr : p->s_state[in],
-                           p->last_ids, pre ? p->part_ids : nullptr, p->end_frames, U, W, T, V,
+  // (the last token of every prefix is read in place: column cur_len - 1 of the prefix buffer)
+  rc = prefix_step_impl(p->lp, pre ? p->lp_t : nullptr, p->r_state[in], step_i == 0 ? nullptr : p->s_state[in],
+                           p->yseq[in] + (cur_len - 1), p->yseq_stride, pre ? p->part_ids : nullptr, p->end_frames, U, W, T, V,
                            pre ? p->snum : V, out_len, out_len > 1 ? out_len : 1, T, p->blank, p->eos,
                            p->logzero, p->r, p->log_psi, p->ctc_scores, pre ? p->idmap : nullptr, p->rsum,
                            (int)p->lp_t_ld, nullptr, stream);

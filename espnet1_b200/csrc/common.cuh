@@ -15,6 +15,13 @@ namespace b200ctc {
 void set_error(const char* fmt, ...);
 void count_launch(int n = 1);
 int check_launch(const char* what);  // cudaGetLastError -> status
+// prefix.cu: b200ctc_prefix_step with a strided last-token array (beam_position.cu)
+int prefix_step_impl(const float* lp, const float* lp_t, const float* r_prev, const float* s_prev,
+                     const int64_t* last_ids, long long last_stride, const int64_t* scoring_ids,
+                     const int64_t* end_frames, int B, int n_hyps, int T, int V, int snum, int out_len,
+                     int start, int end, int blank, int eos, float logzero, float* r, float* log_psi,
+                     float* scores, int64_t* idmap, float* rsum_ws, int lp_t_ld, const int* win_utt,
+                     b200ctc_stream_t stream);
 int sm_count();
 // profiling phases: 0 prep, 1 lse_gather (pass A), 2 lattice, 3 grad_rows (pass B),
 // 4 prefix_step, 5 softmax family

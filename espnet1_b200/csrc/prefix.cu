@@ -24,20 +24,24 @@ __device__ __forceinline__ float lse2_mufu(float a, float b) {
   return fmaxf(a, b) + __logf(1.f + __expf(-fabsf(a - b)));
 }
 
-// (B,T,V) -> (B,V,T) tiled transpose (32x32 tiles through shared memory)
+// (B,T,V) -> (B,V,T) tiled transpose: 64x64 tiles through shared memory, 256-byte runs on both
+// sides (32x32 tiles moved 4 KB per CTA: 80 K CTAs at C3, 1.4 TB/s)
 // frames [tfirst, T) only; `ld` = time stride of the copy (>= T: room for streaming appends)
+constexpr int kTrTile = 64;
 __global__ void __launch_bounds__(256) prefix_transpose_kernel(const float* __restrict__ in,
                                                                float* __restrict__ out, int T,
                                                                int V, int tfirst, int ld) {
-  __shared__ float tile[32][33];
-  const int b = blockIdx.z, v0 = blockIdx.x * 32, t0 = tfirst + blockIdx.y * 32;
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 8 rows per pass
+  __shared__ float tile[kTrTile][kTrTile + 1];
+  const int b = blockIdx.z, v0 = blockIdx.x * kTrTile, t0 = tfirst + blockIdx.y * kTrTile;
+  const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;  // 4 rows per pass
   const float* src = in + (size_t)b * T * V;
   float* dst = out + (size_t)b * V * ld;
-  for (int r = ty; r < 32; r += 8)
-    if (t0 + r < T && v0 + tx < V) tile[r][tx] = src[(size_t)(t0 + r) * V + v0 + tx];
+#pragma unroll 4
+  for (int r = ty; r < kTrTile; r += 4)
+    if (t0 + r < T && v0 + tx < V) tile[r][tx] = __ldcs(src + (size_t)(t0 + r) * V + v0 + tx);
   __syncthreads();
-  for (int r = ty; r < 32; r += 8)
+#pragma unroll 4
+  for (int r = ty; r < kTrTile; r += 4)
     if (v0 + r < V && t0 + tx < T) dst[(size_t)(v0 + r) * ld + t0 + tx] = tile[tx][r];
 }
 
@@ -149,29 +153,32 @@ __global__ void __launch_bounds__(kWinWarps * 32) prefix_window_utt_kernel(
   }
 }
 
-// r_sum[t,h] = logsumexp(r_prev[t,0,h], r_prev[t,1,h])   (:131)
-__global__ void __launch_bounds__(256) prefix_rsum_kernel(const float* __restrict__ r_prev, int T,
-                                                          int n_bh, float* __restrict__ rsum) {
+// Two passes in ONE launch:
+//  r_sum[t,h] = logsumexp(r_prev[t,0,h], r_prev[t,1,h])   (:131)
+//  pre-beam only: log_psi / scores / idmap defaults for tokens that are not scored (:181-185).
+// The fill's one dependent entry (eos: r_sum at the utterance's last frame) is recomputed from
+// r_prev with the same expression instead of being read back, so the passes need no ordering.
+__global__ void __launch_bounds__(256) prefix_prepare_kernel(
+    const float* __restrict__ r_prev, const float* __restrict__ s_prev,
+    const int64_t* __restrict__ end_frames, int T, int n_bh, int n_hyps, int V, int blank, int eos,
+    float logzero, int fill, float* __restrict__ rsum, float* __restrict__ log_psi,
+    float* __restrict__ scores, int64_t* __restrict__ idmap) {
   const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
-  if (i >= (size_t)T * n_bh) return;
-  const size_t t = i / n_bh, h = i - t * n_bh;
-  rsum[i] = lse2f(r_prev[(t * 2 + 0) * n_bh + h], r_prev[(t * 2 + 1) * n_bh + h]);
-}
-
-// pre-beam only: log_psi / scores / idmap defaults for tokens that are not scored
-__global__ void __launch_bounds__(256) prefix_fill_kernel(
-    const float* __restrict__ rsum, const float* __restrict__ s_prev,
-    const int64_t* __restrict__ end_frames, int n_bh, int n_hyps, int V, int blank, int eos,
-    float logzero, float* __restrict__ log_psi, float* __restrict__ scores,
-    int64_t* __restrict__ idmap) {
-  const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
-  if (i >= (size_t)n_bh * V) return;
-  const int h = (int)(i / V), v = (int)(i - (size_t)h * V);
-  float p = logzero;
-  if (v == eos && v != blank) p = rsum[(size_t)end_frames[h / n_hyps] * n_bh + h];
-  log_psi[i] = p;
-  scores[i] = p - (s_prev ? s_prev[i] : 0.f);
-  idmap[i] = -1;
+  if (i < (size_t)T * n_bh) {
+    const size_t t = i / n_bh, h = i - t * n_bh;
+    rsum[i] = lse2f(r_prev[(t * 2 + 0) * n_bh + h], r_prev[(t * 2 + 1) * n_bh + h]);
+  }
+  if (fill && i < (size_t)n_bh * V) {
+    const int h = (int)(i / V), v = (int)(i - (size_t)h * V);
+    float p = logzero;
+    if (v == eos && v != blank) {
+      const size_t t = (size_t)end_frames[h / n_hyps];
+      p = lse2f(r_prev[(t * 2 + 0) * n_bh + h], r_prev[(t * 2 + 1) * n_bh + h]);
+    }
+    log_psi[i] = p;
+    scores[i] = p - (s_prev ? s_prev[i] : 0.f);
+    idmap[i] = -1;
+  }
 }
 
 constexpr int kPF = 16;  // frames fetched ahead of the recursion
@@ -192,7 +199,7 @@ __global__ void __launch_bounds__(128) prefix_step_kernel(
     const int64_t* __restrict__ end_frames, int n_bh, int n_hyps, int T, int V, int snum,
     int out_len, int start, int end, int blank, int eos, float logzero, float* __restrict__ r,
     float* __restrict__ log_psi, float* __restrict__ scores, int64_t* __restrict__ idmap, int ldt,
-    const int* __restrict__ win_utt, int vec) {
+    const int* __restrict__ win_utt, int vec, long long last_stride) {
   const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (size_t)n_bh * snum) return;
   const int h = (int)(idx / snum);
@@ -202,7 +209,7 @@ __global__ void __launch_bounds__(128) prefix_step_kernel(
     end = win_utt[2 * b + 1];
   }
   const int k = scoring_ids ? (int)scoring_ids[idx] : (int)(idx - (size_t)h * snum);
-  const bool same = (k == (int)last_ids[h]);
+  const bool same = (k == (int)last_ids[(size_t)h * last_stride]);
   // per-frame input streams: x_t[k], x_t[blank], phi_{t-1} (= r^b_prev if k repeats the
   // last label, else logsumexp(r^n_prev, r^b_prev), :132-141) with their strides over t
   const float* xk = TC ? lp_t + ((size_t)b * V + k) * ldt : lp + (size_t)b * T * V + k;
@@ -289,7 +296,7 @@ __global__ void __launch_bounds__(128) prefix_step_kernel(
   const size_t o = (size_t)h * V + k;
   if (scoring_ids) {
     idmap[o] = (int64_t)(idx - (size_t)h * snum);
-    if (k == eos || k == blank) return;  // set by prefix_fill_kernel (:181-185)
+    if (k == eos || k == blank) return;  // set by prefix_prepare_kernel (:181-185)
   } else {
     if (k == eos) psi = rsum[(size_t)end_frames[b] * n_bh + h];
     if (k == blank) psi = logzero;
@@ -342,7 +349,7 @@ __global__ void __launch_bounds__(32 * kScanCand, 2) prefix_step_scan_kernel(
     const int64_t* __restrict__ scoring_ids, int n_bh, int n_hyps, int T, int V, int snum, int out_len,
     int start, int end, int blank, int eos, float logzero, float* __restrict__ r,
     float* __restrict__ log_psi, float* __restrict__ scores, int64_t* __restrict__ idmap, int ldt,
-    const int* __restrict__ win_utt, int cap /* frames a staged array can hold */) {
+    const int* __restrict__ win_utt, int cap /* frames a staged array can hold */, long long last_stride) {
   extern __shared__ float sm[];
   const int h = blockIdx.y, c0 = blockIdx.x * kScanCand;
   const int ncand = min(kScanCand, snum - c0);
@@ -384,7 +391,7 @@ __global__ void __launch_bounds__(32 * kScanCand, 2) prefix_step_scan_kernel(
   float* rbo = rb_all + wid * S;
   if (have) {
     k = (int)scoring_ids[idx];
-    same = (k == (int)last_ids[h]);
+    same = (k == (int)last_ids[(size_t)h * last_stride]);
     const float* xk_row = lp_t + ((size_t)b * V + k) * ldt;
     for (int i = lane; i < len; i += 32) xk[slot(i)] = __ldg(xk_row + start + i);
     if (lane == 0) v0s[wid] = (out_len == 0) ? __ldg(xk_row) : logzero;  // r^n_0 of the empty prefix (:129-130)
@@ -458,7 +465,7 @@ __global__ void __launch_bounds__(32 * kScanCand, 2) prefix_step_scan_kernel(
     if (lane == 0) {
       const size_t o = (size_t)h * V + k;
       idmap[o] = (int64_t)(c0 + wid);
-      if (k != eos && k != blank) {  // those two are set by prefix_fill_kernel (:181-185)
+      if (k != eos && k != blank) {  // those two are set by prefix_prepare_kernel (:181-185)
         const float psi = pm + __logf(ps);
         log_psi[o] = psi;
         scores[o] = psi - (s_prev ? s_prev[o] : 0.f);
@@ -467,52 +474,50 @@ __global__ void __launch_bounds__(32 * kScanCand, 2) prefix_step_scan_kernel(
   }
   __syncthreads();
 
-  // ---- rows of r: (t, n|b) -> ncand contiguous values
+  // ---- rows of r: (t, n|b) -> ncand contiguous values, one half-warp per row
   const size_t plane = (size_t)n_bh * snum;
-  const int total = T * 2 * ncand;
-  const unsigned n_magic = ncand > 1 ? (unsigned)(0x100000000ull / (unsigned)ncand) + 1u : 0u;
-  for (int e = tid; e < total; e += NT) {
-    const int tx = ncand > 1 ? (int)__umulhi((unsigned)e, n_magic) : e;
-    const int cc = e - tx * ncand, x = tx & 1, t = tx >> 1;
-    float v = logzero;
-    if (t >= start && t < end) {
-      v = (x ? rb_all : xk_all)[cc * S + slot(t - start)];
-    } else if (t == 0 && x == 0 && t < start) {
-      v = v0s[cc];
+  const int cc = tid & 15, nhw = NT >> 4;
+  float* rdst = r + (size_t)h * snum + c0 + cc;
+  for (int row = tid >> 4; row < 2 * T; row += nhw) {
+    const int t = row >> 1, x = row & 1;
+    if (cc < ncand) {
+      float v = logzero;
+      if (t >= start && t < end) {
+        v = (x ? rb_all : xk_all)[cc * S + slot(t - start)];
+      } else if (row == 0) {
+        v = v0s[cc];
+      }
+      __stcs(rdst + (size_t)row * plane, v);
     }
-    __stcs(r + ((size_t)t * 2 + x) * plane + (size_t)h * snum + c0 + cc, v);
   }
 }
 
-// index_select_state (:189-220)
-__global__ void __launch_bounds__(256) prefix_select_r_kernel(
-    const float* __restrict__ r, const int64_t* __restrict__ idmap,
+// index_select_state (:189-220): both gathers in one launch
+__global__ void __launch_bounds__(256) prefix_select_kernel(
+    const float* __restrict__ r, const float* __restrict__ log_psi, const int64_t* __restrict__ idmap,
     const int64_t* __restrict__ best_ids, int n_hyps, int W, int T, int V, int snum, int n_bh,
-    float* __restrict__ r_new) {
+    float* __restrict__ r_new, float* __restrict__ s_new) {
   const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
   const size_t n_new = (size_t)(n_bh / n_hyps) * W;
-  if (i >= (size_t)T * 2 * n_new) return;
-  const size_t tn = i / n_new;
-  const int hn = (int)(i - tn * n_new);
-  const int b = hn / W;
-  const int64_t best = best_ids[hn];
-  const int hyp = (int)(best / V) + b * n_hyps;
-  const int label = (int)(best % V);
-  int col = label;
-  if (idmap) {
-    const int64_t c = idmap[(size_t)hyp * V + label];
-    col = c < 0 ? 0 : (int)c;
+  if (i < (size_t)T * 2 * n_new) {
+    const size_t tn = i / n_new;
+    const int hn = (int)(i - tn * n_new);
+    const int b = hn / W;
+    const int64_t best = best_ids[hn];
+    const int hyp = (int)(best / V) + b * n_hyps;
+    const int label = (int)(best % V);
+    int col = label;
+    if (idmap) {
+      const int64_t c = idmap[(size_t)hyp * V + label];
+      col = c < 0 ? 0 : (int)c;
+    }
+    r_new[i] = r[(tn * n_bh + hyp) * snum + col];
   }
-  r_new[i] = r[(tn * n_bh + hyp) * snum + col];
-}
-__global__ void __launch_bounds__(256) prefix_select_s_kernel(
-    const float* __restrict__ log_psi, const int64_t* __restrict__ best_ids, int n_hyps, int W,
-    int V, int n_new, float* __restrict__ s_new) {
-  const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
-  if (i >= (size_t)n_new * V) return;
-  const int hn = (int)(i / V);
-  const int b = hn / W;
-  s_new[i] = log_psi[(size_t)b * n_hyps * V + best_ids[hn]];
+  if (i < n_new * V) {
+    const int hn = (int)(i / V);
+    const int b = hn / W;
+    s_new[i] = log_psi[(size_t)b * n_hyps * V + best_ids[hn]];
+  }
 }
 
 static inline unsigned blocks(size_t n, int per) { return (unsigned)((n + per - 1) / per); }
@@ -572,21 +577,21 @@ extern "C" int b200ctc_prefix_transpose(const float* lp, float* lp_t, int B, int
              lp_t_ld);
   if (B == 0 || T == t0) return B200CTC_OK;
   const int nt = T - t0;
-  B2_REQUIRE(B <= 65535 && (nt + 31) / 32 <= 65535, "prefix_transpose: shape too large");
-  prefix_transpose_kernel<<<dim3((V + 31) / 32, (nt + 31) / 32, B), 256, 0,
+  B2_REQUIRE(B <= 65535 && (nt + kTrTile - 1) / kTrTile <= 65535, "prefix_transpose: shape too large");
+  prefix_transpose_kernel<<<dim3((V + kTrTile - 1) / kTrTile, (nt + kTrTile - 1) / kTrTile, B), 256, 0,
                             static_cast<cudaStream_t>(stream)>>>(lp, lp_t, T, V, t0, lp_t_ld);
   count_launch();
   return check_launch("prefix_transpose");
 }
 
-extern "C" int b200ctc_prefix_step(const float* lp, const float* lp_t, const float* r_prev,
-                                   const float* s_prev,
-                                   const int64_t* last_ids, const int64_t* scoring_ids,
-                                   const int64_t* end_frames, int B, int n_hyps, int T, int V,
-                                   int snum, int out_len, int start, int end, int blank, int eos,
-                                   float logzero, float* r, float* log_psi, float* scores,
-                                   int64_t* idmap, float* rsum_ws, int lp_t_ld, const int* win_utt,
-                                   b200ctc_stream_t stream) {
+// b200ctc_prefix_step with the last token of hypothesis h at last_ids[h * last_stride] (the
+// position call reads it straight out of the prefix buffer)
+int b200ctc::prefix_step_impl(const float* lp, const float* lp_t, const float* r_prev, const float* s_prev,
+                              const int64_t* last_ids, long long last_stride, const int64_t* scoring_ids,
+                              const int64_t* end_frames, int B, int n_hyps, int T, int V, int snum,
+                              int out_len, int start, int end, int blank, int eos, float logzero, float* r,
+                              float* log_psi, float* scores, int64_t* idmap, float* rsum_ws, int lp_t_ld,
+                              const int* win_utt, b200ctc_stream_t stream) {
   B2_REQUIRE(lp && r_prev && last_ids && end_frames && r && log_psi && scores && rsum_ws,
              "prefix_step: null pointer");
   B2_REQUIRE(!lp_t || lp_t_ld >= T, "prefix_step: lp_t_ld=%d < T=%d", lp_t_ld, T);
@@ -599,11 +604,11 @@ extern "C" int b200ctc_prefix_step(const float* lp, const float* lp_t, const flo
   const int n_bh = B * n_hyps;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   prof_mark(4, 0, st);
-  prefix_rsum_kernel<<<blocks((size_t)T * n_bh, 256), 256, 0, st>>>(r_prev, T, n_bh, rsum_ws);
-  count_launch();
-  if (scoring_ids) {
-    prefix_fill_kernel<<<blocks((size_t)n_bh * V, 256), 256, 0, st>>>(
-        rsum_ws, s_prev, end_frames, n_bh, n_hyps, V, blank, eos, logzero, log_psi, scores, idmap);
+  {
+    const size_t n1 = (size_t)T * n_bh, n2 = scoring_ids ? (size_t)n_bh * V : 0;
+    prefix_prepare_kernel<<<blocks(n1 > n2 ? n1 : n2, 256), 256, 0, st>>>(
+        r_prev, s_prev, end_frames, T, n_bh, n_hyps, V, blank, eos, logzero, scoring_ids != nullptr, rsum_ws,
+        log_psi, scores, idmap);
     count_launch();
   }
   // the time-contiguous copy pays off when few of the V columns are touched per hypothesis
@@ -624,7 +629,7 @@ extern "C" int b200ctc_prefix_step(const float* lp, const float* lp_t, const flo
     }
     prefix_step_scan_kernel<<<dim3((snum + kScanCand - 1) / kScanCand, n_bh), 32 * scan_warps, scan_smem, st>>>(
         lp_t, r_prev, rsum_ws, s_prev, last_ids, scoring_ids, n_bh, n_hyps, T, V, snum, out_len, start, end,
-        blank, eos, logzero, r, log_psi, scores, idmap, lp_t_ld, win_utt, scan_cap);
+        blank, eos, logzero, r, log_psi, scores, idmap, lp_t_ld, win_utt, scan_cap, last_stride);
   } else if (lp_t && scoring_ids) {
     // small launch: spread the warps over the SMs (see the kernel); 16-byte loads need a
     // 16-byte aligned copy whose time stride is a multiple of 4 frames
@@ -636,19 +641,35 @@ extern "C" int b200ctc_prefix_step(const float* lp, const float* lp_t, const flo
     if (ahead >= 2 && nt < 128)
       prefix_step_kernel<true, 2><<<blocks(pairs, nt), nt, 0, st>>>(
           lp, lp_t, r_prev, rsum_ws, s_prev, last_ids, scoring_ids, end_frames, n_bh, n_hyps, T, V,
-          snum, out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap, lp_t_ld, win_utt, vec);
+          snum, out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap, lp_t_ld, win_utt, vec,
+          last_stride);
     else
       prefix_step_kernel<true, 1><<<blocks(pairs, nt), nt, 0, st>>>(
           lp, lp_t, r_prev, rsum_ws, s_prev, last_ids, scoring_ids, end_frames, n_bh, n_hyps, T, V,
-          snum, out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap, lp_t_ld, win_utt, vec);
+          snum, out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap, lp_t_ld, win_utt, vec,
+          last_stride);
   } else {
     prefix_step_kernel<false, 1><<<blocks(pairs, 128), 128, 0, st>>>(
         lp, lp_t, r_prev, rsum_ws, s_prev, last_ids, scoring_ids, end_frames, n_bh, n_hyps, T, V,
-        snum, out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap, lp_t_ld, win_utt, 0);
+        snum, out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap, lp_t_ld, win_utt, 0,
+        last_stride);
   }
   count_launch();
   prof_mark(4, 1, st);
   return check_launch("prefix_step");
+}
+
+extern "C" int b200ctc_prefix_step(const float* lp, const float* lp_t, const float* r_prev,
+                                   const float* s_prev,
+                                   const int64_t* last_ids, const int64_t* scoring_ids,
+                                   const int64_t* end_frames, int B, int n_hyps, int T, int V,
+                                   int snum, int out_len, int start, int end, int blank, int eos,
+                                   float logzero, float* r, float* log_psi, float* scores,
+                                   int64_t* idmap, float* rsum_ws, int lp_t_ld, const int* win_utt,
+                                   b200ctc_stream_t stream) {
+  return prefix_step_impl(lp, lp_t, r_prev, s_prev, last_ids, 1, scoring_ids, end_frames, B, n_hyps, T, V, snum,
+                          out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap, rsum_ws,
+                          lp_t_ld, win_utt, stream);
 }
 
 extern "C" int b200ctc_prefix_select(const float* r, const float* log_psi, const int64_t* idmap,
@@ -659,10 +680,9 @@ extern "C" int b200ctc_prefix_select(const float* r, const float* log_psi, const
   B2_REQUIRE(B > 0 && n_hyps > 0 && W > 0 && T > 0 && V > 0 && snum > 0, "prefix_select: bad shape");
   const int n_bh = B * n_hyps, n_new = B * W;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  prefix_select_r_kernel<<<blocks((size_t)T * 2 * n_new, 256), 256, 0, st>>>(
-      r, idmap, best_ids, n_hyps, W, T, V, snum, n_bh, r_new);
-  prefix_select_s_kernel<<<blocks((size_t)n_new * V, 256), 256, 0, st>>>(log_psi, best_ids, n_hyps,
-                                                                         W, V, n_new, s_new);
-  count_launch(2);
+  const size_t n1 = (size_t)T * 2 * n_new, n2 = (size_t)n_new * V;
+  prefix_select_kernel<<<blocks(n1 > n2 ? n1 : n2, 256), 256, 0, st>>>(r, log_psi, idmap, best_ids, n_hyps, W,
+                                                                       T, V, snum, n_bh, r_new, s_new);
+  count_launch();
   return check_launch("prefix_select");
 }

@@ -162,7 +162,7 @@ class _PositionPlan:
             "r": torch.empty(T, 2, n, sw, **f32), "log_psi": torch.empty(n, V, **f32),
             "ctc_scores": torch.empty(n, V, **f32),
             "idmap": torch.empty(n, V, **i64) if snum > 0 else None,
-            "rsum": torch.empty(T, n, **f32), "last_ids": torch.empty(n, **i64),
+            "rsum": torch.empty(T, n, **f32),
             "part_ids": torch.empty(n, snum, **i64) if snum > 0 else None,
             "run0": torch.full((U, W), _NEG_INF, **f32), "run1": torch.empty(U, W, **f32),
             "cum0": torch.zeros(K, n, **f32), "cum1": torch.empty(K, n, **f32),
@@ -182,7 +182,7 @@ class _PositionPlan:
         for q, w in enumerate(weights):
             c.weights[q] = float(w)
         for name in ("lp", "lp_t", "end_frames", "r", "log_psi", "ctc_scores", "idmap",
-                     "rsum", "last_ids", "part_ids", "active", "maxlen", "out_val", "out_flat", "pack"):
+                     "rsum", "part_ids", "active", "maxlen", "out_val", "out_flat", "pack"):
             setattr(c, name, None if t[name] is None else t[name].data_ptr())
         c.lp_t_ld = t["lp_t"].shape[2] if snum > 0 else T
         for b in (0, 1):

@@ -339,7 +339,6 @@ typedef struct b200ctc_beam_plan {
   float* ctc_scores;         /* (n,V) */
   int64_t* idmap;            /* (n,V); unused when snum == 0 */
   float* rsum;               /* (T,n) scratch */
-  int64_t* last_ids;         /* (n) scratch: last token of every prefix */
   int64_t* part_ids;         /* (n,snum) scratch: pre-beam candidates */
   /* beam state, device memory; [step_i & 1] is read, [(step_i + 1) & 1] is written */
   float* run_score[2];       /* (n) */
