@@ -29,6 +29,7 @@ SIGNATURES = {
     "b200ctc_profile_read": (c_int, [POINTER(c_float), POINTER(c_int), c_int]),
     "b200ctc_device_info": (c_int, [POINTER(c_int), POINTER(c_int), POINTER(c_int)]),
     "b200ctc_softmax_fwd": (c_int, [_P, _P, c_int64, c_int, c_int, c_int, _P]),
+    "b200ctc_softmax_fwd_bias": (c_int, [_P, _P, _P, c_int64, c_int, c_int, c_int, _P]),
     "b200ctc_softmax_bwd": (c_int, [_P, _P, _P, c_int64, c_int, c_int, c_int, _P]),
     "b200ctc_argmax": (c_int, [_P, _P, c_int64, c_int, c_int, _P]),
     "b200ctc_greedy_decode": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_int, _P, _P, _P]),

@@ -58,20 +58,32 @@ struct BeamScores {
 // serial rounds: one warp selecting k times over the list kept the other warps at a barrier
 // for a third of the kernel.  Ends with a barrier; res_* hold the winners in order.
 template <int NT>
-__device__ __forceinline__ void rank_select(const float* cv, const int* ce, int n, int k, float* res_v,
-                                            int* res_e) {
-  const int tid = threadIdx.x;
+__device__ __forceinline__ void rank_select(const float* cv, const int* ce, int lists, int per, int k,
+                                            float* res_v, int* res_e) {
+  // The candidates come as `lists` lists of `per` entries, each SORTED (best first, empty slots
+  // last): a candidate's rank is its position in its own list plus, per other list, the number
+  // of entries that beat it - a binary search (<= 7 steps) instead of a scan.
+  const int tid = threadIdx.x, n = lists * per;
   if (tid < k) { res_v[tid] = kNegInf; res_e[tid] = 0; }  // fewer than k candidates: like the first version
   __syncthreads();
   for (int i = tid; i < n; i += NT) {
     const float x = cv[i];
     const int e = ce[i];
     if (e == 0x7fffffff) continue;
-    int rank = 0;
-    for (int j = 0; j < n; ++j) {
-      const float y = cv[j];
-      const int f = ce[j];
-      rank += (f != 0x7fffffff && (y > x || (y == x && f < e))) ? 1 : 0;
+    const int own = i / per;
+    int rank = i - own * per;
+    for (int l = 0; l < lists && rank < k; ++l) {
+      if (l == own) continue;
+      const float* lv = cv + l * per;
+      const int* le = ce + l * per;
+      int lo = 0, hi = per;  // first entry of list l that does NOT beat (x, e)
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        const float y = lv[mid];
+        const int f = le[mid];
+        if (f != 0x7fffffff && (y > x || (y == x && f < e))) lo = mid + 1; else hi = mid;
+      }
+      rank += lo;
     }
     if (rank < k) { res_v[rank] = x; res_e[rank] = e; }
   }
@@ -86,12 +98,15 @@ __device__ __forceinline__ void rank_select(const float* cv, const int* ce, int 
 // `off`: the CTA owns elements [off, off + E) of a larger segment (a cluster shares one
 // utterance, below); vals[] is indexed locally, the reported winners res_e[] carry LOCAL
 // indices too (the caller adds `off`; ties inside a slice are by index either way).
-template <int NT>
+// ONE_ROW: the segment is one row of V entries (the pre-beam): no row / column split at all.
+template <int NT, bool ONE_ROW = false>
 __device__ __forceinline__ void segment_topk(const BeamScores& S, long long row0, int V, int E,
                                              const float* __restrict__ run, int k, float* vals,
                                              float* res_v, int* res_e, int off = 0) {
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   constexpr int NWARP = NT / 32, UN = 8;
+  // e / V by multiply-high: exact for e, V < 2^16 (segments hold at most 54 K values)
+  const unsigned v_magic = V > 1 ? (unsigned)(0x100000000ull / (unsigned)V) + 1u : 0u;
   // the thread's best AND second best: a retired winner is replaced without a rescan of the
   // share (a dependent chain of E/NT shared-memory reads - it, not the barriers, was most of a
   // round); only a thread that wins twice rescans
@@ -110,7 +125,7 @@ __device__ __forceinline__ void segment_topk(const BeamScores& S, long long row0
     for (int j = 0; j < UN; ++j) {
       const int e = e0 + j * NT;
       const int ec = (e < E ? e : 0) + off;
-      const int h = ec / V;
+      const int h = ONE_ROW ? 0 : (V > 1 ? (int)__umulhi((unsigned)ec, v_magic) : ec);
       row[j] = row0 + h;
       col[j] = ec - h * V;
       acc[j] = 0.f;
@@ -171,7 +186,7 @@ __device__ __forceinline__ void segment_topk(const BeamScores& S, long long row0
     }
   }
   __syncthreads();
-  rank_select<NT>(wl_v, wl_e, NWARP * k, k, res_v, res_e);
+  rank_select<NT>(wl_v, wl_e, NWARP, k, k, res_v, res_e);
 }
 
 template <int NT>
@@ -257,7 +272,7 @@ __global__ void __launch_bounds__(NT) beam_select_cluster_kernel(
   cluster_sync_all();  // the neighbours may exit: their lists have been copied
   if (c != 0) return;
   __syncthreads();
-  rank_select<NT>(mg_v, mg_e, C * k, k, res_v, res_e);
+  rank_select<NT>(mg_v, mg_e, C, k, k, res_v, res_e);
   const bool act = (active ? active[u] != 0 : true) && !(maxlen && maxlen[u] - 1 == step_i);
   if (tid < k) {
     const int j = tid, e = res_e[j];
@@ -296,7 +311,7 @@ __global__ void __launch_bounds__(NT) beam_prebeam_kernel(const __grid_constant_
   __shared__ float res_v[kBeamMaxK];
   __shared__ int res_e[kBeamMaxK];
   const long long row = blockIdx.x;
-  segment_topk<NT>(S, row, V, V, nullptr, k, vals, res_v, res_e);
+  segment_topk<NT, true>(S, row, V, V, nullptr, k, vals, res_v, res_e);
   __syncthreads();
   if (threadIdx.x < k) out_ids[row * k + threadIdx.x] = res_e[threadIdx.x];
 }

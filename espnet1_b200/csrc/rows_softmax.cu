@@ -73,7 +73,7 @@ __device__ __forceinline__ float block_sum(float v, float* red) {
 // ---------------------------------------------------------------- forward
 template <typename T, int NT, int PER, int MODE>
 __global__ void __launch_bounds__(NT) softmax_fwd_vec(const T* __restrict__ x, T* __restrict__ y,
-                                                      int V) {
+                                                      int V, const T* __restrict__ bias) {
   using C = Chunk<T>;
   __shared__ float red[32];
   const int64_t row = blockIdx.x;
@@ -87,6 +87,12 @@ __global__ void __launch_bounds__(NT) softmax_fwd_vec(const T* __restrict__ x, T
     const int i = threadIdx.x + j * NT;
     if (i < nchunk) {
       c[j].load(xr + i * C::N);
+      if (bias) {  // the projection's bias, added here instead of by a GEMM epilogue pass
+        C bc;
+        bc.load(bias + i * C::N);
+#pragma unroll
+        for (int e = 0; e < C::N; ++e) c[j].v[e] += bc.v[e];
+      }
 #pragma unroll
       for (int e = 0; e < C::N; ++e) m = fmaxf(m, c[j].v[e]);
     }
@@ -125,21 +131,22 @@ __global__ void __launch_bounds__(NT) softmax_fwd_vec(const T* __restrict__ x, T
 // generic fallback: any V / alignment, three passes (row stays in L1/L2)
 template <typename T, int MODE>
 __global__ void __launch_bounds__(256) softmax_fwd_any(const T* __restrict__ x, T* __restrict__ y,
-                                                       int V) {
+                                                       int V, const T* __restrict__ bias) {
   __shared__ float red[32];
   const int64_t row = blockIdx.x;
   const T* xr = x + row * V;
   T* yr = y + row * V;
+  auto at = [&](int i) { return to_f32<T>(xr[i]) + (bias ? to_f32<T>(bias[i]) : 0.f); };
   float m = kNegInf;
-  for (int i = threadIdx.x; i < V; i += 256) m = fmaxf(m, to_f32<T>(xr[i]));
+  for (int i = threadIdx.x; i < V; i += 256) m = fmaxf(m, at(i));
   m = block_max<256>(m, red);
   const float mm = (m == kNegInf || m == -kNegInf) ? 0.f : m;
   float s = 0.f;
-  for (int i = threadIdx.x; i < V; i += 256) s += ex2((to_f32<T>(xr[i]) - mm) * kLog2e);
+  for (int i = threadIdx.x; i < V; i += 256) s += ex2((at(i) - mm) * kLog2e);
   s = block_sum<256>(s, red);
   const float shift = mm + logf(s), inv = 1.f / s;
   for (int i = threadIdx.x; i < V; i += 256) {
-    const float v = to_f32<T>(xr[i]);
+    const float v = at(i);
     yr[i] = from_f32<T>(MODE == 1 ? ex2((v - mm) * kLog2e) * inv : v - shift);
   }
 }
@@ -203,24 +210,26 @@ __global__ void __launch_bounds__(256) softmax_bwd_any(const T* __restrict__ y,
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 template <typename T, int MODE>
-static int launch_fwd(const void* x, void* y, int64_t rows, int V, cudaStream_t st) {
+static int launch_fwd(const void* x, void* y, int64_t rows, int V, cudaStream_t st,
+                      const void* bias = nullptr) {
   constexpr int N = Chunk<T>::N;
   constexpr int PER = (N == 4) ? 8 : 4;
   const T* xi = static_cast<const T*>(x);
   T* yo = static_cast<T*>(y);
-  const bool vec = (V % N == 0) && aligned16(x) && aligned16(y);
+  const T* bi = static_cast<const T*>(bias);
+  const bool vec = (V % N == 0) && aligned16(x) && aligned16(y) && aligned16(bias);
   const int nchunk = V / N;
   dim3 grid((unsigned)rows);
   if (vec && nchunk <= 128 * PER) {
-    softmax_fwd_vec<T, 128, PER, MODE><<<grid, 128, 0, st>>>(xi, yo, V);
+    softmax_fwd_vec<T, 128, PER, MODE><<<grid, 128, 0, st>>>(xi, yo, V, bi);
   } else if (vec && nchunk <= 256 * PER) {
-    softmax_fwd_vec<T, 256, PER, MODE><<<grid, 256, 0, st>>>(xi, yo, V);
+    softmax_fwd_vec<T, 256, PER, MODE><<<grid, 256, 0, st>>>(xi, yo, V, bi);
   } else if (vec && nchunk <= 512 * PER) {
-    softmax_fwd_vec<T, 512, PER, MODE><<<grid, 512, 0, st>>>(xi, yo, V);
+    softmax_fwd_vec<T, 512, PER, MODE><<<grid, 512, 0, st>>>(xi, yo, V, bi);
   } else if (vec && nchunk <= 1024 * PER) {
-    softmax_fwd_vec<T, 1024, PER, MODE><<<grid, 1024, 0, st>>>(xi, yo, V);
+    softmax_fwd_vec<T, 1024, PER, MODE><<<grid, 1024, 0, st>>>(xi, yo, V, bi);
   } else {
-    softmax_fwd_any<T, MODE><<<grid, 256, 0, st>>>(xi, yo, V);
+    softmax_fwd_any<T, MODE><<<grid, 256, 0, st>>>(xi, yo, V, bi);
   }
   count_launch();
   return check_launch("softmax_fwd");
@@ -269,6 +278,26 @@ extern "C" int b200ctc_softmax_fwd(const void* x, void* y, int64_t rows, int V, 
     case 5: return launch_fwd<__nv_bfloat16, 1>(x, y, rows, V, st);
   }
   set_error("softmax_fwd: unknown dtype %d", dtype);
+  return B200CTC_ERR_ARG;
+}
+
+extern "C" int b200ctc_softmax_fwd_bias(const void* x, const void* bias, void* y, int64_t rows, int V,
+                                        int dtype, int mode, b200ctc_stream_t stream) {
+  B2_REQUIRE(x && y && bias, "softmax_fwd_bias: null pointer");
+  B2_REQUIRE(rows >= 0 && rows < (1ll << 31) && V > 0, "softmax_fwd_bias: bad shape rows=%lld V=%d",
+             (long long)rows, V);
+  B2_REQUIRE(mode == 0 || mode == 1, "softmax_fwd_bias: mode must be 0 or 1");
+  if (rows == 0) return B200CTC_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (dtype * 2 + mode) {
+    case 0: return launch_fwd<float, 0>(x, y, rows, V, st, bias);
+    case 1: return launch_fwd<float, 1>(x, y, rows, V, st, bias);
+    case 2: return launch_fwd<__half, 0>(x, y, rows, V, st, bias);
+    case 3: return launch_fwd<__half, 1>(x, y, rows, V, st, bias);
+    case 4: return launch_fwd<__nv_bfloat16, 0>(x, y, rows, V, st, bias);
+    case 5: return launch_fwd<__nv_bfloat16, 1>(x, y, rows, V, st, bias);
+  }
+  set_error("softmax_fwd_bias: unknown dtype %d", dtype);
   return B200CTC_ERR_ARG;
 }
 

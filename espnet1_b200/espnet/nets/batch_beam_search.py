@@ -168,7 +168,7 @@ class _PositionPlan:
             "cum0": torch.zeros(K, n, **f32), "cum1": torch.empty(K, n, **f32),
             "y0": torch.empty(n, stride, **i64), "y1": torch.empty(n, stride, **i64),
             "active": torch.ones(U, dtype=torch.uint8, device=dev),
-            "maxlen": torch.tensor(maxlen, dtype=torch.int32, device=dev),
+            "maxlen": BatchBeamSearch._upload(maxlen, torch.int32, dev),
             "out_val": torch.empty(n, **f32), "out_flat": torch.empty(n, **i64),
             "pack": torch.empty(3 + K, U, W, **f32),
             # two records: position i+1 may be issued while the host still reads position i's
@@ -337,6 +337,13 @@ class BatchBeamSearch(torch.nn.Module):
             merged = [st for st_u in new_states for st in (st_u if st_u is not None else [None] * W)]
         return torch.cat(outs, dim=0), merged
 
+    @staticmethod
+    def _upload(values, dtype, dev) -> torch.Tensor:
+        """A few host values as a device tensor without blocking: a pageable host-to-device copy
+        waits until the GPU has drained everything queued before it (here: the CTC projection)."""
+        t = torch.tensor(values, dtype=dtype)
+        return t.pin_memory().to(dev, non_blocking=True) if dev.type == "cuda" else t.to(dev)
+
     def _maxlen(self, T: int, maxlenratio: float) -> int:
         if maxlenratio == 0:
             return T
@@ -375,7 +382,7 @@ class BatchBeamSearch(torch.nn.Module):
                 if U != 1:
                     raise ValueError(f"partial scorer {k} has no batched-state API: one utterance at a time")
                 part_states[k] = [d.batch_init_state(xs[0, : lens[0]])] * n
-        yseq = torch.tensor(primer, dtype=torch.int64, device=dev).repeat(n, 1)
+        yseq = self._upload(primer, torch.int64, dev).repeat(n, 1)
         names = list(self.full_scorers) + list(self.part_scorers)  # accumulation order (:217-241)
         # a scorer that ignores the encoder output does not need the (n, T, D) copy of it
         need_x = any(not getattr(d, "ignores_x", False) for d in self.full_scorers.values())

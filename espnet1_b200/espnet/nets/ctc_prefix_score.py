@@ -44,7 +44,10 @@ class CTCPrefixScoreTH(object):
         self.dtype = x.dtype
         self.device = x.device
         xl = torch.as_tensor(xlens)
-        self._xlens_dev = xl.to(device=self.device, dtype=torch.int64).contiguous()
+        if xl.is_cuda:
+            self._xlens_dev = xl.to(device=self.device, dtype=torch.int64).contiguous()
+        else:  # from pinned memory, not blocking: a pageable upload would wait for the GPU to drain
+            self._xlens_dev = xl.to(torch.int64).pin_memory().to(self.device, non_blocking=True)
         self.end_frames = xl - 1  # same object kind as the reference (:55)
         self._end_frames_dev = self._xlens_dev - 1
         self._set_lp(x, pad=True)

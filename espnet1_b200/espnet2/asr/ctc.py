@@ -187,13 +187,26 @@ class CTC(torch.nn.Module):
             cur.wait_stream(side)
         return out
 
+    def _projection(self, hs_pad):
+        """``ctc_lo(hs_pad)`` as (GEMM output, bias to add): where the soft-max kernel can take the
+        bias (same dtype as the GEMM output, CUDA) the GEMM runs without it - cuBLASLt adds the
+        bias of this shape in a separate pass over the (B, T, odim) output, a third of the
+        projection's time - and the soft-max's one read of each row absorbs it."""
+        lo = self.ctc_lo
+        if (lo.bias is not None and hs_pad.is_cuda and hs_pad.dtype == lo.weight.dtype == lo.bias.dtype
+                and not torch.is_autocast_enabled()):
+            return F.linear(hs_pad, lo.weight), lo.bias
+        return lo(hs_pad), None
+
     def softmax(self, hs_pad):
         """softmax of frame activations: (B, Tmax, eprojs) -> (B, Tmax, odim)."""
-        return B.softmax(self.ctc_lo(hs_pad))
+        x, bias = self._projection(hs_pad)
+        return B.softmax(x, bias)
 
     def log_softmax(self, hs_pad):
         """log_softmax of frame activations: (B, Tmax, eprojs) -> (B, Tmax, odim)."""
-        return B.log_softmax(self.ctc_lo(hs_pad))
+        x, bias = self._projection(hs_pad)
+        return B.log_softmax(x, bias)
 
     def argmax(self, hs_pad):
         """argmax of frame activations: (B, Tmax, eprojs) -> (B, Tmax) int64."""

@@ -20,14 +20,22 @@ def _rows(x: torch.Tensor):
 class _SoftmaxFn(torch.autograd.Function):
     @staticmethod
     @on_tensor_device
-    def forward(ctx, x, mode):
+    def forward(ctx, x, mode, bias=None):
         require_cuda(x, "softmax input")
         xc = x.contiguous()
         y = torch.empty_like(xc)
         rows, V = _rows(xc)
-        check(lib().b200ctc_softmax_fwd(ptr(xc), ptr(y), rows, V, dtype_code(xc), mode,
-                                        stream_ptr(xc.device)), "softmax_fwd")
+        if bias is None:
+            check(lib().b200ctc_softmax_fwd(ptr(xc), ptr(y), rows, V, dtype_code(xc), mode,
+                                            stream_ptr(xc.device)), "softmax_fwd")
+        else:
+            if bias.dtype != xc.dtype or bias.numel() != V or bias.device != xc.device:
+                raise TypeError("softmax bias must be V values of the input's dtype on its device")
+            bc = bias.contiguous()
+            check(lib().b200ctc_softmax_fwd_bias(ptr(xc), ptr(bc), ptr(y), rows, V, dtype_code(xc), mode,
+                                                 stream_ptr(xc.device)), "softmax_fwd_bias")
         ctx.mode = mode
+        ctx.has_bias = bias is not None
         ctx.save_for_backward(y)
         return y
 
@@ -40,17 +48,19 @@ class _SoftmaxFn(torch.autograd.Function):
         rows, V = _rows(y)
         check(lib().b200ctc_softmax_bwd(ptr(y), ptr(dyc), ptr(dx), rows, V, dtype_code(y),
                                         ctx.mode, stream_ptr(y.device)), "softmax_bwd")
-        return dx, None
+        dbias = dx.reshape(-1, V).sum(0) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
+        return dx, None, dbias
 
 
-def log_softmax(x: torch.Tensor) -> torch.Tensor:
-    """log-softmax over the last dim (espnet2/asr/ctc.py:117)."""
-    return _SoftmaxFn.apply(x, 0)
+def log_softmax(x: torch.Tensor, bias: torch.Tensor = None) -> torch.Tensor:
+    """log-softmax over the last dim (espnet2/asr/ctc.py:117); with ``bias`` (V,) of ``x + bias`` -
+    the projection's bias absorbed into the kernel's one read of the row."""
+    return _SoftmaxFn.apply(x, 0, bias)
 
 
-def softmax(x: torch.Tensor) -> torch.Tensor:
-    """softmax over the last dim (espnet2/asr/ctc.py:107)."""
-    return _SoftmaxFn.apply(x, 1)
+def softmax(x: torch.Tensor, bias: torch.Tensor = None) -> torch.Tensor:
+    """softmax over the last dim (espnet2/asr/ctc.py:107); ``bias`` as in :func:`log_softmax`."""
+    return _SoftmaxFn.apply(x, 1, bias)
 
 
 @on_tensor_device

@@ -114,6 +114,41 @@ def test_softmax_family_vs_fixture(gm):
         np.testing.assert_array_equal(m.argmax(hs).cpu().numpy(), gm["argmax"])
 
 
+@pytest.mark.parametrize("dtype,V", [(torch.float32, 5000), (torch.float32, 37), (torch.bfloat16, 5000),
+                                     (torch.float16, 1024)])
+def test_softmax_with_projection_bias(dtype, V):
+    """`b200ctc_softmax_fwd_bias`: (log_)softmax(x + bias) with the bias absorbed by the kernel,
+    forward and backward (incl. d bias) against torch autograd in fp32 on the same inputs; and
+    `CTC.log_softmax` (GEMM without bias + this) against the plain module arithmetic."""
+    from espnet1_b200 import functional as F
+    from espnet1_b200.espnet2.asr.ctc import CTC
+
+    d = _dev()
+    g = torch.Generator().manual_seed(8)
+    x = (torch.randn(7, 33, V, generator=g) * 3).to(dtype).to(d)
+    b = torch.randn(V, generator=g).to(dtype).to(d)
+    tol = 1e-5 if dtype == torch.float32 else (2e-2 if dtype == torch.bfloat16 else 3e-3)
+    for fn, ref in ((F.log_softmax, torch.log_softmax), (F.softmax, torch.softmax)):
+        xa = x.clone().requires_grad_(True)
+        ba = b.clone().requires_grad_(True)
+        y = fn(xa, ba)
+        xr = x.float().clone().requires_grad_(True)
+        br = b.float().clone().requires_grad_(True)
+        yr = ref(xr + br, -1)
+        close(y.float(), yr.detach().cpu().numpy(), tol, tol)
+        w = torch.randn(y.shape, generator=g).to(d)
+        (y.float() * w).sum().backward()
+        (yr * w).sum().backward()
+        close(xa.grad.float(), xr.grad.cpu().numpy(), 10 * tol, 10 * tol)
+        close(ba.grad.float(), br.grad.cpu().numpy(), 50 * tol, 50 * tol * max(1.0, float(br.grad.abs().max())))
+    if dtype == torch.float32:
+        m = CTC(V, 16).to(d)
+        hs = torch.randn(3, 20, 16, generator=g).to(d)
+        with torch.no_grad():
+            close(m.log_softmax(hs), torch.log_softmax(m.ctc_lo(hs), -1).cpu().numpy(), 1e-5, 2e-6)
+            close(m.softmax(hs), torch.softmax(m.ctc_lo(hs), -1).cpu().numpy(), 1e-5, 1e-7)
+
+
 def test_c1_logits_boundary_vs_fixture_and_oracle():
     from espnet1_b200 import functional as F
     from oracle import ctc_numpy
