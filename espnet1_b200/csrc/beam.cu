@@ -130,16 +130,25 @@ __device__ __forceinline__ void segment_topk(const BeamScores& S, long long row0
       col[j] = ec - h * V;
       acc[j] = 0.f;
     }
-#pragma unroll 1
-    for (int q = 0; q < S.K; ++q) {
+    // scorer q + 1's loads are issued before scorer q's values are consumed (two rounds of
+    // loads in flight; the accumulation order over q stays the reference's)
+    float x[UN];
+    auto fetch = [&](int q, float* dst) {
       const float* __restrict__ p = S.p[q];
       const long long rs = S.rs[q], cs = S.cs[q];
-      const float wq = S.w[q];
-      float x[UN];
 #pragma unroll
-      for (int j = 0; j < UN; ++j) x[j] = __ldg(p + row[j] * rs + (long long)col[j] * cs);
+      for (int j = 0; j < UN; ++j) dst[j] = __ldg(p + row[j] * rs + (long long)col[j] * cs);
+    };
+    fetch(0, x);
+#pragma unroll 1
+    for (int q = 0; q < S.K; ++q) {
+      const float wq = S.w[q];
+      float nx[UN];
+      if (q + 1 < S.K) fetch(q + 1, nx);
 #pragma unroll
       for (int j = 0; j < UN; ++j) acc[j] = __fadd_rn(acc[j], __fmul_rn(wq, x[j]));
+#pragma unroll
+      for (int j = 0; j < UN; ++j) x[j] = nx[j];
     }
 #pragma unroll
     for (int j = 0; j < UN; ++j) {

@@ -57,12 +57,17 @@ extern "C" int b200ctc_beam_position(const b200ctc_beam_plan* p, const float* co
     if (rc != B200CTC_OK) return rc;
   }
   const int out_len = cur_len - 1;
+  // `r` never leaves this call: where the scan kernel takes the step it is kept time-major
+  // (n, snum, 2, T) - the kernel streams whole rows out and the selection below reads them back
+  // coalesced - instead of the reference's (T, 2, n, snum) that the stand-alone entry points expose
+  static const int tm_on = tuning_int("B200CTC_BEAM_TIME_MAJOR", 1);
+  const int tm = (tm_on && pre && prefix_scan_applies(true, true, n, p->snum, T)) ? 1 : 0;
   // (the last token of every prefix is read in place: column cur_len - 1 of the prefix buffer)
   rc = prefix_step_impl(p->lp, pre ? p->lp_t : nullptr, p->r_state[in], step_i == 0 ? nullptr : p->s_state[in],
                            p->yseq[in] + (cur_len - 1), p->yseq_stride, pre ? p->part_ids : nullptr, p->end_frames, U, W, T, V,
                            pre ? p->snum : V, out_len, out_len > 1 ? out_len : 1, T, p->blank, p->eos,
                            p->logzero, p->r, p->log_psi, p->ctc_scores, pre ? p->idmap : nullptr, p->rsum,
-                           (int)p->lp_t_ld, nullptr, stream);
+                           (int)p->lp_t_ld, nullptr, tm, stream);
   if (rc != B200CTC_OK) return rc;
 
   // ---- pruning (batch_beam(), :98-118, and the gathers of :243-283)
@@ -83,8 +88,8 @@ extern "C" int b200ctc_beam_position(const b200ctc_beam_plan* p, const float* co
   if (rc != B200CTC_OK) return rc;
 
   // ---- the surviving slots' CTC state (index_select_state, ctc_prefix_score.py:189-220)
-  rc = b200ctc_prefix_select(p->r, p->log_psi, pre ? p->idmap : nullptr, p->out_flat, U, W, W, T, V,
-                             pre ? p->snum : V, p->r_state[out], p->s_state[out], stream);
+  rc = prefix_select_impl(p->r, p->log_psi, pre ? p->idmap : nullptr, p->out_flat, U, W, W, T, V,
+                          pre ? p->snum : V, p->r_state[out], p->s_state[out], tm, stream);
   if (rc != B200CTC_OK) return rc;
 
   // ---- the one record the host reads per position

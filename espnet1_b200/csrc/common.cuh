@@ -21,7 +21,11 @@ int prefix_step_impl(const float* lp, const float* lp_t, const float* r_prev, co
                      const int64_t* end_frames, int B, int n_hyps, int T, int V, int snum, int out_len,
                      int start, int end, int blank, int eos, float logzero, float* r, float* log_psi,
                      float* scores, int64_t* idmap, float* rsum_ws, int lp_t_ld, const int* win_utt,
-                     b200ctc_stream_t stream);
+                     int r_time_major, b200ctc_stream_t stream);
+bool prefix_scan_applies(bool have_lp_t, bool have_ids, int n_bh, int snum, int T);
+int prefix_select_impl(const float* r, const float* log_psi, const int64_t* idmap, const int64_t* best_ids,
+                       int B, int n_hyps, int W, int T, int V, int snum, float* r_new, float* s_new,
+                       int r_time_major, b200ctc_stream_t stream);
 int sm_count();
 // profiling phases: 0 prep, 1 lse_gather (pass A), 2 lattice, 3 grad_rows (pass B),
 // 4 prefix_step, 5 softmax family

@@ -349,7 +349,8 @@ __global__ void __launch_bounds__(32 * kScanCand, 2) prefix_step_scan_kernel(
     const int64_t* __restrict__ scoring_ids, int n_bh, int n_hyps, int T, int V, int snum, int out_len,
     int start, int end, int blank, int eos, float logzero, float* __restrict__ r,
     float* __restrict__ log_psi, float* __restrict__ scores, int64_t* __restrict__ idmap, int ldt,
-    const int* __restrict__ win_utt, int cap /* frames a staged array can hold */, long long last_stride) {
+    const int* __restrict__ win_utt, int cap /* frames a staged array can hold */, long long last_stride,
+    int time_major /* r as (n_bh, snum, 2, T): the position call's private layout */) {
   extern __shared__ float sm[];
   const int h = blockIdx.y, c0 = blockIdx.x * kScanCand;
   const int ncand = min(kScanCand, snum - c0);
@@ -471,7 +472,27 @@ __global__ void __launch_bounds__(32 * kScanCand, 2) prefix_step_scan_kernel(
         scores[o] = psi - (s_prev ? s_prev[o] : 0.f);
       }
     }
+    if (time_major) {
+      // the pair's two rows of T frames are contiguous: the warp streams them out itself,
+      // 128 bytes per store instruction, no CTA-wide pass and no partial-sector rows
+      __syncwarp();
+      float* rn_row = r + idx * 2 * (size_t)T;
+      float* rb_row = rn_row + T;
+      for (int t = lane; t < T; t += 32) {
+        float vn = logzero, vb = logzero;
+        if (t >= start && t < end) {
+          const int sl = slot(t - start);
+          vn = xk[sl];
+          vb = rbo[sl];
+        } else if (t == 0) {
+          vn = (out_len == 0) ? __ldg(lp_t + ((size_t)b * V + k) * ldt) : logzero;
+        }
+        __stcs(rn_row + t, vn);
+        __stcs(rb_row + t, vb);
+      }
+    }
   }
+  if (time_major) return;
   __syncthreads();
 
   // ---- rows of r: (t, n|b) -> ncand contiguous values, one half-warp per row
@@ -496,10 +517,25 @@ __global__ void __launch_bounds__(32 * kScanCand, 2) prefix_step_scan_kernel(
 __global__ void __launch_bounds__(256) prefix_select_kernel(
     const float* __restrict__ r, const float* __restrict__ log_psi, const int64_t* __restrict__ idmap,
     const int64_t* __restrict__ best_ids, int n_hyps, int W, int T, int V, int snum, int n_bh,
-    float* __restrict__ r_new, float* __restrict__ s_new) {
+    float* __restrict__ r_new, float* __restrict__ s_new, int time_major) {
   const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
   const size_t n_new = (size_t)(n_bh / n_hyps) * W;
-  if (i < (size_t)T * 2 * n_new) {
+  if (time_major && i < (size_t)T * 2 * n_new) {
+    // r is (n_bh, snum, 2, T): consecutive threads walk t (coalesced reads), the (T,2,n_new)
+    // state is written with a stride - the scatter sits on the write side
+    const size_t row = i / T;  // (hn, x)
+    const int t = (int)(i - row * T), hn = (int)(row >> 1), x = (int)(row & 1);
+    const int b = hn / W;
+    const int64_t best = best_ids[hn];
+    const int hyp = (int)(best / V) + b * n_hyps;
+    const int label = (int)(best % V);
+    int col = label;
+    if (idmap) {
+      const int64_t c = idmap[(size_t)hyp * V + label];
+      col = c < 0 ? 0 : (int)c;
+    }
+    r_new[((size_t)t * 2 + x) * n_new + hn] = r[(((size_t)hyp * snum + col) * 2 + x) * T + t];
+  } else if (i < (size_t)T * 2 * n_new) {
     const size_t tn = i / n_new;
     const int hn = (int)(i - tn * n_new);
     const int b = hn / W;
@@ -584,14 +620,25 @@ extern "C" int b200ctc_prefix_transpose(const float* lp, float* lp_t, int B, int
   return check_launch("prefix_transpose");
 }
 
+// few candidates per hypothesis: the scan kernel takes the step (and its shared memory fits)
+bool b200ctc::prefix_scan_applies(bool have_lp_t, bool have_ids, int n_bh, int snum, int T) {
+  static const int scan_on = tuning_int("B200CTC_PREFIX_SCAN", 1);
+  const int scan_warps = snum < kScanCand ? snum : kScanCand;
+  const int scan_cap = 32 * (((T + 31) / 32) | 1);
+  const size_t scan_smem = (size_t)(3 + 2 * scan_warps) * (scan_cap + 1) * sizeof(float);
+  return have_lp_t && have_ids && scan_on && (size_t)n_bh * snum <= 32768 && T >= 64 && T < 2048 &&
+         n_bh <= 65535 && scan_smem <= 100 * 1024;
+}
+
 // b200ctc_prefix_step with the last token of hypothesis h at last_ids[h * last_stride] (the
-// position call reads it straight out of the prefix buffer)
+// position call reads it straight out of the prefix buffer) and, optionally, r in the position
+// call's private time-major layout (n_bh, snum, 2, T)
 int b200ctc::prefix_step_impl(const float* lp, const float* lp_t, const float* r_prev, const float* s_prev,
                               const int64_t* last_ids, long long last_stride, const int64_t* scoring_ids,
                               const int64_t* end_frames, int B, int n_hyps, int T, int V, int snum,
                               int out_len, int start, int end, int blank, int eos, float logzero, float* r,
                               float* log_psi, float* scores, int64_t* idmap, float* rsum_ws, int lp_t_ld,
-                              const int* win_utt, b200ctc_stream_t stream) {
+                              const int* win_utt, int r_time_major, b200ctc_stream_t stream) {
   B2_REQUIRE(lp && r_prev && last_ids && end_frames && r && log_psi && scores && rsum_ws,
              "prefix_step: null pointer");
   B2_REQUIRE(!lp_t || lp_t_ld >= T, "prefix_step: lp_t_ld=%d < T=%d", lp_t_ld, T);
@@ -613,12 +660,12 @@ int b200ctc::prefix_step_impl(const float* lp, const float* lp_t, const float* r
   }
   // the time-contiguous copy pays off when few of the V columns are touched per hypothesis
   const size_t pairs = (size_t)n_bh * snum;
-  static const int scan_on = tuning_int("B200CTC_PREFIX_SCAN", 1);
   const int scan_warps = snum < kScanCand ? snum : kScanCand;
   const int scan_cap = 32 * (((T + 31) / 32) | 1);
   const size_t scan_smem = (size_t)(3 + 2 * scan_warps) * (scan_cap + 1) * sizeof(float);
-  if (lp_t && scoring_ids && scan_on && pairs <= 32768 && T >= 64 && T < 2048 && n_bh <= 65535 &&
-      scan_smem <= 100 * 1024) {
+  const bool scan = prefix_scan_applies(lp_t != nullptr, scoring_ids != nullptr, n_bh, snum, T);
+  B2_REQUIRE(scan || !r_time_major, "prefix_step: the time-major layout of r is the scan kernel's only");
+  if (scan) {
     // few candidates: the frame loop parallel in time, one warp per (hypothesis, candidate)
     if (scan_smem > 48 * 1024 &&  // per device: set on every call (the process may use several)
         cudaFuncSetAttribute(prefix_step_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -629,7 +676,7 @@ int b200ctc::prefix_step_impl(const float* lp, const float* lp_t, const float* r
     }
     prefix_step_scan_kernel<<<dim3((snum + kScanCand - 1) / kScanCand, n_bh), 32 * scan_warps, scan_smem, st>>>(
         lp_t, r_prev, rsum_ws, s_prev, last_ids, scoring_ids, n_bh, n_hyps, T, V, snum, out_len, start, end,
-        blank, eos, logzero, r, log_psi, scores, idmap, lp_t_ld, win_utt, scan_cap, last_stride);
+        blank, eos, logzero, r, log_psi, scores, idmap, lp_t_ld, win_utt, scan_cap, last_stride, r_time_major);
   } else if (lp_t && scoring_ids) {
     // small launch: spread the warps over the SMs (see the kernel); 16-byte loads need a
     // 16-byte aligned copy whose time stride is a multiple of 4 frames
@@ -669,20 +716,27 @@ extern "C" int b200ctc_prefix_step(const float* lp, const float* lp_t, const flo
                                    b200ctc_stream_t stream) {
   return prefix_step_impl(lp, lp_t, r_prev, s_prev, last_ids, 1, scoring_ids, end_frames, B, n_hyps, T, V, snum,
                           out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap, rsum_ws,
-                          lp_t_ld, win_utt, stream);
+                          lp_t_ld, win_utt, 0, stream);
 }
 
-extern "C" int b200ctc_prefix_select(const float* r, const float* log_psi, const int64_t* idmap,
-                                     const int64_t* best_ids, int B, int n_hyps, int W, int T,
-                                     int V, int snum, float* r_new, float* s_new,
-                                     b200ctc_stream_t stream) {
+int b200ctc::prefix_select_impl(const float* r, const float* log_psi, const int64_t* idmap,
+                                const int64_t* best_ids, int B, int n_hyps, int W, int T, int V, int snum,
+                                float* r_new, float* s_new, int r_time_major, b200ctc_stream_t stream) {
   B2_REQUIRE(r && log_psi && best_ids && r_new && s_new, "prefix_select: null pointer");
   B2_REQUIRE(B > 0 && n_hyps > 0 && W > 0 && T > 0 && V > 0 && snum > 0, "prefix_select: bad shape");
   const int n_bh = B * n_hyps, n_new = B * W;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const size_t n1 = (size_t)T * 2 * n_new, n2 = (size_t)n_new * V;
   prefix_select_kernel<<<blocks(n1 > n2 ? n1 : n2, 256), 256, 0, st>>>(r, log_psi, idmap, best_ids, n_hyps, W,
-                                                                       T, V, snum, n_bh, r_new, s_new);
+                                                                       T, V, snum, n_bh, r_new, s_new,
+                                                                       r_time_major);
   count_launch();
   return check_launch("prefix_select");
+}
+
+extern "C" int b200ctc_prefix_select(const float* r, const float* log_psi, const int64_t* idmap,
+                                     const int64_t* best_ids, int B, int n_hyps, int W, int T,
+                                     int V, int snum, float* r_new, float* s_new,
+                                     b200ctc_stream_t stream) {
+  return prefix_select_impl(r, log_psi, idmap, best_ids, B, n_hyps, W, T, V, snum, r_new, s_new, 0, stream);
 }

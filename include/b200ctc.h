@@ -341,7 +341,8 @@ typedef struct b200ctc_beam_plan {
                                 written by init_state first), [(step_i + 1) & 1] written by
                                 prefix_select - so that position i + 1 can be in flight while
                                 the host still copies position i's state */
-  float* r;                  /* (T,2,n,snum or V) */
+  float* r;                  /* T*2*n*(snum or V) floats, private to the call (its layout may
+                                differ from prefix_step's (T,2,n,snum)) */
   float* log_psi;            /* (n,V) */
   float* ctc_scores;         /* (n,V) */
   int64_t* idmap;            /* (n,V); unused when snum == 0 */

@@ -32,6 +32,31 @@ def test_library_exports_every_declared_symbol():
     assert h.b200ctc_loss_workspace_bytes(64, 500, 5000, 150) > 64 * 500 * 301 * 8
 
 
+def test_beam_position_argument_checks_need_no_gpu():
+    """`b200ctc_beam_position` validates its plan before it touches the device: the error paths
+    (and the ctypes mirror of `b200ctc_beam_plan`, whose size the loader checks) run anywhere."""
+    import ctypes
+
+    from espnet1_b200 import _lib
+
+    h = _lib.lib()
+    assert h.b200ctc_beam_plan_bytes() == ctypes.sizeof(_lib.BeamPlan)
+    assert h.b200ctc_beam_position(None, None, None, 0, 1, None) == -1
+    assert b"null plan" in h.b200ctc_last_error()
+    plan = _lib.BeamPlan()
+    plan.U, plan.W, plan.V, plan.T, plan.K_full = 2, 3, 50, 40, 9
+    assert h.b200ctc_beam_position(ctypes.byref(plan), None, None, 0, 1, None) == -1
+    assert b"K_full" in h.b200ctc_last_error()
+    plan.K_full, plan.snum = 0, 5  # a pre-beam without a full scorer to take it from
+    assert h.b200ctc_beam_position(ctypes.byref(plan), None, None, 0, 1, None) == -1
+    assert b"pre-beam" in h.b200ctc_last_error()
+    plan.snum, plan.yseq_stride = 0, 8
+    assert h.b200ctc_beam_position(ctypes.byref(plan), None, None, 0, 8, None) == -1
+    assert b"prefix buffers" in h.b200ctc_last_error()
+    assert h.b200ctc_beam_position(ctypes.byref(plan), None, None, 0, 1, None) == -1
+    assert b"null buffer" in h.b200ctc_last_error()
+
+
 @pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU error path")
 def test_no_gpu_means_error_not_fallback():
     from espnet1_b200 import _lib, functional as F

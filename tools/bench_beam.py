@@ -112,6 +112,21 @@ def run(dev="cuda:0", POS=30, cpu_port=True):
             if bs.prof is not None and name.startswith("engine"):
                 out[name]["phase_ms_per_position"] = {
                     k: round(1e3 * v / POS / (1 if "batch" in name else n_utt), 4) for k, v in bs.prof.items()}
+    if "engine_batch32" in out:
+        # marginal cost of a position: two decodes of 2 x POS and POS positions, set-up and n-best
+        # construction cancel (they are the same in both)
+        with torch.no_grad():
+            ts = []
+            for pos in (POS, 2 * POS):
+                best = 1e9
+                for _ in range(3):
+                    torch.cuda.synchronize()
+                    t0 = time.perf_counter()
+                    bs.forward_batch(xs.clone(), lens, maxlenratio=-pos)
+                    torch.cuda.synchronize()
+                    best = min(best, time.perf_counter() - t0)
+                ts.append(best)
+        out["engine_batch32"]["marginal_ms_per_position"] = 1e3 * (ts[1] - ts[0]) / POS
     out["same_best_hypothesis"] = len({tuple(v["best0"]) for k, v in out.items() if isinstance(v, dict)}) == 1
     return out
 

@@ -10,11 +10,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 VARIANTS = [
     ("default", {}),
     ("no_scan", {"B200CTC_PREFIX_SCAN": "0"}),
+    ("no_time_major", {"B200CTC_BEAM_TIME_MAJOR": "0"}),
     ("no_cluster", {"B200CTC_BEAM_CLUSTER": "0"}),
-    ("prefix_nt128", {"B200CTC_PREFIX_SMALL_NT": "128"}),
-    ("prefix_nt64", {"B200CTC_PREFIX_SMALL_NT": "64"}),
-    ("prefix_ahead1", {"B200CTC_PREFIX_AHEAD": "1"}),
-    ("prefix_novec", {"B200CTC_PREFIX_VEC": "0"}),
     ("all_old", {"B200CTC_BEAM_CLUSTER": "0", "B200CTC_PREFIX_SMALL_NT": "128", "B200CTC_PREFIX_AHEAD": "1",
                  "B200CTC_PREFIX_VEC": "0"}),
 ]
