@@ -56,13 +56,17 @@ __global__ void __launch_bounds__(256) prefix_pad_kernel(float* __restrict__ lp,
 }
 
 // r0[t,0,:] = logzero ; r0[t,1,b*n_hyps+h] = sum_{tau<=t} lp[b,tau,blank]  (:83-91)
-// sequential fp32 accumulation (what torch.cumsum does on CPU); one warp per b
+// Accumulated sequentially in DOUBLE and rounded per element - what torch.cumsum does for a
+// float tensor on the CPU (its accumulation type there is double), i.e. what the reference's
+// decoding computes.  An fp32 running sum is ~1e-3 off at T = 500 (the sum reaches -2000,
+// ulp 1.2e-4), which then sits in every score of the first position
+// (tools/exp/prefix_err.py: 7.7e-4 against 4.6e-5 for the reference's arithmetic).  One warp per b.
 __global__ void __launch_bounds__(32) prefix_init_kernel(const float* __restrict__ lp, int B, int T,
                                                          int V, int n_hyps, int blank,
                                                          float logzero, float* __restrict__ r0) {
   const int b = blockIdx.x, lane = threadIdx.x;
   const size_t n_bh = (size_t)B * n_hyps;
-  float acc = 0.f;
+  double acc = 0.0;
   for (int t0 = 0; t0 < T; t0 += 32) {
     const int t = t0 + lane;
     const float x = t < T ? lp[((size_t)b * T + t) * V + blank] : 0.f;
@@ -70,8 +74,8 @@ __global__ void __launch_bounds__(32) prefix_init_kernel(const float* __restrict
 #pragma unroll
     for (int i = 0; i < 32; ++i) {
       const float xi = __shfl_sync(0xffffffffu, x, i);
-      if (t0 + i < T) acc = (t0 + i == 0) ? xi : acc + xi;
-      if (i == lane) mine = acc;
+      if (t0 + i < T) acc += (double)xi;
+      if (i == lane) mine = (float)acc;
     }
     if (t < T) {
       for (int h = 0; h < n_hyps; ++h) {

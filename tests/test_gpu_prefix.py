@@ -69,6 +69,15 @@ def _drive(scorer, select, B, W, V, T, snum, margin, steps, seed, device):
     (2, 3, 300, 90, None, 0),
     (2, 3, 300, 90, None, 12),
     (32, 10, 5000, 100, 15, 20),   # C3 widths at a shorter T (CPU oracle stays fast)
+    # shapes around the time-parallel (scan) kernel's edges: one candidate, 16 / 17 / 33 candidates
+    # (one, two, three CTAs per hypothesis), T not a multiple of 32, windows that cut chunks short,
+    # and T < 64 (the serial kernel keeps those)
+    (3, 4, 200, 65, 1, 0),
+    (3, 4, 200, 333, 16, 0),
+    (3, 4, 200, 333, 17, 9),
+    (2, 3, 120, 97, 33, 4),
+    (2, 3, 120, 40, 5, 0),
+    (2, 3, 120, 640, 7, 30),
 ])
 def test_vs_oracle_multi_step(B, W, V, T, snum, margin):
     g = torch.Generator().manual_seed(1000 + V + (snum or 0) + margin)
@@ -81,10 +90,29 @@ def test_vs_oracle_multi_step(B, W, V, T, snum, margin):
     ref, yref = _drive(lambda *a: ora.score(*a), ora.select, B, W, V, T, snum, margin, 6, 7, "cpu")
     got, ygot = _drive(cu, cu.index_select_state, B, W, V, T, snum, margin, 6, 7, DEV)
     assert yref == ygot  # identical surviving token sequences
-    for (s0, p0, a0, b0), (s1, p1, a1, b1) in zip(ref, got):
+    if T <= 128:
+        for (s0, p0, a0, b0), (s1, p1, a1, b1) in zip(ref, got):
+            assert (a0, b0) == (a1, b1)
+            close(s1, s0.numpy(), RTOL, ATOL)
+            close(p1, p0.numpy(), RTOL, ATOL)
+        return
+    # Long inputs: hundreds of fp32 additions to values around -500 (ulp 3e-5) leave BOTH fp32
+    # implementations ~1e-3 from exact arithmetic, and the time-parallel kernel adds in another
+    # order than the reference's frame loop - so the yardstick is the same recursion in fp64:
+    # the CUDA result must be as close to it as the reference's own fp32 arithmetic is.
+    ora64 = PrefixOracle(lpz.double().clone(), xlens, 0, eos, margin)
+    if margin > 0:  # the window arithmetic stays the reference's fp32 (same windows in all three)
+        ora64.frame_ids = ora64.frame_ids.float()
+    tru, ytru = _drive(lambda *a: ora64.score(*a), ora64.select, B, W, V, T, snum, margin, 6, 7, "cpu")
+    assert ytru == ygot
+    for (s0, p0, a0, b0), (s1, p1, a1, b1), (s2, p2, _, _) in zip(ref, got, tru):
         assert (a0, b0) == (a1, b1)
-        close(s1, s0.numpy(), RTOL, ATOL)
-        close(p1, p0.numpy(), RTOL, ATOL)
+        for x32, xcu, x64 in ((s0, s1, s2), (p0, p1, p2)):
+            live = x64 > -1e9  # log-zero entries: multiples of -1e10, compared separately
+            e_ref = (x32.double() - x64)[live].abs().max().item() if live.any() else 0.0
+            e_cu = (xcu.double() - x64)[live].abs().max().item() if live.any() else 0.0
+            assert e_cu <= max(2.0 * e_ref, 2e-4), (e_cu, e_ref)
+            close(xcu[~live], x32[~live].numpy(), 1e-6, 0)
 
 
 class _StubCTC:
