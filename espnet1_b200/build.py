@@ -41,8 +41,22 @@ def sources():
     return sorted(glob.glob(os.path.join(CSRC, "*.cu")))
 
 
+FLAGS_FILE = LIB + ".flags"  # the extra flags the library on disk was built with
+
+
+def _built_flags() -> str:
+    try:
+        return open(FLAGS_FILE).read().strip()
+    except OSError:
+        return ""
+
+
 def _stale() -> bool:
     if not os.path.exists(LIB):
+        return True
+    # a tuning build (B200CTC_NVCC_EXTRA=-DB200CTC_TUNING ...) left in the tree must not be
+    # taken for the shipped library, and vice versa
+    if _built_flags() != " ".join(_extra_flags()):
         return True
     t = os.path.getmtime(LIB)
     deps = sources() + glob.glob(os.path.join(CSRC, "*.cuh")) + [
@@ -76,6 +90,8 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n" + r.stdout.decode())
+    with open(FLAGS_FILE, "w") as f:
+        f.write(" ".join(_extra_flags()))
     if verbose:
         print("\n".join(log))
     return LIB
