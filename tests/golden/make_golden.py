@@ -348,6 +348,38 @@ def make_beam_opts():
     print("wrote beam_opts_nbest.json")
 
 
+def c3_beam_inputs(seed=401, T=500, V=5000):
+    """Inputs of the C3-width beam-search case, regenerated from the seed wherever they are needed
+    (a 5000 x 5000 bigram table is 100 MB: not a fixture); the fixture pins their checksums."""
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(T, V, generator=g) * 3
+    table = torch.log_softmax(torch.randn(V, V, generator=g) * 2, dim=1)
+    return x, table
+
+
+def make_beam_c3():
+    """beam-search identity was only pinned for V <= 300.  The REAL reference
+    BatchBeamSearch at C3 widths: V=5000, T=500, beam 10, pre-beam 15 on the full scores, CTC 0.3 +
+    bigram decoder 0.7 + length bonus 0.2, 20 positions (maxlenratio = -20)."""
+    T, V, beam, seed, mlr = 500, 5000, 10, 401, -20.0
+    weights = {"ctc": 0.3, "decoder": 0.7, "length_bonus": 0.2}
+    x, table = c3_beam_inputs(seed, T, V)
+    eos = V - 1
+    scorers = {"ctc": CTCPrefixScorer(_StubCTC(), eos), "length_bonus": LengthBonus(V), "decoder": _Table(table)}
+    bs = BatchBeamSearch(scorers=scorers, weights=weights, beam_size=beam, vocab_size=V, sos=eos, eos=eos,
+                         pre_beam_score_key="full")
+    with torch.no_grad():
+        nbest = bs(x=x.clone(), maxlenratio=mlr, minlenratio=0.0)
+    res = {"T": T, "V": V, "beam_size": beam, "weights": weights, "pre_beam_key": "full", "sos": eos, "eos": eos,
+           "seed": seed, "maxlenratio": mlr,
+           "x_sum": float(x.double().sum()), "table_sum": float(table.double().sum()),
+           "batch": [{"yseq": [int(v) for v in h.yseq], "score": float(h.score),
+                      "scores": {k: float(v) for k, v in h.scores.items()}} for h in nbest]}
+    with open(os.path.join(HERE, "beam_c3_nbest.json"), "w") as f:
+        json.dump(res, f, indent=1)
+    print("wrote beam_c3_nbest.json:", len(nbest), "hypotheses, best", res["batch"][0]["score"])
+
+
 def make_streaming():
     """extend_prob / extend_state (ctc_prefix_score.py:222-269) through the
     CTCPrefixScorer adapter the way batch_beam_search_online.py:306-309 does."""
@@ -454,3 +486,4 @@ if __name__ == "__main__":
     make_beam_opts()
     make_streaming()
     make_align_greedy()
+    make_beam_c3()
