@@ -209,6 +209,7 @@ __global__ void __launch_bounds__(NT) beam_select_kernel(
   extern __shared__ float vals[];  // the segment's W*V weighted scores
   __shared__ float res_v[kBeamMaxK];
   __shared__ int res_e[kBeamMaxK];
+  griddep_wait();  // programmatic stream serialisation: the scorers' kernels come right before
   const int u = blockIdx.x, U = gridDim.x, tid = threadIdx.x;
   const int E = W * V;
   const long long n_in = (long long)U * W, n_out = (long long)U * k;
@@ -264,6 +265,7 @@ __global__ void __launch_bounds__(NT) beam_select_cluster_kernel(
   __shared__ int res_e[kBeamMaxK];
   __shared__ float mg_v[8 * kBeamMaxK];  // CTA 0: the C candidate lists
   __shared__ int mg_e[8 * kBeamMaxK];
+  griddep_wait();
   const int c = (int)cluster_ctarank(), u = blockIdx.x / C, U = gridDim.x / C, tid = threadIdx.x;
   const int E = W * V;
   const int off = c * slice, mine = min(slice, E - off);  // the launcher keeps mine >= k
@@ -319,6 +321,7 @@ __global__ void __launch_bounds__(NT) beam_prebeam_kernel(const __grid_constant_
   extern __shared__ float vals[];
   __shared__ float res_v[kBeamMaxK];
   __shared__ int res_e[kBeamMaxK];
+  griddep_wait();
   const long long row = blockIdx.x;
   segment_topk<NT, true>(S, row, V, V, nullptr, k, vals, res_v, res_e);
   __syncthreads();
@@ -390,13 +393,15 @@ extern "C" int b200ctc_beam_select(const float* const* score_ptrs, const int64_t
     cfg.blockDim = dim3(NT);
     cfg.dynamicSmemBytes = smem_c;
     cfg.stream = st;
-    cudaLaunchAttribute at[1];
+    cudaLaunchAttribute at[2];
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = (unsigned)C;
     at[0].val.clusterDim.y = 1;
     at[0].val.clusterDim.z = 1;
+    at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = pdl_enabled(5) ? 2 : 1;
     cudaError_t e = cudaLaunchKernelEx(&cfg, beam_select_cluster_kernel<NT>, S, run_score, cum_in, yseq_in,
                                        (long long)yseq_in_stride, cur_len, active, maxlen, step_i, W, V, k, eos,
                                        out_val, out_flat, out_run, cum_out, yseq_out,
@@ -417,10 +422,9 @@ extern "C" int b200ctc_beam_select(const float* const* score_ptrs, const int64_t
 #define GO(NT)                                                                                     \
   do {                                                                                             \
     if (int rc = beam_smem(beam_select_kernel<NT>, smem)) return rc;                               \
-    beam_select_kernel<NT><<<U, NT, smem, st>>>(S, run_score, cum_in, yseq_in, yseq_in_stride,     \
-                                                cur_len, active, maxlen, step_i, W, V, k, eos,     \
-                                                out_val, out_flat, out_run, cum_out, yseq_out,     \
-                                                yseq_out_stride, pack);                            \
+    launch_pdl(beam_select_kernel<NT>, dim3(U), dim3(NT), smem, st, 5, S, run_score, cum_in, yseq_in,   \
+               (long long)yseq_in_stride, cur_len, active, maxlen, step_i, W, V, k, eos, out_val,  \
+               out_flat, out_run, cum_out, yseq_out, (long long)yseq_out_stride, pack);            \
   } while (0)
   if (nt == 256) GO(256);
   else if (nt == 512) GO(512);
@@ -445,7 +449,7 @@ extern "C" int b200ctc_beam_prebeam(const float* const* score_ptrs, const int64_
 #define GO(NT)                                                                          \
   do {                                                                                  \
     if (int rc = beam_smem(beam_prebeam_kernel<NT>, smem)) return rc;                   \
-    beam_prebeam_kernel<NT><<<(unsigned)n_rows, NT, smem, st>>>(S, V, k, out_ids);      \
+    launch_pdl(beam_prebeam_kernel<NT>, dim3((unsigned)n_rows), dim3(NT), smem, st, 5, S, V, k, out_ids); \
   } while (0)
   if (nt == 256) GO(256);
   else if (nt == 512) GO(512);

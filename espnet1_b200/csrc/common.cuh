@@ -49,6 +49,11 @@ static inline int pdl_mode() {
   return m;
 }
 
+static inline bool pdl_enabled(int pdl_bit) {
+  static const int pdl_mask = tuning_int("B200CTC_PDL", 63);
+  return pdl_bit >= 0 && ((pdl_mask >> pdl_bit) & 1);
+}
+
 template <typename... KArgs, typename... Args>
 static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
                                      cudaStream_t st, int pdl_bit, Args&&... args) {
@@ -67,9 +72,9 @@ static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 b
   // beside the running gather and the latency-bound recursion shares issue slots
   // (0.405 ms/step); with the trigger at the end, or never (implicit at completion, the
   // default), the kernel boundaries just get cheaper: 0.386 vs 0.393 ms without.
-  // bits: 0 lattice, 1 gradient row pass, 2 nll, 3 emission gather, 4 rescale check
-  static const int pdl_mask = tuning_int("B200CTC_PDL", 31);
-  cfg.numAttrs = (pdl_bit >= 0 && ((pdl_mask >> pdl_bit) & 1)) ? 1 : 0;
+  // bits: 0 lattice, 1 gradient row pass, 2 nll, 3 emission gather, 4 rescale check,
+  // 5 the kernels of a beam-search position (pre-beam, prefix scoring, pruning, state gather)
+  cfg.numAttrs = pdl_enabled(pdl_bit) ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 

@@ -167,6 +167,7 @@ __global__ void __launch_bounds__(256) prefix_prepare_kernel(
     const int64_t* __restrict__ end_frames, int T, int n_bh, int n_hyps, int V, int blank, int eos,
     float logzero, int fill, float* __restrict__ rsum, float* __restrict__ log_psi,
     float* __restrict__ scores, int64_t* __restrict__ idmap) {
+  griddep_wait();  // launched with programmatic stream serialisation: inputs come from the previous kernel
   const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
   if (i < (size_t)T * n_bh) {
     const size_t t = i / n_bh, h = i - t * n_bh;
@@ -356,6 +357,7 @@ __global__ void __launch_bounds__(32 * kScanCand, 2) prefix_step_scan_kernel(
     const int* __restrict__ win_utt, int cap /* frames a staged array can hold */, long long last_stride,
     int time_major /* r as (n_bh, snum, 2, T): the position call's private layout */) {
   extern __shared__ float sm[];
+  griddep_wait();
   const int h = blockIdx.y, c0 = blockIdx.x * kScanCand;
   const int ncand = min(kScanCand, snum - c0);
   const int b = h / n_hyps, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, NT = blockDim.x;
@@ -522,6 +524,7 @@ __global__ void __launch_bounds__(256) prefix_select_kernel(
     const float* __restrict__ r, const float* __restrict__ log_psi, const int64_t* __restrict__ idmap,
     const int64_t* __restrict__ best_ids, int n_hyps, int W, int T, int V, int snum, int n_bh,
     float* __restrict__ r_new, float* __restrict__ s_new, int time_major) {
+  griddep_wait();
   const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
   const size_t n_new = (size_t)(n_bh / n_hyps) * W;
   if (time_major && i < (size_t)T * 2 * n_new) {
@@ -657,9 +660,9 @@ int b200ctc::prefix_step_impl(const float* lp, const float* lp_t, const float* r
   prof_mark(4, 0, st);
   {
     const size_t n1 = (size_t)T * n_bh, n2 = scoring_ids ? (size_t)n_bh * V : 0;
-    prefix_prepare_kernel<<<blocks(n1 > n2 ? n1 : n2, 256), 256, 0, st>>>(
-        r_prev, s_prev, end_frames, T, n_bh, n_hyps, V, blank, eos, logzero, scoring_ids != nullptr, rsum_ws,
-        log_psi, scores, idmap);
+    launch_pdl(prefix_prepare_kernel, dim3(blocks(n1 > n2 ? n1 : n2, 256)), dim3(256), 0, st, 5, r_prev, s_prev,
+               end_frames, T, n_bh, n_hyps, V, blank, eos, logzero, (int)(scoring_ids != nullptr), rsum_ws,
+               log_psi, scores, idmap);
     count_launch();
   }
   // the time-contiguous copy pays off when few of the V columns are touched per hypothesis
@@ -678,9 +681,10 @@ int b200ctc::prefix_step_impl(const float* lp, const float* lp_t, const float* r
       cudaGetLastError();
       return B200CTC_ERR_DEVICE;
     }
-    prefix_step_scan_kernel<<<dim3((snum + kScanCand - 1) / kScanCand, n_bh), 32 * scan_warps, scan_smem, st>>>(
-        lp_t, r_prev, rsum_ws, s_prev, last_ids, scoring_ids, n_bh, n_hyps, T, V, snum, out_len, start, end,
-        blank, eos, logzero, r, log_psi, scores, idmap, lp_t_ld, win_utt, scan_cap, last_stride, r_time_major);
+    launch_pdl(prefix_step_scan_kernel, dim3((snum + kScanCand - 1) / kScanCand, n_bh), dim3(32 * scan_warps),
+               scan_smem, st, 5, lp_t, r_prev, (const float*)rsum_ws, s_prev, last_ids, scoring_ids, n_bh, n_hyps,
+               T, V, snum, out_len, start, end, blank, eos, logzero, r, log_psi, scores, idmap, lp_t_ld, win_utt,
+               scan_cap, last_stride, r_time_major);
   } else if (lp_t && scoring_ids) {
     // small launch: spread the warps over the SMs (see the kernel); 16-byte loads need a
     // 16-byte aligned copy whose time stride is a multiple of 4 frames
@@ -731,9 +735,8 @@ int b200ctc::prefix_select_impl(const float* r, const float* log_psi, const int6
   const int n_bh = B * n_hyps, n_new = B * W;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const size_t n1 = (size_t)T * 2 * n_new, n2 = (size_t)n_new * V;
-  prefix_select_kernel<<<blocks(n1 > n2 ? n1 : n2, 256), 256, 0, st>>>(r, log_psi, idmap, best_ids, n_hyps, W,
-                                                                       T, V, snum, n_bh, r_new, s_new,
-                                                                       r_time_major);
+  launch_pdl(prefix_select_kernel, dim3(blocks(n1 > n2 ? n1 : n2, 256)), dim3(256), 0, st, 5, r, log_psi, idmap,
+             best_ids, n_hyps, W, T, V, snum, n_bh, r_new, s_new, r_time_major);
   count_launch();
   return check_launch("prefix_select");
 }
