@@ -209,7 +209,7 @@ __global__ void __launch_bounds__(NT) beam_select_kernel(
   extern __shared__ float vals[];  // the segment's W*V weighted scores
   __shared__ float res_v[kBeamMaxK];
   __shared__ int res_e[kBeamMaxK];
-  griddep_wait();  // programmatic stream serialisation: the scorers' kernels come right before
+  griddep_wait_chain();  // programmatic stream serialisation: the scorers' kernels come right before
   const int u = blockIdx.x, U = gridDim.x, tid = threadIdx.x;
   const int E = W * V;
   const long long n_in = (long long)U * W, n_out = (long long)U * k;
@@ -265,7 +265,7 @@ __global__ void __launch_bounds__(NT) beam_select_cluster_kernel(
   __shared__ int res_e[kBeamMaxK];
   __shared__ float mg_v[8 * kBeamMaxK];  // CTA 0: the C candidate lists
   __shared__ int mg_e[8 * kBeamMaxK];
-  griddep_wait();
+  griddep_wait_chain();
   const int c = (int)cluster_ctarank(), u = blockIdx.x / C, U = gridDim.x / C, tid = threadIdx.x;
   const int E = W * V;
   const int off = c * slice, mine = min(slice, E - off);  // the launcher keeps mine >= k
@@ -321,7 +321,7 @@ __global__ void __launch_bounds__(NT) beam_prebeam_kernel(const __grid_constant_
   extern __shared__ float vals[];
   __shared__ float res_v[kBeamMaxK];
   __shared__ int res_e[kBeamMaxK];
-  griddep_wait();
+  griddep_wait_chain();
   const long long row = blockIdx.x;
   segment_topk<NT, true>(S, row, V, V, nullptr, k, vals, res_v, res_e);
   __syncthreads();

@@ -140,6 +140,17 @@ __device__ __forceinline__ float warp_sum(float v) {
 // it must call griddep_wait() before touching anything that kernel wrote.
 // Both instructions are no-ops in a normally launched kernel.
 __device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+// the small kernels of a beam-search position: wait, then (tuning: -DB200CTC_BEAM_PDL_EARLY=1)
+// let the next kernel's CTAs become resident at once - they park at their own wait
+#ifndef B200CTC_BEAM_PDL_EARLY
+#define B200CTC_BEAM_PDL_EARLY 0
+#endif
+__device__ __forceinline__ void griddep_wait_chain() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+#if B200CTC_BEAM_PDL_EARLY
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+#endif
+}
 __device__ __forceinline__ void griddep_launch() {
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }

@@ -167,7 +167,7 @@ __global__ void __launch_bounds__(256) prefix_prepare_kernel(
     const int64_t* __restrict__ end_frames, int T, int n_bh, int n_hyps, int V, int blank, int eos,
     float logzero, int fill, float* __restrict__ rsum, float* __restrict__ log_psi,
     float* __restrict__ scores, int64_t* __restrict__ idmap) {
-  griddep_wait();  // launched with programmatic stream serialisation: inputs come from the previous kernel
+  griddep_wait_chain();  // launched with programmatic stream serialisation: inputs come from the previous kernel
   const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
   if (i < (size_t)T * n_bh) {
     const size_t t = i / n_bh, h = i - t * n_bh;
@@ -357,7 +357,7 @@ __global__ void __launch_bounds__(32 * kScanCand, 2) prefix_step_scan_kernel(
     const int* __restrict__ win_utt, int cap /* frames a staged array can hold */, long long last_stride,
     int time_major /* r as (n_bh, snum, 2, T): the position call's private layout */) {
   extern __shared__ float sm[];
-  griddep_wait();
+  griddep_wait_chain();
   const int h = blockIdx.y, c0 = blockIdx.x * kScanCand;
   const int ncand = min(kScanCand, snum - c0);
   const int b = h / n_hyps, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, NT = blockDim.x;
@@ -524,7 +524,7 @@ __global__ void __launch_bounds__(256) prefix_select_kernel(
     const float* __restrict__ r, const float* __restrict__ log_psi, const int64_t* __restrict__ idmap,
     const int64_t* __restrict__ best_ids, int n_hyps, int W, int T, int V, int snum, int n_bh,
     float* __restrict__ r_new, float* __restrict__ s_new, int time_major) {
-  griddep_wait();
+  griddep_wait_chain();
   const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
   const size_t n_new = (size_t)(n_bh / n_hyps) * W;
   if (time_major && i < (size_t)T * 2 * n_new) {
