@@ -137,6 +137,31 @@ class _SlotStates(Mapping):
         return len(self._keys)
 
 
+class _PinnedPool:
+    """Pinned host buffers kept across decodes: the per-position record and the staging of a few
+    small uploads.  Allocating pinned memory per decode now and then costs tens of milliseconds
+    (cudaHostAlloc when the host allocator's cached block is still tied to an unfinished event)."""
+
+    def __init__(self):
+        self._buf: Dict[Any, torch.Tensor] = {}
+
+    def __call__(self, name, shape, dtype) -> torch.Tensor:
+        key = (name, tuple(shape), dtype)
+        if key not in self._buf:
+            self._buf[key] = torch.empty(*shape, dtype=dtype, pin_memory=torch.cuda.is_available())
+        return self._buf[key]
+
+    def upload(self, name, values, dtype, dev) -> torch.Tensor:
+        """A few host values as a device tensor without blocking: a pageable host-to-device copy
+        waits until the GPU has drained everything queued before it (here: the CTC projection)."""
+        t = torch.tensor(values, dtype=dtype)
+        if dev.type != "cuda":
+            return t.to(dev)
+        stage = self(name, t.shape, dtype)
+        stage.copy_(t)
+        return stage.to(dev, non_blocking=True)
+
+
 class _PositionPlan:
     """Buffers of one decode for ``b200ctc_beam_position`` (include/b200ctc.h): everything that
     follows the full scorers in a position - pre-beam, CTC prefix scores, pruning, CTC state
@@ -144,7 +169,7 @@ class _PositionPlan:
     The generic path below makes the same library calls one by one through the scorer classes,
     with ~20 allocations and four argument marshallings per position."""
 
-    def __init__(self, impl, U, W, V, K_full, weights, snum, prebeam_key, eos, yseq0, stride, maxlen):
+    def __init__(self, impl, U, W, V, K_full, weights, snum, prebeam_key, eos, yseq0, stride, maxlen, pinned):
         import ctypes
 
         from ..._lib import BeamPlan
@@ -168,11 +193,11 @@ class _PositionPlan:
             "cum0": torch.zeros(K, n, **f32), "cum1": torch.empty(K, n, **f32),
             "y0": torch.empty(n, stride, **i64), "y1": torch.empty(n, stride, **i64),
             "active": torch.ones(U, dtype=torch.uint8, device=dev),
-            "maxlen": BatchBeamSearch._upload(maxlen, torch.int32, dev),
+            "maxlen": pinned.upload("maxlen", maxlen, torch.int32, dev),
             "out_val": torch.empty(n, **f32), "out_flat": torch.empty(n, **i64),
             "pack": torch.empty(3 + K, U, W, **f32),
             # two records: position i+1 may be issued while the host still reads position i's
-            "pack_host": torch.empty(2, 3 + K, U, W, dtype=torch.float32, pin_memory=True),
+            "pack_host": pinned("pack", (2, 3 + K, U, W), torch.float32),
         }
         t["run0"][:, 0] = 0.0
         t["y0"][:, : yseq0.shape[1]] = yseq0
@@ -274,6 +299,7 @@ class BatchBeamSearch(torch.nn.Module):
         # with the CUDA CTC scorer as the one partial scorer, run everything after the full scorers
         # as ONE library call per position (b200ctc_beam_position); False = the scorer-by-scorer path
         self.fuse_position = True
+        self._pinned = _PinnedPool()
         # B200CTC_BEAM_PROF=1: synchronise after every phase and accumulate wall time per phase
         self.prof: Dict[str, float] = {} if os.environ.get("B200CTC_BEAM_PROF") else None
 
@@ -337,13 +363,6 @@ class BatchBeamSearch(torch.nn.Module):
             merged = [st for st_u in new_states for st in (st_u if st_u is not None else [None] * W)]
         return torch.cat(outs, dim=0), merged
 
-    @staticmethod
-    def _upload(values, dtype, dev) -> torch.Tensor:
-        """A few host values as a device tensor without blocking: a pageable host-to-device copy
-        waits until the GPU has drained everything queued before it (here: the CTC projection)."""
-        t = torch.tensor(values, dtype=dtype)
-        return t.pin_memory().to(dev, non_blocking=True) if dev.type == "cuda" else t.to(dev)
-
     def _maxlen(self, T: int, maxlenratio: float) -> int:
         if maxlenratio == 0:
             return T
@@ -382,7 +401,7 @@ class BatchBeamSearch(torch.nn.Module):
                 if U != 1:
                     raise ValueError(f"partial scorer {k} has no batched-state API: one utterance at a time")
                 part_states[k] = [d.batch_init_state(xs[0, : lens[0]])] * n
-        yseq = self._upload(primer, torch.int64, dev).repeat(n, 1)
+        yseq = self._pinned.upload("primer", primer, torch.int64, dev).repeat(n, 1)
         names = list(self.full_scorers) + list(self.part_scorers)  # accumulation order (:217-241)
         # a scorer that ignores the encoder output does not need the (n, T, D) copy of it
         need_x = any(not getattr(d, "ignores_x", False) for d in self.full_scorers.values())
@@ -402,7 +421,7 @@ class BatchBeamSearch(torch.nn.Module):
                 key = -1 if (not self.do_pre_beam or self.pre_beam_score_key == "full") else fkeys.index(
                     self.pre_beam_score_key)
                 plan = _PositionPlan(dp.impl, U, W, V, len(fkeys), [self.weights[k] for k in names], snum, key,
-                                     self.eos, yseq, P0 + max(maxlen) + 1, maxlen)
+                                     self.eos, yseq, P0 + max(maxlen) + 1, maxlen, self._pinned)
                 yseq = plan.ybuf[0][:, :P0]
         if plan is None:
             score = torch.full((U, W), _NEG_INF, dtype=xs.dtype, device=dev)
