@@ -306,6 +306,29 @@ def bench_softmax_family(x, dev, iters=10):
     return out
 
 
+def bench_decode_family(x, dev, iters=10):
+    """best-path decode (argmax + collapse + blank removal in one kernel, one read of
+    the 640 MB C2 logits) and the forced alignment of one utterance (T=500, 150 labels: a
+    max-semiring lattice with back-pointers, a serial chain over T)."""
+    from espnet1_b200 import functional as F
+
+    peak = peaks()[0]
+    nbytes = x.numel() * x.element_size()
+    out = {}
+    for _ in range(3):
+        F.greedy_decode(x)
+    ms = time_region(lambda: F.greedy_decode(x), iters, False, dev)
+    out["greedy_decode"] = {"ms": ms, "GB_per_s": nbytes / ms / 1e6, "frac_of_measured_peak": nbytes / ms / 1e6 / peak,
+                            "utterances": int(x.shape[0])}
+    lp = F.log_softmax(x[0])
+    tgt = torch.randint(1, x.shape[2], (150,), generator=torch.Generator().manual_seed(3)).to(dev)
+    for _ in range(3):
+        F.forced_align(lp, tgt)
+    ms = time_region(lambda: F.forced_align(lp, tgt), iters, False, dev)
+    out["forced_align"] = {"ms": ms, "T": int(lp.shape[0]), "labels": 150, "frames_per_s": lp.shape[0] / (ms * 1e-3)}
+    return out
+
+
 def bench_other_configs(dev, iters=10):
     """The other loss configurations of BASELINE.json (parity-test shapes, reported for
     completeness): C1 mini_an4 (launch-bound) and C4 long-form (split lattice), one step =
@@ -660,6 +683,7 @@ def run_gpu(args):
         line["torch_cuda_library_ms_per_step"] = time_region(torch_step, 10, False, dev)
         line["prefix_score"] = bench_prefix(dev)
         line["softmax_family"] = bench_softmax_family(x.detach(), dev)
+        line["decode_family"] = bench_decode_family(x.detach(), dev)
         line["amp_variants"] = bench_amp(dev)
         line["e2e_variants"] = bench_e2e_variants(L, host_logits, tg_h, il_h, tl_h, B, T, V, dev)
         line["other_configs"] = bench_other_configs(dev)

@@ -202,8 +202,8 @@ int b200ctc_forced_align(const float* lp, const int64_t* target, int T, int V,
 /* Allocation-free variant of b200ctc_forced_align.  NO counterpart in the
  * reference: added for callers that
  * cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses
- * that forbid it).  Same inputs, outputs and result; the back-pointer scratch
- * lives in a file-scope `static __device__` array of
+ * that forbid it).  Same inputs, outputs and result; the kernels' scratch (gathered
+ * emissions or packed back-pointers) lives in a file-scope `static __device__` array of
  * B200CTC_ALIGN_STATIC_MAX_BYTES that every GPU loading the library holds until
  * exit.  Neither this call nor anything it calls allocates or frees memory.
  * T * (2*tgt_len+1) * 4 bytes beyond the maximum -> B200CTC_ERR_WORKSPACE with

@@ -149,6 +149,26 @@ def test_softmax_with_projection_bias(dtype, V):
             close(m.softmax(hs), torch.softmax(m.ctc_lo(hs), -1).cpu().numpy(), 1e-5, 1e-7)
 
 
+@pytest.mark.parametrize("T,L,V", [(120, 40, 50), (600, 200, 300), (2000, 200, 260), (1100, 520, 600), (40, 1, 9)])
+def test_forced_align_sizes_vs_oracle(T, L, V):
+    """Forced alignment against the numpy restatement of the reference's `forced_align` (pinned to
+    the reference's own outputs in test_oracle_golden) at sizes that take every path of the kernel:
+    packed back-pointers in shared memory, in the global workspace (T=2000: they no longer fit),
+    more states than threads (L=520: 1041 states), and a single label."""
+    from espnet1_b200 import functional as F
+    from oracle import ctc_numpy
+
+    d = _dev()
+    g = torch.Generator().manual_seed(T + L)
+    lp = torch.log_softmax(torch.randn(T, V, generator=g) * 2, -1)
+    y = torch.randint(1, V, (L,), generator=g)
+    if L > 4:
+        y[3] = y[2]  # a repeated label (no skip transition across it)
+    want = ctc_numpy.viterbi_align(lp.numpy(), y.numpy(), 0)
+    got = F.forced_align(lp.to(d), y.to(d))
+    np.testing.assert_array_equal(got.cpu().numpy(), np.asarray(want))
+
+
 def test_c1_logits_boundary_vs_fixture_and_oracle():
     from espnet1_b200 import functional as F
     from oracle import ctc_numpy
