@@ -217,10 +217,12 @@ __global__ void __launch_bounds__(32 * kAlignNW) align_warp_kernel(const float* 
     for (int i = 0; i < R; ++i) {
       const double c1 = i >= 1 ? d[i - 1] : up1;
       const double c2 = i >= 2 ? d[i - 2] : (i == 1 ? up1 : up2);
-      double best = d[i];
-      unsigned code = 0;
-      if (c1 > best) { best = c1; code = 1; }
-      if (((skip >> i) & 1u) && c2 > best) { best = c2; code = 2; }
+      // stay, then previous, then skip; the first maximum wins.  The three comparisons are
+      // independent (one fp64 compare latency on the chain instead of two in a row)
+      const bool p01 = c1 > d[i], p02 = c2 > d[i], p12 = c2 > c1;
+      const bool take2 = ((skip >> i) & 1u) && (p01 ? p12 : p02);
+      const double best = take2 ? c2 : (p01 ? c1 : d[i]);
+      const unsigned code = take2 ? 2u : (p01 ? 1u : 0u);
       n[i] = best + (double)em[i];
       bk[i] |= code << (2 * (t % kAlignGroup));
     }
