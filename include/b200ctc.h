@@ -194,7 +194,10 @@ int b200ctc_grad_rescale_hints(void* grad, int dtype, const float* gscale,
                                b200ctc_stream_t stream);
 /* forced alignment (espnet/nets/pytorch_backend/ctc.py:163-226): max-semiring
  * lattice with back-pointers for ONE utterance; lp (T,V) fp32 log-probs,
- * out_ids (T,) int64 = label emitted at each frame (tgt_len >= 1).            */
+ * out_ids (T,) int64 = label emitted at each frame (tgt_len >= 1).  `ws`: scratch of
+ * b200ctc_align_workspace_bytes(T, tgt_len) bytes, 16-byte aligned (gathered emission columns
+ * of the utterance, or packed back-pointers of inputs too long for shared memory); at most
+ * ~50 k frames.                                                                              */
 size_t b200ctc_align_workspace_bytes(int T, int tgt_len);
 int b200ctc_forced_align(const float* lp, const int64_t* target, int T, int V,
                          int tgt_len, int blank, int64_t* out_ids, void* ws,
