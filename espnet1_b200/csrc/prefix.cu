@@ -162,19 +162,22 @@ __global__ void __launch_bounds__(kWinWarps * 32) prefix_window_utt_kernel(
 //  pre-beam only: log_psi / scores / idmap defaults for tokens that are not scored (:181-185).
 // The fill's one dependent entry (eos: r_sum at the utterance's last frame) is recomputed from
 // r_prev with the same expression instead of being read back, so the passes need no ordering.
+// (2-D grid: row = blockIdx.y, column = blockIdx.x * 256 + thread - no index divisions; with flat
+// 64-bit indices the divisions were most of the kernel's 4.8 M instructions)
 __global__ void __launch_bounds__(256) prefix_prepare_kernel(
     const float* __restrict__ r_prev, const float* __restrict__ s_prev,
     const int64_t* __restrict__ end_frames, int T, int n_bh, int n_hyps, int V, int blank, int eos,
     float logzero, int fill, float* __restrict__ rsum, float* __restrict__ log_psi,
     float* __restrict__ scores, int64_t* __restrict__ idmap) {
   griddep_wait_chain();  // launched with programmatic stream serialisation: inputs come from the previous kernel
-  const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
-  if (i < (size_t)T * n_bh) {
-    const size_t t = i / n_bh, h = i - t * n_bh;
-    rsum[i] = lse2f(r_prev[(t * 2 + 0) * n_bh + h], r_prev[(t * 2 + 1) * n_bh + h]);
+  const int row = blockIdx.y, col = blockIdx.x * 256 + threadIdx.x;
+  if (row < T && col < n_bh) {  // row = t, col = h
+    const size_t t = row;
+    rsum[t * n_bh + col] = lse2f(r_prev[(t * 2 + 0) * n_bh + col], r_prev[(t * 2 + 1) * n_bh + col]);
   }
-  if (fill && i < (size_t)n_bh * V) {
-    const int h = (int)(i / V), v = (int)(i - (size_t)h * V);
+  if (fill && row < n_bh && col < V) {  // row = h, col = v
+    const int h = row, v = col;
+    const size_t i = (size_t)h * V + v;
     float p = logzero;
     if (v == eos && v != blank) {
       const size_t t = (size_t)end_frames[h / n_hyps];
@@ -525,42 +528,38 @@ __global__ void __launch_bounds__(256) prefix_select_kernel(
     const int64_t* __restrict__ best_ids, int n_hyps, int W, int T, int V, int snum, int n_bh,
     float* __restrict__ r_new, float* __restrict__ s_new, int time_major) {
   griddep_wait_chain();
-  const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
-  const size_t n_new = (size_t)(n_bh / n_hyps) * W;
-  if (time_major && i < (size_t)T * 2 * n_new) {
-    // r is (n_bh, snum, 2, T): consecutive threads walk t (coalesced reads), the (T,2,n_new)
-    // state is written with a stride - the scatter sits on the write side
-    const size_t row = i / T;  // (hn, x)
-    const int t = (int)(i - row * T), hn = (int)(row >> 1), x = (int)(row & 1);
-    const int b = hn / W;
-    const int64_t best = best_ids[hn];
-    const int hyp = (int)(best / V) + b * n_hyps;
-    const int label = (int)(best % V);
-    int col = label;
+  // 2-D grid (row = blockIdx.y, column = blockIdx.x * 256 + thread) and 32-bit index arithmetic:
+  // flat 64-bit indices with int64 divisions were 8.5 M instructions for two small gathers
+  const int row = blockIdx.y, c = blockIdx.x * 256 + threadIdx.x;
+  const int n_new = (n_bh / n_hyps) * W;
+  // the winner's (hypothesis, column of r) for new slot hn
+  auto source = [&](int hn, int& hyp, int& col) {
+    const unsigned best = (unsigned)best_ids[hn];  // < n_hyps * V
+    const unsigned ph = best / (unsigned)V;
+    const int label = (int)(best - ph * (unsigned)V);
+    hyp = (int)ph + (hn / W) * n_hyps;
+    col = label;
     if (idmap) {
-      const int64_t c = idmap[(size_t)hyp * V + label];
-      col = c < 0 ? 0 : (int)c;
+      const int64_t m = idmap[(size_t)hyp * V + label];
+      col = m < 0 ? 0 : (int)m;
     }
-    r_new[((size_t)t * 2 + x) * n_new + hn] = r[(((size_t)hyp * snum + col) * 2 + x) * T + t];
-  } else if (i < (size_t)T * 2 * n_new) {
-    const size_t tn = i / n_new;
-    const int hn = (int)(i - tn * n_new);
-    const int b = hn / W;
-    const int64_t best = best_ids[hn];
-    const int hyp = (int)(best / V) + b * n_hyps;
-    const int label = (int)(best % V);
-    int col = label;
-    if (idmap) {
-      const int64_t c = idmap[(size_t)hyp * V + label];
-      col = c < 0 ? 0 : (int)c;
+  };
+  if (time_major) {
+    // r is (n_bh, snum, 2, T): row = (hn, x), consecutive threads walk t (coalesced reads), the
+    // (T,2,n_new) state is written with a stride - the scatter sits on the write side
+    if (row < 2 * n_new && c < T) {
+      const int hn = row >> 1, x = row & 1;
+      int hyp, col;
+      source(hn, hyp, col);
+      r_new[((size_t)c * 2 + x) * n_new + hn] = r[(((size_t)hyp * snum + col) * 2 + x) * T + c];
     }
-    r_new[i] = r[(tn * n_bh + hyp) * snum + col];
+  } else if (row < 2 * T && c < n_new) {  // row = (t, x), column = hn
+    int hyp, col;
+    source(c, hyp, col);
+    r_new[(size_t)row * n_new + c] = r[((size_t)row * n_bh + hyp) * snum + col];
   }
-  if (i < n_new * V) {
-    const int hn = (int)(i / V);
-    const int b = hn / W;
-    s_new[i] = log_psi[(size_t)b * n_hyps * V + best_ids[hn]];
-  }
+  if (row < n_new && c < V)  // row = hn, column = v: the winner's psi for every token (:206-209)
+    s_new[(size_t)row * V + c] = log_psi[(size_t)(row / W) * n_hyps * V + best_ids[row]];
 }
 
 static inline unsigned blocks(size_t n, int per) { return (unsigned)((n + per - 1) / per); }
@@ -659,8 +658,9 @@ int b200ctc::prefix_step_impl(const float* lp, const float* lp_t, const float* r
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   prof_mark(4, 0, st);
   {
-    const size_t n1 = (size_t)T * n_bh, n2 = scoring_ids ? (size_t)n_bh * V : 0;
-    launch_pdl(prefix_prepare_kernel, dim3(blocks(n1 > n2 ? n1 : n2, 256)), dim3(256), 0, st, 5, r_prev, s_prev,
+    const int cols = (scoring_ids && V > n_bh) ? V : n_bh, rows = (scoring_ids && n_bh > T) ? n_bh : T;
+    B2_REQUIRE(rows <= 65535, "prefix_step: more than 65535 frames or hypotheses (%d)", rows);
+    launch_pdl(prefix_prepare_kernel, dim3(blocks(cols, 256), rows), dim3(256), 0, st, 5, r_prev, s_prev,
                end_frames, T, n_bh, n_hyps, V, blank, eos, logzero, (int)(scoring_ids != nullptr), rsum_ws,
                log_psi, scores, idmap);
     count_launch();
@@ -734,8 +734,10 @@ int b200ctc::prefix_select_impl(const float* r, const float* log_psi, const int6
   B2_REQUIRE(B > 0 && n_hyps > 0 && W > 0 && T > 0 && V > 0 && snum > 0, "prefix_select: bad shape");
   const int n_bh = B * n_hyps, n_new = B * W;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const size_t n1 = (size_t)T * 2 * n_new, n2 = (size_t)n_new * V;
-  launch_pdl(prefix_select_kernel, dim3(blocks(n1 > n2 ? n1 : n2, 256)), dim3(256), 0, st, 5, r, log_psi, idmap,
+  const int rows_r = r_time_major ? 2 * n_new : 2 * T, cols_r = r_time_major ? T : n_new;
+  const int rows = rows_r > n_new ? rows_r : n_new, cols = cols_r > V ? cols_r : V;
+  B2_REQUIRE(rows <= 65535 && (long long)n_hyps * V < (1ll << 31), "prefix_select: shape too large");
+  launch_pdl(prefix_select_kernel, dim3(blocks(cols, 256), rows), dim3(256), 0, st, 5, r, log_psi, idmap,
              best_ids, n_hyps, W, T, V, snum, n_bh, r_new, s_new, r_time_major);
   count_launch();
   return check_launch("prefix_select");
