@@ -162,19 +162,26 @@ __global__ void __launch_bounds__(kWinWarps * 32) prefix_window_utt_kernel(
 //  pre-beam only: log_psi / scores / idmap defaults for tokens that are not scored (:181-185).
 // The fill's one dependent entry (eos: r_sum at the utterance's last frame) is recomputed from
 // r_prev with the same expression instead of being read back, so the passes need no ordering.
-// (2-D grid: row = blockIdx.y, column = blockIdx.x * 256 + thread - no index divisions; with flat
-// 64-bit indices the divisions were most of the kernel's 4.8 M instructions)
+// (rows of 256-wide blocks: no per-thread index divisions)
 __global__ void __launch_bounds__(256) prefix_prepare_kernel(
     const float* __restrict__ r_prev, const float* __restrict__ s_prev,
     const int64_t* __restrict__ end_frames, int T, int n_bh, int n_hyps, int V, int blank, int eos,
     float logzero, int fill, float* __restrict__ rsum, float* __restrict__ log_psi,
     float* __restrict__ scores, int64_t* __restrict__ idmap) {
   griddep_wait_chain();  // launched with programmatic stream serialisation: inputs come from the previous kernel
-  const int row = blockIdx.y, col = blockIdx.x * 256 + threadIdx.x;
-  if (row < T && col < n_bh) {  // row = t, col = h
+  // blocks [0, T * cb1): r_sum rows (t, 256 hypotheses); the rest: fill rows (h, 256 tokens) -
+  // one 32-bit division per BLOCK
+  const int cb1 = (n_bh + 255) / 256, cb2 = (V + 255) / 256;
+  const int blk = blockIdx.x;
+  if (blk < T * cb1) {
+    const int row = blk / cb1, col = (blk - row * cb1) * 256 + threadIdx.x;
     const size_t t = row;
-    rsum[t * n_bh + col] = lse2f(r_prev[(t * 2 + 0) * n_bh + col], r_prev[(t * 2 + 1) * n_bh + col]);
+    if (col < n_bh)
+      rsum[t * n_bh + col] = lse2f(r_prev[(t * 2 + 0) * n_bh + col], r_prev[(t * 2 + 1) * n_bh + col]);
+    return;
   }
+  const int fb = blk - T * cb1;
+  const int row = fb / cb2, col = (fb - row * cb2) * 256 + threadIdx.x;
   if (fill && row < n_bh && col < V) {  // row = h, col = v
     const int h = row, v = col;
     const size_t i = (size_t)h * V + v;
@@ -528,10 +535,15 @@ __global__ void __launch_bounds__(256) prefix_select_kernel(
     const int64_t* __restrict__ best_ids, int n_hyps, int W, int T, int V, int snum, int n_bh,
     float* __restrict__ r_new, float* __restrict__ s_new, int time_major) {
   griddep_wait_chain();
-  // 2-D grid (row = blockIdx.y, column = blockIdx.x * 256 + thread) and 32-bit index arithmetic:
-  // flat 64-bit indices with int64 divisions were 8.5 M instructions for two small gathers
-  const int row = blockIdx.y, c = blockIdx.x * 256 + threadIdx.x;
+  // rows of 256-wide blocks - first the r gather's, then the s gather's - and 32-bit index
+  // arithmetic (one division per block, none per thread)
   const int n_new = (n_bh / n_hyps) * W;
+  const int rows_r = time_major ? 2 * n_new : 2 * T, cols_r = time_major ? T : n_new;
+  const int cb_r = (cols_r + 255) / 256, cb_s = (V + 255) / 256;
+  const int blk = blockIdx.x;
+  const bool r_part = blk < rows_r * cb_r;
+  const int fb = r_part ? blk : blk - rows_r * cb_r, cbk = r_part ? cb_r : cb_s;
+  const int row = fb / cbk, c = (fb - row * cbk) * 256 + threadIdx.x;
   // the winner's (hypothesis, column of r) for new slot hn
   auto source = [&](int hn, int& hyp, int& col) {
     const unsigned best = (unsigned)best_ids[hn];  // < n_hyps * V
@@ -544,6 +556,11 @@ __global__ void __launch_bounds__(256) prefix_select_kernel(
       col = m < 0 ? 0 : (int)m;
     }
   };
+  if (!r_part) {  // row = hn, column = v: the winner's psi for every token (:206-209)
+    if (row < n_new && c < V)
+      s_new[(size_t)row * V + c] = log_psi[(size_t)(row / W) * n_hyps * V + best_ids[row]];
+    return;
+  }
   if (time_major) {
     // r is (n_bh, snum, 2, T): row = (hn, x), consecutive threads walk t (coalesced reads), the
     // (T,2,n_new) state is written with a stride - the scatter sits on the write side
@@ -558,8 +575,6 @@ __global__ void __launch_bounds__(256) prefix_select_kernel(
     source(c, hyp, col);
     r_new[(size_t)row * n_new + c] = r[((size_t)row * n_bh + hyp) * snum + col];
   }
-  if (row < n_new && c < V)  // row = hn, column = v: the winner's psi for every token (:206-209)
-    s_new[(size_t)row * V + c] = log_psi[(size_t)(row / W) * n_hyps * V + best_ids[row]];
 }
 
 static inline unsigned blocks(size_t n, int per) { return (unsigned)((n + per - 1) / per); }
@@ -658,9 +673,9 @@ int b200ctc::prefix_step_impl(const float* lp, const float* lp_t, const float* r
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   prof_mark(4, 0, st);
   {
-    const int cols = (scoring_ids && V > n_bh) ? V : n_bh, rows = (scoring_ids && n_bh > T) ? n_bh : T;
-    B2_REQUIRE(rows <= 65535, "prefix_step: more than 65535 frames or hypotheses (%d)", rows);
-    launch_pdl(prefix_prepare_kernel, dim3(blocks(cols, 256), rows), dim3(256), 0, st, 5, r_prev, s_prev,
+    const size_t nblk = (size_t)T * blocks(n_bh, 256) + (scoring_ids ? (size_t)n_bh * blocks(V, 256) : 0);
+    B2_REQUIRE(nblk < (1ull << 31), "prefix_step: shape too large");
+    launch_pdl(prefix_prepare_kernel, dim3((unsigned)nblk), dim3(256), 0, st, 5, r_prev, s_prev,
                end_frames, T, n_bh, n_hyps, V, blank, eos, logzero, (int)(scoring_ids != nullptr), rsum_ws,
                log_psi, scores, idmap);
     count_launch();
@@ -735,9 +750,9 @@ int b200ctc::prefix_select_impl(const float* r, const float* log_psi, const int6
   const int n_bh = B * n_hyps, n_new = B * W;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int rows_r = r_time_major ? 2 * n_new : 2 * T, cols_r = r_time_major ? T : n_new;
-  const int rows = rows_r > n_new ? rows_r : n_new, cols = cols_r > V ? cols_r : V;
-  B2_REQUIRE(rows <= 65535 && (long long)n_hyps * V < (1ll << 31), "prefix_select: shape too large");
-  launch_pdl(prefix_select_kernel, dim3(blocks(cols, 256), rows), dim3(256), 0, st, 5, r, log_psi, idmap,
+  const size_t nblk = (size_t)rows_r * blocks(cols_r, 256) + (size_t)n_new * blocks(V, 256);
+  B2_REQUIRE(nblk < (1ull << 31) && (long long)n_hyps * V < (1ll << 31), "prefix_select: shape too large");
+  launch_pdl(prefix_select_kernel, dim3((unsigned)nblk), dim3(256), 0, st, 5, r, log_psi, idmap,
              best_ids, n_hyps, W, T, V, snum, n_bh, r_new, s_new, r_time_major);
   count_launch();
   return check_launch("prefix_select");
