@@ -1,16 +1,19 @@
 // Batched CTC prefix scoring (CTCPrefixScoreTH, espnet/nets/ctc_prefix_score.py:11-269).
-// One thread per (hypothesis, candidate token): the whole frame loop of the
-// reference (:156-161, ~6 kernel launches per frame there) runs inside ONE
-// kernel launch per beam step; psi is accumulated on the fly.
+// The whole frame loop of the reference (:156-161, ~6 kernel launches per frame there) runs
+// inside ONE kernel launch per beam step; psi is accumulated on the fly.
 // Arithmetic follows the reference formulas in fp32 with its finite log-zero
 // (-1e10, sticky under fp32 addition) in the max-shift form m + log(1 + e^-|a-b|).
 //
-// The step is a dependent chain of T log-sum-exps per thread (latency-bound: ~60 cycles
-// per frame), so everything else is kept off it: the frame's inputs (x_t[k], x_t[blank],
-// phi_{t-1}) are fetched kPF frames ahead into registers, and with a pre-beam
-// (snum << V) x_t[k] comes from a TIME-CONTIGUOUS copy of the posteriors (B,V,T) made
-// once per utterance batch - one cache line then serves 32 frames of a thread instead
-// of one.  Full-vocabulary scoring reads the (B,T,V) rows directly (coalesced over k).
+// Two kernels serve the recursion:
+//  * prefix_step_kernel - one thread per (hypothesis, token) walks the frames: a dependent
+//    chain of T log-sum-exps per thread, its inputs (x_t[k], x_t[blank], phi_{t-1}) fetched
+//    kPF frames ahead into registers.  Full-vocabulary scoring (1.6 M threads at C3, bound by
+//    the write of r) and the fallback of the kernel below.
+//  * prefix_step_scan_kernel - with a pre-beam (snum << V, 4 800 pairs at C3) that chain ran on
+//    1 % of the machine's threads; the recursion is an affine map per frame, so a WARP takes a
+//    pair, every lane a chunk of frames, and a warp scan of the chunk maps makes the frame
+//    loop parallel in time (see the kernel).  x_t[k] comes from a TIME-CONTIGUOUS copy of the
+//    posteriors (B,V,T) made once per utterance batch.
 #include "common.cuh"
 
 namespace b200ctc {
