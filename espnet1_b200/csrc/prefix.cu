@@ -644,13 +644,17 @@ extern "C" int b200ctc_prefix_transpose(const float* lp, float* lp_t, int B, int
   return check_launch("prefix_transpose");
 }
 
-// few candidates per hypothesis: the scan kernel takes the step (and its shared memory fits)
+// few candidates per hypothesis: the scan kernel takes the step (and its shared memory fits).
+// It does ~3x the arithmetic of the serial kernel on all SMs; the serial kernel's latency-bound
+// time barely grows with the number of pairs, so beyond ~12 k pairs it wins again (B200, snum 15,
+// T=500: 9 600 pairs 79 vs 92 us per step, 14 400 pairs 110 vs 101; tools/exp/scan_crossover.py)
+constexpr size_t kScanMaxPairs = 12288;
 bool b200ctc::prefix_scan_applies(bool have_lp_t, bool have_ids, int n_bh, int snum, int T) {
   static const int scan_on = tuning_int("B200CTC_PREFIX_SCAN", 1);
   const int scan_warps = snum < kScanCand ? snum : kScanCand;
   const int scan_cap = 32 * (((T + 31) / 32) | 1);
   const size_t scan_smem = (size_t)(3 + 2 * scan_warps) * (scan_cap + 1) * sizeof(float);
-  return have_lp_t && have_ids && scan_on && (size_t)n_bh * snum <= 32768 && T >= 64 && T < 2048 &&
+  return have_lp_t && have_ids && scan_on && (size_t)n_bh * snum <= kScanMaxPairs && T >= 64 && T < 2048 &&
          n_bh <= 65535 && scan_smem <= 100 * 1024;
 }
 
