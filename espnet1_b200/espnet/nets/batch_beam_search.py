@@ -350,6 +350,10 @@ class BatchBeamSearch(torch.nn.Module):
         if hasattr(d, "batch_score_padded"):
             xl = torch.tensor(lens, device=xs.device).repeat_interleave(W)
             return d.batch_score_padded(yseq, states, xs_rep, xl)
+        if hasattr(d, "batch_select_state"):
+            raise ValueError("a full scorer with device-resident state (batch_select_state) that reads the "
+                             "encoder output must offer batch_score_padded(ys, states, xs, xlens) to decode "
+                             "utterances of different lengths together")
         outs, new_states = [], []
         for u in range(U):
             sl = slice(u * W, (u + 1) * W)
@@ -444,6 +448,12 @@ class BatchBeamSearch(torch.nn.Module):
         maxlen_np = np.asarray(maxlen)
         eos_f = np.float32(self.eos)
         stateful = None  # full scorers that returned states (decided at the first position)
+        # Full scorers with DEVICE-resident state (an extension of the scorer interface, like the
+        # CTC scorer's batched-state API): ``batch_select_state(states, prev_rows)`` with
+        # ``prev_rows`` an (n,) int64 device tensor of the surviving slots' source rows returns the
+        # states of all n slots - no list of per-hypothesis states, no host read between positions.
+        dev_state = [k for k, d in self.full_scorers.items() if hasattr(d, "batch_select_state")]
+        slot0_flat = torch.arange(U, device=dev).repeat_interleave(W) * W  # first row of each slot's utterance
 
         def score_full(i_pos, ys):
             """full scorers of one position (batch_beam_search.py:217-241), fp32 for the kernels"""
@@ -485,8 +495,13 @@ class BatchBeamSearch(torch.nn.Module):
                     kept[j] = (sc_j, st_j)
                     kept.pop(j - 2, None)
                     issued = j
+                    if dev_state:  # rows the new slots came from, on the device (queued behind position j)
+                        prev_rows = torch.div(plan.t["out_flat"], V, rounding_mode="floor") + slot0_flat
+                        for k in dev_state:
+                            if st_j[k] is not None:
+                                full_states[k] = self.full_scorers[k].batch_select_state(st_j[k], prev_rows)
                     if j == 0:
-                        run_ahead = all(v is None for v in st_j.values())
+                        run_ahead = all(v is None or k in dev_state for k, v in st_j.items())
                 step_sc, new_full = kept[i]
                 cur_len = P0 + i
                 pack = plan.wait(i)
@@ -541,12 +556,17 @@ class BatchBeamSearch(torch.nn.Module):
                 for k, d in self.part_scorers.items():
                     if batched[k]:
                         part_states[k] = d.batch_select_state(new_part[k], top)
+                if dev_state:
+                    prev_rows = torch.div(top.reshape(-1), V, rounding_mode="floor") + slot0_flat
+                    for k in dev_state:
+                        if new_full[k] is not None:
+                            full_states[k] = self.full_scorers[k].batch_select_state(new_full[k], prev_rows)
                 tp = self._tick("beam_topk_gathers", tp, dev)
                 pack = pack_d.cpu().numpy()  # the one device->host read of the step
                 tp = self._tick("d2h_read", tp, dev)
             h_val = pack[0]
             if stateful is None:
-                stateful = [k for k in self.full_scorers if new_full[k] is not None]
+                stateful = [k for k in self.full_scorers if new_full[k] is not None and k not in dev_state]
             if stateful or not all(batched.values()):
                 h_prev = pack[1].astype(np.int64)
                 h_tok = pack[2].astype(np.int64)
