@@ -175,7 +175,13 @@ class CTCPrefixScoreTH(object):
             mm = torch.empty(2, dtype=torch.float32, device=dev)
             aw = att_w.to(torch.float32).contiguous()
             check(lib().b200ctc_prefix_window(ptr(aw), n_bh, T, ptr(mm), st), "prefix_window")
-            lo, hi = mm.cpu().tolist()  # the reference syncs here too (:146-147)
+            # the reference syncs here too (:146-147); a cached pinned landing buffer + a stream
+            # wait instead of .cpu() (pageable allocation + blocking copy per step)
+            if getattr(self, "_mm_host", None) is None:
+                self._mm_host = torch.empty(2, dtype=torch.float32, pin_memory=True)
+            self._mm_host.copy_(mm, non_blocking=True)
+            torch.cuda.current_stream(dev).synchronize()
+            lo, hi = self._mm_host.tolist()
             f_min = max(int(lo), f_min_prev)
             f_max = max(int(hi), f_max_prev)
             start = min(f_max_prev, max(f_min - self.margin, output_length, 1))
