@@ -112,6 +112,34 @@ for Tn in (45, 120):
     sco, stp = ps.batch_score_partial(torch.cat((y1, i1[:, :1]), 1), i1, sts, xf[:Tn])
 print("prefix", tuple(s1.shape), tuple(s2.shape), "stream", tuple(sco.shape))
 
+# ---- device-resident beam search: one library call per position, positions issued ahead
+from espnet1_b200.espnet.nets.batch_beam_search import BatchBeamSearch  # noqa: E402
+from espnet1_b200.espnet.nets.scorers.length_bonus import LengthBonus  # noqa: E402
+
+
+class _Tab:
+    ignores_x = True
+
+    def __init__(self, t):
+        self.t = t
+
+    def init_state(self, x):
+        return None
+
+    def batch_score(self, ys, states, xs):
+        return self.t[ys[:, -1]], None
+
+
+Vb2 = 300
+tab = torch.log_softmax(torch.randn(Vb2, Vb2, generator=g) * 2, 1).to(dev)
+bsr = BatchBeamSearch({"ctc": CTCPrefixScorer(_Stub(), Vb2 - 1), "decoder": _Tab(tab), "length_bonus": LengthBonus(Vb2)},
+                      {"ctc": 0.3, "decoder": 0.7, "length_bonus": 0.2}, 5, Vb2, Vb2 - 1, Vb2 - 1,
+                      pre_beam_score_key="full")
+xb = (torch.randn(3, 80, Vb2, generator=g) * 3).to(dev)
+with torch.no_grad():
+    nb = bsr.forward_batch(xb, [80, 61, 72], maxlenratio=-12)
+print("beam engine", [len(v) for v in nb], nb[0][0].yseq.tolist()[:6], round(nb[0][0].score, 3))
+
 # ---- sharded-loss exchange, one rank, deferred consumption
 from espnet1_b200.sharded import PeerLossExchange  # noqa: E402
 
