@@ -85,6 +85,7 @@ __device__ __forceinline__ void rank_select(const float* cv, const int* ce, int 
       }
       rank += lo;
     }
+    B2_DEV_CHECK(rank >= 0);
     if (rank < k) { res_v[rank] = x; res_e[rank] = e; }
   }
   __syncthreads();
@@ -181,6 +182,7 @@ __device__ __forceinline__ void segment_topk(const BeamScores& S, long long row0
       const int oe = __shfl_xor_sync(0xffffffffu, ce, o);
       if (ov > cv || (ov == cv && oe < ce)) { cv = ov; ce = oe; }
     }
+    B2_DEV_CHECK(ce == 0x7fffffff || (ce >= 0 && ce < E));
     if (lane == 0) { wl_v[wid * k + r] = cv; wl_e[wid * k + r] = ce; }
     if (ce == be && ce != 0x7fffffff) {  // mine: retire it
       vals[ce] = __int_as_float(0x7fc00000);
@@ -219,6 +221,7 @@ __global__ void __launch_bounds__(NT) beam_select_kernel(
   if (tid < k) {
     const int j = tid, e = res_e[j];
     const float val = res_v[j];
+    B2_DEV_CHECK(e >= 0 && e < W * V);
     const int prev = e / V, tok = e - prev * V;
     const long long row = (long long)u * W + prev, o = (long long)u * k + j;
     out_val[o] = val;
@@ -269,6 +272,7 @@ __global__ void __launch_bounds__(NT) beam_select_cluster_kernel(
   const int c = (int)cluster_ctarank(), u = blockIdx.x / C, U = gridDim.x / C, tid = threadIdx.x;
   const int E = W * V;
   const int off = c * slice, mine = min(slice, E - off);  // the launcher keeps mine >= k
+  B2_DEV_CHECK(mine >= k && C <= 8);
   const long long n_in = (long long)U * W, n_out = (long long)U * k;
   segment_topk<NT>(S, (long long)u * W, V, mine, run, k, vals, res_v, res_e, off);
   __syncthreads();
@@ -288,6 +292,7 @@ __global__ void __launch_bounds__(NT) beam_select_cluster_kernel(
   if (tid < k) {
     const int j = tid, e = res_e[j];
     const float val = res_v[j];
+    B2_DEV_CHECK(e >= 0 && e < W * V);
     const int prev = e / V, tok = e - prev * V;
     const long long row = (long long)u * W + prev, o = (long long)u * k + j;
     out_val[o] = val;

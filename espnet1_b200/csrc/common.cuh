@@ -155,6 +155,15 @@ __device__ __forceinline__ void griddep_launch() {
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
 
+// Index checks of a -DB200CTC_BOUNDS build (compute-sanitizer is not available on the GPU pool:
+// the checked build runs the GPU tests instead; a violated check traps, which the next CUDA call
+// reports).  Compiled out of the shipped library.
+#ifdef B200CTC_BOUNDS
+#define B2_DEV_CHECK(cond) do { if (!(cond)) __trap(); } while (0)
+#else
+#define B2_DEV_CHECK(cond) do { } while (0)
+#endif
+
 // ---- mbarrier + 1-D bulk async copy (TMA engine, UBLKCP in SASS) -----------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);

@@ -35,7 +35,9 @@ __device__ __forceinline__ void align_backtrack(int s_end, int T, int S, int bla
     for (int t = T - 1; t >= 0; --t) {
       seq[t] = s;
       if (t > 0) {
+        B2_DEV_CHECK(s >= 0 && s < S);
         const unsigned w = back[(size_t)(t / kAlignGroup) * S + s];
+        B2_DEV_CHECK(((w >> (2 * (t % kAlignGroup))) & 3u) < 3u);
         s = align_prev(s, (w >> (2 * (t % kAlignGroup))) & 3u, S);
       }
     }

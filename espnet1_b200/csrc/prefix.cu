@@ -391,6 +391,7 @@ __global__ void __launch_bounds__(32 * kScanCand, 2) prefix_step_scan_kernel(
   const unsigned c_magic = c > 1 ? (unsigned)(0x100000000ull / (unsigned)c) + 1u : 0u;
   auto slot = [&](int i) {
     const int L = c > 1 ? (int)__umulhi((unsigned)i, c_magic) : i;
+    B2_DEV_CHECK(i >= 0 && i < len && L == i / (c > 0 ? c : 1) && i + L * (cs - c) < cap);
     return i + L * (cs - c);
   };
 
@@ -411,6 +412,7 @@ __global__ void __launch_bounds__(32 * kScanCand, 2) prefix_step_scan_kernel(
   float* rbo = rb_all + wid * S;
   if (have) {
     k = (int)scoring_ids[idx];
+    B2_DEV_CHECK(k >= 0 && k < V && idx < (size_t)n_bh * snum);
     same = (k == (int)last_ids[(size_t)h * last_stride]);
     const float* xk_row = lp_t + ((size_t)b * V + k) * ldt;
     for (int i = lane; i < len; i += 32) xk[slot(i)] = __ldg(xk_row + start + i);
@@ -497,6 +499,7 @@ __global__ void __launch_bounds__(32 * kScanCand, 2) prefix_step_scan_kernel(
       __syncwarp();
       float* rn_row = r + idx * 2 * (size_t)T;
       float* rb_row = rn_row + T;
+      B2_DEV_CHECK(start >= 1 && end <= T);
       for (int t = lane; t < T; t += 32) {
         float vn = logzero, vb = logzero;
         if (t >= start && t < end) {
@@ -550,6 +553,7 @@ __global__ void __launch_bounds__(256) prefix_select_kernel(
   // the winner's (hypothesis, column of r) for new slot hn
   auto source = [&](int hn, int& hyp, int& col) {
     const unsigned best = (unsigned)best_ids[hn];  // < n_hyps * V
+    B2_DEV_CHECK(best_ids[hn] >= 0 && best_ids[hn] < (int64_t)n_hyps * V);
     const unsigned ph = best / (unsigned)V;
     const int label = (int)(best - ph * (unsigned)V);
     hyp = (int)ph + (hn / W) * n_hyps;
@@ -558,6 +562,7 @@ __global__ void __launch_bounds__(256) prefix_select_kernel(
       const int64_t m = idmap[(size_t)hyp * V + label];
       col = m < 0 ? 0 : (int)m;
     }
+    B2_DEV_CHECK(hyp >= 0 && hyp < n_bh && col >= 0 && col < snum);
   };
   if (!r_part) {  // row = hn, column = v: the winner's psi for every token (:206-209)
     if (row < n_new && c < V)
