@@ -179,6 +179,7 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
             const bool odd = s & 1;
             const int k = odd ? (s + 1) >> 1 : 0;
             const int v = odd ? (WIDE ? lbs[k] : lb[k]) : blank;
+            B2_DEV_CHECK(v >= 0 && v < V);
             const float em = fmaf(to_f32<T>(xs[v]), kLog2e, -c2);
             const float p = ex2(abw[j] - em);
             if (odd) pbuf[k] = p; else blank_part += p;
@@ -233,6 +234,7 @@ __global__ void __launch_bounds__(NT) grad_rows_kernel(
           const bool odd = s & 1;
           const int k = odd ? (s + 1) >> 1 : 0;
           const int v = odd ? lb[k] : blank;
+          B2_DEV_CHECK(v >= 0 && v < V);
           const float em = fmaf(to_f32<T>(xs[v]), kLog2e, -c2);
           const float p = ex2(abv - em);
           if (odd) pbuf[k] = p; else blank_part += p;

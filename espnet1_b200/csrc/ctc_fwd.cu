@@ -216,6 +216,7 @@ __global__ void __launch_bounds__(kGatherWarps * 32) gather_kernel(
     for (int j = 0; j < kGatherRegs; ++j) {
       const int k = lane + 32 * j;
       const int col = slab[k <= L ? k : 0];
+      B2_DEV_CHECK(col >= 0 && col < V);
 #pragma unroll
       for (int r = 0; r < kGatherRows; ++r) {  // clamped row: always a valid address
         const T* row = logits + (g0 + (r < nr ? r : nr - 1)) * V;
