@@ -32,6 +32,7 @@ SIGNATURES = {
     "b200ctc_softmax_fwd_bias": (c_int, [_P, _P, _P, c_int64, c_int, c_int, c_int, _P]),
     "b200ctc_softmax_bwd": (c_int, [_P, _P, _P, c_int64, c_int, c_int, c_int, _P]),
     "b200ctc_argmax": (c_int, [_P, _P, c_int64, c_int, c_int, _P]),
+    "b200ctc_argmax_bias": (c_int, [_P, _P, _P, c_int64, c_int, c_int, _P]),
     "b200ctc_greedy_decode": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_int, _P, _P, _P]),
     "b200ctc_loss_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "b200ctc_loss_fwd": (c_int, [_P, c_int, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int,

@@ -27,14 +27,19 @@ __device__ __forceinline__ unsigned long long warp_max_u64(unsigned long long v)
 
 template <typename T, int VEC>
 __device__ __forceinline__ unsigned long long row_argmax(const T* __restrict__ xr, int V,
-                                                         unsigned long long* red) {
+                                                         unsigned long long* red,
+                                                         const T* __restrict__ bias) {
   unsigned long long best = 0;
   if (VEC > 1) {
     const int nchunk = V / VEC;
     for (int i = threadIdx.x; i < nchunk; i += blockDim.x) {
       if (VEC == 4) {
         const float4 t = __ldcs(reinterpret_cast<const float4*>(xr) + i);
-        const float f[4] = {t.x, t.y, t.z, t.w};
+        float f[4] = {t.x, t.y, t.z, t.w};
+        if (bias) {
+          const float4 b = __ldg(reinterpret_cast<const float4*>(bias) + i);
+          f[0] += b.x; f[1] += b.y; f[2] += b.z; f[3] += b.w;
+        }
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           const unsigned long long p = pack(order_key(f[e]), i * 4 + e);
@@ -43,16 +48,21 @@ __device__ __forceinline__ unsigned long long row_argmax(const T* __restrict__ x
       } else {
         const uint4 t = __ldcs(reinterpret_cast<const uint4*>(xr) + i);
         const T* h = reinterpret_cast<const T*>(&t);
+        uint4 tb = make_uint4(0, 0, 0, 0);
+        if (bias) tb = __ldg(reinterpret_cast<const uint4*>(bias) + i);
+        const T* hb = reinterpret_cast<const T*>(&tb);
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
-          const unsigned long long p = pack(order_key(to_f32<T>(h[e])), i * 8 + e);
+          const float v = to_f32<T>(h[e]) + (bias ? to_f32<T>(hb[e]) : 0.f);
+          const unsigned long long p = pack(order_key(v), i * 8 + e);
           best = p > best ? p : best;
         }
       }
     }
   } else {
     for (int i = threadIdx.x; i < V; i += blockDim.x) {
-      const unsigned long long p = pack(order_key(to_f32<T>(xr[i])), i);
+      const float v = to_f32<T>(xr[i]) + (bias ? to_f32<T>(bias[i]) : 0.f);
+      const unsigned long long p = pack(order_key(v), i);
       best = p > best ? p : best;
     }
   }
@@ -74,7 +84,8 @@ constexpr int kArgChunks = 5;
 
 template <typename T, int VEC>
 __device__ __forceinline__ unsigned long long row_argmax_regs(const T* __restrict__ xr, int nchunk,
-                                                              unsigned long long* red) {
+                                                              unsigned long long* red,
+                                                              const T* __restrict__ bias) {
   float v[kArgChunks][VEC];
 #pragma unroll
   for (int j = 0; j < kArgChunks; ++j) {
@@ -83,11 +94,21 @@ __device__ __forceinline__ unsigned long long row_argmax_regs(const T* __restric
       if (VEC == 4) {
         const float4 t = __ldcs(reinterpret_cast<const float4*>(xr) + i);
         v[j][0] = t.x; v[j][1] = t.y; v[j][2] = t.z; v[j][3] = t.w;
+        if (bias) {  // the projection's bias (see b200ctc_softmax_fwd_bias)
+          const float4 b = __ldg(reinterpret_cast<const float4*>(bias) + i);
+          v[j][0] += b.x; v[j][1] += b.y; v[j][2] += b.z; v[j][3] += b.w;
+        }
       } else {
         const uint4 t = __ldcs(reinterpret_cast<const uint4*>(xr) + i);
         const T* h = reinterpret_cast<const T*>(&t);
 #pragma unroll
         for (int e = 0; e < VEC; ++e) v[j][e] = to_f32<T>(h[e]);
+        if (bias) {
+          const uint4 tb = __ldg(reinterpret_cast<const uint4*>(bias) + i);
+          const T* hb = reinterpret_cast<const T*>(&tb);
+#pragma unroll
+          for (int e = 0; e < VEC; ++e) v[j][e] += to_f32<T>(hb[e]);
+        }
       }
     } else {
 #pragma unroll
@@ -123,12 +144,13 @@ __device__ __forceinline__ unsigned long long row_argmax_regs(const T* __restric
 
 template <typename T, int VEC>
 __global__ void __launch_bounds__(256) argmax_kernel(const T* __restrict__ x,
-                                                     int64_t* __restrict__ out, int V) {
+                                                     int64_t* __restrict__ out, int V,
+                                                     const T* __restrict__ bias) {
   __shared__ unsigned long long red[32];
   const int64_t row = blockIdx.x;
   unsigned long long best;
-  if (VEC > 1 && V / VEC <= 256 * kArgChunks) best = row_argmax_regs<T, VEC>(x + row * V, V / VEC, red);
-  else best = row_argmax<T, VEC>(x + row * V, V, red);
+  if (VEC > 1 && V / VEC <= 256 * kArgChunks) best = row_argmax_regs<T, VEC>(x + row * V, V / VEC, red, bias);
+  else best = row_argmax<T, VEC>(x + row * V, V, red, bias);
   if (threadIdx.x == 0) out[row] = (int64_t)(0xFFFFFFFFu - (uint32_t)(best & 0xFFFFFFFFull));
 }
 
@@ -172,14 +194,17 @@ __global__ void __launch_bounds__(256) collapse_kernel(int64_t* __restrict__ ids
 }
 
 template <typename T>
-static int launch_argmax(const void* x, int64_t* out, int64_t rows, int V, cudaStream_t st) {
+static int launch_argmax(const void* x, int64_t* out, int64_t rows, int V, cudaStream_t st,
+                         const void* bias = nullptr) {
   const T* xi = static_cast<const T*>(x);
+  const T* bi = static_cast<const T*>(bias);
   constexpr int N = sizeof(T) == 4 ? 4 : 8;
-  const bool vec = (V % N == 0) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0);
+  const bool vec = (V % N == 0) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0) &&
+                   ((reinterpret_cast<uintptr_t>(bias) & 15) == 0);
   if (vec)
-    argmax_kernel<T, N><<<(unsigned)rows, 256, 0, st>>>(xi, out, V);
+    argmax_kernel<T, N><<<(unsigned)rows, 256, 0, st>>>(xi, out, V, bi);
   else
-    argmax_kernel<T, 1><<<(unsigned)rows, 256, 0, st>>>(xi, out, V);
+    argmax_kernel<T, 1><<<(unsigned)rows, 256, 0, st>>>(xi, out, V, bi);
   count_launch();
   return check_launch("argmax");
 }
@@ -200,6 +225,21 @@ extern "C" int b200ctc_argmax(const void* x, int64_t* out, int64_t rows, int V, 
     case B200CTC_BF16: return launch_argmax<__nv_bfloat16>(x, out, rows, V, st);
   }
   set_error("argmax: unknown dtype %d", dtype);
+  return B200CTC_ERR_ARG;
+}
+
+extern "C" int b200ctc_argmax_bias(const void* x, const void* bias, int64_t* out, int64_t rows, int V,
+                                   int dtype, b200ctc_stream_t stream) {
+  B2_REQUIRE(x && bias && out, "argmax_bias: null pointer");
+  B2_REQUIRE(rows >= 0 && rows < (1ll << 31) && V > 0, "argmax_bias: bad shape");
+  if (rows == 0) return B200CTC_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (dtype) {
+    case B200CTC_F32: return launch_argmax<float>(x, out, rows, V, st, bias);
+    case B200CTC_F16: return launch_argmax<__half>(x, out, rows, V, st, bias);
+    case B200CTC_BF16: return launch_argmax<__nv_bfloat16>(x, out, rows, V, st, bias);
+  }
+  set_error("argmax_bias: unknown dtype %d", dtype);
   return B200CTC_ERR_ARG;
 }
 

@@ -210,4 +210,5 @@ class CTC(torch.nn.Module):
 
     def argmax(self, hs_pad):
         """argmax of frame activations: (B, Tmax, eprojs) -> (B, Tmax) int64."""
-        return B.argmax(self.ctc_lo(hs_pad))
+        x, bias = self._projection(hs_pad)
+        return B.argmax(x, bias)

@@ -64,14 +64,22 @@ def softmax(x: torch.Tensor, bias: torch.Tensor = None) -> torch.Tensor:
 
 
 @on_tensor_device
-def argmax(x: torch.Tensor) -> torch.Tensor:
-    """argmax over the last dim, int64, first-max tie rule (espnet2/asr/ctc.py:127)."""
+def argmax(x: torch.Tensor, bias: torch.Tensor = None) -> torch.Tensor:
+    """argmax over the last dim, int64, first-max tie rule (espnet2/asr/ctc.py:127); with ``bias``
+    (V,) of ``x + bias`` (see :func:`log_softmax`)."""
     require_cuda(x, "argmax input")
     xc = x.detach().contiguous()
     rows, V = _rows(xc)
     out = torch.empty(xc.shape[:-1], dtype=torch.int64, device=xc.device)
-    check(lib().b200ctc_argmax(ptr(xc), ptr(out), rows, V, dtype_code(xc), stream_ptr(xc.device)),
-          "argmax")
+    if bias is None:
+        check(lib().b200ctc_argmax(ptr(xc), ptr(out), rows, V, dtype_code(xc), stream_ptr(xc.device)),
+              "argmax")
+    else:
+        if bias.dtype != xc.dtype or bias.numel() != V or bias.device != xc.device:
+            raise TypeError("argmax bias must be V values of the input's dtype on its device")
+        bc = bias.detach().contiguous()
+        check(lib().b200ctc_argmax_bias(ptr(xc), ptr(bc), ptr(out), rows, V, dtype_code(xc),
+                                        stream_ptr(xc.device)), "argmax_bias")
     return out
 
 

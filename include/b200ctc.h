@@ -77,6 +77,10 @@ int b200ctc_softmax_bwd(const void* y, const void* dy, void* dx, int64_t rows,
 /* first index of the row maximum (NaN counts as the maximum), int64 out.      */
 int b200ctc_argmax(const void* x, int64_t* out, int64_t rows, int V, int dtype,
                    b200ctc_stream_t stream);
+/* argmax of x + bias (bias as in b200ctc_softmax_fwd_bias: the projection's GEMM runs without
+ * it; espnet2/asr/ctc.py:127 torch.argmax(self.ctc_lo(hs_pad), dim=2)).  (ABI 6)             */
+int b200ctc_argmax_bias(const void* x, const void* bias, int64_t* out, int64_t rows,
+                        int V, int dtype, b200ctc_stream_t stream);
 /* best-path decode (espnet/nets/e2e_asr_common.py:159-191): argmax per frame,
  * collapse repeats, drop blanks.  x (B,T,V); out_ids (B,T) int64 padded with
  * -1; out_lens (B,) int64.  in_lens may be NULL (all T).                      */

@@ -141,10 +141,15 @@ def test_softmax_with_projection_bias(dtype, V):
         (yr * w).sum().backward()
         close(xa.grad.float(), xr.grad.cpu().numpy(), 10 * tol, 10 * tol)
         close(ba.grad.float(), br.grad.cpu().numpy(), 50 * tol, 50 * tol * max(1.0, float(br.grad.abs().max())))
+    # argmax of x + bias: the fp32 sum's first maximum (ties cannot be told from torch's for 16-bit
+    # inputs summed in another precision, so those compare against the fp32 sum, which is what the kernel forms)
+    want = (x.float() + b.float()).argmax(-1)
+    assert torch.equal(F.argmax(x, b), want)
     if dtype == torch.float32:
         m = CTC(V, 16).to(d)
         hs = torch.randn(3, 20, 16, generator=g).to(d)
         with torch.no_grad():
+            assert torch.equal(m.argmax(hs), m.ctc_lo(hs).argmax(-1))
             close(m.log_softmax(hs), torch.log_softmax(m.ctc_lo(hs), -1).cpu().numpy(), 1e-5, 2e-6)
             close(m.softmax(hs), torch.softmax(m.ctc_lo(hs), -1).cpu().numpy(), 1e-5, 1e-7)
 
