@@ -72,18 +72,27 @@ class CTC(torch.nn.Module):
             self.loss = self.loss.sum()
         return self.loss
 
+    def _projection(self, hs_pad):
+        """``ctc_lo(hs_pad)`` as (GEMM output, bias for the kernel to add) - see
+        :meth:`espnet1_b200.espnet2.asr.ctc.CTC._projection`."""
+        lo = self.ctc_lo
+        if (lo.bias is not None and hs_pad.is_cuda and hs_pad.dtype == lo.weight.dtype == lo.bias.dtype
+                and not torch.is_autocast_enabled()):
+            return torch.nn.functional.linear(hs_pad, lo.weight), lo.bias
+        return lo(hs_pad), None
+
     def softmax(self, hs_pad):
         """softmax of frame activations (B, Tmax, eprojs) -> (B, Tmax, odim)"""
-        self.probs = B.softmax(self.ctc_lo(hs_pad))
+        self.probs = B.softmax(*self._projection(hs_pad))
         return self.probs
 
     def log_softmax(self, hs_pad):
         """log_softmax of frame activations (B, Tmax, eprojs) -> (B, Tmax, odim)"""
-        return B.log_softmax(self.ctc_lo(hs_pad))
+        return B.log_softmax(*self._projection(hs_pad))
 
     def argmax(self, hs_pad):
         """argmax of frame activations (B, Tmax, eprojs) -> (B, Tmax)"""
-        return B.argmax(self.ctc_lo(hs_pad))
+        return B.argmax(*self._projection(hs_pad))
 
     def forced_align(self, h, y, blank_id=0):
         """forced alignment (:163-226).
