@@ -64,7 +64,7 @@ class CTC(torch.nn.Module):
         keep = ys_pad != self.ignore_id  # parse padded ys (:84)
         olens = keep.sum(dim=1)
         ys_true = ys_pad[keep]
-        ys_hat = self.ctc_lo(self.dropout(hs_pad)).transpose(0, 1)
+        ys_hat = self._logits(self.dropout(hs_pad)).transpose(0, 1)
         hlens = torch.as_tensor(hlens).long()
         self.loss = self.loss_fn(ys_hat, ys_true, hlens, olens, max_tgt_len=ys_pad.size(1))
         self.loss = self.loss.to(dtype=hs_pad.dtype)
@@ -72,12 +72,26 @@ class CTC(torch.nn.Module):
             self.loss = self.loss.sum()
         return self.loss
 
+    def _logits(self, hs):
+        """``ctc_lo(hs)`` for the loss.  In fp32 cuBLASLt adds the Linear's bias in a separate pass
+        over the (B, T, odim) activations and autograd sums the gradient's columns for d bias in
+        another one (0.9 ms of 6.4 ms for forward + backward at B=64, T=500, 256 -> 5000 -
+        tools/exp/linear_ones.py - against 0.33 ms for the whole CTC loss step): the bias rides
+        along as a 257th input column instead, ``[hs, 1] @ [W, b]^T`` - same values (bit-identical
+        in that measurement), ``ctc_lo`` keeps its parameters and checkpoint keys."""
+        lo = self.ctc_lo
+        if (isinstance(lo, torch.nn.Linear) and lo.bias is not None and hs.is_cuda and hs.dtype == torch.float32
+                and lo.weight.dtype == torch.float32 and not torch.is_autocast_enabled()):
+            ones = hs.new_ones(*hs.shape[:-1], 1)
+            return torch.nn.functional.linear(torch.cat((hs, ones), -1), torch.cat((lo.weight, lo.bias.unsqueeze(1)), 1))
+        return lo(hs)
+
     def _projection(self, hs_pad):
         """``ctc_lo(hs_pad)`` as (GEMM output, bias for the kernel to add) - see
         :meth:`espnet1_b200.espnet2.asr.ctc.CTC._projection`."""
         lo = self.ctc_lo
-        if (lo.bias is not None and hs_pad.is_cuda and hs_pad.dtype == lo.weight.dtype == lo.bias.dtype
-                and not torch.is_autocast_enabled()):
+        if (isinstance(lo, torch.nn.Linear) and lo.bias is not None and hs_pad.is_cuda
+                and hs_pad.dtype == lo.weight.dtype == lo.bias.dtype and not torch.is_autocast_enabled()):
             return torch.nn.functional.linear(hs_pad, lo.weight), lo.bias
         return lo(hs_pad), None
 

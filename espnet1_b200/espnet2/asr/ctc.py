@@ -112,7 +112,7 @@ class CTC(torch.nn.Module):
             ys_lens: batch of lengths of character sequence (B)
         """
         # NOTE: F.dropout defaults to training=True exactly like the reference (:82)
-        ys_hat = self.ctc_lo(F.dropout(hs_pad, p=self.dropout_rate))
+        ys_hat = self._logits(F.dropout(hs_pad, p=self.dropout_rate))
         ys_hat = ys_hat.transpose(0, 1)  # (B, T, V) -> (T, B, V) view
         # (B, L) -> (sum L,) without the reference's per-utterance Python loop (:91)
         Lmax = ys_pad.size(1)
@@ -146,7 +146,7 @@ class CTC(torch.nn.Module):
         Bn = hs_pads[0].size(0)
         dev = hs_pads[0].device
         hs = torch.cat(list(hs_pads), dim=0)  # (H*B, T, D)
-        ys_hat = self.ctc_lo(F.dropout(hs, p=self.dropout_rate))  # one GEMM, independent masks per head
+        ys_hat = self._logits(F.dropout(hs, p=self.dropout_rate))  # one GEMM, independent masks per head
         Lmax = ys_pad.size(1)
         lens_dev = torch.as_tensor(ys_lens).to(device=ys_pad.device)
         keep = torch.arange(Lmax, device=ys_pad.device).unsqueeze(0) < lens_dev.unsqueeze(1)
@@ -187,14 +187,28 @@ class CTC(torch.nn.Module):
             cur.wait_stream(side)
         return out
 
+    def _logits(self, hs):
+        """``ctc_lo(hs)`` for the loss.  In fp32 cuBLASLt adds the Linear's bias in a separate pass
+        over the (B, T, odim) activations and autograd sums the gradient's columns for d bias in
+        another one (0.9 ms of 6.4 ms for forward + backward at B=64, T=500, 256 -> 5000 -
+        tools/exp/linear_ones.py - against 0.33 ms for the whole CTC loss step): the bias rides
+        along as a 257th input column instead, ``[hs, 1] @ [W, b]^T`` - same values (bit-identical
+        in that measurement), ``ctc_lo`` keeps its parameters and checkpoint keys."""
+        lo = self.ctc_lo
+        if (isinstance(lo, torch.nn.Linear) and lo.bias is not None and hs.is_cuda and hs.dtype == torch.float32
+                and lo.weight.dtype == torch.float32 and not torch.is_autocast_enabled()):
+            ones = hs.new_ones(*hs.shape[:-1], 1)
+            return F.linear(torch.cat((hs, ones), -1), torch.cat((lo.weight, lo.bias.unsqueeze(1)), 1))
+        return lo(hs)
+
     def _projection(self, hs_pad):
         """``ctc_lo(hs_pad)`` as (GEMM output, bias to add): where the soft-max kernel can take the
         bias (same dtype as the GEMM output, CUDA) the GEMM runs without it - cuBLASLt adds the
         bias of this shape in a separate pass over the (B, T, odim) output, a third of the
         projection's time - and the soft-max's one read of each row absorbs it."""
         lo = self.ctc_lo
-        if (lo.bias is not None and hs_pad.is_cuda and hs_pad.dtype == lo.weight.dtype == lo.bias.dtype
-                and not torch.is_autocast_enabled()):
+        if (isinstance(lo, torch.nn.Linear) and lo.bias is not None and hs_pad.is_cuda
+                and hs_pad.dtype == lo.weight.dtype == lo.bias.dtype and not torch.is_autocast_enabled()):
             return F.linear(hs_pad, lo.weight), lo.bias
         return lo(hs_pad), None
 

@@ -174,6 +174,37 @@ def test_forced_align_sizes_vs_oracle(T, L, V):
     np.testing.assert_array_equal(got.cpu().numpy(), np.asarray(want))
 
 
+def test_training_projection_with_the_bias_as_an_input_column():
+    """`CTC.forward` runs `ctc_lo` as one GEMM over [hs, 1] x [W, b]^T in fp32 (no separate bias
+    pass): loss and the gradients of hs, ctc_lo.weight and ctc_lo.bias equal those of the plain
+    `ctc_lo(hs)` formulation; under autocast / for 16-bit weights the plain Linear is used."""
+    from espnet1_b200 import functional as F
+    from espnet1_b200.espnet2.asr.ctc import CTC
+
+    d = _dev()
+    g = torch.Generator().manual_seed(17)
+    Bn, T, D, V = 5, 40, 24, 50
+    m = CTC(V, D).to(d)
+    hs = torch.randn(Bn, T, D, generator=g).to(d).requires_grad_(True)
+    hl = torch.tensor([40, 33, 40, 21, 37], device=d)
+    yl = torch.tensor([6, 3, 9, 2, 5], device=d)
+    ys = torch.randint(1, V, (Bn, 9), generator=g).to(d)
+    loss = m(hs, hl, ys, yl)
+    loss.backward()
+    got = (float(loss.detach()), hs.grad.clone(), m.ctc_lo.weight.grad.clone(), m.ctc_lo.bias.grad.clone())
+    hs.grad = None
+    m.zero_grad()
+    ys_true = torch.cat([ys[i, : int(yl[i])] for i in range(Bn)])
+    ref = F.ctc_loss(m.ctc_lo(hs), ys_true, hl, yl, reduce_scale=F._f32_recip(Bn))
+    ref.backward()
+    assert abs(got[0] - float(ref.detach())) <= 1e-6 * abs(float(ref.detach()))
+    close(got[1], hs.grad.cpu().numpy(), 1e-5, 1e-6)
+    close(got[2], m.ctc_lo.weight.grad.cpu().numpy(), 1e-5, 1e-6)
+    close(got[3], m.ctc_lo.bias.grad.cpu().numpy(), 1e-5, 1e-6)
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        assert m._logits(hs.detach()).dtype == torch.bfloat16  # the plain Linear under autocast
+
+
 def test_c1_logits_boundary_vs_fixture_and_oracle():
     from espnet1_b200 import functional as F
     from oracle import ctc_numpy
